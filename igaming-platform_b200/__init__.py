@@ -1,0 +1,214 @@
+"""B200-native batched fraud-scoring engine — Python host side over the C ABI (include/igs.h).
+
+`Engine` is a thin handle over `libigs.so`; `scoring.ScoringEngine` / `scoring.BatchScorer`
+mirror the reference's operator interface (services/risk/internal/scoring/engine.go).  The only
+compute path is the CUDA library: importing works anywhere, creating an Engine needs a B200.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import abi
+
+
+class IgsError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"igs status {status}: {message}")
+        self.status = status
+
+
+def default_config(**overrides) -> abi.Config:
+    """DefaultConfig() of the reference (scoring/engine.go:215-228) through the C ABI."""
+    cfg = abi.Config()
+    abi.load_library().igs_default_config(C.byref(cfg))
+    for k, v in overrides.items():
+        if k == "reason_weight":
+            for i, w in enumerate(v):
+                cfg.reason_weight[i] = w
+        else:
+            setattr(cfg, k, v)
+    return cfg
+
+
+@dataclass
+class GbdtModel:
+    """Host copy of a tree ensemble in the igs_gbdt_desc layout."""
+    feat: np.ndarray   # [n_trees, 255] uint8
+    thr: np.ndarray    # [n_trees, 255] float32
+    leaf: np.ndarray   # [n_trees, 256] float32
+    base_score: float = 0.0
+    post_transform: int = abi.POST_LOGISTIC
+    n_features: int = abi.NUM_FEATURES
+
+    @property
+    def n_trees(self) -> int:
+        return int(self.feat.shape[0])
+
+    def desc(self) -> abi.GbdtDesc:
+        self.feat = np.ascontiguousarray(self.feat, dtype=np.uint8)
+        self.thr = np.ascontiguousarray(self.thr, dtype=np.float32)
+        self.leaf = np.ascontiguousarray(self.leaf, dtype=np.float32)
+        assert self.feat.shape == (self.n_trees, abi.TREE_NODES)
+        assert self.thr.shape == (self.n_trees, abi.TREE_NODES)
+        assert self.leaf.shape == (self.n_trees, abi.TREE_LEAVES)
+        return abi.GbdtDesc(self.n_trees, self.n_features, self.post_transform,
+                            float(np.float32(self.base_score)),
+                            abi.ptr(self.feat), abi.ptr(self.thr), abi.ptr(self.leaf))
+
+
+@dataclass
+class MlpModel:
+    """Host copy of the LTV MLP in the igs_mlp_desc layout (bf16 bit patterns + fp32 biases)."""
+    w1: np.ndarray; b1: np.ndarray
+    w2: np.ndarray; b2: np.ndarray
+    w3: np.ndarray; b3: np.ndarray
+    w4: np.ndarray; b4: np.ndarray
+
+    def desc(self) -> abi.MlpDesc:
+        for k in ("w1", "w2", "w3", "w4"):
+            setattr(self, k, np.ascontiguousarray(getattr(self, k), dtype=np.uint16))
+        for k in ("b1", "b2", "b3", "b4"):
+            setattr(self, k, np.ascontiguousarray(getattr(self, k), dtype=np.float32))
+        assert self.w1.shape == (abi.MLP_HIDDEN, abi.MLP_IN)
+        assert self.w2.shape == self.w3.shape == (abi.MLP_HIDDEN, abi.MLP_HIDDEN)
+        assert self.w4.shape == (1, abi.MLP_HIDDEN)
+        return abi.MlpDesc(*(abi.ptr(getattr(self, k)) for k in
+                             ("w1", "b1", "w2", "b2", "w3", "b3", "w4", "b4")))
+
+
+@dataclass
+class Events:
+    """Event history columns (igs_event_cols)."""
+    account: np.ndarray  # uint32
+    ts: np.ndarray       # uint32
+    amount: np.ndarray   # int64
+    tx_type: np.ndarray  # uint8
+
+    def __len__(self) -> int:
+        return int(self.account.shape[0])
+
+    def cols(self) -> abi.EventCols:
+        self.account = np.ascontiguousarray(self.account, dtype=np.uint32)
+        self.ts = np.ascontiguousarray(self.ts, dtype=np.uint32)
+        self.amount = np.ascontiguousarray(self.amount, dtype=np.int64)
+        self.tx_type = np.ascontiguousarray(self.tx_type, dtype=np.uint8)
+        n = len(self)
+        assert self.ts.shape == (n,) and self.amount.shape == (n,) and self.tx_type.shape == (n,)
+        return abi.EventCols(abi.ptr(self.account), abi.ptr(self.ts), abi.ptr(self.amount),
+                             abi.ptr(self.tx_type))
+
+
+class Engine:
+    """One engine per CUDA device (igs_engine).  Host-buffer calls are synchronous."""
+
+    def __init__(self, device: int = 0):
+        self._lib = abi.load_library()
+        h = C.c_void_p()
+        st = self._lib.igs_engine_create(device, C.byref(h))
+        if st != abi.OK:
+            raise IgsError(st, (self._lib.igs_last_error(None) or b"").decode())
+        self._h = h
+        self.device = device
+        self._n_trees = 0
+
+    # -- life cycle ---------------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.igs_engine_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st: int) -> None:
+        if st != abi.OK:
+            raise IgsError(st, (self._lib.igs_last_error(self._h) or b"").decode())
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._h
+
+    # -- loads --------------------------------------------------------------------------------
+    def load_gbdt(self, model: GbdtModel) -> None:
+        d = model.desc()
+        self._check(self._lib.igs_load_gbdt(self._h, C.byref(d)))
+        self._n_trees = model.n_trees
+
+    def load_mlp(self, model: MlpModel) -> None:
+        d = model.desc()
+        self._check(self._lib.igs_load_mlp(self._h, C.byref(d)))
+
+    def load_players(self, rows: np.ndarray) -> None:
+        rows = np.ascontiguousarray(rows, dtype=abi.player_row_dtype)
+        self._check(self._lib.igs_load_players(self._h, abi.ptr(rows), rows.shape[0]))
+
+    def load_events(self, ev: Events, n_accounts: int) -> None:
+        c = ev.cols()
+        self._check(self._lib.igs_load_events(self._h, C.byref(c), len(ev), n_accounts))
+
+    # -- path A -------------------------------------------------------------------------------
+    def score_features(self, cfg: abi.Config, features: np.ndarray, rows: np.ndarray,
+                       want_leaves: bool = False, n_trees: int | None = None):
+        features = np.ascontiguousarray(features, dtype=np.float32)
+        rows = np.ascontiguousarray(rows, dtype=abi.rule_row_dtype)
+        n = rows.shape[0]
+        assert features.shape == (n, abi.NUM_FEATURES)
+        out = np.zeros(n, dtype=abi.result_dtype)
+        leaves = None
+        if want_leaves:
+            nt = n_trees if n_trees is not None else self._n_trees
+            leaves = np.zeros((n, nt), dtype=np.uint8)
+        self._check(self._lib.igs_score_features(self._h, C.byref(cfg), abi.ptr(features),
+                                                 abi.ptr(rows), n, abi.ptr(out), abi.ptr(leaves)))
+        return (out, leaves) if want_leaves else out
+
+    def score_features_device(self, cfg: abi.Config, d_features: int, d_rows: int, n: int,
+                              d_out: int, d_leaves: int = 0, stream: int = 0) -> None:
+        self._check(self._lib.igs_score_features_device(self._h, C.byref(cfg), d_features, d_rows,
+                                                        n, d_out, d_leaves, stream))
+
+    # -- velocity -----------------------------------------------------------------------------
+    def get_velocity(self, queries: np.ndarray) -> np.ndarray:
+        queries = np.ascontiguousarray(queries, dtype=abi.query_dtype)
+        out = np.zeros(queries.shape[0], dtype=abi.velocity_dtype)
+        self._check(self._lib.igs_get_velocity(self._h, abi.ptr(queries), queries.shape[0],
+                                               abi.ptr(out)))
+        return out
+
+    # -- path B -------------------------------------------------------------------------------
+    def score_batch(self, cfg: abi.Config, tx: np.ndarray, want_features: bool = False,
+                    want_velocity: bool = False):
+        tx = np.ascontiguousarray(tx, dtype=abi.tx_dtype)
+        n = tx.shape[0]
+        out = np.zeros(n, dtype=abi.result_dtype)
+        feats = np.zeros((n, abi.NUM_FEATURES), dtype=np.float32) if want_features else None
+        vel = np.zeros(n, dtype=abi.velocity_dtype) if want_velocity else None
+        self._check(self._lib.igs_score_batch(self._h, C.byref(cfg), abi.ptr(tx), n, abi.ptr(out),
+                                              abi.ptr(feats), abi.ptr(vel)))
+        if want_features or want_velocity:
+            return out, feats, vel
+        return out
+
+    # -- LTV ----------------------------------------------------------------------------------
+    def ltv_batch(self, x_bf16: np.ndarray, rows: np.ndarray, want_raw: bool = False):
+        x_bf16 = np.ascontiguousarray(x_bf16, dtype=np.uint16)
+        rows = np.ascontiguousarray(rows, dtype=abi.ltv_row_dtype)
+        n = rows.shape[0]
+        assert x_bf16.shape == (n, abi.MLP_IN)
+        out = np.zeros(n, dtype=abi.ltv_result_dtype)
+        raw = np.zeros(n, dtype=np.float32) if want_raw else None
+        self._check(self._lib.igs_ltv_batch(self._h, abi.ptr(x_bf16), abi.ptr(rows), n,
+                                            abi.ptr(out), abi.ptr(raw)))
+        return (out, raw) if want_raw else out

@@ -1,0 +1,386 @@
+/*
+ * igs.h — C ABI of the B200 batched fraud-scoring engine ("igs" = iGaming Scoring).
+ *
+ * This is the drop-in boundary for the scoring path of the reference's Risk & Prediction
+ * service (services/risk).  Every entry point names the reference interface it replaces
+ * (paths relative to the reference root).  Plain C: pointers, sizes, PODs.  No C++
+ * exceptions cross this boundary; every call returns IGS_OK or a negative status and
+ * leaves a message retrievable through igs_last_error().
+ *
+ * Ownership: the caller owns every host buffer (use igs_alloc_pinned() for anything that is
+ * passed to a *host-buffer* entry point on the hot path — pageable memory works but is slower).
+ * The engine owns device memory, streams and staging.  Inputs are never mutated
+ * (the reference mutates the caller's vector in Normalize(), ml/onnx_model.go:213 — we do not).
+ *
+ * Threading: one engine per device.  Calls on different *slots* of one engine may be issued
+ * from different host threads concurrently; calls on the same slot must be serialised by the
+ * caller.  Configuration (weights / thresholds) is passed by value with every call, so there is
+ * no shared mutable config (the reference has a latent race there: scoring/engine.go:304-306
+ * vs :498-504).
+ *
+ * There is NO CPU fallback behind this ABI: without a CUDA device igs_engine_create() fails.
+ */
+#ifndef IGS_H_
+#define IGS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* status codes                                                                               */
+/* ------------------------------------------------------------------------------------------ */
+#define IGS_OK            0
+#define IGS_ERR_INVALID  (-1) /* bad argument (null pointer, size out of range, bad enum)      */
+#define IGS_ERR_CUDA     (-2) /* a CUDA runtime call failed; igs_last_error() has the text     */
+#define IGS_ERR_STATE    (-3) /* call needs state that was not loaded (model, players, events) */
+#define IGS_ERR_NOMEM    (-4) /* host or device allocation failed                              */
+
+/* ------------------------------------------------------------------------------------------ */
+/* fixed shapes of the path                                                                   */
+/* ------------------------------------------------------------------------------------------ */
+#define IGS_NUM_FEATURES  64   /* model input width (north-star); idx 0..29 = reference order   */
+#define IGS_REF_FEATURES  30   /* ml.FeatureVector, ml/onnx_model.go:86-130 / ToSlice :133-166  */
+#define IGS_TREE_DEPTH     8
+#define IGS_TREE_NODES   255   /* internal nodes of one complete depth-8 tree, heap order       */
+#define IGS_TREE_LEAVES  256
+#define IGS_NUM_SLOTS      4   /* independent stream + staging sets per engine                  */
+
+/* Reason bits.  Bit order = ReasonCode const order, scoring/engine.go:17-28.                    */
+#define IGS_R_HIGH_VELOCITY           (1u << 0)
+#define IGS_R_NEW_ACCOUNT_LARGE_TX    (1u << 1)
+#define IGS_R_IP_COUNTRY_MISMATCH     (1u << 2)
+#define IGS_R_MULTIPLE_DEVICES        (1u << 3)
+#define IGS_R_SUSPICIOUS_PATTERN      (1u << 4) /* declared by the reference, never emitted     */
+#define IGS_R_VPN_DETECTED            (1u << 5)
+#define IGS_R_KNOWN_FRAUDSTER         (1u << 6)
+#define IGS_R_RAPID_DEPOSIT_WITHDRAW  (1u << 7)
+#define IGS_R_BONUS_ABUSE             (1u << 8)
+#define IGS_R_ML_HIGH_RISK            (1u << 9)
+#define IGS_NUM_REASONS 10
+
+/* Action, numbered as proto/risk/v1/risk.proto:84-89.                                          */
+#define IGS_ACTION_APPROVE 1
+#define IGS_ACTION_REVIEW  2
+#define IGS_ACTION_BLOCK   3
+
+/* Transaction type (ScoreRequest.TxType string, scoring/engine.go:44).                         */
+#define IGS_TX_BET      0
+#define IGS_TX_DEPOSIT  1
+#define IGS_TX_WITHDRAW 2
+#define IGS_TX_OTHER    3
+
+/* Per-row bits.                                                                               */
+#define IGS_BIT_VPN         (1u << 0) /* IPInfo.IsVPN   scoring/engine.go:403                    */
+#define IGS_BIT_PROXY       (1u << 1) /* IPInfo.IsProxy :404                                     */
+#define IGS_BIT_TOR         (1u << 2) /* IPInfo.IsTor   :405                                     */
+#define IGS_BIT_BONUS_ONLY  (1u << 3) /* FeatureVector.BonusOnlyPlayer :384-386 (feature rows)   */
+#define IGS_BIT_BLACKLISTED (1u << 4) /* verdict of Blacklist.Check :470 (host-side set lookup)  */
+#define IGS_BIT_VALID       (1u << 5) /* 0 = the host could not stage this row's model input:
+                                         the model "fails" and ml = 0.5, scoring/engine.go:279-282 */
+
+/* Which model the MLModel slot holds (scoring/engine.go:153-155,276-288).                      */
+#define IGS_MODEL_NONE 0 /* model == nil : ml = 0, no ML_HIGH_RISK                              */
+#define IGS_MODEL_MOCK 1 /* ml/onnx_model.go:258-308 mockPredict (the only runnable reference)  */
+#define IGS_MODEL_GBDT 2 /* tree ensemble loaded with igs_load_gbdt (stands in for fraud_model.onnx) */
+
+/* Output transform of the ensemble margin (ONNX TreeEnsemble post_transform).                 */
+#define IGS_POST_NONE     0 /* ml = clamp(margin, 0, 1)                                          */
+#define IGS_POST_LOGISTIC 1 /* ml = clamp(igs_sigmoid(margin), 0, 1)                             */
+
+typedef struct igs_engine igs_engine;
+
+/* ------------------------------------------------------------------------------------------ */
+/* configuration — mirrors ScoringConfig (scoring/engine.go:196-228) + ruleWeights (:246-257)    */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct igs_config {
+    int32_t block_threshold;       /* >= this score = block   (default 80)  */
+    int32_t review_threshold;      /* >= this score = review  (default 50)  */
+    int32_t max_tx_per_minute;     /* R1: c1m > this          (default 10)  */
+    int32_t max_tx_per_hour;       /* configured, unused by the reference (default 100) */
+    int32_t new_account_days;      /* R2: age < this          (default 7)   */
+    int32_t max_devices_per_day;   /* R3: devices > this      (default 3)   */
+    int32_t max_ips_per_day;       /* R4: ips > this          (default 5)   */
+    int32_t model_kind;            /* IGS_MODEL_*                           */
+    int64_t large_deposit_amount;  /* R2: amount > this, cents (default 100000) */
+    double  ml_weight;             /* default 0.6 */
+    double  rule_weight;           /* default 0.4 */
+    int32_t reason_weight[IGS_NUM_REASONS]; /* indexed by reason bit number; defaults 20,30,25,15,20,15,50,25,20,30 */
+    int32_t reserved[2];
+} igs_config;
+
+/* Fills *cfg with DefaultConfig() (scoring/engine.go:215-228) + the constructor's rule weights
+ * (:246-257) and model_kind = IGS_MODEL_MOCK (what the reference runs when no .onnx exists,
+ * ml/onnx_model.go:50-60).  Pure host code, needs no GPU.                                       */
+void igs_default_config(igs_config* cfg);
+
+/* ------------------------------------------------------------------------------------------ */
+/* row layouts                                                                                */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Rule sideband of one pre-assembled feature row: the exact integers applyRules needs
+ * (scoring/engine.go:420-483) — the normalised floats of the model input cannot reproduce
+ * the integer comparisons.  48 bytes.                                                          */
+typedef struct igs_rule_row {
+    int64_t  amount;             /* ScoreRequest.Amount, cents                  engine.go:43   */
+    int64_t  total_deposits;     /* FeatureVector.TotalDeposits                 engine.go:83   */
+    int64_t  total_withdrawals;  /* FeatureVector.TotalWithdrawals              engine.go:84   */
+    uint32_t tx_count_1m;        /* FeatureVector.TxCount1Min                   engine.go:69   */
+    int32_t  account_age_days;   /* FeatureVector.AccountAge                    engine.go:82   */
+    uint32_t time_since_last_tx; /* FeatureVector.TimeSinceLastTx, seconds      engine.go:90   */
+    uint32_t deposit_count;      /* FeatureVector.DepositCount                  engine.go:86   */
+    uint16_t unique_devices_24h; /* FeatureVector.UniqueDevices24h              engine.go:76   */
+    uint16_t unique_ips_24h;     /* FeatureVector.UniqueIPs24h                  engine.go:77   */
+    uint8_t  tx_type;            /* IGS_TX_*                                                   */
+    uint8_t  bits;               /* IGS_BIT_*                                                  */
+    uint8_t  pad[2];
+} igs_rule_row;
+
+/* Result of scoring one transaction.  8 bytes.  Replaces the scalar part of ScoreResponse
+ * (scoring/engine.go:56-64); rule_score is recomputed on the host from `flags`
+ * (igs_rule_score_from_flags), reason strings from `flags` in emission order.                  */
+typedef struct igs_result {
+    float    ml_score; /* ScoreResponse.MLScore narrowed to the wire type (risk.proto:67)       */
+    uint16_t flags;    /* IGS_R_* bits                                                          */
+    uint8_t  score;    /* ScoreResponse.Score 0..100                                            */
+    uint8_t  action;   /* IGS_ACTION_*                                                          */
+} igs_result;
+
+/* Compact transaction record for the fused path (assembly on device).  32 bytes.
+ * Replaces the fields of ScoreRequest the reference actually reads (scoring/engine.go:40-53)
+ * plus the host-side verdicts (IP intelligence :397, blacklist :470, HLL uniques
+ * features/redis_store.go:80-81).                                                               */
+typedef struct igs_tx {
+    int64_t  amount;             /* cents                                                       */
+    uint32_t account;            /* dense player index of this engine's shard                   */
+    uint32_t ts;                 /* unix seconds; plays the role of time.Now() (engine.go:350)   */
+    uint32_t seq_limit;          /* the query sees events of its account ordered before
+                                    (ts, seq_limit); UINT32_MAX = every event with ts' <= ts     */
+    uint16_t unique_devices_24h;
+    uint16_t unique_ips_24h;
+    uint8_t  tx_type;            /* IGS_TX_*                                                    */
+    uint8_t  bits;               /* IGS_BIT_VPN|PROXY|TOR|BLACKLISTED|VALID                      */
+    uint8_t  pad[6];
+} igs_tx;
+
+/* One player's hourly batch features: BatchFeatures, scoring/engine.go:127-140.  96 bytes.      */
+typedef struct igs_player_row {
+    int64_t  total_deposits;
+    int64_t  total_withdrawals;
+    int64_t  total_bets;
+    int64_t  total_wins;
+    int64_t  account_created_at;   /* unix seconds                                              */
+    double   avg_bet_size;
+    double   bonus_wager_complete;
+    int32_t  deposit_count;
+    int32_t  withdraw_count;
+    int32_t  bet_count;
+    int32_t  win_count;
+    int32_t  bonus_claim_count;
+    int32_t  reserved[5];
+} igs_player_row;
+
+/* Event history, struct of arrays (17 bytes per event).  Replaces the writes of
+ * UpdateRealTimeFeatures, features/redis_store.go:119-168.  Arrival order = array order.        */
+typedef struct igs_event_cols {
+    const uint32_t* account;   /* dense player index                                            */
+    const uint32_t* ts;        /* unix seconds                                                  */
+    const int64_t*  amount;    /* cents                                                         */
+    const uint8_t*  tx_type;   /* IGS_TX_*                                                      */
+} igs_event_cols;
+
+/* Velocity query: "what would GetRealTimeFeatures return for this account at time ts".          */
+typedef struct igs_query {
+    uint32_t account;
+    uint32_t ts;
+    uint32_t seq_limit;        /* see igs_tx.seq_limit                                          */
+    uint32_t reserved;
+} igs_query;
+
+/* Per-type sliding window aggregate of the north-star extension (plain multiset semantics,
+ * inclusive lower bound, prior events only).                                                   */
+typedef struct igs_window {
+    int64_t  sum;
+    uint32_t count;
+    uint32_t pad;
+} igs_window;
+
+/* Velocity block of one query.  Replaces RealTimeFeatures (features/redis_store.go:38-47 as
+ * filled by GetRealTimeFeatures :60-116) and adds the extension windows.  128 bytes.           */
+typedef struct igs_velocity {
+    int64_t  tx_sum_1h;            /* Redis key tx_sum:1h — a chain sum, not a sliding window   */
+    uint32_t tx_count_1m;          /* ZCOUNT [now-60,+inf)   distinct "ts:amount" members       */
+    uint32_t tx_count_5m;          /* ZCOUNT [now-300,+inf)                                     */
+    uint32_t tx_count_1h;          /* ZCOUNT [now-3600,+inf) after the 1h trim                  */
+    uint32_t time_since_last_tx;   /* now - last_tx  iff key alive (7d), else 0                 */
+    uint32_t session_duration;     /* now - session_start iff key alive (30m chain), else 0     */
+    uint32_t n_prior;              /* events of the account ordered before the query            */
+    igs_window win[2][3];          /* [IGS_TX_BET|IGS_TX_DEPOSIT][1m,1h,24h]                     */
+} igs_velocity;
+
+/* Tree ensemble: n_trees complete depth-8 trees in implicit heap order (node i has children
+ * 2i+1 / 2i+2; leaf j of the bottom level follows internal node 127+j/2).  Branch rule =
+ * ONNX BRANCH_LEQ: go left iff x[feat] <= thr; NaN goes right.  margin = base_score +
+ * leaves summed in tree-index order in fp32.  Stands in for fraud_model.onnx
+ * (services/risk/cmd/main.go:62; ml/onnx_model.go:63-68,238).                                  */
+typedef struct igs_gbdt_desc {
+    uint32_t       n_trees;
+    uint32_t       n_features;     /* <= IGS_NUM_FEATURES                                        */
+    uint32_t       post_transform; /* IGS_POST_*                                                 */
+    float          base_score;
+    const uint8_t* feat;           /* n_trees * 255                                              */
+    const float*   thr;            /* n_trees * 255                                              */
+    const float*   leaf;           /* n_trees * 256                                              */
+} igs_gbdt_desc;
+
+/* LTV head: 256 -> 1024 -> 1024 -> 1024 -> 1, ReLU between layers, bf16 operands, fp32
+ * accumulate.  Weights row-major [out][in] as raw bf16 bit patterns; biases fp32.  Stands in for
+ * ltv_model.onnx (services/risk/cmd/main.go:63; ml/onnx_model.go:396-432).                    */
+#define IGS_MLP_IN     256
+#define IGS_MLP_HIDDEN 1024
+typedef struct igs_mlp_desc {
+    const uint16_t* w1; const float* b1; /* [1024][256], [1024]  */
+    const uint16_t* w2; const float* b2; /* [1024][1024], [1024] */
+    const uint16_t* w3; const float* b3; /* [1024][1024], [1024] */
+    const uint16_t* w4; const float* b4; /* [1][1024], [1]       */
+} igs_mlp_desc;
+
+/* Per-player sideband of the LTV epilogue: the PlayerFeatures fields that the post-model steps
+ * of LTVPredictor.Predict read (prediction/ltv.go:124-139,228-382).  80 bytes.                 */
+typedef struct igs_ltv_row {
+    double  sessions_per_week;
+    double  deposit_frequency;
+    double  total_deposits;
+    double  total_withdrawals;
+    double  net_revenue;
+    double  bonus_conversion_rate;
+    int32_t days_since_registration;
+    int32_t days_since_last_deposit;
+    int32_t days_since_last_bet;
+    int32_t bet_count;
+    int32_t support_tickets;
+    int32_t bonuses_claimed;
+    int32_t games_played;
+    uint8_t push_enabled, email_opt_in, has_vip_manager, pad;
+} igs_ltv_row;
+
+/* LTVPrediction (prediction/ltv.go:26-35) without the uuid / timestamp.  32 bytes.              */
+#define IGS_SEG_VIP 1
+#define IGS_SEG_HIGH 2
+#define IGS_SEG_MEDIUM 3
+#define IGS_SEG_LOW 4
+#define IGS_SEG_CHURNING 5       /* numbered as risk.proto:122-129 */
+typedef struct igs_ltv_result {
+    double  predicted_ltv;       /* adjusted LTV, ltv.go:127                                     */
+    double  churn_risk;
+    float   confidence;
+    int32_t days_survival;
+    uint8_t segment;             /* IGS_SEG_*                                                    */
+    uint8_t next_best_action;    /* index into igs_ltv_action_name()                             */
+    uint8_t pad[6];
+} igs_ltv_result;
+
+/* ------------------------------------------------------------------------------------------ */
+/* engine life cycle                                                                          */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Replaces NewScoringEngine (scoring/engine.go:231-259) + ml.NewONNXModel (ml/onnx_model.go:44-82):
+ * binds the engine to CUDA device `device`, creates IGS_NUM_SLOTS stream slots.  Fails with
+ * IGS_ERR_CUDA when there is no usable device.                                                  */
+int  igs_engine_create(int device, igs_engine** out);
+/* Replaces ONNXModel.Close (ml/onnx_model.go:348-356).                                          */
+void igs_engine_destroy(igs_engine* e);
+/* Text of the last error on this engine (or of the last failed igs_engine_create when e==NULL). */
+const char* igs_last_error(const igs_engine* e);
+
+/* Pinned host memory for hot-path host buffers (cgo cannot hand Go memory to an async copy).   */
+void* igs_alloc_pinned(size_t bytes);
+void  igs_free_pinned(void* p);
+
+/* Replaces the model file load of ml.NewONNXModel (ml/onnx_model.go:62-81).                      */
+int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d);
+/* Replaces ml.NewLTVModel (ml/onnx_model.go:396-402).                                            */
+int igs_load_mlp(igs_engine* e, const igs_mlp_desc* d);
+/* Replaces FeatureStore.GetBatchFeatures (scoring/engine.go:110; "ClickHouse, computed hourly"):
+ * the whole BatchFeatures table of this shard becomes device resident.                          */
+int igs_load_players(igs_engine* e, const igs_player_row* rows, uint64_t n);
+/* Replaces the Redis state written by UpdateRealTimeFeatures (features/redis_store.go:119-168):
+ * sorts the events by (account, ts, arrival) and builds the per-account scan columns.
+ * n_accounts = size of the dense account index space.                                          */
+int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts);
+
+/* ------------------------------------------------------------------------------------------ */
+/* scoring — replaces ScoringEngine.Score (scoring/engine.go:262-323) applied to a batch, i.e.   */
+/* rpc ScoreBatch (proto/risk/v1/risk.proto:13,76-82) and ONNXModel.PredictBatch                 */
+/* (ml/onnx_model.go:311-326)                                                                   */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Path A: pre-assembled model input.  features = n x 64 fp32 rows, already normalised
+ * (ml/onnx_model.go:169-184); rows = the rule sideband.  Host buffers; synchronous.
+ * leaf_idx (optional, may be NULL) receives n x n_trees bytes: the leaf reached in every tree.  */
+int igs_score_features(igs_engine* e, const igs_config* cfg, const float* features,
+                       const igs_rule_row* rows, uint64_t n, igs_result* out, uint8_t* leaf_idx);
+/* Same, asynchronous on slot `slot` (0..IGS_NUM_SLOTS-1); host buffers must be pinned and stay
+ * valid until igs_wait(e, slot) returns.                                                        */
+int igs_score_features_async(igs_engine* e, int slot, const igs_config* cfg, const float* features,
+                             const igs_rule_row* rows, uint64_t n, igs_result* out);
+int igs_wait(igs_engine* e, int slot);
+/* Same on device-resident buffers; enqueues on `stream` (a cudaStream_t, NULL = default) and
+ * returns without synchronising.                                                                */
+int igs_score_features_device(igs_engine* e, const igs_config* cfg, const float* d_features,
+                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
+                              uint8_t* d_leaf_idx, void* stream);
+
+/* Velocity only — replaces FeatureStore.GetRealTimeFeatures (features/redis_store.go:60-116)
+ * for n queries against the loaded event history.                                              */
+int igs_get_velocity(igs_engine* e, const igs_query* q, uint64_t n, igs_velocity* out);
+int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
+                        void* stream);
+
+/* Path B, the fused path: compact tx records in, results out; velocity lookup, extractFeatures
+ * (scoring/engine.go:326-417), the scoring->ml mapping + Normalize (ml/onnx_model.go:133-184),
+ * applyRules (:420-483), the model and the blend (:284-310) all run on the device against the
+ * loaded players / events / model.  features_out (optional, may be NULL) receives the n x 64
+ * assembled model input, velocity_out (optional) the n velocity blocks.                         */
+int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n,
+                    igs_result* out, float* features_out, igs_velocity* velocity_out);
+int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const igs_tx* tx,
+                          uint64_t n, igs_result* out);
+int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
+                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+                           void* stream);
+
+/* LTV — replaces LTVPredictor.BatchPredict (prediction/ltv.go:385-398): x = n x 256 bf16 model
+ * input (raw bit patterns), rows = epilogue sideband.  The MLP output replaces calculateLTV
+ * (:155-178); churn / adjust / segment / survival / action / confidence follow :124-139.
+ * ltv_raw (optional) receives the fp32 model output.                                           */
+int igs_ltv_batch(igs_engine* e, const uint16_t* x, const igs_ltv_row* rows, uint64_t n,
+                  igs_ltv_result* out, float* ltv_raw);
+int igs_ltv_batch_device(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,
+                         igs_ltv_result* d_out, float* d_ltv_raw, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* host-side helpers (pure C, no GPU)                                                          */
+/* ------------------------------------------------------------------------------------------ */
+
+/* min(100, sum of the weights of the rule bits in flags) — ScoreResponse.RuleScore,
+ * scoring/engine.go:421-482.  ML_HIGH_RISK does not contribute.                                 */
+int32_t igs_rule_score_from_flags(const igs_config* cfg, uint32_t flags);
+/* Reason strings in the order applyRules emits them (R1..R8, then ML): writes up to
+ * IGS_NUM_REASONS pointers to static strings into out[], returns how many.                      */
+int igs_reason_codes(uint32_t flags, const char* out[IGS_NUM_REASONS]);
+const char* igs_action_name(int action);       /* "approve" | "review" | "block"                */
+const char* igs_ltv_action_name(int idx);      /* prediction/ltv.go:300-343 strings             */
+const char* igs_segment_name(int seg);         /* prediction/ltv.go:17-23                       */
+/* shard = splitmix64(lo ^ hi) % n_shards for a 16-byte account uuid (ScoreRequest.AccountID).   */
+uint32_t igs_shard_of(uint64_t uuid_lo, uint64_t uuid_hi, uint32_t n_shards);
+/* Library / build identification, e.g. "igs 0.1 sm_100a".                                       */
+const char* igs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGS_H_ */
