@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 fraud-scoring engine.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): 1M transactions x 64 fp32 features, 500-tree depth-8
+ensemble + the 8 rule checks + blend/action, per GPU.  A "step" = one pass of the fused score
+kernel over one 1M-tx batch.  N>1 (torchrun): every rank owns one GPU and one shard of the same
+size (transactions shard by player hash, no collective on the data path) -> weak scaling.
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput, `e2e` = the same metric
+through the host-buffer C-ABI call (H2D + kernel + D2H inside the timed region), `roofline` and
+`cpu_baseline` as the task contract describes.  `--impl reference` times the CPU oracle (the
+restatement of the reference's per-request path; the Go + ONNX Runtime original cannot run here)
+on all host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+
+N_TX = 1_000_000
+N_TREES = 500
+LAT_BATCH = 65_536
+ALGO_BYTES_PER_TX = 256 + 48 + 8            # features + rule sideband in, result out
+MODEL_BYTES = N_TREES * (255 * 5 + 256 * 4)  # 1 149 500 B in the ABI layout (feat u8 + thr f32 + leaves)
+METRIC = "transactions scored/sec"
+UNIT = "tx/s"
+
+
+def env_int(k, d):
+    try:
+        return int(os.environ.get(k, d))
+    except ValueError:
+        return d
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            j = json.load(open(p))
+            return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.idx = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(np.max(mx)) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def pinned_array(lib, shape, dtype):
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    p = lib.igs_alloc_pinned(nbytes)
+    if not p:
+        raise RuntimeError("igs_alloc_pinned failed")
+    buf = (C.c_uint8 * nbytes).from_address(p)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape), p
+
+
+def cpu_baseline(orc, cfg, model, feats, rows, threads, target_s=3.0):
+    """Oracle (kind "port") timed on `threads` host threads on a bounded sample of the workload."""
+    n_cal = 4096
+    t0 = time.perf_counter()
+    orc.score_features(cfg, model, feats[:n_cal], rows[:n_cal], threads=threads)
+    dt = max(time.perf_counter() - t0, 1e-4)
+    n = int(min(feats.shape[0], max(n_cal, target_s * n_cal / dt)))
+    t0 = time.perf_counter()
+    orc.score_features(cfg, model, feats[:n], rows[:n], threads=threads)
+    dt = time.perf_counter() - t0
+    return n / dt, n, dt
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement of the reference's per-request scoring loop
+    (ml/onnx_model.go:311-326 PredictBatch + scoring/engine.go:262-323), all host threads."""
+    if rank != 0:
+        return
+    from oracle import oracle as orc
+    from tests import synth
+    pkg = ge.load_package()
+    threads = os.cpu_count() or 1
+    model = synth.make_gbdt(n_trees=N_TREES)
+    n_pool = 262_144
+    feats, rows = synth.make_feature_batch(n_pool)
+    cfg = orc.default_config(model_kind=pkg.abi.MODEL_GBDT)
+    # size the per-step sample so warmup+steps end within a few minutes
+    rate, _, _ = cpu_baseline(orc, cfg, model, feats, rows, threads, target_s=1.0)
+    n_step = int(min(n_pool, max(4096, rate * 2.0)))
+    for _ in range(args.warmup):
+        orc.score_features(cfg, model, feats[:n_step], rows[:n_step], threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.score_features(cfg, model, feats[:n_step], rows[:n_step], threads=threads)
+    dt = time.perf_counter() - t0
+    value = n_step * args.steps / dt
+    sample = f"{n_step} tx per step from the same seeded C2 batch, {N_TREES} trees depth 8"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "C2: 1M tx x 64 f32 features, 500-tree depth-8 GBDT + 8 rules + blend "
+                               "(bounded sample per step)", "n_trees": N_TREES, "n_features": 64},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference Go + ONNX Runtime + Redis cannot be built or run in this image; this is "
+                "the C restatement of its per-request loop (oracle/), all host threads",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n-tx", type=int, default=N_TX)
+    ap.add_argument("--skip-latency", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    ge.build_library()
+    pkg = ge.load_package()
+    abi = pkg.abi
+    lib = abi.load_library()
+    from tests import synth
+
+    n = args.n_tx
+    model = synth.make_gbdt(n_trees=N_TREES)
+    feats, rows = synth.make_feature_batch(n, seed=synth.MASTER_SEED + 7919 * rank)
+    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    eng = pkg.Engine(device=local)
+    eng.load_gbdt(model)
+
+    dev = torch.device("cuda", local)
+    d_feats = torch.from_numpy(feats).to(dev)
+    d_rows = torch.from_numpy(rows.view(np.uint8).reshape(n, -1)).to(dev)
+    d_out = torch.zeros((n, 8), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        eng.score_features_device(cfg, d_feats.data_ptr(), d_rows.data_ptr(), n, d_out.data_ptr(), 0, stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) and per-launch time of the score kernel ----------
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    evs[0].record()
+    for i in range(args.steps):
+        step()
+        evs[i + 1].record()
+    barrier()
+    total_ms = evs[0].elapsed_time(evs[-1])
+    per_launch_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    value = n * world * args.steps / (total_ms_max * 1e-3)
+
+    # sanity: the bench batch really is what the oracle says (small prefix, rank 0)
+    got = np.frombuffer(d_out[:2048].cpu().numpy().tobytes(), dtype=abi.result_dtype)
+
+    # ---- end to end through the host-buffer C ABI (pinned host memory) --------------------------
+    h_feats, p1 = pinned_array(lib, (n, 64), np.float32)
+    h_rows, p2 = pinned_array(lib, (n,), abi.rule_row_dtype)
+    h_out, p3 = pinned_array(lib, (n,), abi.result_dtype)
+    h_feats[:] = feats
+    h_rows[:] = rows
+
+    def e2e_step():
+        st = lib.igs_score_features(eng.handle, C.byref(cfg), h_feats.ctypes.data, h_rows.ctypes.data,
+                                    n, h_out.ctypes.data, None)
+        if st != 0:
+            raise RuntimeError(lib.igs_last_error(eng.handle).decode())
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = n * world * e2e_steps / float(t.item())
+    assert h_out[:2048].tobytes() == got.tobytes(), "host-buffer and device-buffer paths disagree"
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- p99 batch latency: 65 536-tx batches, host call -> results visible ---------------------
+    lat = None
+    if not args.skip_latency and rank == 0:
+        nb = LAT_BATCH
+        lats = []
+        for i in range(1020):
+            off = (i * nb) % (n - nb)
+            t0 = time.perf_counter()
+            st = lib.igs_score_features(eng.handle, C.byref(cfg), h_feats[off:].ctypes.data,
+                                        h_rows[off:].ctypes.data, nb, h_out[off:].ctypes.data, None)
+            lats.append(time.perf_counter() - t0)
+            assert st == 0
+        lats = np.array(lats[20:]) * 1e3
+        lat = {"batch": nb, "batches": int(lats.size), "p50_ms": float(np.percentile(lats, 50)),
+               "p99_ms": float(np.percentile(lats, 99)), "max_ms": float(lats.max())}
+
+    # ---- CPU baseline (oracle port) on rank 0, N=1 only ----------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        from oracle import oracle as orc
+        threads = os.cpu_count() or 1
+        ocfg = orc.default_config(model_kind=abi.MODEL_GBDT)
+        want = orc.score_features(ocfg, model, feats[:2048], rows[:2048])
+        assert want.tobytes() == got.tobytes(), "bench batch disagrees with the oracle"
+        r_all, n_all, s_all = cpu_baseline(orc, ocfg, model, feats, rows, threads, target_s=4.0)
+        r_one, n_one, s_one = cpu_baseline(orc, ocfg, model, feats, rows, 1, target_s=3.0)
+        cpu = {"value": r_all, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"first {n_all} tx of the same batch ({s_all:.1f} s wall on {threads} threads)",
+               "single_thread": {"value": r_one, "sample": f"first {n_one} tx ({s_one:.1f} s)"}}
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        k_ms = float(np.mean(per_launch_ms))
+        algo_bytes = n * ALGO_BYTES_PER_TX + MODEL_BYTES
+        achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+        visits = n * N_TREES * 8 / (k_ms * 1e-3)
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "C2: 1M tx x 64 f32 features, 500-tree depth-8 GBDT + 8 rules + blend, per GPU",
+                       "tx_per_gpu": n, "n_trees": N_TREES, "n_features": 64, "depth": 8,
+                       "sharding": f"player-hash shards x{world}, no collective",
+                       "l2": "inputs 312 MB per step > 126 MB L2, no flush needed"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT,
+                    "h2d_bytes_per_step": int(n * (256 + 48)), "d2h_bytes_per_step": int(n * 8),
+                    "steps": e2e_steps, "api": "igs_score_features (pinned host buffers)"},
+            "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "kernel": "k_score_features", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "launch_ms": k_ms,
+                         "note": "algorithmic bytes = 312 B/tx + model once; this kernel is bound by "
+                                 "shared-memory gathers / issue slots (4000 dependent node visits per "
+                                 "tx), not HBM — see on_chip"},
+            "on_chip": {"node_visits_per_s": visits,
+                        "node_visits_per_sm_cycle": visits / (148 * sm_mhz * 1e6),
+                        "sm_mhz_used": sm_mhz},
+            "cpu_baseline": cpu,
+            "p99_batch_latency": lat,
+        }
+        print(json.dumps(line), flush=True)
+
+    for p in (p1, p2, p3):
+        lib.igs_free_pinned(p)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,506 @@
+// igs_engine.cu — the C ABI of include/igs.h: engine life cycle, loads, host-buffer staging.
+// All compute is in the k_*.cu kernels; there is no CPU fallback in this file or anywhere else
+// in the library.
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <cmath>
+#include <new>
+#include <vector>
+
+#include "igs_internal.cuh"
+
+static thread_local char g_create_error[512] = "";
+
+void igs_set_error(igs_engine* e, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(e ? e->err : g_create_error, 512, fmt, ap);
+    va_end(ap);
+}
+
+int igs_reserve(igs_engine* e, igs_buf* b, size_t bytes) {
+    if (bytes <= b->cap) return IGS_OK;
+    if (b->p) {
+        IGS_CUDA(e, cudaFree(b->p));
+        b->p = nullptr;
+        b->cap = 0;
+    }
+    size_t cap = std::max(bytes, (size_t)1 << 20);
+    cap = (cap + 255) & ~(size_t)255;
+    cudaError_t st = cudaMalloc(&b->p, cap);
+    if (st != cudaSuccess) {
+        igs_set_error(e, "cudaMalloc(%zu) failed: %s", cap, cudaGetErrorString(st));
+        b->p = nullptr;
+        return st == cudaErrorMemoryAllocation ? IGS_ERR_NOMEM : IGS_ERR_CUDA;
+    }
+    b->cap = cap;
+    return IGS_OK;
+}
+
+static void free_buf(igs_buf* b) {
+    if (b->p) cudaFree(b->p);
+    b->p = nullptr;
+    b->cap = 0;
+}
+
+#define IGS_TRY(call)                      \
+    do {                                   \
+        int rc__ = (call);                 \
+        if (rc__ != IGS_OK) return rc__;   \
+    } while (0)
+
+#define IGS_ENGINE(e)                                        \
+    do {                                                     \
+        if (!(e)) {                                          \
+            igs_set_error(nullptr, "engine handle is null"); \
+            return IGS_ERR_INVALID;                          \
+        }                                                    \
+        cudaError_t sd__ = cudaSetDevice((e)->device);       \
+        if (sd__ != cudaSuccess) {                           \
+            igs_set_error((e), "cudaSetDevice(%d) failed: %s", (e)->device, cudaGetErrorString(sd__)); \
+            return IGS_ERR_CUDA;                             \
+        }                                                    \
+    } while (0)
+
+extern "C" {
+
+// ------------------------------------------------------------------------------------------------
+// life cycle
+// ------------------------------------------------------------------------------------------------
+int igs_engine_create(int device, igs_engine** out) {
+    if (!out) {
+        igs_set_error(nullptr, "out pointer is null");
+        return IGS_ERR_INVALID;
+    }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t st = cudaGetDeviceCount(&count);
+    if (st != cudaSuccess || count == 0) {
+        igs_set_error(nullptr, "no CUDA device available (%s); this library has no CPU fallback",
+                      st != cudaSuccess ? cudaGetErrorString(st) : "device count is 0");
+        return IGS_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) {
+        igs_set_error(nullptr, "device %d out of range (0..%d)", device, count - 1);
+        return IGS_ERR_INVALID;
+    }
+    st = cudaSetDevice(device);
+    if (st != cudaSuccess) {
+        igs_set_error(nullptr, "cudaSetDevice(%d) failed: %s", device, cudaGetErrorString(st));
+        return IGS_ERR_CUDA;
+    }
+    cudaDeviceProp prop;
+    st = cudaGetDeviceProperties(&prop, device);
+    if (st != cudaSuccess) {
+        igs_set_error(nullptr, "cudaGetDeviceProperties failed: %s", cudaGetErrorString(st));
+        return IGS_ERR_CUDA;
+    }
+    if (prop.major != 10) {
+        igs_set_error(nullptr, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                      prop.major, prop.minor);
+        return IGS_ERR_CUDA;
+    }
+    igs_engine* e = new (std::nothrow) igs_engine();
+    if (!e) {
+        igs_set_error(nullptr, "out of host memory");
+        return IGS_ERR_NOMEM;
+    }
+    e->device = device;
+    e->sm_count = prop.multiProcessorCount;
+    for (int s = 0; s < IGS_NUM_SLOTS; ++s) {
+        if (cudaStreamCreateWithFlags(&e->slot[s].stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&e->slot[s].ev_in, cudaEventDisableTiming) != cudaSuccess) {
+            igs_set_error(nullptr, "stream/event creation failed: %s",
+                          cudaGetErrorString(cudaGetLastError()));
+            igs_engine_destroy(e);
+            return IGS_ERR_CUDA;
+        }
+    }
+    *out = e;
+    return IGS_OK;
+}
+
+void igs_engine_destroy(igs_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    for (int s = 0; s < IGS_NUM_SLOTS; ++s) {
+        igs_slot& sl = e->slot[s];
+        free_buf(&sl.in0); free_buf(&sl.in1); free_buf(&sl.out0); free_buf(&sl.aux0); free_buf(&sl.aux1);
+        if (sl.ev_in) cudaEventDestroy(sl.ev_in);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
+    }
+    if (e->d_model) cudaFree(e->d_model);
+    if (e->d_players) cudaFree(e->d_players);
+    igs_free_event_index(e);
+    igs_mlp_free(e);
+    delete e;
+}
+
+const char* igs_last_error(const igs_engine* e) { return e ? e->err : g_create_error; }
+
+void* igs_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void igs_free_pinned(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+// ------------------------------------------------------------------------------------------------
+// loads
+// ------------------------------------------------------------------------------------------------
+int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, d != nullptr, "desc is null");
+    IGS_REQUIRE(e, d->n_features >= 1 && d->n_features <= IGS_NUM_FEATURES, "n_features must be 1..64");
+    IGS_REQUIRE(e, d->post_transform <= IGS_POST_LOGISTIC, "post_transform");
+    IGS_REQUIRE(e, d->n_trees <= (1u << 20), "n_trees must be <= 2^20");
+    IGS_REQUIRE(e, d->n_trees == 0 || (d->feat && d->thr && d->leaf), "feat/thr/leaf pointer is null");
+    IGS_REQUIRE(e, std::isfinite(d->base_score), "base_score must be finite");
+    std::lock_guard<std::mutex> lk(e->mu);
+    // host-side repack into the device layout (see igs_internal.cuh)
+    const size_t bytes = (size_t)d->n_trees * IGS_DEV_TREE_BYTES;
+    std::vector<uint8_t> img(bytes ? bytes : 16, 0);
+    for (uint32_t t = 0; t < d->n_trees; ++t) {
+        igs_dev_node* nodes = reinterpret_cast<igs_dev_node*>(img.data() + (size_t)t * IGS_DEV_TREE_BYTES);
+        float* leaves = reinterpret_cast<float*>(img.data() + (size_t)t * IGS_DEV_TREE_BYTES + 2048);
+        for (int i = 0; i < IGS_TREE_NODES; ++i) {
+            const uint8_t f = d->feat[(size_t)t * IGS_TREE_NODES + i];
+            if (f >= d->n_features) {
+                igs_set_error(e, "tree %u node %d: feature index %u >= n_features %u", t, i, f, d->n_features);
+                return IGS_ERR_INVALID;
+            }
+            nodes[i].feat_off = (uint32_t)f * 128u;
+            nodes[i].thr = d->thr[(size_t)t * IGS_TREE_NODES + i];
+        }
+        for (int i = 0; i < IGS_TREE_LEAVES; ++i) {
+            const float lf = d->leaf[(size_t)t * IGS_TREE_LEAVES + i];
+            if (!std::isfinite(lf) || fabsf(lf) > 1e30f) {
+                igs_set_error(e, "tree %u leaf %d is not finite or exceeds 1e30", t, i);
+                return IGS_ERR_INVALID;
+            }
+            leaves[i] = lf;
+        }
+    }
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    if (e->d_model) {
+        IGS_CUDA(e, cudaFree(e->d_model));
+        e->d_model = nullptr;
+    }
+    e->has_gbdt = false;
+    IGS_CUDA(e, cudaMalloc(&e->d_model, img.size()));
+    IGS_CUDA(e, cudaMemcpy(e->d_model, img.data(), img.size(), cudaMemcpyHostToDevice));
+    e->n_trees = d->n_trees;
+    e->n_features = d->n_features;
+    e->post_transform = d->post_transform;
+    e->base_score = d->base_score;
+    e->has_gbdt = true;
+    return IGS_OK;
+}
+
+int igs_load_mlp(igs_engine* e, const igs_mlp_desc* d) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, d != nullptr, "desc is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_mlp_upload(e, d);
+}
+
+int igs_load_players(igs_engine* e, const igs_player_row* rows, uint64_t n) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || rows != nullptr, "rows is null");
+    IGS_REQUIRE(e, n < (1ull << 32), "at most 2^32-1 players per shard");
+    std::lock_guard<std::mutex> lk(e->mu);
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    if (e->d_players) {
+        IGS_CUDA(e, cudaFree(e->d_players));
+        e->d_players = nullptr;
+    }
+    e->n_players = 0;
+    if (n) {
+        IGS_CUDA(e, cudaMalloc(&e->d_players, n * sizeof(igs_player_row)));
+        IGS_CUDA(e, cudaMemcpy(e->d_players, rows, n * sizeof(igs_player_row), cudaMemcpyHostToDevice));
+    }
+    e->n_players = n;
+    return IGS_OK;
+}
+
+int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, ev != nullptr, "event columns are null");
+    IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
+    IGS_REQUIRE(e, n < 0xFFFFFFFFull, "at most 2^32-2 events per shard");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_build_event_index(e, ev, n, n_accounts);
+}
+
+// ------------------------------------------------------------------------------------------------
+// path A
+// ------------------------------------------------------------------------------------------------
+// Host-buffer scoring on one slot: the batch is cut into chunks; each chunk's H2D copy, kernel and
+// D2H copy are queued on the slot's stream, so chunk k+1 uploads while chunk k computes only when
+// the caller uses several slots.  (One stream keeps result order trivially correct.)
+static int score_features_host(igs_engine* e, int s, const igs_config* cfg, const float* features,
+                               const igs_rule_row* rows, uint64_t n, igs_result* out, uint8_t* leaf_idx) {
+    IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
+    IGS_REQUIRE(e, n == 0 || (rows && out), "rows / out is null");
+    IGS_REQUIRE(e, n == 0 || cfg->model_kind == IGS_MODEL_NONE || features, "features is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[s];
+    const bool need_feat = cfg->model_kind != IGS_MODEL_NONE;
+    const bool leaves = leaf_idx != nullptr && cfg->model_kind == IGS_MODEL_GBDT;
+    const uint32_t nt = e->n_trees;
+    IGS_TRY(igs_reserve(e, &sl.in0, need_feat ? n * IGS_NUM_FEATURES * sizeof(float) : 0));
+    IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_rule_row)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_result)));
+    if (leaves) IGS_TRY(igs_reserve(e, &sl.aux0, n * (size_t)nt));
+    if (need_feat)
+        IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, features, n * IGS_NUM_FEATURES * sizeof(float),
+                                    cudaMemcpyHostToDevice, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in1.p, rows, n * sizeof(igs_rule_row), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_score_features(e, cfg, (const float*)sl.in0.p, (const igs_rule_row*)sl.in1.p, n,
+                                      (igs_result*)sl.out0.p, leaves ? (uint8_t*)sl.aux0.p : nullptr,
+                                      sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_result), cudaMemcpyDeviceToHost, sl.stream));
+    if (leaves)
+        IGS_CUDA(e, cudaMemcpyAsync(leaf_idx, sl.aux0.p, n * (size_t)nt, cudaMemcpyDeviceToHost, sl.stream));
+    return IGS_OK;
+}
+
+int igs_score_features(igs_engine* e, const igs_config* cfg, const float* features,
+                       const igs_rule_row* rows, uint64_t n, igs_result* out, uint8_t* leaf_idx) {
+    IGS_ENGINE(e);
+    IGS_TRY(score_features_host(e, 0, cfg, features, rows, n, out, leaf_idx));
+    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
+    return IGS_OK;
+}
+
+int igs_score_features_async(igs_engine* e, int slot, const igs_config* cfg, const float* features,
+                             const igs_rule_row* rows, uint64_t n, igs_result* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, slot >= 0 && slot < IGS_NUM_SLOTS, "slot out of range");
+    return score_features_host(e, slot, cfg, features, rows, n, out, nullptr);
+}
+
+int igs_wait(igs_engine* e, int slot) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, slot >= 0 && slot < IGS_NUM_SLOTS, "slot out of range");
+    IGS_CUDA(e, cudaStreamSynchronize(e->slot[slot].stream));
+    return IGS_OK;
+}
+
+int igs_score_features_device(igs_engine* e, const igs_config* cfg, const float* d_features,
+                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
+                              uint8_t* d_leaf_idx, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
+    return igs_launch_score_features(e, cfg, d_features, d_rows, n, d_out, d_leaf_idx, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// velocity
+// ------------------------------------------------------------------------------------------------
+int igs_get_velocity(igs_engine* e, const igs_query* q, uint64_t n, igs_velocity* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (q && out), "q / out is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[0];
+    IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_query)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_velocity)));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, q, n * sizeof(igs_query), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_velocity(e, (const igs_query*)sl.in0.p, n, (igs_velocity*)sl.out0.p, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_velocity), cudaMemcpyDeviceToHost, sl.stream));
+    IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
+    return IGS_OK;
+}
+
+int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
+                            void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (d_q && d_out), "q / out is null");
+    return igs_launch_velocity(e, d_q, n, d_out, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// path B
+// ------------------------------------------------------------------------------------------------
+static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const igs_tx* tx, uint64_t n,
+                            igs_result* out, float* features_out, igs_velocity* velocity_out) {
+    IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
+    IGS_REQUIRE(e, n == 0 || (tx && out), "tx / out is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[s];
+    IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_tx)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_result)));
+    if (features_out) IGS_TRY(igs_reserve(e, &sl.aux0, n * IGS_NUM_FEATURES * sizeof(float)));
+    if (velocity_out) IGS_TRY(igs_reserve(e, &sl.aux1, n * sizeof(igs_velocity)));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, tx, n * sizeof(igs_tx), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_score_batch(e, cfg, (const igs_tx*)sl.in0.p, n, (igs_result*)sl.out0.p,
+                                   features_out ? (float*)sl.aux0.p : nullptr,
+                                   velocity_out ? (igs_velocity*)sl.aux1.p : nullptr, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_result), cudaMemcpyDeviceToHost, sl.stream));
+    if (features_out)
+        IGS_CUDA(e, cudaMemcpyAsync(features_out, sl.aux0.p, n * IGS_NUM_FEATURES * sizeof(float),
+                                    cudaMemcpyDeviceToHost, sl.stream));
+    if (velocity_out)
+        IGS_CUDA(e, cudaMemcpyAsync(velocity_out, sl.aux1.p, n * sizeof(igs_velocity),
+                                    cudaMemcpyDeviceToHost, sl.stream));
+    return IGS_OK;
+}
+
+int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n, igs_result* out,
+                    float* features_out, igs_velocity* velocity_out) {
+    IGS_ENGINE(e);
+    IGS_TRY(score_batch_host(e, 0, cfg, tx, n, out, features_out, velocity_out));
+    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
+    return IGS_OK;
+}
+
+int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const igs_tx* tx, uint64_t n,
+                          igs_result* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, slot >= 0 && slot < IGS_NUM_SLOTS, "slot out of range");
+    return score_batch_host(e, slot, cfg, tx, n, out, nullptr, nullptr);
+}
+
+int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
+                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+                           void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
+    IGS_REQUIRE(e, n == 0 || (d_tx && d_out), "tx / out is null");
+    return igs_launch_score_batch(e, cfg, d_tx, n, d_out, d_features_out, d_velocity_out,
+                                  (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// LTV
+// ------------------------------------------------------------------------------------------------
+int igs_ltv_batch(igs_engine* e, const uint16_t* x, const igs_ltv_row* rows, uint64_t n,
+                  igs_ltv_result* out, float* ltv_raw) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (x && rows && out), "x / rows / out is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[0];
+    IGS_TRY(igs_reserve(e, &sl.in0, n * IGS_MLP_IN * sizeof(uint16_t)));
+    IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_ltv_row)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_ltv_result)));
+    IGS_TRY(igs_reserve(e, &sl.aux0, n * sizeof(float)));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, x, n * IGS_MLP_IN * sizeof(uint16_t), cudaMemcpyHostToDevice, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in1.p, rows, n * sizeof(igs_ltv_row), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_ltv(e, (const uint16_t*)sl.in0.p, (const igs_ltv_row*)sl.in1.p, n,
+                           (igs_ltv_result*)sl.out0.p, (float*)sl.aux0.p, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_ltv_result), cudaMemcpyDeviceToHost, sl.stream));
+    if (ltv_raw)
+        IGS_CUDA(e, cudaMemcpyAsync(ltv_raw, sl.aux0.p, n * sizeof(float), cudaMemcpyDeviceToHost, sl.stream));
+    IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
+    return IGS_OK;
+}
+
+int igs_ltv_batch_device(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,
+                         igs_ltv_result* d_out, float* d_ltv_raw, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (d_x && d_rows && d_out), "x / rows / out is null");
+    return igs_launch_ltv(e, d_x, d_rows, n, d_out, d_ltv_raw, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side helpers
+// ------------------------------------------------------------------------------------------------
+void igs_default_config(igs_config* c) {
+    if (!c) return;
+    memset(c, 0, sizeof(*c));
+    c->block_threshold = 80;       // scoring/engine.go:217
+    c->review_threshold = 50;      // :218
+    c->max_tx_per_minute = 10;     // :219
+    c->max_tx_per_hour = 100;      // :220
+    c->new_account_days = 7;       // :221
+    c->large_deposit_amount = 100000;  // :222
+    c->max_devices_per_day = 3;    // :223
+    c->max_ips_per_day = 5;        // :224
+    c->ml_weight = 0.6;            // :225
+    c->rule_weight = 0.4;          // :226
+    c->model_kind = IGS_MODEL_MOCK;
+    static const int32_t w[IGS_NUM_REASONS] = {20, 30, 25, 15, 20, 15, 50, 25, 20, 30};  // :246-257
+    memcpy(c->reason_weight, w, sizeof(w));
+}
+
+int32_t igs_rule_score_from_flags(const igs_config* cfg, uint32_t flags) {
+    if (!cfg) return 0;
+    int32_t total = 0;
+    for (int b = 0; b < IGS_NUM_REASONS; ++b)
+        if ((flags >> b) & 1u)
+            if ((1u << b) != IGS_R_ML_HIGH_RISK) total += cfg->reason_weight[b];
+    return total > 100 ? 100 : total;
+}
+
+int igs_reason_codes(uint32_t flags, const char* out[IGS_NUM_REASONS]) {
+    // emission order of applyRules (scoring/engine.go:424-475), then the ML reason (:285-287)
+    static const struct { uint32_t bit; const char* name; } order[] = {
+        {IGS_R_HIGH_VELOCITY, "HIGH_VELOCITY"},
+        {IGS_R_NEW_ACCOUNT_LARGE_TX, "NEW_ACCOUNT_LARGE_TX"},
+        {IGS_R_MULTIPLE_DEVICES, "MULTIPLE_DEVICES"},
+        {IGS_R_IP_COUNTRY_MISMATCH, "IP_COUNTRY_MISMATCH"},
+        {IGS_R_VPN_DETECTED, "VPN_DETECTED"},
+        {IGS_R_RAPID_DEPOSIT_WITHDRAW, "RAPID_DEPOSIT_WITHDRAW"},
+        {IGS_R_BONUS_ABUSE, "BONUS_ABUSE"},
+        {IGS_R_KNOWN_FRAUDSTER, "KNOWN_FRAUDSTER"},
+        {IGS_R_SUSPICIOUS_PATTERN, "SUSPICIOUS_PATTERN"},
+        {IGS_R_ML_HIGH_RISK, "ML_HIGH_RISK"},
+    };
+    int k = 0;
+    for (const auto& o : order)
+        if (flags & o.bit) out[k++] = o.name;
+    return k;
+}
+
+const char* igs_action_name(int action) {
+    switch (action) {
+    case IGS_ACTION_APPROVE: return "approve";
+    case IGS_ACTION_REVIEW: return "review";
+    case IGS_ACTION_BLOCK: return "block";
+    default: return "";
+    }
+}
+
+const char* igs_ltv_action_name(int idx) {
+    static const char* names[] = {
+        "NO_ACTION", "SEND_WINBACK_BONUS", "SEND_ENGAGEMENT_EMAIL", "VIP_MANAGER_CALL",
+        "EXCLUSIVE_EVENT_INVITE", "ASSIGN_VIP_MANAGER", "RETENTION_BONUS", "LOYALTY_REWARD",
+        "SUGGEST_BONUS", "RECOMMEND_NEW_GAMES", "STANDARD_PROMOTION", "ONBOARDING_GUIDE",
+        "SMALL_DEPOSIT_BONUS"};
+    return idx >= 0 && idx < (int)(sizeof(names) / sizeof(names[0])) ? names[idx] : "";
+}
+
+const char* igs_segment_name(int seg) {
+    switch (seg) {
+    case IGS_SEG_VIP: return "vip";
+    case IGS_SEG_HIGH: return "high";
+    case IGS_SEG_MEDIUM: return "medium";
+    case IGS_SEG_LOW: return "low";
+    case IGS_SEG_CHURNING: return "churning";
+    default: return "";
+    }
+}
+
+static uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+uint32_t igs_shard_of(uint64_t lo, uint64_t hi, uint32_t n_shards) {
+    return n_shards ? (uint32_t)(splitmix64(lo ^ hi) % n_shards) : 0;
+}
+
+const char* igs_version(void) { return "igs 0.1 sm_100a"; }
+
+}  // extern "C"

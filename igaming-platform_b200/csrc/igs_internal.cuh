@@ -1,0 +1,120 @@
+// igs_internal.cuh — engine object and helpers shared by the translation units of libigs.so.
+// Not part of the ABI (that is include/igs.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <mutex>
+
+#include "igs.h"
+
+// ---------------------------------------------------------------------------------------------
+// device-resident model layout
+// ---------------------------------------------------------------------------------------------
+// One tree = 256 node slots of 8 bytes (slot 255 unused) followed by 256 fp32 leaves = 3072 B,
+// so a chunk of trees is one contiguous 16B-aligned block that a single cp.async.bulk moves.
+// Node = { feat_off = feature index * 128 (byte offset of that feature's row in a [64][32] fp32
+// warp tile), thr }.
+struct __align__(8) igs_dev_node {
+    uint32_t feat_off;
+    float    thr;
+};
+constexpr int IGS_DEV_TREE_BYTES = 256 * 8 + 256 * 4;  // 3072
+
+// ---------------------------------------------------------------------------------------------
+// per-slot staging (device buffers that mirror the caller's host buffers)
+// ---------------------------------------------------------------------------------------------
+struct igs_buf {
+    void*  p = nullptr;
+    size_t cap = 0;
+};
+
+struct igs_slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  ev_in = nullptr;   // inputs of the current chunk landed
+    igs_buf      in0, in1, out0, aux0, aux1;
+};
+
+// event history index (see k_velocity.cu)
+struct igs_event_index {
+    uint64_t n = 0;
+    uint32_t n_accounts = 0;
+    uint32_t* seg = nullptr;      // [n_accounts + 1] first sorted position of each account
+    uint32_t* ts = nullptr;       // sorted by (account, ts, arrival)
+    uint32_t* seq = nullptr;      // arrival index of the sorted event
+    int64_t*  amount = nullptr;   // sorted amounts
+    uint32_t* dcnt = nullptr;     // [n+1] exclusive prefix: distinct (account, ts, amount) members
+    uint32_t* tcnt = nullptr;     // [2][n+1] exclusive prefix count per type (bet, deposit)
+    int64_t*  tsum = nullptr;     // [2][n+1] exclusive prefix sum per type
+    int64_t*  chain_sum = nullptr;   // inclusive chain sum (gaps <= 3600) ending at each event
+    uint32_t* sess_start = nullptr;  // ts of the first event of the session chain (gaps <= 1800)
+};
+
+struct igs_engine {
+    int  device = 0;
+    int  sm_count = 0;
+    char err[512] = {0};
+    std::mutex mu;                // guards loads vs. scoring calls
+    igs_slot slot[IGS_NUM_SLOTS];
+
+    // tree ensemble
+    uint8_t* d_model = nullptr;   // n_trees * IGS_DEV_TREE_BYTES
+    uint32_t n_trees = 0, n_features = 0, post_transform = 0;
+    float    base_score = 0.f;
+    bool     has_gbdt = false;
+
+    // players
+    igs_player_row* d_players = nullptr;
+    uint64_t n_players = 0;
+
+    // events
+    igs_event_index ev;
+    bool has_events = false;
+
+    // MLP
+    void* d_mlp = nullptr;        // see k_ltv.cu
+    bool  has_mlp = false;
+};
+
+// ---------------------------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------------------------
+void igs_set_error(igs_engine* e, const char* fmt, ...);
+
+#define IGS_CUDA(e, call)                                                                  \
+    do {                                                                                   \
+        cudaError_t st__ = (call);                                                         \
+        if (st__ != cudaSuccess) {                                                         \
+            igs_set_error((e), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(st__),   \
+                          __FILE__, __LINE__);                                             \
+            return IGS_ERR_CUDA;                                                           \
+        }                                                                                  \
+    } while (0)
+
+#define IGS_REQUIRE(e, cond, msg)                                  \
+    do {                                                           \
+        if (!(cond)) {                                             \
+            igs_set_error((e), "invalid argument: %s", (msg));     \
+            return IGS_ERR_INVALID;                                \
+        }                                                          \
+    } while (0)
+
+int igs_reserve(igs_engine* e, igs_buf* b, size_t bytes);
+
+// kernel launchers (defined next to their kernels)
+int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
+                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
+                              uint8_t* d_leaf_idx, cudaStream_t stream);
+int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
+                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+                           cudaStream_t stream);
+int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
+                        cudaStream_t stream);
+int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts);
+void igs_free_event_index(igs_engine* e);
+int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
+void igs_mlp_free(igs_engine* e);
+int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,
+                   igs_ltv_result* d_out, float* d_ltv_raw, cudaStream_t stream);

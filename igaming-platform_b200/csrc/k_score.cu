@@ -1,0 +1,292 @@
+// k_score.cu — fused rules + tree-ensemble + blend kernel (SURVEY K5+K6+K7), sm_100a.
+//
+// One persistent CTA per SM, 8 warps, one transaction per lane (256 tx per tile).
+//   * Each warp stages its 32 x 64 fp32 feature rows into a private smem tile laid out
+//     [feature][lane]: lane l only ever touches bank l, so the data-dependent x[feat] gather of
+//     the tree walk is bank-conflict free whatever features the 32 lanes ask for.
+//   * The ensemble streams through smem in chunks of 25 trees (76.8 KB) moved by one
+//     cp.async.bulk (TMA bulk copy, SASS UBLKCP) each, double buffered behind mbarriers, so the
+//     L2->smem traffic overlaps the walk of the previous chunk.
+//   * A lane walks 5 trees at once (5 independent LDS->LDS->FSETP chains) to cover the ~2x29
+//     cycle shared-memory latency of one node visit with only 8 warps per SM.
+//   * Leaves are added to the margin in tree-index order in fp32 — the oracle's order — so the
+//     margin, the logistic (igs_sigmoid), the fp64 blend and the integer score are bit-identical
+//     to the CPU restatement.
+// Replaces: ScoringEngine.Score steps 2-5 (scoring/engine.go:272-310), ONNXModel.PredictBatch
+// (ml/onnx_model.go:311-326).
+#include "igs_internal.cuh"
+#include "igs_math.cuh"
+
+namespace {
+
+constexpr int kWarps = 8;
+constexpr int kThreads = kWarps * 32;
+constexpr int kTileTx = kThreads;
+constexpr int kChunkTrees = 25;
+constexpr int kIlp = 5;
+constexpr int kFeatTileFloats = IGS_NUM_FEATURES * 32;           // per warp
+constexpr int kFeatTileBytes = kFeatTileFloats * 4;              // 8 KB
+constexpr int kChunkBytes = kChunkTrees * IGS_DEV_TREE_BYTES;    // 76 800
+constexpr int kSmemBytes = kWarps * kFeatTileBytes + 2 * kChunkBytes + 64;
+static_assert(kChunkTrees % kIlp == 0, "chunk must be a whole number of ILP groups");
+static_assert(kSmemBytes <= 227 * 1024, "smem budget");
+
+struct ScoreParams {
+    igs_config cfg;
+    const float* features;
+    const igs_rule_row* rows;
+    igs_result* out;
+    uint8_t* leaf_idx;
+    unsigned long long n;
+    const uint8_t* model;
+    unsigned n_trees;
+    float base_score;
+    unsigned post;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            " selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+// Walk `trees` trees of the chunk at `cb` for this lane's transaction.  `tile` = this warp's
+// [64][32] fp32 feature tile already offset by lane.  Adds leaves to *margin in tree order.
+template <bool kLeaves>
+__device__ __forceinline__ void walk_chunk(const uint8_t* __restrict__ cb, int trees,
+                                           const uint8_t* __restrict__ tile_lane, float* margin,
+                                           uint8_t* leaf_out) {
+    float m = *margin;
+    int t = 0;
+    for (; t + kIlp <= trees; t += kIlp) {
+        const uint8_t* tb = cb + t * IGS_DEV_TREE_BYTES;
+        uint32_t j[kIlp];
+#pragma unroll
+        for (int k = 0; k < kIlp; ++k) j[k] = 0;
+#pragma unroll
+        for (int d = 0; d < IGS_TREE_DEPTH; ++d) {
+#pragma unroll
+            for (int k = 0; k < kIlp; ++k) {
+                const uint2 nd = *reinterpret_cast<const uint2*>(tb + k * IGS_DEV_TREE_BYTES +
+                                                                 ((1 << d) - 1) * 8 + j[k]);
+                const float x = *reinterpret_cast<const float*>(tile_lane + nd.x);
+                j[k] = 2 * j[k] + ((x <= __uint_as_float(nd.y)) ? 0u : 8u);   // BRANCH_LEQ, NaN -> right
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < kIlp; ++k) {
+            const float lf = *reinterpret_cast<const float*>(tb + k * IGS_DEV_TREE_BYTES + 2048 + (j[k] >> 1));
+            m = __fadd_rn(m, lf);
+            if (kLeaves) leaf_out[t + k] = (uint8_t)(j[k] >> 3);
+        }
+    }
+    for (; t < trees; ++t) {
+        const uint8_t* tb = cb + t * IGS_DEV_TREE_BYTES;
+        uint32_t j = 0;
+#pragma unroll
+        for (int d = 0; d < IGS_TREE_DEPTH; ++d) {
+            const uint2 nd = *reinterpret_cast<const uint2*>(tb + ((1 << d) - 1) * 8 + j);
+            const float x = *reinterpret_cast<const float*>(tile_lane + nd.x);
+            j = 2 * j + ((x <= __uint_as_float(nd.y)) ? 0u : 8u);
+        }
+        m = __fadd_rn(m, *reinterpret_cast<const float*>(tb + 2048 + (j >> 1)));
+        if (kLeaves) leaf_out[t] = (uint8_t)(j >> 3);
+    }
+    *margin = m;
+}
+
+// mockPredict, ml/onnx_model.go:258-308, on the already-normalised tile column of this lane.
+__device__ __forceinline__ double mock_predict(const float* tile_lane) {
+    auto v = [&](int i) { return tile_lane[i * 32]; };
+    double s = 0.0;
+    if (v(0) > 0.5f) s = __dadd_rn(s, 0.2);                        // :262
+    if (v(2) > 0.5f) s = __dadd_rn(s, 0.15);                       // :265
+    if (v(5) > 0.3f) s = __dadd_rn(s, 0.15);                       // :270
+    if (v(6) > 0.25f) s = __dadd_rn(s, 0.1);                       // :273
+    if (v(19) > 0.f || v(20) > 0.f) s = __dadd_rn(s, 0.15);        // :278
+    if (v(21) > 0.f) s = __dadd_rn(s, 0.25);                       // :281
+    if (v(9) < 0.02f && v(26) > 0.5f) s = __dadd_rn(s, 0.2);       // :286
+    if (v(25) > 0.f) s = __dadd_rn(s, 0.15);                       // :291
+    if (v(15) < 0.01f && v(28) > 0.f) {                            // :296
+        if (v(11) > __fmul_rn(v(10), 0.8f)) s = __dadd_rn(s, 0.2); // :297 (f32 multiply)
+    }
+    if (s > 1.0) s = 1.0;                                          // :303
+    return s;
+}
+
+template <bool kLeaves>
+__global__ void __launch_bounds__(kThreads, 1)
+k_score_features(const __grid_constant__ ScoreParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    float* feat_tiles = reinterpret_cast<float*>(smem);
+    uint8_t* chunk_buf = smem + kWarps * kFeatTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(chunk_buf + 2 * kChunkBytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar0 = smem_u32(bars);
+    if (threadIdx.x == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int model_kind = p.cfg.model_kind;
+    const unsigned n_chunks = (p.n_trees + kChunkTrees - 1) / kChunkTrees;
+    const bool use_gbdt = model_kind == IGS_MODEL_GBDT && n_chunks > 0;
+    const unsigned long long n_tiles = (p.n + kTileTx - 1) / kTileTx;
+    const unsigned long long my_tiles =
+        n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const unsigned long long total_chunks = use_gbdt ? my_tiles * n_chunks : 0;
+
+    auto issue = [&](unsigned long long g) {   // g-th chunk of this CTA's sequence; thread 0 only
+        const unsigned c = (unsigned)(g % n_chunks);
+        const unsigned b = (unsigned)(g & 1);
+        const unsigned trees = min((unsigned)kChunkTrees, p.n_trees - c * kChunkTrees);
+        const uint32_t bytes = trees * IGS_DEV_TREE_BYTES;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(bar0 + 8 * b, bytes);
+        bulk_g2s(smem_u32(chunk_buf + b * kChunkBytes), p.model + (size_t)c * kChunkBytes, bytes,
+                 bar0 + 8 * b);
+    };
+    if (threadIdx.x == 0) {
+        if (total_chunks > 0) issue(0);
+        if (total_chunks > 1) issue(1);
+    }
+
+    float* my_tile = feat_tiles + warp * kFeatTileFloats;
+    const uint8_t* tile_lane = reinterpret_cast<const uint8_t*>(my_tile + lane);
+    unsigned long long g = 0;
+
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const unsigned long long row = tile * kTileTx + threadIdx.x;
+        const bool in_range = row < p.n;
+
+        // ---- stage this warp's 32 feature rows, transposed to [feature][lane] ----------------
+        if (model_kind != IGS_MODEL_NONE) {
+            const float4* src = reinterpret_cast<const float4*>(p.features + row * IGS_NUM_FEATURES);
+#pragma unroll
+            for (int q = 0; q < IGS_NUM_FEATURES / 4; ++q) {
+                float4 v = in_range ? __ldg(src + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                my_tile[(4 * q + 0) * 32 + lane] = v.x;
+                my_tile[(4 * q + 1) * 32 + lane] = v.y;
+                my_tile[(4 * q + 2) * 32 + lane] = v.z;
+                my_tile[(4 * q + 3) * 32 + lane] = v.w;
+            }
+        }
+        __syncwarp();
+
+        // ---- rule sideband -> flags + rule score (applyRules) ---------------------------------
+        igs_rule_row rr;
+        {
+            uint4* dst = reinterpret_cast<uint4*>(&rr);
+            const uint4* src = reinterpret_cast<const uint4*>(p.rows + row);
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            dst[0] = in_range ? __ldg(src + 0) : z;
+            dst[1] = in_range ? __ldg(src + 1) : z;
+            dst[2] = in_range ? __ldg(src + 2) : z;
+        }
+        unsigned flags;
+        const int rule = igs_apply_rules(p.cfg, rr.amount, rr.tx_type, rr.tx_count_1m,
+                                         rr.account_age_days, rr.unique_devices_24h,
+                                         rr.unique_ips_24h, rr.bits, rr.time_since_last_tx,
+                                         rr.deposit_count, rr.total_deposits, rr.total_withdrawals,
+                                         &flags);
+        const bool valid = (rr.bits & IGS_BIT_VALID) != 0;
+
+        // ---- model ----------------------------------------------------------------------------
+        double ml = 0.0;
+        if (model_kind == IGS_MODEL_MOCK) {
+            ml = mock_predict(my_tile + lane);
+        } else if (model_kind == IGS_MODEL_GBDT) {
+            float margin = p.base_score;
+            uint8_t* leaf_row = kLeaves && in_range ? p.leaf_idx + row * p.n_trees : nullptr;
+            for (unsigned c = 0; c < n_chunks; ++c, ++g) {
+                const unsigned b = (unsigned)(g & 1);
+                const int trees = (int)min((unsigned)kChunkTrees, p.n_trees - c * kChunkTrees);
+                mbar_wait(bar0 + 8 * b, (uint32_t)((g >> 1) & 1));
+                if (kLeaves) {
+                    uint8_t tmp[kChunkTrees];
+                    walk_chunk<true>(chunk_buf + b * kChunkBytes, trees, tile_lane, &margin, tmp);
+                    if (leaf_row)
+                        for (int t = 0; t < trees; ++t) leaf_row[c * kChunkTrees + t] = valid ? tmp[t] : 0;
+                } else {
+                    walk_chunk<false>(chunk_buf + b * kChunkBytes, trees, tile_lane, &margin, nullptr);
+                }
+                __syncthreads();   // every lane is done with buffer b
+                if (threadIdx.x == 0 && g + 2 < total_chunks) issue(g + 2);
+            }
+            float y = p.post == IGS_POST_LOGISTIC ? igs_sigmoid(margin) : margin;
+            if (y < 0.f) y = 0.f;                                   // ml/onnx_model.go:247-252
+            if (y > 1.f) y = 1.f;
+            ml = (double)y;                                         // float64(result) :254
+        }
+        if (model_kind != IGS_MODEL_NONE && !valid) ml = 0.5;      // scoring/engine.go:279-282
+
+        // ---- blend + action -------------------------------------------------------------------
+        if (in_range) {
+            igs_result r;
+            igs_blend(p.cfg, rule, flags, ml, model_kind != IGS_MODEL_NONE, &r);
+            p.out[row] = r;
+        }
+        __syncwarp();   // tile is rewritten by the next iteration
+    }
+}
+
+}  // namespace
+
+int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
+                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
+                              uint8_t* d_leaf_idx, cudaStream_t stream) {
+    if (n == 0) return IGS_OK;
+    IGS_REQUIRE(e, cfg->model_kind >= IGS_MODEL_NONE && cfg->model_kind <= IGS_MODEL_GBDT,
+                "cfg.model_kind");
+    if (cfg->model_kind == IGS_MODEL_GBDT && !e->has_gbdt) {
+        igs_set_error(e, "model_kind = IGS_MODEL_GBDT but no ensemble was loaded (igs_load_gbdt)");
+        return IGS_ERR_STATE;
+    }
+    IGS_REQUIRE(e, d_rows && d_out, "rows / out pointer is null");
+    IGS_REQUIRE(e, cfg->model_kind == IGS_MODEL_NONE || d_features, "features pointer is null");
+    ScoreParams p;
+    p.cfg = *cfg;
+    p.features = d_features;
+    p.rows = d_rows;
+    p.out = d_out;
+    p.leaf_idx = d_leaf_idx;
+    p.n = n;
+    p.model = e->d_model;
+    p.n_trees = e->has_gbdt ? e->n_trees : 0;
+    p.base_score = e->base_score;
+    p.post = e->post_transform;
+    const bool leaves = d_leaf_idx != nullptr && cfg->model_kind == IGS_MODEL_GBDT;
+    auto kern = leaves ? k_score_features<true> : k_score_features<false>;
+    // per-device attribute; a few hundred ns, so simply set on every launch
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    const unsigned long long n_tiles = (n + kTileTx - 1) / kTileTx;
+    const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : e->sm_count);
+    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
+}
