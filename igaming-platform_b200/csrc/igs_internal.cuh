@@ -37,19 +37,17 @@ struct igs_slot {
     igs_buf      in0, in1, out0, aux0, aux1;
 };
 
-// event history index (see k_velocity.cu)
+// event history index (see velocity.cuh / k_velocity.cu)
+struct igs_prefix_rec;
+struct igs_tail_rec;
 struct igs_event_index {
     uint64_t n = 0;
     uint32_t n_accounts = 0;
-    uint32_t* seg = nullptr;      // [n_accounts + 1] first sorted position of each account
-    uint32_t* ts = nullptr;       // sorted by (account, ts, arrival)
-    uint32_t* seq = nullptr;      // arrival index of the sorted event
-    int64_t*  amount = nullptr;   // sorted amounts
-    uint32_t* dcnt = nullptr;     // [n+1] exclusive prefix: distinct (account, ts, amount) members
-    uint32_t* tcnt = nullptr;     // [2][n+1] exclusive prefix count per type (bet, deposit)
-    int64_t*  tsum = nullptr;     // [2][n+1] exclusive prefix sum per type
-    int64_t*  chain_sum = nullptr;   // inclusive chain sum (gaps <= 3600) ending at each event
-    uint32_t* sess_start = nullptr;  // ts of the first event of the session chain (gaps <= 1800)
+    uint32_t* seg = nullptr;          // [n_accounts + 1] first sorted position of each account
+    uint32_t* ts = nullptr;           // [n] sorted by (account, ts, arrival)
+    uint32_t* seq = nullptr;          // [n] arrival index of the sorted event
+    igs_prefix_rec* pre = nullptr;    // [n + 1] exclusive prefix columns
+    igs_tail_rec* tail = nullptr;     // [n] inclusive chain columns
 };
 
 struct igs_engine {

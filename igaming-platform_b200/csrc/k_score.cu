@@ -12,10 +12,19 @@
 //   * Leaves are added to the margin in tree-index order in fp32 — the oracle's order — so the
 //     margin, the logistic (igs_sigmoid), the fp64 blend and the integer score are bit-identical
 //     to the CPU restatement.
-// Replaces: ScoringEngine.Score steps 2-5 (scoring/engine.go:272-310), ONNXModel.PredictBatch
-// (ml/onnx_model.go:311-326).
+// Two input sources share the kernel body:
+//   kSrcFeatures (path A): pre-assembled normalised 64-float rows + the 48-byte rule sideband.
+//   kSrcTx       (path B): 32-byte tx records; the lane looks its account up in the event index
+//                (velocity.cuh), gathers the player row, runs extractFeatures + the scoring->ml
+//                mapping + Normalize in registers and writes the 64 floats straight into the
+//                smem tile — the assembled row never touches HBM (SURVEY K3-lookup + K4 fused).
+// Replaces: ScoringEngine.Score (scoring/engine.go:262-323) incl. extractFeatures (:326-417),
+// ONNXModel.PredictBatch (ml/onnx_model.go:311-326), Normalize (:169-184).
 #include "igs_internal.cuh"
 #include "igs_math.cuh"
+#include "velocity.cuh"
+
+#include <string.h>
 
 namespace {
 
@@ -31,10 +40,22 @@ constexpr int kSmemBytes = kWarps * kFeatTileBytes + 2 * kChunkBytes + 64;
 static_assert(kChunkTrees % kIlp == 0, "chunk must be a whole number of ILP groups");
 static_assert(kSmemBytes <= 227 * 1024, "smem budget");
 
+constexpr int kSrcFeatures = 0;
+constexpr int kSrcTx = 1;
+
 struct ScoreParams {
     igs_config cfg;
+    // path A
     const float* features;
     const igs_rule_row* rows;
+    // path B
+    const igs_tx* tx;
+    const igs_player_row* players;
+    unsigned long long n_players;
+    igs_index_view ix;
+    float* features_out;
+    igs_velocity* velocity_out;
+    // common
     igs_result* out;
     uint8_t* leaf_idx;
     unsigned long long n;
@@ -42,6 +63,13 @@ struct ScoreParams {
     unsigned n_trees;
     float base_score;
     unsigned post;
+};
+
+// What applyRules reads, in registers.
+struct RuleIn {
+    long long amount, total_deposits, total_withdrawals;
+    unsigned tx_count_1m, tslt, deposit_count, uniq_dev, uniq_ip, bits;
+    int account_age, tx_type;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -136,9 +164,108 @@ __device__ __forceinline__ double mock_predict(const float* tile_lane) {
     return s;
 }
 
-template <bool kLeaves>
+// Path B staging for one lane: velocity lookup + player gather + extractFeatures
+// (scoring/engine.go:326-417) + scoring->ml mapping (ToSlice order, ml/onnx_model.go:133-166) +
+// Normalize (:169-184) + extension block.  Writes the lane's column of the [64][32] tile.
+__device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long long row, bool in_range,
+                                            float* tile_lane /* my_tile + lane */, RuleIn* r) {
+    igs_tx t;
+    {
+        uint4* dst = reinterpret_cast<uint4*>(&t);
+        const uint4* src = reinterpret_cast<const uint4*>(p.tx + row);
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        dst[0] = in_range ? __ldg(src + 0) : z;
+        dst[1] = in_range ? __ldg(src + 1) : z;
+    }
+    igs_velocity_a16 vb;
+    igs_velocity_lookup(p.ix, in_range ? t.account : 0xFFFFFFFFu, t.ts, t.seq_limit, &vb.v);
+    const igs_velocity& v = vb.v;
+    if (p.velocity_out && in_range) {
+        uint4* dst = reinterpret_cast<uint4*>(p.velocity_out + row);
+#pragma unroll
+        for (int k = 0; k < (int)(sizeof(igs_velocity) / 16); ++k) dst[k] = vb.q[k];
+    }
+    // BatchFeatures row (GetBatchFeatures, scoring/engine.go:362); absent -> zero features (:363-366)
+    const bool have_player = in_range && (unsigned long long)t.account < p.n_players;
+    union __align__(16) { igs_player_row r; uint4 q[sizeof(igs_player_row) / 16]; } pl;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(p.players + (have_player ? t.account : 0));
+        const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int k = 0; k < (int)(sizeof(igs_player_row) / 16); ++k) pl.q[k] = have_player ? __ldg(src + k) : z;
+    }
+    const long long now = t.ts;
+    int account_age = 0;
+    float win_rate = 0.f;
+    bool bonus_only = false;
+    if (have_player) {
+        account_age = (int)((now - pl.r.account_created_at) / 86400);          // :374
+        if (pl.r.bet_count > 0)                                                // :379-381
+            win_rate = __double2float_rn(__ddiv_rn((double)pl.r.win_count, (double)pl.r.bet_count));
+        bonus_only = pl.r.bonus_claim_count > 3 && pl.r.total_deposits < 5000;  // :384-386
+    }
+    float avg1h = 0.f;
+    if (v.tx_count_1h > 0)                                                     // :412-414
+        avg1h = __double2float_rn(__ddiv_rn((double)v.tx_sum_1h, (double)v.tx_count_1h));
+    const long long net = pl.r.total_deposits - pl.r.total_withdrawals;        // :370
+    auto put = [&](int i, float x) { tile_lane[i * 32] = x; };
+    put(0, igs_min_max(__uint2float_rn(v.tx_count_1m), 20.f));
+    put(1, igs_min_max(__uint2float_rn(v.tx_count_5m), 50.f));
+    put(2, igs_min_max(__uint2float_rn(v.tx_count_1h), 200.f));
+    put(3, igs_log_transform(__ll2float_rn(v.tx_sum_1h)));
+    put(4, avg1h);
+    put(5, igs_min_max(__uint2float_rn(t.unique_devices_24h), 10.f));
+    put(6, igs_min_max(__uint2float_rn(t.unique_ips_24h), 20.f));
+    put(7, 0.f);                                   // IPCountryChanges: never set by the reference
+    put(8, 0.f);                                   // DeviceAge: never set
+    put(9, igs_min_max(__int2float_rn(account_age), 365.f));
+    put(10, igs_log_transform(__ll2float_rn(pl.r.total_deposits)));
+    put(11, igs_log_transform(__ll2float_rn(pl.r.total_withdrawals)));
+    put(12, __ll2float_rn(net));
+    put(13, __int2float_rn(pl.r.deposit_count));
+    put(14, __int2float_rn(pl.r.withdraw_count));
+    put(15, igs_min_max(__uint2float_rn(v.time_since_last_tx), 86400.f));
+    put(16, __uint2float_rn(v.session_duration));
+    put(17, __double2float_rn(pl.r.avg_bet_size));
+    put(18, win_rate);
+    put(19, (t.bits & IGS_BIT_VPN) ? 1.f : 0.f);
+    put(20, (t.bits & IGS_BIT_PROXY) ? 1.f : 0.f);
+    put(21, (t.bits & IGS_BIT_TOR) ? 1.f : 0.f);
+    put(22, 0.f);                                  // DisposableEmail: never set
+    put(23, __int2float_rn(pl.r.bonus_claim_count));
+    put(24, __double2float_rn(pl.r.bonus_wager_complete));
+    put(25, bonus_only ? 1.f : 0.f);
+    put(26, igs_log_transform(__ll2float_rn(t.amount)));
+    put(27, t.tx_type == IGS_TX_DEPOSIT ? 1.f : 0.f);
+    put(28, t.tx_type == IGS_TX_WITHDRAW ? 1.f : 0.f);
+    put(29, t.tx_type == IGS_TX_BET ? 1.f : 0.f);
+    int k = 30;                                    // north-star extension block, idx 30..41
+#pragma unroll
+    for (int ty = 0; ty < 2; ++ty)
+#pragma unroll
+        for (int w = 0; w < 3; ++w) {
+            put(k++, __uint2float_rn(v.win[ty][w].count));
+            put(k++, __ll2float_rn(v.win[ty][w].sum));
+        }
+#pragma unroll
+    for (int i = 42; i < IGS_NUM_FEATURES; ++i) put(i, 0.f);
+    r->amount = t.amount;
+    r->total_deposits = pl.r.total_deposits;
+    r->total_withdrawals = pl.r.total_withdrawals;
+    r->tx_count_1m = v.tx_count_1m;
+    r->tslt = v.time_since_last_tx;
+    r->deposit_count = (unsigned)pl.r.deposit_count;
+    r->uniq_dev = t.unique_devices_24h;
+    r->uniq_ip = t.unique_ips_24h;
+    r->bits = (t.bits & (IGS_BIT_VPN | IGS_BIT_PROXY | IGS_BIT_TOR | IGS_BIT_BLACKLISTED | IGS_BIT_VALID)) |
+              (bonus_only ? IGS_BIT_BONUS_ONLY : 0u);
+    r->account_age = account_age;
+    r->tx_type = t.tx_type;
+}
+
+template <int kSrc, bool kLeaves>
 __global__ void __launch_bounds__(kThreads, 1)
-k_score_features(const __grid_constant__ ScoreParams p) {
+k_score(const __grid_constant__ ScoreParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     float* feat_tiles = reinterpret_cast<float*>(smem);
     uint8_t* chunk_buf = smem + kWarps * kFeatTileBytes;
@@ -184,37 +311,51 @@ k_score_features(const __grid_constant__ ScoreParams p) {
         const unsigned long long row = tile * kTileTx + threadIdx.x;
         const bool in_range = row < p.n;
 
-        // ---- stage this warp's 32 feature rows, transposed to [feature][lane] ----------------
-        if (model_kind != IGS_MODEL_NONE) {
-            const float4* src = reinterpret_cast<const float4*>(p.features + row * IGS_NUM_FEATURES);
+        RuleIn ri;
+        if (kSrc == kSrcFeatures) {
+            // ---- stage this warp's 32 feature rows, transposed to [feature][lane] ------------
+            if (model_kind != IGS_MODEL_NONE) {
+                const float4* src = reinterpret_cast<const float4*>(p.features + row * IGS_NUM_FEATURES);
 #pragma unroll
-            for (int q = 0; q < IGS_NUM_FEATURES / 4; ++q) {
-                float4 v = in_range ? __ldg(src + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-                my_tile[(4 * q + 0) * 32 + lane] = v.x;
-                my_tile[(4 * q + 1) * 32 + lane] = v.y;
-                my_tile[(4 * q + 2) * 32 + lane] = v.z;
-                my_tile[(4 * q + 3) * 32 + lane] = v.w;
+                for (int q = 0; q < IGS_NUM_FEATURES / 4; ++q) {
+                    float4 v = in_range ? __ldg(src + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    my_tile[(4 * q + 0) * 32 + lane] = v.x;
+                    my_tile[(4 * q + 1) * 32 + lane] = v.y;
+                    my_tile[(4 * q + 2) * 32 + lane] = v.z;
+                    my_tile[(4 * q + 3) * 32 + lane] = v.w;
+                }
             }
-        }
-        __syncwarp();
-
-        // ---- rule sideband -> flags + rule score (applyRules) ---------------------------------
-        igs_rule_row rr;
-        {
+            // ---- rule sideband ---------------------------------------------------------------
+            igs_rule_row rr;
             uint4* dst = reinterpret_cast<uint4*>(&rr);
             const uint4* src = reinterpret_cast<const uint4*>(p.rows + row);
             const uint4 z = make_uint4(0, 0, 0, 0);
             dst[0] = in_range ? __ldg(src + 0) : z;
             dst[1] = in_range ? __ldg(src + 1) : z;
             dst[2] = in_range ? __ldg(src + 2) : z;
+            ri.amount = rr.amount; ri.total_deposits = rr.total_deposits;
+            ri.total_withdrawals = rr.total_withdrawals; ri.tx_count_1m = rr.tx_count_1m;
+            ri.tslt = rr.time_since_last_tx; ri.deposit_count = rr.deposit_count;
+            ri.uniq_dev = rr.unique_devices_24h; ri.uniq_ip = rr.unique_ips_24h; ri.bits = rr.bits;
+            ri.account_age = rr.account_age_days; ri.tx_type = rr.tx_type;
+        } else {
+            assemble_tx(p, row, in_range, my_tile + lane, &ri);
+            if (p.features_out && in_range) {
+                float4* dst = reinterpret_cast<float4*>(p.features_out + row * IGS_NUM_FEATURES);
+#pragma unroll
+                for (int q = 0; q < IGS_NUM_FEATURES / 4; ++q)
+                    dst[q] = make_float4(my_tile[(4 * q + 0) * 32 + lane], my_tile[(4 * q + 1) * 32 + lane],
+                                         my_tile[(4 * q + 2) * 32 + lane], my_tile[(4 * q + 3) * 32 + lane]);
+            }
         }
+        __syncwarp();
+
+        // ---- flags + rule score (applyRules) --------------------------------------------------
         unsigned flags;
-        const int rule = igs_apply_rules(p.cfg, rr.amount, rr.tx_type, rr.tx_count_1m,
-                                         rr.account_age_days, rr.unique_devices_24h,
-                                         rr.unique_ips_24h, rr.bits, rr.time_since_last_tx,
-                                         rr.deposit_count, rr.total_deposits, rr.total_withdrawals,
-                                         &flags);
-        const bool valid = (rr.bits & IGS_BIT_VALID) != 0;
+        const int rule = igs_apply_rules(p.cfg, ri.amount, ri.tx_type, ri.tx_count_1m, ri.account_age,
+                                         ri.uniq_dev, ri.uniq_ip, ri.bits, ri.tslt, ri.deposit_count,
+                                         ri.total_deposits, ri.total_withdrawals, &flags);
+        const bool valid = (ri.bits & IGS_BIT_VALID) != 0;
 
         // ---- model ----------------------------------------------------------------------------
         double ml = 0.0;
@@ -257,36 +398,72 @@ k_score_features(const __grid_constant__ ScoreParams p) {
 
 }  // namespace
 
-int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
-                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
-                              uint8_t* d_leaf_idx, cudaStream_t stream) {
-    if (n == 0) return IGS_OK;
+static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cudaStream_t stream) {
+    void (*kern)(const ScoreParams) = nullptr;
+    if (src == kSrcFeatures) kern = leaves ? k_score<kSrcFeatures, true> : k_score<kSrcFeatures, false>;
+    else kern = leaves ? k_score<kSrcTx, true> : k_score<kSrcTx, false>;
+    // per-device attribute; a few hundred ns, so simply set on every launch
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    const unsigned long long n_tiles = (p.n + kTileTx - 1) / kTileTx;
+    const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : e->sm_count);
+    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
+}
+
+static int check_model(igs_engine* e, const igs_config* cfg) {
     IGS_REQUIRE(e, cfg->model_kind >= IGS_MODEL_NONE && cfg->model_kind <= IGS_MODEL_GBDT,
                 "cfg.model_kind");
     if (cfg->model_kind == IGS_MODEL_GBDT && !e->has_gbdt) {
         igs_set_error(e, "model_kind = IGS_MODEL_GBDT but no ensemble was loaded (igs_load_gbdt)");
         return IGS_ERR_STATE;
     }
+    return IGS_OK;
+}
+
+static void fill_common(igs_engine* e, const igs_config* cfg, ScoreParams* p) {
+    memset(p, 0, sizeof(*p));
+    p->cfg = *cfg;
+    p->model = e->d_model;
+    p->n_trees = e->has_gbdt ? e->n_trees : 0;
+    p->base_score = e->base_score;
+    p->post = e->post_transform;
+}
+
+int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
+                              const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
+                              uint8_t* d_leaf_idx, cudaStream_t stream) {
+    if (n == 0) return IGS_OK;
+    int rc = check_model(e, cfg);
+    if (rc != IGS_OK) return rc;
     IGS_REQUIRE(e, d_rows && d_out, "rows / out pointer is null");
     IGS_REQUIRE(e, cfg->model_kind == IGS_MODEL_NONE || d_features, "features pointer is null");
     ScoreParams p;
-    p.cfg = *cfg;
+    fill_common(e, cfg, &p);
     p.features = d_features;
     p.rows = d_rows;
     p.out = d_out;
     p.leaf_idx = d_leaf_idx;
     p.n = n;
-    p.model = e->d_model;
-    p.n_trees = e->has_gbdt ? e->n_trees : 0;
-    p.base_score = e->base_score;
-    p.post = e->post_transform;
     const bool leaves = d_leaf_idx != nullptr && cfg->model_kind == IGS_MODEL_GBDT;
-    auto kern = leaves ? k_score_features<true> : k_score_features<false>;
-    // per-device attribute; a few hundred ns, so simply set on every launch
-    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    const unsigned long long n_tiles = (n + kTileTx - 1) / kTileTx;
-    const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : e->sm_count);
-    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
-    IGS_CUDA(e, cudaGetLastError());
-    return IGS_OK;
+    return launch(e, kSrcFeatures, p, leaves, stream);
+}
+
+int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
+                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+                           cudaStream_t stream) {
+    if (n == 0) return IGS_OK;
+    int rc = check_model(e, cfg);
+    if (rc != IGS_OK) return rc;
+    ScoreParams p;
+    fill_common(e, cfg, &p);
+    p.tx = d_tx;
+    p.players = e->d_players;
+    p.n_players = e->d_players ? e->n_players : 0;
+    p.ix = igs_index_view_of(e);       // n_accounts = 0 when no history is loaded: empty velocity
+    p.features_out = d_features_out;
+    p.velocity_out = d_velocity_out;
+    p.out = d_out;
+    p.n = n;
+    return launch(e, kSrcTx, p, false, stream);
 }

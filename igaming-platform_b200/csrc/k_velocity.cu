@@ -1,17 +1,573 @@
-// k_velocity.cu — placeholder until the event index lands (next commit).
-#include "igs_internal.cuh"
+// k_velocity.cu — event-history index: radix sort + segmented scans (K3) + the
+// per-query velocity kernel.  sm_100a; all kernels are HBM-streaming integer work.
+//
+// Build (igs_load_events), replaces the Redis state of UpdateRealTimeFeatures
+// (features/redis_store.go:119-168):
+//   1. key = (account << ts_bits) | (ts - ts_min), value = arrival index; LSD radix sort, stable,
+//      <= 10-bit digits sized so that the key's significant bits take the fewest passes
+//      (ZSET ordering by score, :127-130).
+//   2. gather amount / type by the sorted arrival index; CSR `seg` of account boundaries.
+//   3. distinct flag per event: first occurrence of (account, ts, amount) — the ZSET member
+//      "ts:amount" dedupe (:129).
+//   4. one fused scan over the sorted events producing, per position, the exclusive prefix
+//      {distinct count, per-type count, per-type sum} and, per event, the inclusive segmented
+//      {chain sum with head = new account || gap > 3600, session start with head = new account ||
+//      gap > 1800}.  Three phases (tile reduce, scan of tile aggregates, tile apply).
+// Query (igs_get_velocity*, and inlined into the fused score kernel): velocity.cuh.
+#include <vector>
 
-int igs_build_event_index(igs_engine* e, const igs_event_cols*, uint64_t, uint32_t) {
-    igs_set_error(e, "event index: not built into this library yet");
-    return IGS_ERR_STATE;
+#include "igs_internal.cuh"
+#include "velocity.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+constexpr int kThreads = 256;
+
+__global__ void k_minmax(const uint32_t* __restrict__ account, const uint32_t* __restrict__ ts,
+                         uint32_t n, uint32_t* __restrict__ out /* ts_min, ts_max, acct_max */) {
+    uint32_t tmin = 0xFFFFFFFFu, tmax = 0, amax = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t t = __ldg(ts + i), a = __ldg(account + i);
+        tmin = min(tmin, t); tmax = max(tmax, t); amax = max(amax, a);
+    }
+    for (int o = 16; o; o >>= 1) {
+        tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+        tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+        amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(out + 0, tmin);
+        atomicMax(out + 1, tmax);
+        atomicMax(out + 2, amax);
+    }
 }
-void igs_free_event_index(igs_engine*) {}
-int igs_launch_velocity(igs_engine* e, const igs_query*, uint64_t, igs_velocity*, cudaStream_t) {
-    igs_set_error(e, "velocity: not built into this library yet");
-    return IGS_ERR_STATE;
+
+__global__ void k_make_keys(const uint32_t* __restrict__ account, const uint32_t* __restrict__ ts,
+                            uint32_t n, uint32_t ts_min, int ts_bits, uint64_t* __restrict__ keys,
+                            uint32_t* __restrict__ vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = ((uint64_t)__ldg(account + i) << ts_bits) | (uint64_t)(__ldg(ts + i) - ts_min);
+    vals[i] = i;
 }
-int igs_launch_score_batch(igs_engine* e, const igs_config*, const igs_tx*, uint64_t, igs_result*, float*,
-                           igs_velocity*, cudaStream_t) {
-    igs_set_error(e, "fused path: not built into this library yet");
-    return IGS_ERR_STATE;
+
+// ------------------------------------------------------------------------------------------------
+// LSD radix sort pass: histogram -> exclusive scan (bin-major) -> stable scatter
+// ------------------------------------------------------------------------------------------------
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kThreads * kSortItems;   // 2048 keys per block
+constexpr int kSortWarps = kThreads / 32;
+
+__global__ void __launch_bounds__(kThreads)
+k_radix_hist(const uint64_t* __restrict__ keys, uint32_t n, int shift, uint32_t bins,
+             uint32_t* __restrict__ hist_g, uint32_t nblocks) {
+    extern __shared__ uint32_t sh_hist[];
+    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) sh_hist[d] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kSortTile;
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+        const uint32_t i = base + r * kThreads + threadIdx.x;
+        if (i < n) atomicAdd(&sh_hist[(uint32_t)(__ldg(keys + i) >> shift) & (bins - 1)], 1u);
+    }
+    __syncthreads();
+    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) hist_g[(size_t)d * nblocks + blockIdx.x] = sh_hist[d];
+}
+
+// Stable scatter.  Warp w owns the contiguous span [base + w*256, +256) of the tile and walks it in
+// 8 rounds of 32 keys; __match_any_sync ranks equal digits inside a round, a per-warp counter table
+// carries the rank across rounds, and a per-digit scan over the 8 warps orders the warps.
+__global__ void __launch_bounds__(kThreads)
+k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
+                uint32_t bins, const uint32_t* __restrict__ hist_scan_g, uint32_t nblocks) {
+    extern __shared__ uint32_t sh_cnt[];   // [kSortWarps][bins]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (uint32_t d = threadIdx.x; d < bins * kSortWarps; d += kThreads) sh_cnt[d] = 0;
+    __syncthreads();
+    uint32_t* my_cnt = sh_cnt + warp * bins;
+    const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32);
+    uint64_t key[kSortItems];
+    uint32_t rank[kSortItems];
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        const bool valid = i < n;
+        key[r] = valid ? __ldg(keys_in + i) : 0;
+        const uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & (bins - 1)) : (bins + lane);
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        const uint32_t before = valid ? my_cnt[digit] : 0;
+        __syncwarp();
+        if (valid && (peers & lt_mask) == 0) my_cnt[digit] = before + __popc(peers);
+        __syncwarp();
+        rank[r] = before + __popc(peers & lt_mask);
+    }
+    __syncthreads();
+    // per digit: exclusive scan over warps + global base of this (digit, block)
+    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) {
+        uint32_t run = __ldg(hist_scan_g + (size_t)d * nblocks + blockIdx.x);
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w) {
+            const uint32_t c = sh_cnt[w * bins + d];
+            sh_cnt[w * bins + d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        if (i < n) {
+            const uint32_t digit = (uint32_t)(key[r] >> shift) & (bins - 1);
+            const uint32_t pos = my_cnt[digit] + rank[r];
+            keys_out[pos] = key[r];
+            vals_out[pos] = __ldg(vals_in + i);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// u32 exclusive scan (in place), 3 phases, recursive on the tile sums
+// ------------------------------------------------------------------------------------------------
+constexpr int kScanItems = 4;
+constexpr int kScanTile = kThreads * kScanItems;   // 1024
+
+__global__ void __launch_bounds__(kThreads)
+k_scan_u32_tile(uint32_t* __restrict__ data, uint32_t n, uint32_t* __restrict__ tile_sums) {
+    __shared__ uint32_t warp_tot[kThreads / 32];
+    const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    uint32_t v[kScanItems], tot = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        v[k] = base + k < n ? data[base + k] : 0;
+        const uint32_t t = v[k];
+        v[k] = tot;
+        tot += t;
+    }
+    uint32_t inc = tot;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) {
+        if (w < warp) woff += warp_tot[w];
+        total += warp_tot[w];
+    }
+    const uint32_t excl = woff + inc - tot;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+        if (base + k < n) data[base + k] = v[k] + excl;
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_scan_u32_add(uint32_t* __restrict__ data, uint32_t n, const uint32_t* __restrict__ tile_offsets) {
+    const uint32_t off = __ldg(tile_offsets + blockIdx.x);
+    const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k)
+        if (base + k < n) data[base + k] += off;
+}
+
+size_t scan_u32_scratch_elems(uint32_t n) {
+    size_t total = 0;
+    while (n > 1) {
+        n = (n + kScanTile - 1) / kScanTile;
+        total += n;
+        if (n == 1) break;
+    }
+    return total + 1;
+}
+
+// exclusive scan of data[0..n) in place; scratch has scan_u32_scratch_elems(n) elements
+int scan_u32(igs_engine* e, uint32_t* data, uint32_t n, uint32_t* scratch, cudaStream_t st) {
+    if (n == 0) return IGS_OK;
+    const uint32_t nb = (n + kScanTile - 1) / kScanTile;
+    k_scan_u32_tile<<<nb, kThreads, 0, st>>>(data, n, scratch);
+    IGS_CUDA(e, cudaGetLastError());
+    if (nb > 1) {
+        int rc = scan_u32(e, scratch, nb, scratch + nb, st);
+        if (rc != IGS_OK) return rc;
+        k_scan_u32_add<<<nb, kThreads, 0, st>>>(data, n, scratch);
+        IGS_CUDA(e, cudaGetLastError());
+    }
+    return IGS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// post-sort columns
+// ------------------------------------------------------------------------------------------------
+__global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ seq,
+                                const int64_t* __restrict__ amount_in, const uint8_t* __restrict__ type_in,
+                                uint32_t n, uint32_t ts_min, int ts_bits, uint32_t* __restrict__ acct,
+                                uint32_t* __restrict__ ts, int64_t* __restrict__ amount,
+                                uint8_t* __restrict__ type) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t k = __ldg(keys + i);
+    acct[i] = (uint32_t)(k >> ts_bits);
+    ts[i] = ts_min + (uint32_t)(k & ((1ull << ts_bits) - 1ull));
+    const uint32_t s = __ldg(seq + i);
+    amount[i] = __ldg(amount_in + s);
+    type[i] = __ldg(type_in + s);
+}
+
+__global__ void k_segments(const uint32_t* __restrict__ acct, uint32_t n, uint32_t n_accounts,
+                           uint32_t* __restrict__ seg) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t a = __ldg(acct + i);
+    if (i == 0) {
+        for (uint32_t x = 0; x <= a; ++x) seg[x] = 0;
+    } else {
+        const uint32_t p = __ldg(acct + i - 1);
+        for (uint32_t x = p + 1; x <= a; ++x) seg[x] = i;
+    }
+    if (i == n - 1)
+        for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
+}
+
+// distinct flag: no earlier event of the same (account, ts) group has the same amount
+__global__ void k_distinct(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
+                           const int64_t* __restrict__ amount, uint32_t n, uint8_t* __restrict__ dflag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t a = __ldg(acct + i), t = __ldg(ts + i);
+    const int64_t m = __ldg(amount + i);
+    uint8_t d = 1;
+    for (uint32_t j = i; j-- > 0;) {
+        if (__ldg(acct + j) != a || __ldg(ts + j) != t) break;
+        if (__ldg(amount + j) == m) { d = 0; break; }
+    }
+    dflag[i] = d;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused scan of the velocity columns
+// ------------------------------------------------------------------------------------------------
+struct VScan {
+    int64_t  s0, s1, chain;
+    uint32_t d, c0, c1, st;
+    uint32_t cf, sf;   // segment-head flags seen (chain / session)
+};
+
+__device__ __forceinline__ VScan vs_identity() {
+    VScan r; r.s0 = r.s1 = r.chain = 0; r.d = r.c0 = r.c1 = r.st = 0; r.cf = r.sf = 0; return r;
+}
+__device__ __forceinline__ VScan vs_combine(const VScan& a, const VScan& b) {   // a earlier
+    VScan r;
+    r.d = a.d + b.d; r.c0 = a.c0 + b.c0; r.c1 = a.c1 + b.c1;
+    r.s0 = a.s0 + b.s0; r.s1 = a.s1 + b.s1;
+    r.chain = b.cf ? b.chain : a.chain + b.chain; r.cf = a.cf | b.cf;
+    r.st = b.sf ? b.st : a.st; r.sf = a.sf | b.sf;
+    return r;
+}
+struct VCols {
+    const uint32_t* acct; const uint32_t* ts; const int64_t* amount; const uint8_t* type;
+    const uint8_t* dflag; uint32_t n;
+};
+__device__ __forceinline__ VScan vs_element(const VCols& c, uint32_t i) {
+    VScan r = vs_identity();
+    const uint32_t t = __ldg(c.ts + i);
+    const int64_t m = __ldg(c.amount + i);
+    const uint8_t ty = __ldg(c.type + i);
+    bool new_acct = i == 0;
+    long long gap = 0;
+    if (i > 0) {
+        new_acct = __ldg(c.acct + i) != __ldg(c.acct + i - 1);
+        gap = (long long)t - (long long)__ldg(c.ts + i - 1);
+    }
+    r.d = __ldg(c.dflag + i);
+    if (ty == IGS_TX_BET) { r.c0 = 1; r.s0 = m; }
+    if (ty == IGS_TX_DEPOSIT) { r.c1 = 1; r.s1 = m; }
+    r.chain = m;
+    r.cf = (new_acct || gap > 3600) ? 1u : 0u;        // tx_sum:1h key expired (redis_store.go:138)
+    r.sf = (new_acct || gap > 1800) ? 1u : 0u;        // session key expired (:159-160)
+    r.st = r.sf ? t : 0u;
+    return r;
+}
+
+constexpr int kVItems = 8;
+constexpr int kVTile = kThreads * kVItems;   // 2048
+
+// inclusive block scan of one VScan per thread through shared memory (Hillis-Steele)
+__device__ __forceinline__ VScan vs_block_scan(VScan mine, VScan* sh /* [2][kThreads] */, VScan* block_total) {
+    int cur = 0;
+    sh[threadIdx.x] = mine;
+    __syncthreads();
+    for (int off = 1; off < kThreads; off <<= 1) {
+        VScan v = sh[cur * kThreads + threadIdx.x];
+        if ((int)threadIdx.x >= off) v = vs_combine(sh[cur * kThreads + threadIdx.x - off], v);
+        sh[(cur ^ 1) * kThreads + threadIdx.x] = v;
+        cur ^= 1;
+        __syncthreads();
+    }
+    const VScan inc = sh[cur * kThreads + threadIdx.x];
+    *block_total = sh[cur * kThreads + kThreads - 1];
+    __syncthreads();
+    return inc;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_vscan_reduce(VCols c, VScan* __restrict__ agg) {
+    __shared__ VScan sh[2 * kThreads];
+    const uint32_t base = blockIdx.x * kVTile + threadIdx.x * kVItems;
+    VScan t = vs_identity();
+#pragma unroll
+    for (int k = 0; k < kVItems; ++k)
+        if (base + k < c.n) t = vs_combine(t, vs_element(c, base + k));
+    VScan total;
+    vs_block_scan(t, sh, &total);
+    if (threadIdx.x == 0) agg[blockIdx.x] = total;
+}
+
+// exclusive scan of the tile aggregates in place, single block
+__global__ void __launch_bounds__(kThreads)
+k_vscan_prefix(VScan* __restrict__ agg, uint32_t nb) {
+    __shared__ VScan sh[2 * kThreads];
+    VScan carry = vs_identity();
+    for (uint32_t base = 0; base < nb; base += kThreads) {
+        const uint32_t i = base + threadIdx.x;
+        const VScan mine = i < nb ? agg[i] : vs_identity();
+        VScan total;
+        const VScan inc = vs_block_scan(mine, sh, &total);
+        // exclusive = carry (+) inclusive-of-previous-thread
+        __shared__ VScan prev[kThreads];
+        prev[threadIdx.x] = inc;
+        __syncthreads();
+        VScan ex = carry;
+        if (threadIdx.x > 0) ex = vs_combine(carry, prev[threadIdx.x - 1]);
+        if (i < nb) agg[i] = ex;
+        carry = vs_combine(carry, total);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_vscan_apply(VCols c, const VScan* __restrict__ agg, igs_prefix_rec* __restrict__ pre,
+              igs_tail_rec* __restrict__ tail) {
+    __shared__ VScan sh[2 * kThreads];
+    __shared__ VScan prev[kThreads];
+    const uint32_t base = blockIdx.x * kVTile + threadIdx.x * kVItems;
+    VScan el[kVItems];
+    VScan t = vs_identity();
+#pragma unroll
+    for (int k = 0; k < kVItems; ++k) {
+        el[k] = base + k < c.n ? vs_element(c, base + k) : vs_identity();
+        t = vs_combine(t, el[k]);
+    }
+    VScan total;
+    const VScan inc = vs_block_scan(t, sh, &total);
+    prev[threadIdx.x] = inc;
+    __syncthreads();
+    VScan run = agg[blockIdx.x];
+    if (threadIdx.x > 0) run = vs_combine(run, prev[threadIdx.x - 1]);
+#pragma unroll
+    for (int k = 0; k < kVItems; ++k) {
+        const uint32_t i = base + k;
+        if (i <= c.n) {
+            igs_prefix_rec p;
+            p.dcnt = run.d; p.cnt[0] = run.c0; p.cnt[1] = run.c1; p.pad = 0;
+            p.sum[0] = run.s0; p.sum[1] = run.s1;
+            pre[i] = p;
+        }
+        if (i < c.n) {
+            run = vs_combine(run, el[k]);
+            igs_tail_rec tl;
+            tl.chain_sum = run.chain; tl.sess_start = run.st; tl.pad = 0;
+            tail[i] = tl;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// query kernel
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_velocity(igs_index_view ix, const igs_query* __restrict__ q, unsigned long long n,
+           igs_velocity* __restrict__ out) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 qq = __ldg(reinterpret_cast<const uint4*>(q + i));
+    igs_velocity_a16 v;
+    igs_velocity_lookup(ix, qq.x, qq.y, qq.z, &v.v);
+    uint4* dst = reinterpret_cast<uint4*>(out + i);
+#pragma unroll
+    for (int k = 0; k < (int)(sizeof(igs_velocity) / 16); ++k) dst[k] = v.q[k];
+}
+
+int bits_for(uint64_t v) {   // number of bits needed to represent v
+    int b = 0;
+    while (v) { ++b; v >>= 1; }
+    return b;
+}
+
+struct Scratch {
+    std::vector<void*> ptrs;
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    template <typename T> cudaError_t alloc(T** p, size_t count) {
+        cudaError_t st = cudaMalloc((void**)p, (count ? count : 1) * sizeof(T));
+        if (st == cudaSuccess) ptrs.push_back(*p);
+        return st;
+    }
+};
+
+}  // namespace
+
+igs_index_view igs_index_view_of(const igs_engine* e) {
+    igs_index_view v;
+    v.seg = e->ev.seg; v.ts = e->ev.ts; v.seq = e->ev.seq; v.pre = e->ev.pre; v.tail = e->ev.tail;
+    v.n_accounts = e->has_events ? e->ev.n_accounts : 0;
+    v.n = (uint32_t)e->ev.n;
+    return v;
+}
+
+void igs_free_event_index(igs_engine* e) {
+    igs_event_index& x = e->ev;
+    if (x.seg) cudaFree(x.seg);
+    if (x.ts) cudaFree(x.ts);
+    if (x.seq) cudaFree(x.seq);
+    if (x.pre) cudaFree(x.pre);
+    if (x.tail) cudaFree(x.tail);
+    x = igs_event_index();
+    e->has_events = false;
+}
+
+int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64, uint32_t n_accounts) {
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    igs_free_event_index(e);
+    const uint32_t n = (uint32_t)n64;
+    cudaStream_t st = e->slot[0].stream;
+    igs_event_index& x = e->ev;
+    Scratch sc;
+
+    IGS_CUDA(e, cudaMalloc(&x.seg, ((size_t)n_accounts + 1) * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.ts, (n ? n : 1) * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.seq, (n ? n : 1) * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.pre, ((size_t)n + 1) * sizeof(igs_prefix_rec)));
+    IGS_CUDA(e, cudaMalloc(&x.tail, (n ? n : 1) * sizeof(igs_tail_rec)));
+    x.n = n;
+    x.n_accounts = n_accounts;
+    IGS_CUDA(e, cudaMemsetAsync(x.seg, 0, ((size_t)n_accounts + 1) * sizeof(uint32_t), st));
+    IGS_CUDA(e, cudaMemsetAsync(x.pre, 0, sizeof(igs_prefix_rec), st));
+    if (n == 0) {
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+        e->has_events = true;
+        return IGS_OK;
+    }
+
+    // ---- upload the columns ---------------------------------------------------------------------
+    uint32_t *d_acct_in, *d_ts_in; int64_t* d_amt_in; uint8_t* d_type_in; uint32_t* d_mm;
+    IGS_CUDA(e, sc.alloc(&d_acct_in, n));
+    IGS_CUDA(e, sc.alloc(&d_ts_in, n));
+    IGS_CUDA(e, sc.alloc(&d_amt_in, n));
+    IGS_CUDA(e, sc.alloc(&d_type_in, n));
+    IGS_CUDA(e, sc.alloc(&d_mm, 4));
+    IGS_CUDA(e, cudaMemcpyAsync(d_acct_in, ev->account, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    IGS_CUDA(e, cudaMemcpyAsync(d_ts_in, ev->ts, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    IGS_CUDA(e, cudaMemcpyAsync(d_amt_in, ev->amount, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    IGS_CUDA(e, cudaMemcpyAsync(d_type_in, ev->tx_type, (size_t)n, cudaMemcpyHostToDevice, st));
+
+    // ---- key range ------------------------------------------------------------------------------
+    const uint32_t mm_init[4] = {0xFFFFFFFFu, 0u, 0u, 0u};
+    IGS_CUDA(e, cudaMemcpyAsync(d_mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, st));
+    const uint32_t nb_el = (n + kThreads - 1) / kThreads;
+    k_minmax<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct_in, d_ts_in, n, d_mm);
+    IGS_CUDA(e, cudaGetLastError());
+    uint32_t mm[4];
+    IGS_CUDA(e, cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, st));
+    IGS_CUDA(e, cudaStreamSynchronize(st));
+    if (mm[2] >= n_accounts) {
+        igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
+        igs_free_event_index(e);
+        return IGS_ERR_INVALID;
+    }
+    const uint32_t ts_min = mm[0];
+    const int ts_bits = bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1;
+    const int key_bits = ts_bits + (bits_for(mm[2]) > 0 ? bits_for(mm[2]) : 1);
+    const int passes = (key_bits + 9) / 10;
+    const int digit_bits = (key_bits + passes - 1) / passes;      // <= 10
+    const uint32_t bins = 1u << digit_bits;
+
+    // ---- radix sort -----------------------------------------------------------------------------
+    uint64_t* d_keys[2]; uint32_t* d_vals[2];
+    IGS_CUDA(e, sc.alloc(&d_keys[0], n));
+    IGS_CUDA(e, sc.alloc(&d_keys[1], n));
+    IGS_CUDA(e, sc.alloc(&d_vals[0], n));
+    IGS_CUDA(e, sc.alloc(&d_vals[1], n));
+    const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
+    const uint32_t hist_elems = bins * nb_sort;
+    uint32_t *d_hist, *d_scan_scratch;
+    IGS_CUDA(e, sc.alloc(&d_hist, hist_elems));
+    IGS_CUDA(e, sc.alloc(&d_scan_scratch, scan_u32_scratch_elems(hist_elems)));
+    k_make_keys<<<nb_el, kThreads, 0, st>>>(d_acct_in, d_ts_in, n, ts_min, ts_bits, d_keys[0], d_vals[0]);
+    IGS_CUDA(e, cudaGetLastError());
+    int cur = 0;
+    for (int p = 0; p < passes; ++p) {
+        const int shift = p * digit_bits;
+        k_radix_hist<<<nb_sort, kThreads, bins * sizeof(uint32_t), st>>>(d_keys[cur], n, shift, bins, d_hist, nb_sort);
+        IGS_CUDA(e, cudaGetLastError());
+        int rc = scan_u32(e, d_hist, hist_elems, d_scan_scratch, st);
+        if (rc != IGS_OK) return rc;
+        k_radix_scatter<<<nb_sort, kThreads, (size_t)bins * kSortWarps * sizeof(uint32_t), st>>>(
+            d_keys[cur], d_vals[cur], d_keys[cur ^ 1], d_vals[cur ^ 1], n, shift, bins, d_hist, nb_sort);
+        IGS_CUDA(e, cudaGetLastError());
+        cur ^= 1;
+    }
+
+    // ---- sorted columns, segments, distinct flags -----------------------------------------------
+    uint32_t* d_acct; int64_t* d_amt; uint8_t *d_type, *d_dflag;
+    IGS_CUDA(e, sc.alloc(&d_acct, n));
+    IGS_CUDA(e, sc.alloc(&d_amt, n));
+    IGS_CUDA(e, sc.alloc(&d_type, n));
+    IGS_CUDA(e, sc.alloc(&d_dflag, n));
+    IGS_CUDA(e, cudaMemcpyAsync(x.seq, d_vals[cur], (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_amt_in, d_type_in, n, ts_min, ts_bits,
+                                                d_acct, x.ts, d_amt, d_type);
+    IGS_CUDA(e, cudaGetLastError());
+    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, n, n_accounts, x.seg);
+    IGS_CUDA(e, cudaGetLastError());
+    k_distinct<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, d_amt, n, d_dflag);
+    IGS_CUDA(e, cudaGetLastError());
+
+    // ---- fused scan -----------------------------------------------------------------------------
+    const uint32_t nb_v = (n + kVTile - 1) / kVTile;
+    // the apply phase also writes pre[n]; when n is a multiple of the tile that position belongs to
+    // one more (otherwise empty) tile
+    const uint32_t nb_apply = n / kVTile + 1;
+    VScan* d_agg;
+    IGS_CUDA(e, sc.alloc(&d_agg, (size_t)nb_apply + 1));
+    IGS_CUDA(e, cudaMemsetAsync(d_agg, 0, ((size_t)nb_apply + 1) * sizeof(VScan), st));
+    VCols cols{d_acct, x.ts, d_amt, d_type, d_dflag, n};
+    k_vscan_reduce<<<nb_v, kThreads, 0, st>>>(cols, d_agg);
+    IGS_CUDA(e, cudaGetLastError());
+    k_vscan_prefix<<<1, kThreads, 0, st>>>(d_agg, nb_apply);
+    IGS_CUDA(e, cudaGetLastError());
+    k_vscan_apply<<<nb_apply, kThreads, 0, st>>>(cols, d_agg, x.pre, x.tail);
+    IGS_CUDA(e, cudaGetLastError());
+    IGS_CUDA(e, cudaStreamSynchronize(st));
+    e->has_events = true;
+    return IGS_OK;
+}
+
+int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
+                        cudaStream_t stream) {
+    if (!e->has_events) {
+        igs_set_error(e, "no event history loaded (igs_load_events)");
+        return IGS_ERR_STATE;
+    }
+    if (n == 0) return IGS_OK;
+    const unsigned long long nb = (n + kThreads - 1) / kThreads;
+    k_velocity<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
 }

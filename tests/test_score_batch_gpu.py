@@ -1,0 +1,114 @@
+"""GPU: the fused path (compact tx -> velocity lookup -> feature assembly -> rules -> model ->
+blend in one kernel) through igs_score_batch vs the oracle's per-request pipeline.
+Flags / velocity / assembled features / ml / score / action all bit-exact."""
+import numpy as np
+import pytest
+
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def check(engine, orc, pkg, cfg, model, players, ev, tx):
+    got, gf, gv = engine.score_batch(cfg, tx, want_features=True, want_velocity=True)
+    want, wf, wv = orc.score_batch(cfg, model, players, ev, tx, want_features=True, want_velocity=True)
+    assert gv.tobytes() == wv.tobytes(), "velocity blocks differ"
+    assert np.array_equal(gf.view(np.uint32), wf.view(np.uint32)), \
+        f"assembled features differ in columns {np.unique(np.nonzero(gf.view(np.uint32) != wf.view(np.uint32))[1])}"
+    assert np.array_equal(got["flags"], want["flags"]), "flags differ"
+    assert np.max(np.abs(got["ml_score"].astype(np.float64) - want["ml_score"]), initial=0) <= 1e-5
+    assert got.tobytes() == want.tobytes(), "results differ"
+    return want
+
+
+@pytest.mark.parametrize("kind", ["none", "mock", "gbdt"])
+def test_fused_path_matches_oracle(engine, orc, pkg, kind):
+    abi = pkg.abi
+    n_players, n_events, n = 3000, 40000, 20000
+    now = synth.T0 + 6 * 3600
+    players = synth.make_players(n_players, seed=5, now=now)
+    ev = synth.make_events(n_events, n_players, seed=6, span=6 * 3600, collision_rate=0.03)
+    tx = synth.make_tx(n, n_players, seed=7, t_lo=synth.T0 + 3600, t_hi=now, invalid_rate=0.03)
+    # a few rows from accounts beyond the player table / the index (feature store "fails" -> zeros)
+    tx["account"][::997] = n_players + 3
+    engine.load_players(players)
+    engine.load_events(ev, n_players)
+    model = None
+    mk = {"none": abi.MODEL_NONE, "mock": abi.MODEL_MOCK, "gbdt": abi.MODEL_GBDT}[kind]
+    if kind == "gbdt":
+        model = synth.make_gbdt(n_trees=120, seed=8)
+        # make the extension block and raw-magnitude features matter to the trees
+        engine.load_gbdt(model)
+    cfg = pkg.default_config(model_kind=mk)
+    want = check(engine, orc, pkg, cfg, model, players, ev, tx)
+    seen = np.bitwise_or.reduce(want["flags"])
+    for bit in (abi.R_HIGH_VELOCITY, abi.R_NEW_ACCOUNT_LARGE_TX, abi.R_MULTIPLE_DEVICES,
+                abi.R_IP_COUNTRY_MISMATCH, abi.R_VPN_DETECTED, abi.R_KNOWN_FRAUDSTER, abi.R_BONUS_ABUSE):
+        assert seen & bit, f"rule bit {bit} never fired"
+
+
+def test_fused_path_stream_mode(engine, orc, pkg):
+    """Score-then-apply stream (the reference's real-time order): tx i sees the events that
+    arrived before it (seq_limit = i) — the events ARE the transactions."""
+    abi = pkg.abi
+    n_players, n = 200, 6000
+    players = synth.make_players(n_players, seed=15, now=synth.T0 + 3 * 3600)
+    ev = synth.make_events(n, n_players, seed=16, span=3 * 3600, collision_rate=0.05, zipf_s=0.8)
+    order = np.argsort(ev.ts, kind="stable")
+    ev = pkg.Events(ev.account[order], ev.ts[order], ev.amount[order], ev.tx_type[order])
+    tx = np.zeros(n, dtype=abi.tx_dtype)
+    tx["account"], tx["ts"], tx["amount"], tx["tx_type"] = ev.account, ev.ts, ev.amount, ev.tx_type
+    tx["seq_limit"] = np.arange(n)
+    tx["unique_devices_24h"] = 1
+    tx["unique_ips_24h"] = 1
+    tx["bits"] = abi.BIT_VALID
+    engine.load_players(players)
+    engine.load_events(ev, n_players)
+    cfg = pkg.default_config(model_kind=abi.MODEL_MOCK)
+    want = check(engine, orc, pkg, cfg, None, players, ev, tx)
+    assert (want["flags"] & abi.R_HIGH_VELOCITY).any(), "bursts should trip HIGH_VELOCITY"
+
+
+def test_fused_path_without_state(pkg, orc):
+    """No players, no events loaded: the reference degrades to zero features (engine.go:267-270)."""
+    abi = pkg.abi
+    with pkg.Engine(device=0) as fresh:
+        tx = synth.make_tx(3000, 50, seed=3)
+        cfg = pkg.default_config(model_kind=abi.MODEL_MOCK)
+        got = fresh.score_batch(cfg, tx)
+        empty = pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64), np.zeros(0, np.uint8))
+        want = orc.score_batch(cfg, None, np.zeros(0, abi.player_row_dtype), empty, tx)
+        assert got.tobytes() == want.tobytes()
+
+
+def test_fused_equals_two_step_path(engine, pkg):
+    """Path B == velocity query + host-visible features fed back through path A."""
+    abi = pkg.abi
+    n_players = 1000
+    players = synth.make_players(n_players, seed=25)
+    ev = synth.make_events(30000, n_players, seed=26, span=12 * 3600)
+    tx = synth.make_tx(8000, n_players, seed=27, t_lo=synth.T0 + 6 * 3600, t_hi=synth.T0 + 12 * 3600)
+    model = synth.make_gbdt(n_trees=75, seed=28)
+    engine.load_players(players)
+    engine.load_events(ev, n_players)
+    engine.load_gbdt(model)
+    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    got, feats, vel = engine.score_batch(cfg, tx, want_features=True, want_velocity=True)
+    v2 = engine.get_velocity(synth.queries_of(tx))
+    assert vel.tobytes() == v2.tobytes()
+    rows = np.zeros(tx.shape[0], dtype=abi.rule_row_dtype)
+    p = players[tx["account"]]
+    rows["amount"] = tx["amount"]
+    rows["total_deposits"] = p["total_deposits"]
+    rows["total_withdrawals"] = p["total_withdrawals"]
+    rows["tx_count_1m"] = vel["tx_count_1m"]
+    rows["account_age_days"] = (tx["ts"].astype(np.int64) - p["account_created_at"]) // 86400
+    rows["time_since_last_tx"] = vel["time_since_last_tx"]
+    rows["deposit_count"] = p["deposit_count"]
+    rows["unique_devices_24h"] = tx["unique_devices_24h"]
+    rows["unique_ips_24h"] = tx["unique_ips_24h"]
+    rows["tx_type"] = tx["tx_type"]
+    bonus_only = (p["bonus_claim_count"] > 3) & (p["total_deposits"] < 5000)
+    rows["bits"] = tx["bits"] | (bonus_only * abi.BIT_BONUS_ONLY).astype(np.uint8)
+    again = engine.score_features(cfg, feats, rows)
+    assert got.tobytes() == again.tobytes()
