@@ -201,6 +201,12 @@ class Engine:
             return out, feats, vel
         return out
 
+    # -- shard partition ----------------------------------------------------------------------
+    def partition_tx_device(self, d_tx: int, n: int, n_shards: int, d_tx_out: int, d_perm: int,
+                            d_offsets: int, stream: int = 0) -> None:
+        self._check(self._lib.igs_partition_tx_device(self._h, d_tx, n, n_shards, d_tx_out, d_perm,
+                                                      d_offsets, stream))
+
     # -- LTV ----------------------------------------------------------------------------------
     def ltv_batch(self, x_bf16: np.ndarray, rows: np.ndarray, want_raw: bool = False):
         x_bf16 = np.ascontiguousarray(x_bf16, dtype=np.uint16)

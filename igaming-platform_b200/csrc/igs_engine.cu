@@ -133,6 +133,7 @@ void igs_engine_destroy(igs_engine* e) {
         if (sl.ev_in) cudaEventDestroy(sl.ev_in);
         if (sl.stream) cudaStreamDestroy(sl.stream);
     }
+    free_buf(&e->part_scratch);
     if (e->d_model) cudaFree(e->d_model);
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
@@ -378,6 +379,24 @@ int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d
     IGS_REQUIRE(e, n == 0 || (d_tx && d_out), "tx / out is null");
     return igs_launch_score_batch(e, cfg, d_tx, n, d_out, d_features_out, d_velocity_out,
                                   (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// shard partition
+// ------------------------------------------------------------------------------------------------
+int igs_partition_tx_device(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards,
+                            igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n_shards >= 1 && n_shards <= 256, "n_shards must be 1..256");
+    IGS_REQUIRE(e, n < (1ull << 32), "at most 2^32-1 records per call");
+    IGS_REQUIRE(e, d_offsets != nullptr, "offsets is null");
+    IGS_REQUIRE(e, n == 0 || (d_tx && d_tx_out), "tx / tx_out is null");
+    {
+        std::lock_guard<std::mutex> lk(e->mu);
+        IGS_TRY(igs_reserve(e, &e->part_scratch, igs_partition_scratch_words(n, n_shards) * sizeof(uint32_t)));
+    }
+    return igs_partition_run(e, d_tx, n, n_shards, (uint32_t*)e->part_scratch.p, d_tx_out, d_perm, d_offsets,
+                             (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -56,6 +56,7 @@ struct igs_engine {
     char err[512] = {0};
     std::mutex mu;                // guards loads vs. scoring calls
     igs_slot slot[IGS_NUM_SLOTS];
+    igs_buf  part_scratch;        // shard-partition counters (k_partition.cu)
 
     // tree ensemble
     uint8_t* d_model = nullptr;   // n_trees * IGS_DEV_TREE_BYTES
@@ -116,3 +117,6 @@ int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);
 int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,
                    igs_ltv_result* d_out, float* d_ltv_raw, cudaStream_t stream);
+int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards, uint32_t* counts,
+                      igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, cudaStream_t stream);
+size_t igs_partition_scratch_words(uint64_t n, uint32_t n_shards);

@@ -1,0 +1,158 @@
+// k_partition.cu — shard partition of a transaction batch, sm_100a.
+//
+// shard = splitmix64(account) % n_shards — the key the reference's feature store is addressed by is
+// the account (features/redis_store.go:61); every feature, rule and score depends on one account
+// only, so shards are independent and no collective follows.  Three kernels, all streaming:
+//   1. per-block shard histogram             -> counts[shard][block]       (scratch)
+//   2. exclusive scan of counts, shard-major -> bases + offsets[n_shards+1]
+//   3. stable scatter of the 32-byte records (+ their original index) to their shard's range.
+// Stability keeps the arrival order inside a shard, which the velocity semantics depend on.
+#include "igs_internal.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kItems = 8;
+constexpr int kTile = kThreads * kItems;   // 2048 records per block
+constexpr int kWarps = kThreads / 32;
+constexpr unsigned kMaxShards = 256;
+
+__device__ __forceinline__ uint32_t shard_of(uint32_t account, uint32_t n_shards) {
+    uint64_t x = (uint64_t)account + 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    return (uint32_t)(x % n_shards);
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_part_hist(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards, uint32_t* __restrict__ counts,
+            uint32_t nblocks) {
+    __shared__ uint32_t hist[kMaxShards];
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) hist[s] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kTile;
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+        const uint32_t i = base + r * kThreads + threadIdx.x;
+        if (i < n) atomicAdd(&hist[shard_of(__ldg(&tx[i].account), n_shards)], 1u);
+    }
+    __syncthreads();
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) counts[(size_t)s * nblocks + blockIdx.x] = hist[s];
+}
+
+// single block: exclusive scan of counts[0..m) in place (m = n_shards * nblocks), shard offsets out
+__global__ void __launch_bounds__(kThreads)
+k_part_scan(uint32_t* __restrict__ counts, uint32_t m, uint32_t n_shards, uint32_t nblocks, uint32_t n,
+            uint32_t* __restrict__ offsets) {
+    __shared__ uint32_t warp_tot[kWarps];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < m; base += kThreads * 4) {
+        const uint32_t i0 = base + threadIdx.x * 4;
+        uint32_t v[4], tot = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t t = i0 + k < m ? counts[i0 + k] : 0;
+            v[k] = tot;
+            tot += t;
+        }
+        uint32_t inc = tot;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += y;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        uint32_t woff = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            if (w < warp) woff += warp_tot[w];
+            total += warp_tot[w];
+        }
+        const uint32_t excl = carry_s + woff + inc - tot;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (i0 + k < m) counts[i0 + k] = v[k] + excl;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s += total;
+        __syncthreads();
+    }
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) offsets[s] = counts[(size_t)s * nblocks];
+    if (threadIdx.x == 0) offsets[n_shards] = n;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
+               const uint32_t* __restrict__ bases, uint32_t nblocks, igs_tx* __restrict__ tx_out,
+               uint32_t* __restrict__ perm) {
+    __shared__ uint32_t cnt[kWarps * kMaxShards];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (uint32_t d = threadIdx.x; d < n_shards * kWarps; d += kThreads) cnt[d] = 0;
+    __syncthreads();
+    uint32_t* my_cnt = cnt + warp * n_shards;
+    const uint32_t wbase = blockIdx.x * kTile + warp * (kItems * 32);
+    uint32_t shard[kItems], rank[kItems];
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        const bool valid = i < n;
+        shard[r] = valid ? shard_of(__ldg(&tx[i].account), n_shards) : (kMaxShards + lane);
+        const uint32_t peers = __match_any_sync(0xffffffffu, shard[r]);
+        const uint32_t before = valid ? my_cnt[shard[r]] : 0;
+        __syncwarp();
+        if (valid && (peers & lt_mask) == 0) my_cnt[shard[r]] = before + __popc(peers);
+        __syncwarp();
+        rank[r] = before + __popc(peers & lt_mask);
+    }
+    __syncthreads();
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) {
+        uint32_t run = __ldg(bases + (size_t)s * nblocks + blockIdx.x);
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            const uint32_t c = cnt[w * n_shards + s];
+            cnt[w * n_shards + s] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+        const uint32_t i = wbase + r * 32 + lane;
+        if (i < n) {
+            const uint32_t pos = my_cnt[shard[r]] + rank[r];
+            const uint4* src = reinterpret_cast<const uint4*>(tx + i);
+            uint4* dst = reinterpret_cast<uint4*>(tx_out + pos);
+            dst[0] = __ldg(src + 0);
+            dst[1] = __ldg(src + 1);
+            if (perm) perm[pos] = i;
+        }
+    }
+}
+
+}  // namespace
+
+// Runs the three kernels with `counts` (>= n_shards * ceil(n / 2048) words) as their scratch.
+int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t n_shards, uint32_t* counts,
+                      igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, cudaStream_t stream) {
+    const uint32_t n = (uint32_t)n64;
+    const uint32_t nblocks = (n + kTile - 1) / kTile;
+    if (n == 0) {
+        IGS_CUDA(e, cudaMemsetAsync(d_offsets, 0, ((size_t)n_shards + 1) * sizeof(uint32_t), stream));
+        return IGS_OK;
+    }
+    k_part_hist<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks);
+    IGS_CUDA(e, cudaGetLastError());
+    k_part_scan<<<1, kThreads, 0, stream>>>(counts, n_shards * nblocks, n_shards, nblocks, n, d_offsets);
+    IGS_CUDA(e, cudaGetLastError());
+    k_part_scatter<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
+}
+
+size_t igs_partition_scratch_words(uint64_t n, uint32_t n_shards) {
+    return (size_t)n_shards * ((n + kTile - 1) / kTile);
+}

@@ -353,6 +353,16 @@ int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d
                            igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            void* stream);
 
+/* Shard partition (device buffers): groups n tx records by shard = splitmix64(account) % n_shards
+ * (n_shards <= 256), keeping arrival order inside a shard.  The reference has no batch partition;
+ * the key is the one its feature store is addressed by (AccountID, features/redis_store.go:61,
+ * scoring/engine.go:41) and the per-shard queues it would feed are QueueRiskScoring
+ * (pkg/events/publisher.go:40).  d_tx_out[n] receives the grouped records, d_perm[n] (optional) the
+ * original index of each output record, d_offsets[n_shards + 1] the first output position of each
+ * shard.  Scratch comes from the engine (allocated on first use / growth).  Enqueues on `stream`.  */
+int igs_partition_tx_device(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards,
+                            igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, void* stream);
+
 /* LTV — replaces LTVPredictor.BatchPredict (prediction/ltv.go:385-398): x = n x 256 bf16 model
  * input (raw bit patterns), rows = epilogue sideband.  The MLP output replaces calculateLTV
  * (:155-178); churn / adjust / segment / survival / action / confidence follow :124-139.
@@ -375,7 +385,8 @@ int igs_reason_codes(uint32_t flags, const char* out[IGS_NUM_REASONS]);
 const char* igs_action_name(int action);       /* "approve" | "review" | "block"                */
 const char* igs_ltv_action_name(int idx);      /* prediction/ltv.go:300-343 strings             */
 const char* igs_segment_name(int seg);         /* prediction/ltv.go:17-23                       */
-/* shard = splitmix64(lo ^ hi) % n_shards for a 16-byte account uuid (ScoreRequest.AccountID).   */
+/* shard = splitmix64(lo ^ hi) % n_shards for a 16-byte account uuid (ScoreRequest.AccountID);
+ * igs_shard_of(account, 0, n) is the shard igs_partition_tx_device assigns to a dense index.     */
 uint32_t igs_shard_of(uint64_t uuid_lo, uint64_t uuid_hi, uint32_t n_shards);
 /* Library / build identification, e.g. "igs 0.1 sm_100a".                                       */
 const char* igs_version(void);
