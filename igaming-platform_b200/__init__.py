@@ -218,3 +218,6 @@ class Engine:
         self._check(self._lib.igs_ltv_batch(self._h, abi.ptr(x_bf16), abi.ptr(rows), n,
                                             abi.ptr(out), abi.ptr(raw)))
         return (out, raw) if want_raw else out
+
+
+from . import scoring  # noqa: E402  (reference-facing mirror: ScoringEngine / ScoreRequest / ScoreResponse)
