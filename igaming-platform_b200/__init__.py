@@ -207,6 +207,15 @@ class Engine:
         self._check(self._lib.igs_partition_tx_device(self._h, d_tx, n, n_shards, d_tx_out, d_perm,
                                                       d_offsets, stream))
 
+    def partition_tx_static(self, d_tx: int, n: int, n_shards: int, d_tx_out: int, d_perm: int,
+                            d_offsets: int, stream: int = 0) -> None:
+        """igs_partition_tx_static: the partition for callers that must not allocate (an ingest
+        thread sharing the GPU with in-flight scoring, or a fixed GPU memory budget).  Counters come
+        from a 1 MiB array inside the library, so n_shards * ceil(n / 2048) must stay within
+        abi.PARTITION_STATIC_WORDS; calls that overlap on one GPU race on that array."""
+        self._check(self._lib.igs_partition_tx_static(self._h, d_tx, n, n_shards, d_tx_out, d_perm,
+                                                      d_offsets, stream))
+
     # -- LTV ----------------------------------------------------------------------------------
     def ltv_batch(self, x_bf16: np.ndarray, rows: np.ndarray, want_raw: bool = False):
         x_bf16 = np.ascontiguousarray(x_bf16, dtype=np.uint16)

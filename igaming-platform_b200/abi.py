@@ -42,6 +42,7 @@ MODEL_NONE, MODEL_MOCK, MODEL_GBDT = 0, 1, 2
 POST_NONE, POST_LOGISTIC = 0, 1
 SEG_VIP, SEG_HIGH, SEG_MEDIUM, SEG_LOW, SEG_CHURNING = 1, 2, 3, 4, 5
 SEQ_ALL = 0xFFFFFFFF
+PARTITION_STATIC_WORDS = 256 * 1024
 
 rule_row_dtype = np.dtype([
     ("amount", "<i8"), ("total_deposits", "<i8"), ("total_withdrawals", "<i8"),
@@ -132,7 +133,8 @@ EXPORTS = [
     "igs_alloc_pinned", "igs_free_pinned", "igs_load_gbdt", "igs_load_mlp", "igs_load_players",
     "igs_load_events", "igs_score_features", "igs_score_features_async", "igs_wait",
     "igs_score_features_device", "igs_get_velocity", "igs_get_velocity_device", "igs_score_batch",
-    "igs_score_batch_async", "igs_score_batch_device", "igs_partition_tx_device", "igs_ltv_batch", "igs_ltv_batch_device",
+    "igs_score_batch_async", "igs_score_batch_device", "igs_partition_tx_device", "igs_partition_tx_static",
+    "igs_ltv_batch", "igs_ltv_batch_device",
     "igs_rule_score_from_flags", "igs_reason_codes", "igs_action_name", "igs_ltv_action_name",
     "igs_segment_name", "igs_shard_of", "igs_version",
 ]
@@ -184,6 +186,7 @@ def load_library() -> C.CDLL:
     lib.igs_score_batch_async.argtypes = [vp, i32, C.POINTER(Config), vp, u64, vp]
     lib.igs_score_batch_device.argtypes = [vp, C.POINTER(Config), vp, u64, vp, vp, vp, vp]
     lib.igs_partition_tx_device.argtypes = [vp, vp, u64, C.c_uint32, vp, vp, vp, vp]
+    lib.igs_partition_tx_static.argtypes = [vp, vp, u64, C.c_uint32, vp, vp, vp, vp]
     lib.igs_ltv_batch.argtypes = [vp, vp, vp, u64, vp, vp]
     lib.igs_ltv_batch_device.argtypes = [vp, vp, vp, u64, vp, vp, vp]
     lib.igs_rule_score_from_flags.argtypes = [C.POINTER(Config), C.c_uint32]

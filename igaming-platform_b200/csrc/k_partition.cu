@@ -156,3 +156,66 @@ int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t 
 size_t igs_partition_scratch_words(uint64_t n, uint32_t n_shards) {
     return (size_t)n_shards * ((n + kTile - 1) / kTile);
 }
+
+// ------------------------------------------------------------------------------------------------
+// igs_partition_tx_static — the same three kernels, with their counters in memory that is part of
+// the library image instead of memory obtained from the allocator.
+// ------------------------------------------------------------------------------------------------
+// Who needs this.  A risk-service shard partitions incoming batches on its ingest thread while
+// scoring batches of other slots are in flight on the same GPU.  igs_partition_tx_device takes its
+// counters from the engine, which calls cudaMalloc the first time and again whenever a batch needs
+// more counters than any batch before it (cudaFree + cudaMalloc).  Both calls serialise against
+// everything running on the device, so that one ingest call would stall every in-flight scoring
+// call and surface as a latency spike.  The other such caller is a deployment that fixes its GPU
+// memory budget at start-up (a shard sharing the GPU with another tenant) and treats any later
+// allocation as a fault.  Neither can afford an allocating call on this path.
+//
+// The counters therefore live in the array below: 1 MiB that every GPU which loads this library
+// holds from module load until the process exits, whether or not this entry point is ever used.
+#define IGS_PARTITION_STATIC_WORDS_ (256u * 1024u)
+static_assert(IGS_PARTITION_STATIC_WORDS_ == IGS_PARTITION_STATIC_WORDS, "keep igs.h in step");
+static __device__ __align__(256) uint32_t g_part_counters[IGS_PARTITION_STATIC_WORDS_];
+
+// In host code `g_part_counters` is only a handle for the runtime, not a device address; the
+// address has to be asked for, once per device and with that device current.
+namespace {
+constexpr int kMaxDevices = 64;
+uint32_t*  g_part_counters_dev[kMaxDevices] = {nullptr};
+std::mutex g_part_mu;
+}  // namespace
+
+extern "C" int igs_partition_tx_static(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards,
+                                       igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, void* stream) {
+    if (!e) {
+        igs_set_error(nullptr, "engine handle is null");
+        return IGS_ERR_INVALID;
+    }
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    IGS_REQUIRE(e, e->device >= 0 && e->device < kMaxDevices, "device ordinal beyond 63");
+    IGS_REQUIRE(e, n_shards >= 1 && n_shards <= 256, "n_shards must be 1..256");
+    IGS_REQUIRE(e, n < (1ull << 32), "at most 2^32-1 records per call");
+    IGS_REQUIRE(e, d_offsets != nullptr, "offsets is null");
+    IGS_REQUIRE(e, n == 0 || (d_tx && d_tx_out), "tx / tx_out is null");
+    const size_t words = igs_partition_scratch_words(n, n_shards);
+    if (words > IGS_PARTITION_STATIC_WORDS_) {
+        igs_set_error(e,
+                      "igs_partition_tx_static: n_shards * ceil(n / 2048) = %zu counters, the built-in array "
+                      "holds %u; split the batch or use igs_partition_tx_device",
+                      words, IGS_PARTITION_STATIC_WORDS_);
+        return IGS_ERR_INVALID;
+    }
+    uint32_t* counters;
+    {
+        std::lock_guard<std::mutex> lk(g_part_mu);
+        if (!g_part_counters_dev[e->device]) {
+            // first call on this device: resolve the array's address there
+            uint32_t* p = nullptr;
+            IGS_CUDA(e, cudaGetSymbolAddress((void**)&p, g_part_counters));
+            g_part_counters_dev[e->device] = p;
+        }
+        counters = g_part_counters_dev[e->device];
+    }
+    // Nothing has to be cleared: the histogram kernel writes every counter the scan and the scatter
+    // read (n_shards * ceil(n / 2048) words), whatever an earlier call left behind.
+    return igs_partition_run(e, d_tx, n, n_shards, counters, d_tx_out, d_perm, d_offsets, (cudaStream_t)stream);
+}

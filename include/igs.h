@@ -363,6 +363,28 @@ int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d
 int igs_partition_tx_device(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards,
                             igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, void* stream);
 
+/* The same partition for callers that must not allocate.  No counterpart in the reference.
+ * Who they are: a shard's ingest thread that partitions batches while scoring calls of other slots
+ * are in flight on the same GPU (igs_partition_tx_device obtains its counters with cudaMalloc on
+ * first use and again on growth, and an allocation stalls everything running on the device), and
+ * deployments that fix their GPU memory budget at start-up and treat a later allocation as a fault.
+ * This variant calls no allocator at all: its counters are a 1 MiB array inside the library image
+ * (IGS_PARTITION_STATIC_WORDS 32-bit words), resident on every GPU that loads the library, from
+ * load until the process exits.
+ *   - Limit: n_shards * ceil(n / 2048) <= IGS_PARTITION_STATIC_WORDS (8 shards: n <= 67 108 864;
+ *     256 shards: n <= 2 097 152).  Larger requests fail with IGS_ERR_INVALID and a message that
+ *     says so; nothing is launched.
+ *   - The first call on a device looks up the array's device address (one runtime query, then
+ *     cached).  Make that first call before starting any stream capture.
+ *   - All calls on one device share the array, and it keeps whatever the previous call left.
+ *     That is harmless for sequential calls (every counter a call reads, it has written first),
+ *     but two calls whose kernels overlap on the GPU — different streams, different engines or
+ *     threads on the same device — race on it and return garbage: order them yourself.
+ * Arguments, outputs and stream semantics are those of igs_partition_tx_device.                   */
+#define IGS_PARTITION_STATIC_WORDS (256u * 1024u)
+int igs_partition_tx_static(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards,
+                            igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, void* stream);
+
 /* LTV — replaces LTVPredictor.BatchPredict (prediction/ltv.go:385-398): x = n x 256 bf16 model
  * input (raw bit patterns), rows = epilogue sideband.  The MLP output replaces calculateLTV
  * (:155-178); churn / adjust / segment / survival / action / confidence follow :124-139.
