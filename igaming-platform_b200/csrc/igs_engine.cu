@@ -111,8 +111,13 @@ int igs_engine_create(int device, igs_engine** out) {
     e->device = device;
     e->sm_count = prop.multiProcessorCount;
     for (int s = 0; s < IGS_NUM_SLOTS; ++s) {
-        if (cudaStreamCreateWithFlags(&e->slot[s].stream, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&e->slot[s].ev_in, cudaEventDisableTiming) != cudaSuccess) {
+        igs_slot& sl = e->slot[s];
+        bool ok = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&sl.ev_fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int k = 0; ok && k < IGS_PIPE_STREAMS; ++k)
+            ok = cudaStreamCreateWithFlags(&sl.pipe[k], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&sl.ev_join[k], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) {
             igs_set_error(nullptr, "stream/event creation failed: %s",
                           cudaGetErrorString(cudaGetLastError()));
             igs_engine_destroy(e);
@@ -130,7 +135,11 @@ void igs_engine_destroy(igs_engine* e) {
     for (int s = 0; s < IGS_NUM_SLOTS; ++s) {
         igs_slot& sl = e->slot[s];
         free_buf(&sl.in0); free_buf(&sl.in1); free_buf(&sl.out0); free_buf(&sl.aux0); free_buf(&sl.aux1);
-        if (sl.ev_in) cudaEventDestroy(sl.ev_in);
+        if (sl.ev_fork) cudaEventDestroy(sl.ev_fork);
+        for (int k = 0; k < IGS_PIPE_STREAMS; ++k) {
+            if (sl.ev_join[k]) cudaEventDestroy(sl.ev_join[k]);
+            if (sl.pipe[k]) cudaStreamDestroy(sl.pipe[k]);
+        }
         if (sl.stream) cudaStreamDestroy(sl.stream);
     }
     free_buf(&e->part_scratch);
@@ -242,6 +251,36 @@ int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_
     return igs_build_event_index(e, ev, n, n_accounts);
 }
 
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// chunk pipeline of the host-buffer calls
+// ------------------------------------------------------------------------------------------------
+// A host-buffer call is PCIe-bound (path A moves 312 B/tx against ~2 ns/tx of kernel time), so the
+// batch is cut into chunks that go round-robin over the slot's worker streams: the H2D copy of chunk
+// k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The workers fork from and join
+// back into the slot's stream, so ordering against earlier calls on the slot and igs_wait() hold.
+constexpr uint64_t kPipeChunkRows = 128 * 1024;
+
+template <typename Body>
+static int run_pipelined(igs_engine* e, igs_slot& sl, uint64_t n, Body&& body /* (stream, off, cnt) -> int */) {
+    if (n <= 2 * kPipeChunkRows) return body(sl.stream, (uint64_t)0, n);
+    IGS_CUDA(e, cudaEventRecord(sl.ev_fork, sl.stream));
+    for (int k = 0; k < IGS_PIPE_STREAMS; ++k) IGS_CUDA(e, cudaStreamWaitEvent(sl.pipe[k], sl.ev_fork, 0));
+    int k = 0;
+    for (uint64_t off = 0; off < n; off += kPipeChunkRows, k = (k + 1) % IGS_PIPE_STREAMS) {
+        const uint64_t cnt = std::min(kPipeChunkRows, n - off);
+        IGS_TRY(body(sl.pipe[k], off, cnt));
+    }
+    for (int j = 0; j < IGS_PIPE_STREAMS; ++j) {
+        IGS_CUDA(e, cudaEventRecord(sl.ev_join[j], sl.pipe[j]));
+        IGS_CUDA(e, cudaStreamWaitEvent(sl.stream, sl.ev_join[j], 0));
+    }
+    return IGS_OK;
+}
+
+extern "C" {
+
 // ------------------------------------------------------------------------------------------------
 // path A
 // ------------------------------------------------------------------------------------------------
@@ -262,17 +301,23 @@ static int score_features_host(igs_engine* e, int s, const igs_config* cfg, cons
     IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_rule_row)));
     IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_result)));
     if (leaves) IGS_TRY(igs_reserve(e, &sl.aux0, n * (size_t)nt));
-    if (need_feat)
-        IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, features, n * IGS_NUM_FEATURES * sizeof(float),
-                                    cudaMemcpyHostToDevice, sl.stream));
-    IGS_CUDA(e, cudaMemcpyAsync(sl.in1.p, rows, n * sizeof(igs_rule_row), cudaMemcpyHostToDevice, sl.stream));
-    IGS_TRY(igs_launch_score_features(e, cfg, (const float*)sl.in0.p, (const igs_rule_row*)sl.in1.p, n,
-                                      (igs_result*)sl.out0.p, leaves ? (uint8_t*)sl.aux0.p : nullptr,
-                                      sl.stream));
-    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_result), cudaMemcpyDeviceToHost, sl.stream));
-    if (leaves)
-        IGS_CUDA(e, cudaMemcpyAsync(leaf_idx, sl.aux0.p, n * (size_t)nt, cudaMemcpyDeviceToHost, sl.stream));
-    return IGS_OK;
+    float* d_feat = (float*)sl.in0.p;
+    igs_rule_row* d_rows = (igs_rule_row*)sl.in1.p;
+    igs_result* d_out = (igs_result*)sl.out0.p;
+    uint8_t* d_leaf = leaves ? (uint8_t*)sl.aux0.p : nullptr;
+    return run_pipelined(e, sl, n, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
+        if (need_feat)
+            IGS_CUDA(e, cudaMemcpyAsync(d_feat + off * IGS_NUM_FEATURES, features + off * IGS_NUM_FEATURES,
+                                        cnt * IGS_NUM_FEATURES * sizeof(float), cudaMemcpyHostToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(d_rows + off, rows + off, cnt * sizeof(igs_rule_row), cudaMemcpyHostToDevice, st));
+        IGS_TRY(igs_launch_score_features(e, cfg, d_feat + off * IGS_NUM_FEATURES, d_rows + off, cnt, d_out + off,
+                                          leaves ? d_leaf + off * nt : nullptr, st));
+        IGS_CUDA(e, cudaMemcpyAsync(out + off, d_out + off, cnt * sizeof(igs_result), cudaMemcpyDeviceToHost, st));
+        if (leaves)
+            IGS_CUDA(e, cudaMemcpyAsync(leaf_idx + off * nt, d_leaf + off * nt, cnt * (size_t)nt,
+                                        cudaMemcpyDeviceToHost, st));
+        return IGS_OK;
+    });
 }
 
 int igs_score_features(igs_engine* e, const igs_config* cfg, const float* features,
@@ -342,18 +387,24 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
     IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_result)));
     if (features_out) IGS_TRY(igs_reserve(e, &sl.aux0, n * IGS_NUM_FEATURES * sizeof(float)));
     if (velocity_out) IGS_TRY(igs_reserve(e, &sl.aux1, n * sizeof(igs_velocity)));
-    IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, tx, n * sizeof(igs_tx), cudaMemcpyHostToDevice, sl.stream));
-    IGS_TRY(igs_launch_score_batch(e, cfg, (const igs_tx*)sl.in0.p, n, (igs_result*)sl.out0.p,
-                                   features_out ? (float*)sl.aux0.p : nullptr,
-                                   velocity_out ? (igs_velocity*)sl.aux1.p : nullptr, sl.stream));
-    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_result), cudaMemcpyDeviceToHost, sl.stream));
-    if (features_out)
-        IGS_CUDA(e, cudaMemcpyAsync(features_out, sl.aux0.p, n * IGS_NUM_FEATURES * sizeof(float),
-                                    cudaMemcpyDeviceToHost, sl.stream));
-    if (velocity_out)
-        IGS_CUDA(e, cudaMemcpyAsync(velocity_out, sl.aux1.p, n * sizeof(igs_velocity),
-                                    cudaMemcpyDeviceToHost, sl.stream));
-    return IGS_OK;
+    igs_tx* d_tx = (igs_tx*)sl.in0.p;
+    igs_result* d_out = (igs_result*)sl.out0.p;
+    float* d_feat = features_out ? (float*)sl.aux0.p : nullptr;
+    igs_velocity* d_vel = velocity_out ? (igs_velocity*)sl.aux1.p : nullptr;
+    return run_pipelined(e, sl, n, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
+        IGS_CUDA(e, cudaMemcpyAsync(d_tx + off, tx + off, cnt * sizeof(igs_tx), cudaMemcpyHostToDevice, st));
+        IGS_TRY(igs_launch_score_batch(e, cfg, d_tx + off, cnt, d_out + off,
+                                       d_feat ? d_feat + off * IGS_NUM_FEATURES : nullptr,
+                                       d_vel ? d_vel + off : nullptr, st));
+        IGS_CUDA(e, cudaMemcpyAsync(out + off, d_out + off, cnt * sizeof(igs_result), cudaMemcpyDeviceToHost, st));
+        if (features_out)
+            IGS_CUDA(e, cudaMemcpyAsync(features_out + off * IGS_NUM_FEATURES, d_feat + off * IGS_NUM_FEATURES,
+                                        cnt * IGS_NUM_FEATURES * sizeof(float), cudaMemcpyDeviceToHost, st));
+        if (velocity_out)
+            IGS_CUDA(e, cudaMemcpyAsync(velocity_out + off, d_vel + off, cnt * sizeof(igs_velocity),
+                                        cudaMemcpyDeviceToHost, st));
+        return IGS_OK;
+    });
 }
 
 int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n, igs_result* out,

@@ -31,9 +31,13 @@ struct igs_buf {
     size_t cap = 0;
 };
 
+constexpr int IGS_PIPE_STREAMS = 3;   // chunk pipeline depth of a host-buffer call
+
 struct igs_slot {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t  ev_in = nullptr;   // inputs of the current chunk landed
+    cudaStream_t stream = nullptr;                    // the slot's stream: igs_wait() syncs this one
+    cudaStream_t pipe[IGS_PIPE_STREAMS] = {nullptr};  // workers of the chunk pipeline
+    cudaEvent_t  ev_fork = nullptr;                   // slot stream -> workers
+    cudaEvent_t  ev_join[IGS_PIPE_STREAMS] = {nullptr};  // workers -> slot stream
     igs_buf      in0, in1, out0, aux0, aux1;
 };
 
