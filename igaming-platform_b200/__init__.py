@@ -228,5 +228,8 @@ class Engine:
                                             abi.ptr(out), abi.ptr(raw)))
         return (out, raw) if want_raw else out
 
+    def ltv_hidden_device(self, d_x: int, n: int, layer: int, d_hidden: int, stream: int = 0) -> None:
+        self._check(self._lib.igs_ltv_hidden_device(self._h, d_x, n, layer, d_hidden, stream))
+
 
 from . import scoring  # noqa: E402  (reference-facing mirror: ScoringEngine / ScoreRequest / ScoreResponse)

@@ -134,7 +134,7 @@ EXPORTS = [
     "igs_load_events", "igs_score_features", "igs_score_features_async", "igs_wait",
     "igs_score_features_device", "igs_get_velocity", "igs_get_velocity_device", "igs_score_batch",
     "igs_score_batch_async", "igs_score_batch_device", "igs_partition_tx_device", "igs_partition_tx_static",
-    "igs_ltv_batch", "igs_ltv_batch_device",
+    "igs_ltv_batch", "igs_ltv_batch_device", "igs_ltv_hidden_device",
     "igs_rule_score_from_flags", "igs_reason_codes", "igs_action_name", "igs_ltv_action_name",
     "igs_segment_name", "igs_shard_of", "igs_version",
 ]
@@ -189,6 +189,7 @@ def load_library() -> C.CDLL:
     lib.igs_partition_tx_static.argtypes = [vp, vp, u64, C.c_uint32, vp, vp, vp, vp]
     lib.igs_ltv_batch.argtypes = [vp, vp, vp, u64, vp, vp]
     lib.igs_ltv_batch_device.argtypes = [vp, vp, vp, u64, vp, vp, vp]
+    lib.igs_ltv_hidden_device.argtypes = [vp, vp, u64, i32, vp, vp]
     lib.igs_rule_score_from_flags.argtypes = [C.POINTER(Config), C.c_uint32]
     lib.igs_rule_score_from_flags.restype = C.c_int32
     lib.igs_reason_codes.argtypes = [C.c_uint32, C.POINTER(C.c_char_p * NUM_REASONS)]

@@ -481,6 +481,13 @@ int igs_ltv_batch_device(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* 
     return igs_launch_ltv(e, d_x, d_rows, n, d_out, d_ltv_raw, (cudaStream_t)stream);
 }
 
+int igs_ltv_hidden_device(igs_engine* e, const uint16_t* d_x, uint64_t n, int layer, uint16_t* d_hidden,
+                          void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (d_x && d_hidden), "x / hidden is null");
+    return igs_launch_ltv_hidden(e, d_x, n, layer, d_hidden, (cudaStream_t)stream);
+}
+
 // ------------------------------------------------------------------------------------------------
 // host-side helpers
 // ------------------------------------------------------------------------------------------------

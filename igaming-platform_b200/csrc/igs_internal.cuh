@@ -124,3 +124,5 @@ int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows
 int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n, uint32_t n_shards, uint32_t* counts,
                       igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, cudaStream_t stream);
 size_t igs_partition_scratch_words(uint64_t n, uint32_t n_shards);
+int igs_launch_ltv_hidden(igs_engine* e, const uint16_t* d_x, uint64_t n, int layer, uint16_t* d_hidden,
+                          cudaStream_t stream);

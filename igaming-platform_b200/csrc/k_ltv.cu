@@ -1,13 +1,504 @@
-// k_ltv.cu — placeholder until the tcgen05 MLP lands.
+// k_ltv.cu — LTV head (SURVEY K8 + K9), sm_100a: 256 -> 1024 -> 1024 -> 1024 -> 1 MLP in bf16 with fp32
+// accumulation on the 5th-generation tensor cores, then the post-model steps of
+// LTVPredictor.Predict (prediction/ltv.go:124-139) in fp64.
+//
+// k_mlp_gemm — one layer, out[M,N] = relu(A[M,K] * W[N,K]^T + bias) rounded to bf16.
+//   Persistent, one CTA per SM, 128 x 256 output tiles, warp-specialised:
+//     warp 0 (one lane)  TMA producer: cp.async.bulk.tensor 2D loads of the A (128 x 64) and W
+//                        (256 x 64) k-blocks into a 4-stage 128B-swizzled smem ring (SASS UTMALDG)
+//     warp 1 (one lane)  MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M=128 N=256 K=16, smem
+//                        descriptors advanced 32 B per K step, accumulators in TMEM (2 x 256 columns,
+//                        double buffered so the epilogue of tile i overlaps the MMAs of tile i+1);
+//                        tcgen05.commit releases smem stages / publishes the accumulator (SASS UTCHMMA)
+//     warp 2             TMEM allocation (512 columns) and release
+//     warps 4-7          epilogue: tcgen05.ld 32x32b.x32 (SASS LDTM) -> +bias, ReLU, bf16 -> global
+//   Synchronisation is mbarrier-only inside the tile loop (full/empty per smem stage, full/empty per
+//   TMEM accumulator).
+// k_ltv_head — layer 4 (1024 -> 1) as one warp per player + the fp64 epilogue (churn, adjusted LTV,
+//   segment, survival, next-best-action, confidence; prediction/ltv.go:228-382).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <vector>
+
 #include "igs_internal.cuh"
 
-int igs_mlp_upload(igs_engine* e, const igs_mlp_desc*) {
-    igs_set_error(e, "LTV MLP: not built into this library yet");
-    return IGS_ERR_STATE;
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// PTX helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
-void igs_mlp_free(igs_engine*) {}
-int igs_launch_ltv(igs_engine* e, const uint16_t*, const igs_ltv_row*, uint64_t, igs_ltv_result*, float*,
-                   cudaStream_t) {
-    igs_set_error(e, "LTV MLP: not built into this library yet");
-    return IGS_ERR_STATE;
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            " selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+        " tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------
+// GEMM layer
+// ------------------------------------------------------------------------------------------------
+constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 4;
+constexpr int kGemmThreads = 256;
+constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
+constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
+constexpr uint32_t kStageBytes = kABytes + kBBytes;
+constexpr uint32_t kTmemCols = 512;           // 2 accumulators x 256 fp32 columns
+constexpr uint32_t kGemmSmem = STAGES * kStageBytes + 1024 /* alignment slack */ + 256 /* barriers */;
+// instruction descriptor, kind::f16: D=F32 (bit 4), A=BF16 (bit 7), B=BF16 (bit 10), both K-major,
+// N>>3 at bit 17, M>>4 at bit 24
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// smem matrix descriptor (K-major, SWIZZLE_128B): LBO = 1 (unused for swizzled K-major), SBO = 1024 B
+// between 8-row groups, descriptor version 1 (sm_100), layout type 2
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
+    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+struct GemmParams {
+    CUtensorMap tm_a;     // A  [M, K] bf16, K contiguous; box 64 x 128
+    CUtensorMap tm_b;     // W  [N, K] bf16, K contiguous; box 64 x 256
+    const float* bias;    // [N]
+    uint16_t* out;        // [M, N] bf16
+    uint32_t M, N, K;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+k_mlp_gemm(const __grid_constant__ GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment for the 128B swizzle atoms
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t a_base = base;
+    const uint32_t b_base = base + STAGES * kABytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+    const uint32_t bar_full = smem_u32(bars);             // [STAGES]
+    const uint32_t bar_empty = bar_full + 8 * STAGES;     // [STAGES]
+    const uint32_t bar_tfull = bar_empty + 8 * STAGES;    // [2]
+    const uint32_t bar_tempty = bar_tfull + 16;           // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const uint32_t m_blks = (p.M + BM - 1) / BM, n_blks = p.N / BN, k_blks = p.K / BK;
+    const uint32_t n_tiles = m_blks * n_blks;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int m0 = (int)(t / n_blks) * BM, n0 = (int)(t % n_blks) * BN;
+                for (uint32_t kb = 0; kb < k_blks; ++kb) {
+                    mbar_wait(bar_empty + 8 * s, ph ^ 1);
+                    mbar_expect_tx(bar_full + 8 * s, kStageBytes);
+                    tma_load_2d(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, bar_full + 8 * s);
+                    tma_load_2d(b_base + s * kBBytes, &p.tm_b, (int)(kb * BK), n0, bar_full + 8 * s);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0, it = 0;
+            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+                const uint32_t acc = it & 1;
+                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (uint32_t kb = 0; kb < k_blks; ++kb) {
+                    mbar_wait(bar_full + 8 * s, ph);
+                    tc_fence_after();
+                    const uint64_t adesc = make_desc(a_base + s * kABytes);
+                    const uint64_t bdesc = make_desc(b_base + s * kBBytes);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        // +32 bytes (2 x 16 B units) per K step inside the 128B swizzle atom
+                        tc_mma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
+                                   (kb | (uint32_t)k) != 0 ? 1u : 0u);
+                    tc_commit(bar_empty + 8 * s);                          // frees the smem stage when the MMAs retire
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+                tc_commit(bar_tfull + 8 * acc);                            // accumulator complete
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp - 4;                                            // TMEM lane quarter of this warp
+        uint32_t it = 0;
+        for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+            const uint32_t acc = it & 1;
+            const uint32_t m0 = (t / n_blks) * BM, n0 = (t % n_blks) * BN;
+            mbar_wait(bar_tfull + 8 * acc, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t row = m0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+            uint16_t* orow = p.out + (size_t)row * p.N + n0;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tc_ld_32x32b_x32(taddr + c, r);
+                tc_wait_ld();
+                uint32_t packed[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    float v0 = __fadd_rn(__uint_as_float(r[2 * j]), __ldg(p.bias + n0 + c + 2 * j));
+                    float v1 = __fadd_rn(__uint_as_float(r[2 * j + 1]), __ldg(p.bias + n0 + c + 2 * j + 1));
+                    v0 = v0 > 0.f ? v0 : 0.f;
+                    v1 = v1 > 0.f ? v1 : 0.f;
+                    const __nv_bfloat162 b2 = __floats2bfloat162_rn(v0, v1);   // .x (low half) = v0
+                    packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
+                }
+                if (row < p.M) {
+                    uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// layer 4 + fp64 epilogue, one warp per player
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float bf16_bits_to_f32(uint32_t b) { return __uint_as_float(b << 16); }
+
+// calculateEngagementScore, prediction/ltv.go:181-225
+__device__ __forceinline__ double ltv_engagement(const igs_ltv_row& f) {
+    double s = 0.0;
+    if (f.days_since_last_bet < 3) s += 0.3; else if (f.days_since_last_bet < 7) s += 0.2;
+    else if (f.days_since_last_bet < 14) s += 0.1;
+    if (f.sessions_per_week >= 5) s += 0.2; else if (f.sessions_per_week >= 3) s += 0.15;
+    else if (f.sessions_per_week >= 1) s += 0.1;
+    if (f.deposit_frequency >= 4) s += 0.2; else if (f.deposit_frequency >= 2) s += 0.15;
+    else if (f.deposit_frequency >= 1) s += 0.1;
+    if (f.push_enabled) s += 0.1;
+    if (f.email_opt_in) s += 0.1;
+    if (f.has_vip_manager) s += 0.1;
+    return s < 1.0 ? s : 1.0;
+}
+// calculateChurnRisk, :228-262
+__device__ __forceinline__ double ltv_churn(const igs_ltv_row& f) {
+    double r = 0.0;
+    if (f.days_since_last_bet > 30) r += 0.5; else if (f.days_since_last_bet > 14) r += 0.3;
+    else if (f.days_since_last_bet > 7) r += 0.15;
+    if (f.sessions_per_week < 1 && f.days_since_registration > 30) r += 0.2;
+    if (f.days_since_last_deposit > 30) r += 0.2;
+    if (f.support_tickets > 3) r += 0.1;
+    if (f.total_withdrawals > f.total_deposits) r += 0.1;
+    return r < 1.0 ? r : 1.0;
+}
+// Predict after the model output, :124-139 (+ :265-382)
+__device__ __forceinline__ void ltv_epilogue(const igs_ltv_row& f, double ltv, igs_ltv_result* out) {
+    const double churn = ltv_churn(f);
+    const double adjusted = __dmul_rn(ltv, __dsub_rn(1.0, __dmul_rn(churn, 0.5)));          // :127
+    int seg;
+    if (churn > 0.7) seg = IGS_SEG_CHURNING;                                                // :267
+    else if (adjusted >= 10000) seg = IGS_SEG_VIP;
+    else if (adjusted >= 1000) seg = IGS_SEG_HIGH;
+    else if (adjusted >= 100) seg = IGS_SEG_MEDIUM;
+    else seg = IGS_SEG_LOW;
+    double surv = __dmul_rn(__dmul_rn(90.0, __dadd_rn(1.0, ltv_engagement(f))), __dsub_rn(1.0, churn));  // :286-294
+    if (!(surv > 0)) surv = 0;
+    int act = 0;                                                                            // :300-343
+    switch (seg) {
+    case IGS_SEG_CHURNING: act = f.net_revenue > 0 ? 1 : 2; break;
+    case IGS_SEG_VIP: act = f.days_since_last_deposit > 7 ? 3 : 4; break;
+    case IGS_SEG_HIGH: act = !f.has_vip_manager ? 5 : (churn > 0.3 ? 6 : 7); break;
+    case IGS_SEG_MEDIUM: act = f.bonuses_claimed < 3 ? 8 : (f.games_played < 5 ? 9 : 10); break;
+    case IGS_SEG_LOW: act = f.days_since_registration < 7 ? 11 : (f.bonus_conversion_rate > 0.8 ? 0 : 12); break;
+    }
+    double conf = 0.0;                                                                      // :346-382
+    if (f.days_since_registration > 90) conf += 0.3; else if (f.days_since_registration > 30) conf += 0.2;
+    else conf += 0.1;
+    if (f.bet_count > 100) conf += 0.3; else if (f.bet_count > 20) conf += 0.2; else conf += 0.1;
+    if (f.deposit_frequency > 2) conf += 0.2; else if (f.deposit_frequency > 0) conf += 0.1;
+    if (f.days_since_last_bet < 7) conf += 0.2; else if (f.days_since_last_bet < 30) conf += 0.1;
+    if (conf > 1.0) conf = 1.0;
+    out->predicted_ltv = adjusted;
+    out->churn_risk = churn;
+    out->confidence = (float)conf;
+    out->days_survival = (int32_t)surv;
+    out->segment = (uint8_t)seg;
+    out->next_best_action = (uint8_t)act;
+    for (int i = 0; i < 6; ++i) out->pad[i] = 0;
+}
+
+constexpr int kHeadThreads = 256;
+
+__global__ void __launch_bounds__(kHeadThreads)
+k_ltv_head(const uint16_t* __restrict__ h3, const uint16_t* __restrict__ w4, float b4,
+           const igs_ltv_row* __restrict__ rows, unsigned long long n, igs_ltv_result* __restrict__ out,
+           float* __restrict__ raw) {
+    __shared__ float w[IGS_MLP_HIDDEN];
+    for (int i = threadIdx.x; i < IGS_MLP_HIDDEN; i += kHeadThreads) w[i] = bf16_bits_to_f32(__ldg(w4 + i));
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const unsigned long long warp_global = ((unsigned long long)blockIdx.x * kHeadThreads + threadIdx.x) >> 5;
+    const unsigned long long n_warps = ((unsigned long long)gridDim.x * kHeadThreads) >> 5;
+    for (unsigned long long row = warp_global; row < n; row += n_warps) {
+        const uint4* src = reinterpret_cast<const uint4*>(h3 + row * IGS_MLP_HIDDEN);
+        float acc = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint4 v = __ldg(src + c * 32 + lane);
+            const int k0 = (c * 32 + lane) * 8;
+            const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                acc = __fmaf_rn(bf16_bits_to_f32(u[j] & 0xFFFFu), w[k0 + 2 * j], acc);
+                acc = __fmaf_rn(bf16_bits_to_f32(u[j] >> 16), w[k0 + 2 * j + 1], acc);
+            }
+        }
+        for (int o = 16; o; o >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, o));
+        if (lane == 0) {
+            const float y = __fadd_rn(acc, b4);
+            if (raw) raw[row] = y;
+            igs_ltv_row f = rows[row];
+            igs_ltv_result r;
+            ltv_epilogue(f, (double)y, &r);
+            out[row] = r;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+struct MlpDevice {
+    uint16_t *w1 = nullptr, *w2 = nullptr, *w3 = nullptr, *w4 = nullptr;
+    float *b1 = nullptr, *b2 = nullptr, *b3 = nullptr;
+    float b4 = 0.f;
+    igs_buf act[2];   // ping-pong activations of one row chunk
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = (EncodeTiledFn)p;
+    return fn;
+}
+
+// 2D bf16 row-major [rows, cols] tensor map with a (64 x box_rows) box and 128B swizzle
+int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        igs_set_error(e, "cuTensorMapEncodeTiled is not available from the driver");
+        return IGS_ERR_CUDA;
+    }
+    const cuuint64_t gdim[2] = {cols, rows};
+    const cuuint64_t gstride[1] = {cols * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        igs_set_error(e, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        return IGS_ERR_CUDA;
+    }
+    return IGS_OK;
+}
+
+int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float* bias, uint16_t* out, uint32_t M,
+                uint32_t N, uint32_t K, cudaStream_t st) {
+    GemmParams p;
+    int rc = make_tmap(e, &p.tm_a, a, M, K, BM);
+    if (rc != IGS_OK) return rc;
+    rc = make_tmap(e, &p.tm_b, w, N, K, BN);
+    if (rc != IGS_OK) return rc;
+    p.bias = bias; p.out = out; p.M = M; p.N = N; p.K = K;
+    IGS_CUDA(e, cudaFuncSetAttribute(k_mlp_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    const uint32_t tiles = ((M + BM - 1) / BM) * (N / BN);
+    const uint32_t grid = tiles < (uint32_t)e->sm_count ? tiles : (uint32_t)e->sm_count;
+    k_mlp_gemm<<<grid, kGemmThreads, kGemmSmem, st>>>(p);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
+}
+
+constexpr uint64_t kLtvChunkRows = 256 * 1024;   // 512 MB of bf16 activations per ping-pong buffer
+
+}  // namespace
+
+void igs_mlp_free(igs_engine* e) {
+    MlpDevice* m = (MlpDevice*)e->d_mlp;
+    if (!m) return;
+    for (void* p : {(void*)m->w1, (void*)m->w2, (void*)m->w3, (void*)m->w4, (void*)m->b1, (void*)m->b2, (void*)m->b3})
+        if (p) cudaFree(p);
+    for (igs_buf& b : m->act)
+        if (b.p) cudaFree(b.p);
+    delete m;
+    e->d_mlp = nullptr;
+    e->has_mlp = false;
+}
+
+int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d) {
+    IGS_REQUIRE(e, d->w1 && d->w2 && d->w3 && d->w4 && d->b1 && d->b2 && d->b3 && d->b4, "a weight / bias pointer is null");
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    igs_mlp_free(e);
+    MlpDevice* m = new MlpDevice();
+    e->d_mlp = m;
+    const size_t H = IGS_MLP_HIDDEN, I = IGS_MLP_IN;
+    struct { uint16_t** dst; const uint16_t* src; size_t n; } ws[] = {
+        {&m->w1, d->w1, H * I}, {&m->w2, d->w2, H * H}, {&m->w3, d->w3, H * H}, {&m->w4, d->w4, H}};
+    for (auto& w : ws) {
+        IGS_CUDA(e, cudaMalloc(w.dst, w.n * 2));
+        IGS_CUDA(e, cudaMemcpy(*w.dst, w.src, w.n * 2, cudaMemcpyHostToDevice));
+    }
+    struct { float** dst; const float* src; } bs[] = {{&m->b1, d->b1}, {&m->b2, d->b2}, {&m->b3, d->b3}};
+    for (auto& b : bs) {
+        IGS_CUDA(e, cudaMalloc(b.dst, H * 4));
+        IGS_CUDA(e, cudaMemcpy(*b.dst, b.src, H * 4, cudaMemcpyHostToDevice));
+    }
+    m->b4 = d->b4[0];
+    e->has_mlp = true;
+    return IGS_OK;
+}
+
+// Runs layers 1..n_layers (1..3) on rows [0, n) of d_x and leaves the bf16 activations of the last one
+// in *h_out (a chunk buffer owned by the engine); n <= kLtvChunkRows.
+static int run_hidden(igs_engine* e, MlpDevice* m, const uint16_t* d_x, uint32_t n, int n_layers, uint16_t** h_out,
+                      cudaStream_t st) {
+    const uint32_t H = IGS_MLP_HIDDEN;
+    for (igs_buf& b : m->act) {
+        int rc = igs_reserve(e, &b, (size_t)kLtvChunkRows * H * 2);
+        if (rc != IGS_OK) return rc;
+    }
+    uint16_t* a0 = (uint16_t*)m->act[0].p;
+    uint16_t* a1 = (uint16_t*)m->act[1].p;
+    int rc = launch_gemm(e, d_x, m->w1, m->b1, a0, n, H, IGS_MLP_IN, st);
+    if (rc != IGS_OK) return rc;
+    *h_out = a0;
+    if (n_layers >= 2) {
+        rc = launch_gemm(e, a0, m->w2, m->b2, a1, n, H, H, st);
+        if (rc != IGS_OK) return rc;
+        *h_out = a1;
+    }
+    if (n_layers >= 3) {
+        rc = launch_gemm(e, a1, m->w3, m->b3, a0, n, H, H, st);
+        if (rc != IGS_OK) return rc;
+        *h_out = a0;
+    }
+    return IGS_OK;
+}
+
+int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n, igs_ltv_result* d_out,
+                   float* d_ltv_raw, cudaStream_t st) {
+    if (!e->has_mlp) {
+        igs_set_error(e, "no LTV model loaded (igs_load_mlp)");
+        return IGS_ERR_STATE;
+    }
+    MlpDevice* m = (MlpDevice*)e->d_mlp;
+    for (uint64_t off = 0; off < n; off += kLtvChunkRows) {
+        const uint32_t cnt = (uint32_t)(n - off < kLtvChunkRows ? n - off : kLtvChunkRows);
+        uint16_t* h3 = nullptr;
+        int rc = run_hidden(e, m, d_x + off * IGS_MLP_IN, cnt, 3, &h3, st);
+        if (rc != IGS_OK) return rc;
+        const unsigned grid = (unsigned)std::min<uint64_t>((cnt + 7) / 8, (uint64_t)e->sm_count * 8);
+        k_ltv_head<<<grid, kHeadThreads, 0, st>>>(h3, m->w4, m->b4, d_rows + off, cnt, d_out + off,
+                                                  d_ltv_raw ? d_ltv_raw + off : nullptr);
+        IGS_CUDA(e, cudaGetLastError());
+    }
+    return IGS_OK;
+}
+
+int igs_launch_ltv_hidden(igs_engine* e, const uint16_t* d_x, uint64_t n, int layer, uint16_t* d_hidden,
+                          cudaStream_t st) {
+    if (!e->has_mlp) {
+        igs_set_error(e, "no LTV model loaded (igs_load_mlp)");
+        return IGS_ERR_STATE;
+    }
+    IGS_REQUIRE(e, layer >= 1 && layer <= 3, "layer must be 1..3");
+    IGS_REQUIRE(e, n <= kLtvChunkRows, "at most 262144 rows per diagnostic call");
+    if (n == 0) return IGS_OK;
+    MlpDevice* m = (MlpDevice*)e->d_mlp;
+    uint16_t* h = nullptr;
+    int rc = run_hidden(e, m, d_x, (uint32_t)n, layer, &h, st);
+    if (rc != IGS_OK) return rc;
+    IGS_CUDA(e, cudaMemcpyAsync(d_hidden, h, n * IGS_MLP_HIDDEN * 2, cudaMemcpyDeviceToDevice, st));
+    return IGS_OK;
 }

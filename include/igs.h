@@ -394,6 +394,13 @@ int igs_ltv_batch(igs_engine* e, const uint16_t* x, const igs_ltv_row* rows, uin
 int igs_ltv_batch_device(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,
                          igs_ltv_result* d_out, float* d_ltv_raw, void* stream);
 
+/* Verify mode of the LTV model (the counterpart of leaf_idx in igs_score_features): runs the first
+ * `layer` (1..3) layers on n <= 262144 rows and returns the n x 1024 bf16 activations, so a test can
+ * check one GEMM at a time.  No reference counterpart (the reference's LTVModel holds session: nil,
+ * ml/onnx_model.go:399).                                                                          */
+int igs_ltv_hidden_device(igs_engine* e, const uint16_t* d_x, uint64_t n, int layer, uint16_t* d_hidden,
+                          void* stream);
+
 /* ------------------------------------------------------------------------------------------ */
 /* host-side helpers (pure C, no GPU)                                                          */
 /* ------------------------------------------------------------------------------------------ */

@@ -1,0 +1,147 @@
+"""GPU: LTV head — tcgen05 bf16 MLP (256 -> 1024 -> 1024 -> 1024 -> 1) + fp64 epilogue vs the oracle.
+
+Tolerances (written here): operands and activations are rounded to bf16 at the same
+points on both sides and accumulation is fp32 (tensor core) vs fp64-then-fp32 (oracle), so
+  * one layer from identical inputs: every activation within 1 bf16 ulp (+ 2e-5 absolute, the fp32
+    accumulation error scale, which is what decides the sign next to the ReLU zero crossing),
+    >= 99.5 % bit-identical;
+  * the fp32 model output from identical layer-3 activations: |dy| <= 1e-5 * max(1, |y|);
+  * end to end (a 1-ulp bf16 flip of one activation, 2^-8 relative, propagates through up to 3
+    layers): |dy| <= 1e-2 * max(1, |y|, rms(y) of the batch) for every row, <= 1e-3 for 90 % of them;
+  * everything after the model output (churn, adjusted LTV, segment, survival, action, confidence):
+    exact, given the same model output.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tests import synth
+from tests.test_oracle_kat import LTV_ACTIONS, SEGS, load
+
+pytestmark = pytest.mark.gpu
+
+
+def hidden_on_device(engine, x_bf16, layer):
+    import torch
+    n = x_bf16.shape[0]
+    dev = torch.device("cuda", 0)
+    d_x = torch.from_numpy(x_bf16.view(np.int16)).to(dev)
+    d_h = torch.zeros((n, 1024), dtype=torch.int16, device=dev)
+    engine.ltv_hidden_device(d_x.data_ptr(), n, layer, d_h.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    return d_h.cpu().numpy().view(np.uint16)
+
+
+def oracle_layer(orc, w, b, inp_bf16):
+    """relu + bf16 rounding of orc_mlp_layer for every row of inp_bf16."""
+    n_out, n_in = w.shape
+    out = np.zeros((inp_bf16.shape[0], n_out), dtype=np.uint16)
+    pre = np.zeros(n_out, dtype=np.float32)
+    L = orc.lib()
+    for i in range(inp_bf16.shape[0]):
+        row = np.ascontiguousarray(inp_bf16[i])
+        L.orc_mlp_layer(w.ctypes.data, b.ctypes.data, n_out, n_in, row.ctypes.data, pre.ctypes.data)
+        out[i] = synth.f32_to_bf16(np.maximum(pre, 0))
+    return out
+
+
+def assert_bf16_close(got, want, what):
+    g, w = synth.bf16_to_f32(got).astype(np.float64), synth.bf16_to_f32(want).astype(np.float64)
+    same = np.mean(got == want)
+    ulp = np.maximum(np.abs(w), np.abs(g)) * 2.0 ** -7
+    bad = np.abs(g - w) > ulp + 2e-5
+    assert not bad.any(), (f"{what}: {int(bad.sum())} activations off by more than 1 bf16 ulp, e.g. "
+                           f"got {g[bad][:4]} want {w[bad][:4]}")
+    assert same >= 0.995, f"{what}: only {same:.4%} of activations are bit-identical"
+
+
+def test_each_layer_from_identical_inputs(engine, orc, pkg):
+    model = synth.make_mlp(seed=5)
+    engine.load_mlp(model)
+    x, _ = synth.make_ltv_inputs(192, seed=6)
+    h1 = hidden_on_device(engine, x, 1)
+    assert_bf16_close(h1, oracle_layer(orc, model.w1, model.b1, x), "layer 1")
+    h2 = hidden_on_device(engine, x, 2)
+    assert_bf16_close(h2, oracle_layer(orc, model.w2, model.b2, h1), "layer 2 (from the device's layer 1)")
+    h3 = hidden_on_device(engine, x, 3)
+    assert_bf16_close(h3, oracle_layer(orc, model.w3, model.b3, h2), "layer 3 (from the device's layer 2)")
+    assert (h3 != 0).mean() > 0.2, "layer 3 should not be dead"
+    # model output from the device's own layer-3 activations
+    _, rows = synth.make_ltv_inputs(192, seed=6)
+    _, raw = engine.ltv_batch(x, rows, want_raw=True)
+    y = np.zeros(1, dtype=np.float32)
+    for i in range(x.shape[0]):
+        orc.lib().orc_mlp_layer(model.w4.ctypes.data, model.b4.ctypes.data, 1, 1024,
+                                np.ascontiguousarray(h3[i]).ctypes.data, y.ctypes.data)
+        assert abs(float(raw[i]) - float(y[0])) <= 1e-5 * max(1.0, abs(float(y[0]))), f"row {i}"
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 1000])
+def test_end_to_end_vs_oracle(engine, orc, pkg, n):
+    model = synth.make_mlp(seed=9)
+    # scale the output layer by 2^12 (exact in bf16) so that predicted LTVs spread over the segments
+    model.w4 = synth.f32_to_bf16(synth.bf16_to_f32(model.w4) * np.float32(4096.0))
+    engine.load_mlp(model)
+    x, rows = synth.make_ltv_inputs(n, seed=10 + n)
+    out, raw = engine.ltv_batch(x, rows, want_raw=True)
+    m = min(n, 200)
+    want = orc.mlp_forward(model, x[:m])
+    # relative to the output scale of the batch (single rows cancel to ~0)
+    scale = np.maximum(np.maximum(1.0, np.abs(want)), np.sqrt(np.mean(want.astype(np.float64) ** 2)))
+    err = np.abs(raw[:m].astype(np.float64) - want) / scale
+    assert err.max() <= 1e-2, f"max relative error {err.max():.3e}"
+    assert np.percentile(err, 90) <= 1e-3, f"90th percentile of the relative error {np.percentile(err, 90):.3e}"
+    # the epilogue is exact given the device's model output
+    want_out = orc.ltv_epilogue(rows, raw.astype(np.float64))
+    assert out.tobytes() == want_out.tobytes()
+    assert len(set(out["segment"].tolist())) >= (3 if n >= 1000 else 1)
+
+
+def test_chunked_batch_is_consistent(engine, pkg):
+    """n > one activation chunk (262 144 rows): rows must not depend on their chunk / tile position."""
+    model = synth.make_mlp(seed=9)
+    engine.load_mlp(model)
+    n = 262_144 + 1000
+    x, rows = synth.make_ltv_inputs(4096, seed=3)
+    reps = -(-n // 4096)
+    xb = np.tile(x, (reps, 1))[:n]
+    rb = np.tile(rows, reps)[:n]
+    out, raw = engine.ltv_batch(xb, rb, want_raw=True)
+    assert np.array_equal(raw[:4096].view(np.uint32), raw[4096:8192].view(np.uint32))
+    assert np.array_equal(raw[:1000].view(np.uint32), raw[262_144:262_144 + 1000].view(np.uint32))
+    assert out[:1000].tobytes() == out[262_144:].tobytes()
+
+
+@pytest.mark.parametrize("case", load("kat_ltv.json")["cases"], ids=lambda c: c["id"])
+def test_kat_set_c_epilogue_on_device(engine, pkg, case):
+    """KAT set C through the device epilogue: a model with zero weights and b4 = the heuristic LTV
+    stands in for calculateLTV (prediction/ltv.go:155-178), everything after it is the kernel."""
+    abi = pkg.abi
+    z = lambda *s: np.zeros(s, np.uint16)  # noqa: E731
+    f = lambda n, v=0.0: np.full(n, v, np.float32)  # noqa: E731
+    model = pkg.MlpModel(z(1024, 256), f(1024), z(1024, 1024), f(1024), z(1024, 1024), f(1024), z(1, 1024),
+                         f(1, case["ltv"]))
+    engine.load_mlp(model)
+    row = np.zeros(1, dtype=abi.ltv_row_dtype)
+    for k, v in case["f"].items():
+        row[k] = v
+    out, raw = engine.ltv_batch(np.zeros((1, 256), np.uint16), row, want_raw=True)
+    assert float(raw[0]) == case["ltv"]
+    o = out[0]
+    assert float(o["predicted_ltv"]) == pytest.approx(case["adjusted"], rel=1e-12)
+    assert float(o["churn_risk"]) == pytest.approx(case["churn"], rel=1e-12, abs=1e-15)
+    assert SEGS[int(o["segment"])] == case["segment"]
+    assert int(o["days_survival"]) == case["survival"]
+    assert float(o["confidence"]) == pytest.approx(case["confidence"], rel=1e-6)
+    assert LTV_ACTIONS[int(o["next_best_action"])] == case["action"]
+
+
+def test_ltv_needs_a_model(pkg):
+    with pkg.Engine(device=0) as fresh:
+        x, rows = synth.make_ltv_inputs(4, seed=1)
+        with pytest.raises(pkg.IgsError) as ei:
+            fresh.ltv_batch(x, rows)
+        assert ei.value.status == pkg.abi.ERR_STATE
