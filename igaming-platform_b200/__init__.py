@@ -232,4 +232,4 @@ class Engine:
         self._check(self._lib.igs_ltv_hidden_device(self._h, d_x, n, layer, d_hidden, stream))
 
 
-from . import scoring  # noqa: E402  (reference-facing mirror: ScoringEngine / ScoreRequest / ScoreResponse)
+from . import scoring, sharding  # noqa: E402  (reference-facing mirror: ScoringEngine / ScoreRequest / ScoreResponse)
