@@ -180,17 +180,29 @@ int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d) {
     const size_t bytes = (size_t)d->n_trees * IGS_DEV_TREE_BYTES;
     std::vector<uint8_t> img(bytes ? bytes : 16, 0);
     for (uint32_t t = 0; t < d->n_trees; ++t) {
-        igs_dev_node* nodes = reinterpret_cast<igs_dev_node*>(img.data() + (size_t)t * IGS_DEV_TREE_BYTES);
-        float* leaves = reinterpret_cast<float*>(img.data() + (size_t)t * IGS_DEV_TREE_BYTES + 2048);
-        for (int i = 0; i < IGS_TREE_NODES; ++i) {
-            const uint8_t f = d->feat[(size_t)t * IGS_TREE_NODES + i];
-            if (f >= d->n_features) {
-                igs_set_error(e, "tree %u node %d: feature index %u >= n_features %u", t, i, f, d->n_features);
+        uint8_t* tb = img.data() + (size_t)t * IGS_DEV_TREE_BYTES;
+        const uint8_t* feat = d->feat + (size_t)t * IGS_TREE_NODES;
+        const float* thr = d->thr + (size_t)t * IGS_TREE_NODES;
+        for (int i = 0; i < IGS_TREE_NODES; ++i)
+            if (feat[i] >= d->n_features) {
+                igs_set_error(e, "tree %u node %d: feature index %u >= n_features %u", t, i, feat[i], d->n_features);
                 return IGS_ERR_INVALID;
             }
-            nodes[i].feat_off = (uint32_t)f * 128u;
-            nodes[i].thr = d->thr[(size_t)t * IGS_TREE_NODES + i];
+        for (int lvl = 0; lvl < IGS_TREE_DEPTH; ++lvl) {
+            const int first = (1 << lvl) - 1, count = 1 << lvl;
+            for (int j = 0; j < count; ++j) {
+                const int i = first + j;
+                if ((lvl & 1) == 0) {
+                    igs_dev_node nd;
+                    nd.feats = ((uint32_t)feat[i] << 7) | ((uint32_t)feat[2 * i + 1] << 13) | ((uint32_t)feat[2 * i + 2] << 19);
+                    nd.thr = thr[i];
+                    memcpy(tb + igs_dev_level_off(lvl) + j * 8, &nd, 8);
+                } else {
+                    memcpy(tb + igs_dev_level_off(lvl) + j * 4, &thr[i], 4);
+                }
+            }
         }
+        float* leaves = reinterpret_cast<float*>(tb + IGS_DEV_LEAF_OFF);
         for (int i = 0; i < IGS_TREE_LEAVES; ++i) {
             const float lf = d->leaf[(size_t)t * IGS_TREE_LEAVES + i];
             if (!std::isfinite(lf) || fabsf(lf) > 1e30f) {

@@ -13,15 +13,29 @@
 // ---------------------------------------------------------------------------------------------
 // device-resident model layout
 // ---------------------------------------------------------------------------------------------
-// One tree = 256 node slots of 8 bytes (slot 255 unused) followed by 256 fp32 leaves = 3072 B,
-// so a chunk of trees is one contiguous 16B-aligned block that a single cp.async.bulk moves.
-// Node = { feat_off = feature index * 128 (byte offset of that feature's row in a [64][32] fp32
-// warp tile), thr }.
+// One tree = 2384 B, contiguous and 16B-aligned so that a chunk of trees is one cp.async.bulk.
+// Levels are packed in pairs so that a walk needs 5 shared-memory wavefronts per two levels instead
+// of 6: an even-level node (8 bytes) carries its threshold, its own feature and the features of
+// both children; an odd-level node is only a 4-byte threshold (its feature came with the parent).
+//   level 0  1 x 8 B  @    0      level 1    2 x 4 B @    8
+//   level 2  4 x 8 B  @   16      level 3    8 x 4 B @   48
+//   level 4 16 x 8 B  @   80      level 5   32 x 4 B @  208
+//   level 6 64 x 8 B  @  336      level 7  128 x 4 B @  848
+//   leaves 256 x 4 B  @ 1360
+// A level of <= 128 contiguous bytes covers every bank at most once, so levels 0..5 are free of
+// bank conflicts whatever nodes the 32 lanes visit.
 struct __align__(8) igs_dev_node {
-    uint32_t feat_off;
+    uint32_t feats;   // own feature * 128 (bits 7..12) | left child's feature << 13 | right child's << 19
     float    thr;
 };
-constexpr int IGS_DEV_TREE_BYTES = 256 * 8 + 256 * 4;  // 3072
+__host__ __device__ constexpr int igs_dev_level_off(int d) {   // 0, 8, 16, 48, 80, 208, 336, 848
+    int off = 0;
+    for (int l = 0; l < d; ++l) off += (1 << l) * ((l & 1) ? 4 : 8);
+    return off;
+}
+static_assert(igs_dev_level_off(7) == 848 && igs_dev_level_off(8) == 1360, "tree image layout");
+constexpr int IGS_DEV_LEAF_OFF = 1360;
+constexpr int IGS_DEV_TREE_BYTES = 1360 + 256 * 4;  // 2384
 
 // ---------------------------------------------------------------------------------------------
 // per-slot staging (device buffers that mirror the caller's host buffers)

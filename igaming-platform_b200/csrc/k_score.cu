@@ -24,21 +24,28 @@
 #include "igs_math.cuh"
 #include "velocity.cuh"
 
+#include <stdlib.h>
 #include <string.h>
 
 namespace {
 
-constexpr int kWarps = 8;
-constexpr int kThreads = kWarps * 32;
-constexpr int kTileTx = kThreads;
-constexpr int kChunkTrees = 25;
 constexpr int kIlp = 5;
 constexpr int kFeatTileFloats = IGS_NUM_FEATURES * 32;           // per warp
 constexpr int kFeatTileBytes = kFeatTileFloats * 4;              // 8 KB
-constexpr int kChunkBytes = kChunkTrees * IGS_DEV_TREE_BYTES;    // 76 800
-constexpr int kSmemBytes = kWarps * kFeatTileBytes + 2 * kChunkBytes + 64;
-static_assert(kChunkTrees % kIlp == 0, "chunk must be a whole number of ILP groups");
-static_assert(kSmemBytes <= 227 * 1024, "smem budget");
+
+// Launch shape: W warps per CTA (one tx per lane -> 32 W tx per tile), tree chunks of C trees.
+// smem = W x 8 KB feature tiles + 2 x C x 3 KB chunk buffers.
+template <int W, int C>
+struct Shape {
+    static constexpr int kWarps = W;
+    static constexpr int kThreads = W * 32;
+    static constexpr int kTileTx = W * 32;
+    static constexpr int kChunkTrees = C;
+    static constexpr int kChunkBytes = C * IGS_DEV_TREE_BYTES;
+    static constexpr int kSmemBytes = W * kFeatTileBytes + 2 * kChunkBytes + 64;
+    static_assert(C % kIlp == 0, "chunk must be a whole number of ILP groups");
+    static_assert(kSmemBytes <= 227 * 1024, "smem budget");
+};
 
 constexpr int kSrcFeatures = 0;
 constexpr int kSrcTx = 1;
@@ -100,47 +107,85 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     } while (!ok);
 }
 
-// Walk `trees` trees of the chunk at `cb` for this lane's transaction.  `tile` = this warp's
-// [64][32] fp32 feature tile already offset by lane.  Adds leaves to *margin in tree order.
+// --- instruction-mix helpers -------------------------------------------------------------------
+// The walk is bound by the ALU pipe and the shared-memory pipe together, so the index arithmetic is
+// written to land on the FMA pipe (IMAD) and the compare produces a mask (FSET) instead of a
+// predicate + select.
+__device__ __forceinline__ uint32_t fset_gtu(float x, float thr) {     // 0xFFFFFFFF iff !(x <= thr): BRANCH_LEQ, NaN -> right
+    uint32_t m;
+    asm("set.gtu.u32.f32 %0, %1, %2;" : "=r"(m) : "f"(x), "f"(thr));
+    return m;
+}
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+template <int kOff>
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(addr), "n"(kOff));
+    return v;
+}
+template <int kOff>
+__device__ __forceinline__ float lds32f(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(kOff));
+    return v;
+}
+
+// One level pair for one tree: even level `kD` (8-byte node) and odd level kD+1 (4-byte threshold).
+// n = minus the node index inside the level (so that "2*index + went_right" is one IMAD: n' = 2n + mask).
+template <int kD>
+__device__ __forceinline__ void walk_pair(uint32_t tree_addr, uint32_t tile_lane_addr, uint32_t& n) {
+    const uint2 nd = lds64<igs_dev_level_off(kD)>(imad(n, 0xFFFFFFF8u /* -8 */, tree_addr));
+    const float x0 = lds32f<0>((nd.x & 0x1F80u) + tile_lane_addr);
+    const uint32_t m0 = fset_gtu(x0, __uint_as_float(nd.y));
+    const uint32_t sh = imad(m0, 0xFFFFFFFAu /* -6 */, 6u);             // 6: left child's field, 12: right child's
+    const uint32_t child = ((nd.x >> sh) & 0x1F80u) + tile_lane_addr;
+    n = imad(n, 2u, m0);
+    const float thr1 = lds32f<igs_dev_level_off(kD + 1)>(imad(n, 0xFFFFFFFCu /* -4 */, tree_addr));
+    const float x1 = lds32f<0>(child);
+    n = imad(n, 2u, fset_gtu(x1, thr1));
+}
+
+// Walk `trees` trees of the chunk at smem address `cb` for this lane's transaction.  `tile_lane_addr` =
+// smem address of this warp's [64][32] fp32 feature tile offset by lane.  Adds leaves to *margin in
+// tree order.  Levels are visited in pairs (igs_internal.cuh): LDS.64 {feats, thr} at the even level,
+// LDS.32 thr at the odd level whose feature came with the parent.
 template <bool kLeaves>
-__device__ __forceinline__ void walk_chunk(const uint8_t* __restrict__ cb, int trees,
-                                           const uint8_t* __restrict__ tile_lane, float* margin,
+__device__ __forceinline__ void walk_chunk(uint32_t cb, int trees, uint32_t tile_lane_addr, float* margin,
                                            uint8_t* leaf_out) {
     float m = *margin;
     int t = 0;
     for (; t + kIlp <= trees; t += kIlp) {
-        const uint8_t* tb = cb + t * IGS_DEV_TREE_BYTES;
-        uint32_t j[kIlp];
+        const uint32_t tb = cb + t * IGS_DEV_TREE_BYTES;
+        uint32_t n[kIlp];
 #pragma unroll
-        for (int k = 0; k < kIlp; ++k) j[k] = 0;
+        for (int k = 0; k < kIlp; ++k) n[k] = 0;
 #pragma unroll
-        for (int d = 0; d < IGS_TREE_DEPTH; ++d) {
+        for (int k = 0; k < kIlp; ++k) walk_pair<0>(tb + k * IGS_DEV_TREE_BYTES, tile_lane_addr, n[k]);
 #pragma unroll
-            for (int k = 0; k < kIlp; ++k) {
-                const uint2 nd = *reinterpret_cast<const uint2*>(tb + k * IGS_DEV_TREE_BYTES +
-                                                                 ((1 << d) - 1) * 8 + j[k]);
-                const float x = *reinterpret_cast<const float*>(tile_lane + nd.x);
-                j[k] = 2 * j[k] + ((x <= __uint_as_float(nd.y)) ? 0u : 8u);   // BRANCH_LEQ, NaN -> right
-            }
-        }
+        for (int k = 0; k < kIlp; ++k) walk_pair<2>(tb + k * IGS_DEV_TREE_BYTES, tile_lane_addr, n[k]);
+#pragma unroll
+        for (int k = 0; k < kIlp; ++k) walk_pair<4>(tb + k * IGS_DEV_TREE_BYTES, tile_lane_addr, n[k]);
+#pragma unroll
+        for (int k = 0; k < kIlp; ++k) walk_pair<6>(tb + k * IGS_DEV_TREE_BYTES, tile_lane_addr, n[k]);
 #pragma unroll
         for (int k = 0; k < kIlp; ++k) {
-            const float lf = *reinterpret_cast<const float*>(tb + k * IGS_DEV_TREE_BYTES + 2048 + (j[k] >> 1));
-            m = __fadd_rn(m, lf);
-            if (kLeaves) leaf_out[t + k] = (uint8_t)(j[k] >> 3);
+            m = __fadd_rn(m, lds32f<IGS_DEV_LEAF_OFF>(imad(n[k], 0xFFFFFFFCu, tb + k * IGS_DEV_TREE_BYTES)));
+            if (kLeaves) leaf_out[t + k] = (uint8_t)(0u - n[k]);
         }
     }
     for (; t < trees; ++t) {
-        const uint8_t* tb = cb + t * IGS_DEV_TREE_BYTES;
-        uint32_t j = 0;
-#pragma unroll
-        for (int d = 0; d < IGS_TREE_DEPTH; ++d) {
-            const uint2 nd = *reinterpret_cast<const uint2*>(tb + ((1 << d) - 1) * 8 + j);
-            const float x = *reinterpret_cast<const float*>(tile_lane + nd.x);
-            j = 2 * j + ((x <= __uint_as_float(nd.y)) ? 0u : 8u);
-        }
-        m = __fadd_rn(m, *reinterpret_cast<const float*>(tb + 2048 + (j >> 1)));
-        if (kLeaves) leaf_out[t] = (uint8_t)(j >> 3);
+        const uint32_t tb = cb + t * IGS_DEV_TREE_BYTES;
+        uint32_t n = 0;
+        walk_pair<0>(tb, tile_lane_addr, n);
+        walk_pair<2>(tb, tile_lane_addr, n);
+        walk_pair<4>(tb, tile_lane_addr, n);
+        walk_pair<6>(tb, tile_lane_addr, n);
+        m = __fadd_rn(m, lds32f<IGS_DEV_LEAF_OFF>(imad(n, 0xFFFFFFFCu, tb)));
+        if (kLeaves) leaf_out[t] = (uint8_t)(0u - n);
     }
     *margin = m;
 }
@@ -263,9 +308,11 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
     r->tx_type = t.tx_type;
 }
 
-template <int kSrc, bool kLeaves>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int kSrc, bool kLeaves, typename S>
+__global__ void __launch_bounds__(S::kThreads, 1)
 k_score(const __grid_constant__ ScoreParams p) {
+    constexpr int kWarps = S::kWarps, kTileTx = S::kTileTx, kChunkTrees = S::kChunkTrees,
+                  kChunkBytes = S::kChunkBytes;
     extern __shared__ __align__(128) uint8_t smem[];
     float* feat_tiles = reinterpret_cast<float*>(smem);
     uint8_t* chunk_buf = smem + kWarps * kFeatTileBytes;
@@ -304,7 +351,8 @@ k_score(const __grid_constant__ ScoreParams p) {
     }
 
     float* my_tile = feat_tiles + warp * kFeatTileFloats;
-    const uint8_t* tile_lane = reinterpret_cast<const uint8_t*>(my_tile + lane);
+    const uint32_t tile_lane_addr = smem_u32(my_tile + lane);
+    const uint32_t chunk_addr = smem_u32(chunk_buf);
     unsigned long long g = 0;
 
     for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -370,11 +418,11 @@ k_score(const __grid_constant__ ScoreParams p) {
                 mbar_wait(bar0 + 8 * b, (uint32_t)((g >> 1) & 1));
                 if (kLeaves) {
                     uint8_t tmp[kChunkTrees];
-                    walk_chunk<true>(chunk_buf + b * kChunkBytes, trees, tile_lane, &margin, tmp);
+                    walk_chunk<true>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, tmp);
                     if (leaf_row)
                         for (int t = 0; t < trees; ++t) leaf_row[c * kChunkTrees + t] = valid ? tmp[t] : 0;
                 } else {
-                    walk_chunk<false>(chunk_buf + b * kChunkBytes, trees, tile_lane, &margin, nullptr);
+                    walk_chunk<false>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, nullptr);
                 }
                 __syncthreads();   // every lane is done with buffer b
                 if (threadIdx.x == 0 && g + 2 < total_chunks) issue(g + 2);
@@ -398,17 +446,32 @@ k_score(const __grid_constant__ ScoreParams p) {
 
 }  // namespace
 
-static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cudaStream_t stream) {
+template <typename S>
+static int launch_shape(igs_engine* e, int src, const ScoreParams& p, bool leaves, cudaStream_t stream) {
     void (*kern)(const ScoreParams) = nullptr;
-    if (src == kSrcFeatures) kern = leaves ? k_score<kSrcFeatures, true> : k_score<kSrcFeatures, false>;
-    else kern = leaves ? k_score<kSrcTx, true> : k_score<kSrcTx, false>;
+    if (src == kSrcFeatures) kern = leaves ? k_score<kSrcFeatures, true, S> : k_score<kSrcFeatures, false, S>;
+    else kern = leaves ? k_score<kSrcTx, true, S> : k_score<kSrcTx, false, S>;
     // per-device attribute; a few hundred ns, so simply set on every launch
-    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    const unsigned long long n_tiles = (p.n + kTileTx - 1) / kTileTx;
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kSmemBytes));
+    const unsigned long long n_tiles = (p.n + S::kTileTx - 1) / S::kTileTx;
     const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : e->sm_count);
-    kern<<<grid, kThreads, kSmemBytes, stream>>>(p);
+    kern<<<grid, S::kThreads, S::kSmemBytes, stream>>>(p);
     IGS_CUDA(e, cudaGetLastError());
     return IGS_OK;
+}
+
+static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cudaStream_t stream) {
+    static const int variant = getenv("IGS_SCORE_SHAPE") ? atoi(getenv("IGS_SCORE_SHAPE")) : 0;   // tuning knob
+    switch (variant) {
+    case 1: return launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
+    case 2: return launch_shape<Shape<16, 15>>(e, src, p, leaves, stream);
+    case 3: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
+    case 4: return launch_shape<Shape<12, 25>>(e, src, p, leaves, stream);
+    case 5: return launch_shape<Shape<16, 20>>(e, src, p, leaves, stream);
+    case 6: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
+    default: return src == kSrcTx ? launch_shape<Shape<16, 10>>(e, src, p, leaves, stream)
+                                  : launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
+    }
 }
 
 static int check_model(igs_engine* e, const igs_config* cfg) {
