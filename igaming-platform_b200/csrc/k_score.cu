@@ -1,17 +1,23 @@
-// k_score.cu — fused rules + tree-ensemble + blend kernel (SURVEY K5+K6+K7), sm_100a.
+// k_score.cu — fused rules + tree-ensemble + blend kernel (SURVEY K5+K6+K7, and K3-lookup+K4 for the
+// fused path), sm_100a.
 //
-// One persistent CTA per SM, 8 warps, one transaction per lane (256 tx per tile).
+// One persistent CTA per SM, W warps, one transaction per lane (32 W tx per tile).
 //   * Each warp stages its 32 x 64 fp32 feature rows into a private smem tile laid out
 //     [feature][lane]: lane l only ever touches bank l, so the data-dependent x[feat] gather of
 //     the tree walk is bank-conflict free whatever features the 32 lanes ask for.
-//   * The ensemble streams through smem in chunks of 25 trees (76.8 KB) moved by one
-//     cp.async.bulk (TMA bulk copy, SASS UBLKCP) each, double buffered behind mbarriers, so the
-//     L2->smem traffic overlaps the walk of the previous chunk.
-//   * A lane walks 5 trees at once (5 independent LDS->LDS->FSETP chains) to cover the ~2x29
-//     cycle shared-memory latency of one node visit with only 8 warps per SM.
+//   * The ensemble streams through smem in chunks of C trees moved by one cp.async.bulk (TMA bulk
+//     copy, SASS UBLKCP) each, double buffered behind mbarriers, so the L2->smem traffic overlaps
+//     the walk of the previous chunk.
+//   * Tree levels are packed in pairs (igs_internal.cuh): 5 shared-memory wavefronts per two levels
+//     instead of 6, and levels 0..5 are conflict free.
+//   * A lane walks 5 trees at once (independent LDS->LDS->FSET chains) to cover the shared-memory
+//     latency; the index arithmetic is written for the FMA pipe (IMAD) because the ALU pipe and
+//     the shared-memory pipe are the two limiters (profiles/).
 //   * Leaves are added to the margin in tree-index order in fp32 — the oracle's order — so the
 //     margin, the logistic (igs_sigmoid), the fp64 blend and the integer score are bit-identical
 //     to the CPU restatement.
+//   * Launch shapes (W x C): 12 x 20 for pre-assembled rows, 16 x 10 for the fused path, where more
+//     warps hide the latency of the velocity lookups.
 // Two input sources share the kernel body:
 //   kSrcFeatures (path A): pre-assembled normalised 64-float rows + the 48-byte rule sideband.
 //   kSrcTx       (path B): 32-byte tx records; the lane looks its account up in the event index
@@ -142,8 +148,8 @@ __device__ __forceinline__ void walk_pair(uint32_t tree_addr, uint32_t tile_lane
     const float x0 = lds32f<0>((nd.x & 0x1F80u) + tile_lane_addr);
     const uint32_t m0 = fset_gtu(x0, __uint_as_float(nd.y));
     const uint32_t sh = imad(m0, 0xFFFFFFFAu /* -6 */, 6u);             // 6: left child's field, 12: right child's
-    const uint32_t child = ((nd.x >> sh) & 0x1F80u) + tile_lane_addr;
     n = imad(n, 2u, m0);
+    const uint32_t child = ((nd.x >> sh) & 0x1F80u) + tile_lane_addr;
     const float thr1 = lds32f<igs_dev_level_off(kD + 1)>(imad(n, 0xFFFFFFFCu /* -4 */, tree_addr));
     const float x1 = lds32f<0>(child);
     n = imad(n, 2u, fset_gtu(x1, thr1));
