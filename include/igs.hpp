@@ -1,0 +1,207 @@
+// igs.hpp — C++17 host side over the C ABI (igs.h), header only.
+//
+// The reference's host code is Go (services/risk); this image has no Go toolchain, so the compiled-language
+// mirror of its operator interface is written in C++ (the cgo equivalent is sketched in INTEGRATION.md).
+// Names, argument meaning and error behaviour follow services/risk/internal/scoring/engine.go:
+//   ScoreRequest :40-53, ScoreResponse :56-64, NewScoringEngine :231-259, Score :262-323,
+//   GetThresholds / SetThresholds :491-504, ScoreWithExplanation :507-543, DefaultConfig :215-228.
+// Everything here is marshalling; every number in a response comes from the CUDA library.
+#pragma once
+
+#include <array>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <functional>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <utility>
+#include <vector>
+
+#include "igs.h"
+
+namespace igs {
+
+struct Error : std::runtime_error {
+    int status;
+    Error(int st, const std::string& what) : std::runtime_error(what), status(st) {}
+};
+
+using AccountID = std::array<uint8_t, 16>;   // uuid.UUID
+
+struct ScoreRequest {          // scoring.ScoreRequest
+    AccountID account_id{};
+    std::string player_id;
+    int64_t amount = 0;
+    std::string tx_type = "bet";   // "deposit" | "withdraw" | "bet"
+    std::string currency, game_id, ip, device_id, fingerprint, user_agent, session_id;
+    int64_t timestamp = 0;         // unix seconds; 0 = now
+};
+
+struct ScoreResponse {         // scoring.ScoreResponse
+    int score = 0;
+    std::string action;
+    std::vector<std::string> reason_codes;
+    int rule_score = 0;
+    double ml_score = 0;
+    int64_t response_time_ms = 0;
+};
+
+inline igs_config DefaultConfig() {
+    igs_config c;
+    igs_default_config(&c);
+    return c;
+}
+
+// account uuid -> dense index of this shard (unknown accounts map beyond every table: the engine then
+// scores them with zero batch / velocity features, as the reference does on a feature-store error)
+class PlayerDirectory {
+public:
+    uint32_t Add(const AccountID& id) { return idx_.emplace(id, (uint32_t)idx_.size()).first->second; }
+    uint32_t Get(const AccountID& id) const {
+        auto it = idx_.find(id);
+        return it == idx_.end() ? 0xFFFFFFFEu : it->second;
+    }
+    size_t size() const { return idx_.size(); }
+    static uint32_t ShardOf(const AccountID& id, uint32_t n_shards) {
+        uint64_t lo = 0, hi = 0;
+        for (int i = 0; i < 8; ++i) { lo |= (uint64_t)id[15 - i] << (8 * i); hi |= (uint64_t)id[7 - i] << (8 * i); }
+        return igs_shard_of(lo, hi, n_shards);
+    }
+private:
+    std::map<AccountID, uint32_t> idx_;
+};
+
+using IPIntelligence = std::function<std::tuple<bool, bool, bool>(const std::string& ip)>;           // vpn, proxy, tor
+using Blacklist = std::function<bool(const std::string& device, const std::string& fp, const std::string& ip)>;
+using Uniques = std::function<std::pair<int, int>(const AccountID&)>;                                // devices, ips (24h)
+
+template <typename T>
+class Pinned {                  // host staging from igs_alloc_pinned
+public:
+    ~Pinned() { igs_free_pinned(p_); }
+    T* reserve(size_t n) {
+        if (n > cap_) {
+            igs_free_pinned(p_);
+            p_ = static_cast<T*>(igs_alloc_pinned((n ? n : 1) * sizeof(T)));
+            if (!p_) throw Error(IGS_ERR_NOMEM, "igs_alloc_pinned failed");
+            cap_ = n;
+        }
+        return p_;
+    }
+private:
+    T* p_ = nullptr;
+    size_t cap_ = 0;
+};
+
+class ScoringEngine {
+public:
+    // NewScoringEngine(features, model, ipIntel, blacklist, logger, config): the feature store and the
+    // model live on the device (Load*), ipIntel / blacklist / uniques may be empty like the reference's nil.
+    ScoringEngine(int device, const igs_config& config, PlayerDirectory* directory, IPIntelligence ip_intel = nullptr,
+                  Blacklist blacklist = nullptr, Uniques uniques = nullptr)
+        : cfg_(config), dir_(directory), ip_(std::move(ip_intel)), bl_(std::move(blacklist)), uq_(std::move(uniques)) {
+        const int rc = igs_engine_create(device, &e_);
+        if (rc != IGS_OK) throw Error(rc, igs_last_error(nullptr));
+    }
+    ~ScoringEngine() { igs_engine_destroy(e_); }
+    ScoringEngine(const ScoringEngine&) = delete;
+    ScoringEngine& operator=(const ScoringEngine&) = delete;
+
+    igs_engine* handle() { return e_; }
+    void LoadGBDT(const igs_gbdt_desc& d) { check(igs_load_gbdt(e_, &d)); }
+    void LoadPlayers(const igs_player_row* rows, uint64_t n) { check(igs_load_players(e_, rows, n)); }
+    void LoadEvents(const igs_event_cols& ev, uint64_t n, uint32_t n_accounts) { check(igs_load_events(e_, &ev, n, n_accounts)); }
+
+    std::vector<igs_tx> Marshal(const std::vector<ScoreRequest>& reqs) const {
+        const int64_t now = std::chrono::duration_cast<std::chrono::seconds>(
+                                std::chrono::system_clock::now().time_since_epoch()).count();
+        std::vector<igs_tx> tx(reqs.size());
+        for (size_t i = 0; i < reqs.size(); ++i) {
+            const ScoreRequest& r = reqs[i];
+            igs_tx t{};
+            t.amount = r.amount;
+            t.account = dir_ ? dir_->Get(r.account_id) : 0xFFFFFFFEu;
+            t.ts = (uint32_t)(r.timestamp ? r.timestamp : now);
+            t.seq_limit = 0xFFFFFFFFu;
+            t.tx_type = r.tx_type == "bet" ? IGS_TX_BET : r.tx_type == "deposit" ? IGS_TX_DEPOSIT
+                      : r.tx_type == "withdraw" ? IGS_TX_WITHDRAW : IGS_TX_OTHER;
+            uint8_t bits = IGS_BIT_VALID;
+            if (ip_ && !r.ip.empty()) {                                   // engine.go:394-405
+                auto [vpn, proxy, tor] = ip_(r.ip);
+                bits |= (vpn ? IGS_BIT_VPN : 0) | (proxy ? IGS_BIT_PROXY : 0) | (tor ? IGS_BIT_TOR : 0);
+            }
+            if (bl_ && bl_(r.device_id, r.fingerprint, r.ip)) bits |= IGS_BIT_BLACKLISTED;   // :469-475
+            t.bits = bits;
+            if (uq_) {
+                auto [d, p] = uq_(r.account_id);
+                t.unique_devices_24h = (uint16_t)(d > 0xFFFF ? 0xFFFF : d);
+                t.unique_ips_24h = (uint16_t)(p > 0xFFFF ? 0xFFFF : p);
+            }
+            tx[i] = t;
+        }
+        return tx;
+    }
+
+    // rpc ScoreBatch (risk.proto:13): one C-ABI call per batch.
+    std::vector<ScoreResponse> ScoreBatch(const std::vector<ScoreRequest>& reqs) {
+        const auto t0 = std::chrono::steady_clock::now();
+        const std::vector<igs_tx> tx = Marshal(reqs);
+        const size_t n = tx.size();
+        igs_tx* h_tx = tx_.reserve(n);
+        igs_result* h_out = out_.reserve(n);
+        std::copy(tx.begin(), tx.end(), h_tx);
+        check(igs_score_batch(e_, &cfg_, h_tx, n, h_out, nullptr, nullptr));
+        const int64_t ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+        std::vector<ScoreResponse> res(n);
+        const char* names[IGS_NUM_REASONS];
+        for (size_t i = 0; i < n; ++i) {
+            ScoreResponse& r = res[i];
+            r.score = h_out[i].score;
+            r.action = igs_action_name(h_out[i].action);
+            const int k = igs_reason_codes(h_out[i].flags, names);
+            r.reason_codes.assign(names, names + k);
+            r.rule_score = igs_rule_score_from_flags(&cfg_, h_out[i].flags);
+            r.ml_score = h_out[i].ml_score;
+            r.response_time_ms = ms;
+        }
+        return res;
+    }
+    ScoreResponse Score(const ScoreRequest& req) { return ScoreBatch({req})[0]; }
+
+    std::pair<int, int> GetThresholds() const { return {cfg_.block_threshold, cfg_.review_threshold}; }
+    void SetThresholds(int block, int review) { cfg_.block_threshold = block; cfg_.review_threshold = review; }
+
+    std::string ScoreWithExplanation(const ScoreRequest& req) {
+        const ScoreResponse r = Score(req);
+        char buf[256];
+        std::snprintf(buf, sizeof(buf), "\nFraud Score Analysis\n====================\nFinal Score: %d/100\nAction: %s\n"
+                      "Response Time: %lldms\n\nRule Contribution: %d\nML Contribution: %.2f (%.2f * 100)\n\nTriggered Rules:\n",
+                      r.score, r.action.c_str(), (long long)r.response_time_ms, r.rule_score, r.ml_score, r.ml_score);
+        std::string s = buf;
+        static const char* order[IGS_NUM_REASONS] = {"HIGH_VELOCITY", "NEW_ACCOUNT_LARGE_TX", "IP_COUNTRY_MISMATCH",
+            "MULTIPLE_DEVICES", "SUSPICIOUS_PATTERN", "VPN_DETECTED", "KNOWN_FRAUDSTER", "RAPID_DEPOSIT_WITHDRAW",
+            "BONUS_ABUSE", "ML_HIGH_RISK"};
+        for (const std::string& code : r.reason_codes)
+            for (int b = 0; b < IGS_NUM_REASONS; ++b)
+                if (code == order[b]) s += "  - " + code + " (+" + std::to_string(cfg_.reason_weight[b]) + ")\n";
+        return s;
+    }
+
+private:
+    void check(int rc) const {
+        if (rc != IGS_OK) throw Error(rc, igs_last_error(e_));
+    }
+    igs_engine* e_ = nullptr;
+    igs_config cfg_;
+    PlayerDirectory* dir_;
+    IPIntelligence ip_;
+    Blacklist bl_;
+    Uniques uq_;
+    Pinned<igs_tx> tx_;
+    Pinned<igs_result> out_;
+};
+
+}  // namespace igs

@@ -1,0 +1,132 @@
+// C++ host mirror (include/igs.hpp) driven the way a test of scoring.ScoringEngine would read, checked
+// against the oracle's per-request pipeline (the oracle is linked here as the checker only).
+//   usage: test_scoring_engine            -> needs a B200; exit 0 on success
+//          test_scoring_engine --compile-only-check  -> returns 0 without touching the GPU
+#include <cinttypes>
+#include <cstdio>
+#include <cstring>
+#include <random>
+
+#include "igs.hpp"
+#include "../../oracle/igs_oracle.h"
+
+#define REQUIRE(c)                                                         \
+    do {                                                                   \
+        if (!(c)) { std::fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #c); return 1; } \
+    } while (0)
+
+static igs::AccountID make_id(uint32_t k) {
+    igs::AccountID id{};
+    std::memcpy(id.data() + 12, &k, 4);
+    id[0] = 0xAB;
+    return id;
+}
+
+int main(int argc, char** argv) {
+    if (argc > 1 && std::strcmp(argv[1], "--compile-only-check") == 0) {
+        igs_config c = igs::DefaultConfig();
+        REQUIRE(c.block_threshold == 80 && c.review_threshold == 50);
+        return 0;
+    }
+    const int n_players = 200, n_events = 6000;
+    const int64_t now = 1700003600;
+    std::mt19937_64 rng(7);
+    std::vector<igs_player_row> players(n_players);
+    igs::PlayerDirectory dir;
+    for (int i = 0; i < n_players; ++i) {
+        igs_player_row p{};
+        p.account_created_at = now - (int64_t)(rng() % 900) * 86400 - (int64_t)(rng() % 86400);
+        p.total_deposits = (int64_t)(rng() % 200000);
+        p.total_withdrawals = (int64_t)(rng() % 250000);
+        p.deposit_count = (int32_t)(rng() % 10);
+        p.withdraw_count = (int32_t)(rng() % 5);
+        p.bet_count = (int32_t)(rng() % 1000);
+        p.win_count = p.bet_count / 2;
+        p.avg_bet_size = 10.0 + (double)(rng() % 5000) / 7.0;
+        p.bonus_claim_count = (int32_t)(rng() % 7);
+        p.bonus_wager_complete = (double)(rng() % 100) / 100.0;
+        players[i] = p;
+        dir.Add(make_id(i));
+    }
+    std::vector<uint32_t> ea(n_events), et(n_events);
+    std::vector<int64_t> em(n_events);
+    std::vector<uint8_t> ey(n_events);
+    for (int i = 0; i < n_events; ++i) {
+        ea[i] = (uint32_t)(rng() % 40);                 // hot accounts: velocity rules fire
+        // accounts 0..9 burst inside the last minute (HIGH_VELOCITY), the rest spread over the hour
+        et[i] = (uint32_t)(now - 1 - (int64_t)(rng() % (ea[i] < 10 ? 60 : 3600)));
+        em[i] = (int64_t)(100 + rng() % 100000);
+        ey[i] = (uint8_t)(rng() % 3);
+    }
+    igs_event_cols ev{ea.data(), et.data(), em.data(), ey.data()};
+
+    igs_config cfg = igs::DefaultConfig();               // model_kind = mock: the only model the reference can run
+    igs::ScoringEngine engine(
+        0, cfg, &dir, [](const std::string& ip) { return std::make_tuple(ip == "10.1.1.1", false, ip == "tor-exit"); },
+        [](const std::string& dev, const std::string&, const std::string&) { return dev == "stolen-phone"; },
+        [](const igs::AccountID& id) { return std::make_pair(id[12] % 7, id[12] % 9); });
+    engine.LoadPlayers(players.data(), players.size());
+    engine.LoadEvents(ev, n_events, n_players);
+
+    std::vector<igs::ScoreRequest> reqs;
+    const char* types[3] = {"bet", "deposit", "withdraw"};
+    for (int i = 0; i < 3000; ++i) {
+        igs::ScoreRequest r;
+        r.account_id = make_id((uint32_t)(rng() % (n_players + 5)));     // a few unknown accounts
+        r.amount = (int64_t)(rng() % 300000);
+        r.tx_type = types[rng() % 3];
+        r.ip = (rng() % 20 == 0) ? "10.1.1.1" : (rng() % 50 == 0) ? "tor-exit" : "8.8.8.8";
+        r.device_id = (rng() % 100 == 0) ? "stolen-phone" : "phone";
+        r.timestamp = now;
+        reqs.push_back(r);
+    }
+    const std::vector<igs::ScoreResponse> res = engine.ScoreBatch(reqs);
+    REQUIRE(res.size() == reqs.size());
+
+    // the same batch through the oracle
+    const std::vector<igs_tx> tx = engine.Marshal(reqs);
+    std::vector<igs_result> want(tx.size());
+    orc_score_batch(&cfg, nullptr, players.data(), players.size(), &ev, n_events, tx.data(), tx.size(), want.data(), nullptr,
+                    nullptr);
+    uint32_t seen = 0;
+    for (size_t i = 0; i < res.size(); ++i) {
+        REQUIRE(res[i].score == want[i].score);
+        REQUIRE(res[i].action == igs_action_name(want[i].action));
+        REQUIRE((float)res[i].ml_score == want[i].ml_score);
+        REQUIRE(res[i].rule_score == igs_rule_score_from_flags(&cfg, want[i].flags));
+        const char* names[IGS_NUM_REASONS];
+        const int k = igs_reason_codes(want[i].flags, names);
+        REQUIRE((int)res[i].reason_codes.size() == k);
+        for (int j = 0; j < k; ++j) REQUIRE(res[i].reason_codes[j] == names[j]);
+        seen |= want[i].flags;
+    }
+    REQUIRE(seen & IGS_R_HIGH_VELOCITY);
+    REQUIRE(seen & IGS_R_VPN_DETECTED);
+    REQUIRE(seen & IGS_R_KNOWN_FRAUDSTER);
+    REQUIRE(seen & IGS_R_ML_HIGH_RISK);
+
+    // Score == ScoreBatch of one; SetThresholds moves the action, not the score (engine.go:498-504)
+    const igs::ScoreResponse one = engine.Score(reqs[0]);
+    REQUIRE(one.score == res[0].score && one.action == res[0].action);
+    REQUIRE(engine.GetThresholds() == std::make_pair(80, 50));
+    engine.SetThresholds(101, 101);
+    for (const auto& r : engine.ScoreBatch(reqs)) REQUIRE(r.action == "approve");
+    engine.SetThresholds(0, 0);
+    for (const auto& r : engine.ScoreBatch(reqs)) REQUIRE(r.action == "block");
+    engine.SetThresholds(80, 50);
+    REQUIRE(engine.ScoreWithExplanation(reqs[0]).find("Final Score:") != std::string::npos);
+
+    // errors surface as exceptions with the library's message (no fallback)
+    bool threw = false;
+    try {
+        igs_config g = cfg;
+        g.model_kind = IGS_MODEL_GBDT;                   // no ensemble loaded
+        igs::ScoringEngine e2(0, g, &dir);
+        e2.ScoreBatch(reqs);
+    } catch (const igs::Error& e) {
+        threw = e.status == IGS_ERR_STATE;
+    }
+    REQUIRE(threw);
+    std::printf("test_scoring_engine: %zu requests, flags seen 0x%x: ok\n", res.size(), seen);
+    return 0;
+}
