@@ -14,10 +14,14 @@
 //     warps 4-7          epilogue: tcgen05.ld 32x32b.x32 (SASS LDTM) -> +bias, ReLU, bf16 -> global
 //   Synchronisation is mbarrier-only inside the tile loop (full/empty per smem stage, full/empty per
 //   TMEM accumulator).
-// k_ltv_head — layer 4 (1024 -> 1) as one warp per player + the fp64 epilogue (churn, adjusted LTV,
-//   segment, survival, next-best-action, confidence; prediction/ltv.go:228-382).
+//   Layer 3 runs the kHead variant: a CTA owns whole 128-row tiles and walks their 4 column tiles in order;
+//   the epilogue thread that owns a row accumulates layer 4 (1024 -> 1) on the bf16-rounded activations in a
+//   fixed order and finishes with the fp64 epilogue (churn, adjusted LTV, segment, survival,
+//   next-best-action, confidence; prediction/ltv.go:228-382) — the layer-3 activations never reach HBM.
 #include <cuda.h>
 #include <cuda_bf16.h>
+
+#include <string.h>
 
 #include <algorithm>
 #include <vector>
@@ -85,156 +89,7 @@ __device__ __forceinline__ void tc_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[3
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------------
-// GEMM layer
-// ------------------------------------------------------------------------------------------------
-constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 4;
-constexpr int kGemmThreads = 256;
-constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
-constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
-constexpr uint32_t kStageBytes = kABytes + kBBytes;
-constexpr uint32_t kTmemCols = 512;           // 2 accumulators x 256 fp32 columns
-constexpr uint32_t kGemmSmem = STAGES * kStageBytes + 1024 /* alignment slack */ + 256 /* barriers */;
-// instruction descriptor, kind::f16: D=F32 (bit 4), A=BF16 (bit 7), B=BF16 (bit 10), both K-major,
-// N>>3 at bit 17, M>>4 at bit 24
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-// smem matrix descriptor (K-major, SWIZZLE_128B): LBO = 1 (unused for swizzled K-major), SBO = 1024 B
-// between 8-row groups, descriptor version 1 (sm_100), layout type 2
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
-    const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
-    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
-    return ((uint64_t)hi << 32) | lo;
-}
-
-struct GemmParams {
-    CUtensorMap tm_a;     // A  [M, K] bf16, K contiguous; box 64 x 128
-    CUtensorMap tm_b;     // W  [N, K] bf16, K contiguous; box 64 x 256
-    const float* bias;    // [N]
-    uint16_t* out;        // [M, N] bf16
-    uint32_t M, N, K;
-};
-
-__global__ void __launch_bounds__(kGemmThreads, 1)
-k_mlp_gemm(const __grid_constant__ GemmParams p) {
-    extern __shared__ uint8_t smem_raw[];
-    // 1024-byte alignment for the 128B swizzle atoms
-    const uint32_t raw = smem_u32(smem_raw);
-    const uint32_t base = (raw + 1023u) & ~1023u;
-    uint8_t* smem = smem_raw + (base - raw);
-    const uint32_t a_base = base;
-    const uint32_t b_base = base + STAGES * kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
-    const uint32_t bar_full = smem_u32(bars);             // [STAGES]
-    const uint32_t bar_empty = bar_full + 8 * STAGES;     // [STAGES]
-    const uint32_t bar_tfull = bar_empty + 8 * STAGES;    // [2]
-    const uint32_t bar_tempty = bar_tfull + 16;           // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-
-    const uint32_t m_blks = (p.M + BM - 1) / BM, n_blks = p.N / BN, k_blks = p.K / BK;
-    const uint32_t n_tiles = m_blks * n_blks;
-
-    if (warp == 0) {
-        if (lane == 0) {
-            uint32_t s = 0, ph = 0;
-            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const int m0 = (int)(t / n_blks) * BM, n0 = (int)(t % n_blks) * BN;
-                for (uint32_t kb = 0; kb < k_blks; ++kb) {
-                    mbar_wait(bar_empty + 8 * s, ph ^ 1);
-                    mbar_expect_tx(bar_full + 8 * s, kStageBytes);
-                    tma_load_2d(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, bar_full + 8 * s);
-                    tma_load_2d(b_base + s * kBBytes, &p.tm_b, (int)(kb * BK), n0, bar_full + 8 * s);
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            uint32_t s = 0, ph = 0, it = 0;
-            for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-                const uint32_t acc = it & 1;
-                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue drained this accumulator
-                tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * BN;
-                for (uint32_t kb = 0; kb < k_blks; ++kb) {
-                    mbar_wait(bar_full + 8 * s, ph);
-                    tc_fence_after();
-                    const uint64_t adesc = make_desc(a_base + s * kABytes);
-                    const uint64_t bdesc = make_desc(b_base + s * kBBytes);
-#pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k)
-                        // +32 bytes (2 x 16 B units) per K step inside the 128B swizzle atom
-                        tc_mma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
-                                   (kb | (uint32_t)k) != 0 ? 1u : 0u);
-                    tc_commit(bar_empty + 8 * s);                          // frees the smem stage when the MMAs retire
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
-                }
-                tc_commit(bar_tfull + 8 * acc);                            // accumulator complete
-            }
-        }
-    } else if (warp >= 4) {
-        const int q = warp - 4;                                            // TMEM lane quarter of this warp
-        uint32_t it = 0;
-        for (uint32_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-            const uint32_t acc = it & 1;
-            const uint32_t m0 = (t / n_blks) * BM, n0 = (t % n_blks) * BN;
-            mbar_wait(bar_tfull + 8 * acc, (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t row = m0 + q * 32 + lane;
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-            uint16_t* orow = p.out + (size_t)row * p.N + n0;
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t r[32];
-                tc_ld_32x32b_x32(taddr + c, r);
-                tc_wait_ld();
-                uint32_t packed[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    float v0 = __fadd_rn(__uint_as_float(r[2 * j]), __ldg(p.bias + n0 + c + 2 * j));
-                    float v1 = __fadd_rn(__uint_as_float(r[2 * j + 1]), __ldg(p.bias + n0 + c + 2 * j + 1));
-                    v0 = v0 > 0.f ? v0 : 0.f;
-                    v1 = v1 > 0.f ? v1 : 0.f;
-                    const __nv_bfloat162 b2 = __floats2bfloat162_rn(v0, v1);   // .x (low half) = v0
-                    packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
-                }
-                if (row < p.M) {
-                    uint4* dst = reinterpret_cast<uint4*>(orow + c);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 2) {
-        tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// layer 4 + fp64 epilogue, one warp per player
+// fp64 epilogue helpers (prediction/ltv.go)
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float bf16_bits_to_f32(uint32_t b) { return __uint_as_float(b << 16); }
 
@@ -299,41 +154,200 @@ __device__ __forceinline__ void ltv_epilogue(const igs_ltv_row& f, double ltv, i
     for (int i = 0; i < 6; ++i) out->pad[i] = 0;
 }
 
-constexpr int kHeadThreads = 256;
+// ------------------------------------------------------------------------------------------------
+// GEMM layer
+// ------------------------------------------------------------------------------------------------
+constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 4;
+constexpr int kNonEpiWarps = 4;   // TMA producer, MMA issuer, TMEM allocator, spare
+constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
+constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
+constexpr uint32_t kStageBytes = kABytes + kBBytes;
+constexpr uint32_t kTmemCols = 512;           // 2 accumulators x 256 fp32 columns
+constexpr uint32_t kGemmSmem = STAGES * kStageBytes + 1024 /* alignment slack */ + 256 /* barriers */ +
+                               4096 /* w4 as fp32 */ + 4096 /* bias */;
+// instruction descriptor, kind::f16: D=F32 (bit 4), A=BF16 (bit 7), B=BF16 (bit 10), both K-major,
+// N>>3 at bit 17, M>>4 at bit 24
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// smem matrix descriptor (K-major, SWIZZLE_128B): LBO = 1 (unused for swizzled K-major), SBO = 1024 B
+// between 8-row groups, descriptor version 1 (sm_100), layout type 2
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
+    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    return ((uint64_t)hi << 32) | lo;
+}
 
-__global__ void __launch_bounds__(kHeadThreads)
-k_ltv_head(const uint16_t* __restrict__ h3, const uint16_t* __restrict__ w4, float b4,
-           const igs_ltv_row* __restrict__ rows, unsigned long long n, igs_ltv_result* __restrict__ out,
-           float* __restrict__ raw) {
-    __shared__ float w[IGS_MLP_HIDDEN];
-    for (int i = threadIdx.x; i < IGS_MLP_HIDDEN; i += kHeadThreads) w[i] = bf16_bits_to_f32(__ldg(w4 + i));
+struct GemmParams {
+    CUtensorMap tm_a;     // A  [M, K] bf16, K contiguous; box 64 x 128
+    CUtensorMap tm_b;     // W  [N, K] bf16, K contiguous; box 64 x 256
+    const float* bias;    // [N]
+    uint16_t* out;        // [M, N] bf16 (null when the head is fused and nobody wants the activations)
+    uint32_t M, N, K;
+    // fused head (layer 3 only): layer 4 dot product + fp64 epilogue in the GEMM epilogue
+    const uint16_t* w4;   // [N] bf16, null = no head
+    float b4;
+    const igs_ltv_row* rows;
+    igs_ltv_result* res;
+    float* raw;           // optional fp32 model output
+};
+
+// kHead = false: work items are 128 x 256 output tiles, round-robin over the CTAs.
+// kHead = true : work items are 128-row tiles; a CTA walks the N/256 column tiles of its row tile in order, so
+//               the thread that owns a row accumulates that row's layer-4 dot product in a fixed order and
+//               finishes with the fp64 epilogue — the layer-3 activations never go to HBM.
+// kEpiWarps = 4: one epilogue warp per TMEM lane quarter, all 256 columns each.
+// kEpiWarps = 8: two per quarter, 128 columns each — for the K=256 layer, whose MMAs per tile are too short
+//               to hide a 4-warp epilogue.
+template <bool kHead, int kEpiWarps>
+__global__ void __launch_bounds__((kNonEpiWarps + kEpiWarps) * 32, 1)
+k_mlp_gemm(const __grid_constant__ GemmParams p) {
+    constexpr int kGemmThreads = (kNonEpiWarps + kEpiWarps) * 32;
+    static_assert(!kHead || kEpiWarps == 4, "the fused head keeps one thread per row");
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment for the 128B swizzle atoms
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t a_base = base;
+    const uint32_t b_base = base + STAGES * kABytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+    const uint32_t bar_full = smem_u32(bars);             // [STAGES]
+    const uint32_t bar_empty = bar_full + 8 * STAGES;     // [STAGES]
+    const uint32_t bar_tfull = bar_empty + 8 * STAGES;    // [2]
+    const uint32_t bar_tempty = bar_tfull + 16;           // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    float* w4s = reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256);
+    float* bias_s = w4s + IGS_MLP_HIDDEN;
+    if (kHead)
+        for (int i = threadIdx.x; i < IGS_MLP_HIDDEN; i += kGemmThreads) w4s[i] = bf16_bits_to_f32(__ldg(p.w4 + i));
+    for (uint32_t i = threadIdx.x; i < p.N; i += kGemmThreads) bias_s[i] = __ldg(p.bias + i);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, kEpiWarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const unsigned long long warp_global = ((unsigned long long)blockIdx.x * kHeadThreads + threadIdx.x) >> 5;
-    const unsigned long long n_warps = ((unsigned long long)gridDim.x * kHeadThreads) >> 5;
-    for (unsigned long long row = warp_global; row < n; row += n_warps) {
-        const uint4* src = reinterpret_cast<const uint4*>(h3 + row * IGS_MLP_HIDDEN);
-        float acc = 0.f;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const uint4 v = __ldg(src + c * 32 + lane);
-            const int k0 = (c * 32 + lane) * 8;
-            const uint32_t u[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                acc = __fmaf_rn(bf16_bits_to_f32(u[j] & 0xFFFFu), w[k0 + 2 * j], acc);
-                acc = __fmaf_rn(bf16_bits_to_f32(u[j] >> 16), w[k0 + 2 * j + 1], acc);
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const uint32_t m_blks = (p.M + BM - 1) / BM, n_blks = p.N / BN, k_blks = p.K / BK;
+    const uint32_t n_tiles = m_blks * n_blks;
+    // i-th work tile of this CTA -> global tile index (m-major: tile / n_blks = row tile)
+    const uint32_t my_tiles = kHead ? (m_blks > blockIdx.x ? (m_blks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0) * n_blks
+                                    : (n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0);
+    auto tile_of = [&](uint32_t i) -> uint32_t {
+        return kHead ? (blockIdx.x + (i / n_blks) * gridDim.x) * n_blks + i % n_blks : blockIdx.x + i * gridDim.x;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (uint32_t i = 0; i < my_tiles; ++i) {
+                const uint32_t t = tile_of(i);
+                const int m0 = (int)(t / n_blks) * BM, n0 = (int)(t % n_blks) * BN;
+                for (uint32_t kb = 0; kb < k_blks; ++kb) {
+                    mbar_wait(bar_empty + 8 * s, ph ^ 1);
+                    mbar_expect_tx(bar_full + 8 * s, kStageBytes);
+                    tma_load_2d(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, bar_full + 8 * s);
+                    tma_load_2d(b_base + s * kBBytes, &p.tm_b, (int)(kb * BK), n0, bar_full + 8 * s);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
             }
         }
-        for (int o = 16; o; o >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, o));
+    } else if (warp == 1) {
         if (lane == 0) {
-            const float y = __fadd_rn(acc, b4);
-            if (raw) raw[row] = y;
-            igs_ltv_row f = rows[row];
-            igs_ltv_result r;
-            ltv_epilogue(f, (double)y, &r);
-            out[row] = r;
+            uint32_t s = 0, ph = 0, it = 0;
+            for (; it < my_tiles; ++it) {
+                const uint32_t acc = it & 1;
+                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (uint32_t kb = 0; kb < k_blks; ++kb) {
+                    mbar_wait(bar_full + 8 * s, ph);
+                    tc_fence_after();
+                    const uint64_t adesc = make_desc(a_base + s * kABytes);
+                    const uint64_t bdesc = make_desc(b_base + s * kBBytes);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        // +32 bytes (2 x 16 B units) per K step inside the 128B swizzle atom
+                        tc_mma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
+                                   (kb | (uint32_t)k) != 0 ? 1u : 0u);
+                    tc_commit(bar_empty + 8 * s);                          // frees the smem stage when the MMAs retire
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+                tc_commit(bar_tfull + 8 * acc);                            // accumulator complete
+            }
         }
+    } else if (warp >= 4) {
+        const int q = (warp - kNonEpiWarps) & 3;                           // TMEM lane quarter of this warp (= warp % 4)
+        constexpr int kCols = BN / (kEpiWarps / 4);                        // columns handled by this warp
+        const int c0 = ((warp - kNonEpiWarps) >> 2) * kCols;
+        float dot = 0.f;                                                   // layer-4 partial of this thread's row
+        for (uint32_t it = 0; it < my_tiles; ++it) {
+            const uint32_t t = tile_of(it);
+            const uint32_t acc = it & 1;
+            const uint32_t m0 = (t / n_blks) * BM, n0 = (t % n_blks) * BN;
+            mbar_wait(bar_tfull + 8 * acc, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t row = m0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+            uint16_t* orow = p.out ? p.out + (size_t)row * p.N + n0 : nullptr;
+#pragma unroll 1
+            for (int c = c0; c < c0 + kCols; c += 32) {
+                uint32_t r[32];
+                tc_ld_32x32b_x32(taddr + c, r);
+                tc_wait_ld();
+                uint32_t packed[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 bb = *reinterpret_cast<const float2*>(bias_s + n0 + c + 2 * j);   // smem broadcast
+                    float v0 = __fadd_rn(__uint_as_float(r[2 * j]), bb.x);
+                    float v1 = __fadd_rn(__uint_as_float(r[2 * j + 1]), bb.y);
+                    v0 = v0 > 0.f ? v0 : 0.f;
+                    v1 = v1 > 0.f ? v1 : 0.f;
+                    const __nv_bfloat162 b2 = __floats2bfloat162_rn(v0, v1);   // .x (low half) = v0
+                    packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
+                    if (kHead) {                                               // layer 4 on the bf16-rounded activations
+                        dot = __fmaf_rn(bf16_bits_to_f32(packed[j] & 0xFFFFu), w4s[n0 + c + 2 * j], dot);
+                        dot = __fmaf_rn(bf16_bits_to_f32(packed[j] >> 16), w4s[n0 + c + 2 * j + 1], dot);
+                    }
+                }
+                if (orow && row < p.M) {
+                    uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+            if (kHead && (t % n_blks) == n_blks - 1) {                        // row complete: model output + epilogue
+                if (row < p.M) {
+                    const float y = __fadd_rn(dot, p.b4);
+                    if (p.raw) p.raw[row] = y;
+                    const igs_ltv_row f = p.rows[row];
+                    igs_ltv_result res;
+                    ltv_epilogue(f, (double)y, &res);
+                    p.res[row] = res;
+                }
+                dot = 0.f;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
     }
 }
 
@@ -384,18 +398,32 @@ int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, ui
     return IGS_OK;
 }
 
+struct HeadArgs {
+    const uint16_t* w4 = nullptr;
+    float b4 = 0.f;
+    const igs_ltv_row* rows = nullptr;
+    igs_ltv_result* res = nullptr;
+    float* raw = nullptr;
+};
+
 int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float* bias, uint16_t* out, uint32_t M,
-                uint32_t N, uint32_t K, cudaStream_t st) {
+                uint32_t N, uint32_t K, cudaStream_t st, const HeadArgs* head = nullptr) {
     GemmParams p;
+    memset(&p, 0, sizeof(p));
     int rc = make_tmap(e, &p.tm_a, a, M, K, BM);
     if (rc != IGS_OK) return rc;
     rc = make_tmap(e, &p.tm_b, w, N, K, BN);
     if (rc != IGS_OK) return rc;
     p.bias = bias; p.out = out; p.M = M; p.N = N; p.K = K;
-    IGS_CUDA(e, cudaFuncSetAttribute(k_mlp_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    const uint32_t tiles = ((M + BM - 1) / BM) * (N / BN);
-    const uint32_t grid = tiles < (uint32_t)e->sm_count ? tiles : (uint32_t)e->sm_count;
-    k_mlp_gemm<<<grid, kGemmThreads, kGemmSmem, st>>>(p);
+    if (head) { p.w4 = head->w4; p.b4 = head->b4; p.rows = head->rows; p.res = head->res; p.raw = head->raw; }
+    // the short-K layer gets 8 epilogue warps; long-K layers hide a 4-warp epilogue behind their MMAs
+    const bool wide_epi = !head && K <= 256;
+    auto kern = head ? k_mlp_gemm<true, 4> : wide_epi ? k_mlp_gemm<false, 8> : k_mlp_gemm<false, 4>;
+    const int threads = (kNonEpiWarps + (wide_epi ? 8 : 4)) * 32;
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+    const uint32_t items = head ? (M + BM - 1) / BM : ((M + BM - 1) / BM) * (N / BN);
+    const uint32_t grid = items < (uint32_t)e->sm_count ? items : (uint32_t)e->sm_count;
+    kern<<<grid, threads, kGemmSmem, st>>>(p);
     IGS_CUDA(e, cudaGetLastError());
     return IGS_OK;
 }
@@ -473,15 +501,24 @@ int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows
         return IGS_ERR_STATE;
     }
     MlpDevice* m = (MlpDevice*)e->d_mlp;
+    const uint32_t H = IGS_MLP_HIDDEN;
+    for (igs_buf& b : m->act) {
+        int rc = igs_reserve(e, &b, (size_t)kLtvChunkRows * H * 2);
+        if (rc != IGS_OK) return rc;
+    }
+    uint16_t* a0 = (uint16_t*)m->act[0].p;
+    uint16_t* a1 = (uint16_t*)m->act[1].p;
     for (uint64_t off = 0; off < n; off += kLtvChunkRows) {
         const uint32_t cnt = (uint32_t)(n - off < kLtvChunkRows ? n - off : kLtvChunkRows);
-        uint16_t* h3 = nullptr;
-        int rc = run_hidden(e, m, d_x + off * IGS_MLP_IN, cnt, 3, &h3, st);
+        int rc = launch_gemm(e, d_x + off * IGS_MLP_IN, m->w1, m->b1, a0, cnt, H, IGS_MLP_IN, st);
         if (rc != IGS_OK) return rc;
-        const unsigned grid = (unsigned)std::min<uint64_t>((cnt + 7) / 8, (uint64_t)e->sm_count * 8);
-        k_ltv_head<<<grid, kHeadThreads, 0, st>>>(h3, m->w4, m->b4, d_rows + off, cnt, d_out + off,
-                                                  d_ltv_raw ? d_ltv_raw + off : nullptr);
-        IGS_CUDA(e, cudaGetLastError());
+        rc = launch_gemm(e, a0, m->w2, m->b2, a1, cnt, H, H, st);
+        if (rc != IGS_OK) return rc;
+        HeadArgs head;                       // layer 3 + layer 4 + fp64 epilogue in one kernel
+        head.w4 = m->w4; head.b4 = m->b4; head.rows = d_rows + off; head.res = d_out + off;
+        head.raw = d_ltv_raw ? d_ltv_raw + off : nullptr;
+        rc = launch_gemm(e, a1, m->w3, m->b3, nullptr, cnt, H, H, st, &head);
+        if (rc != IGS_OK) return rc;
     }
     return IGS_OK;
 }
