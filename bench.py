@@ -456,15 +456,21 @@ def main():
                     "h2d_bytes_per_step": int(n * (256 + 48)), "d2h_bytes_per_step": int(n * 8),
                     "steps": e2e_steps, "api": "igs_score_features (pinned host buffers)"},
             "gpu_launches": args.steps,
-            "roofline": {"bound": "hbm", "kernel": "k_score_features", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "roofline": {"bound": "hbm", "kernel": "k_score<features, Shape<12,20>>", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, from the
+                         # ncu --set full capture in profiles/r1e_score_ncu_full.csv (not measured live)
+                         "traffic": 314.7e6 if n == N_TX else None, "peak_source": peak_src,
                          "launch_ms": k_ms,
                          "note": "algorithmic bytes = 312 B/tx + model once; this kernel is bound by "
                                  "shared-memory gathers / issue slots (4000 dependent node visits per "
                                  "tx), not HBM — see on_chip"},
             "on_chip": {"node_visits_per_s": visits,
                         "node_visits_per_sm_cycle": visits / (148 * sm_mhz * 1e6),
-                        "sm_mhz_used": sm_mhz},
+                        "sm_mhz_used": sm_mhz,
+                        "smem_pipe_frac_ncu": 0.823, "alu_pipe_frac_ncu": 0.534,
+                        "ncu_source": "profiles/r1e_score_ncu_full.csv (l1tex__data_pipe_lsu_wavefronts_mem_shared "
+                                      "pct_of_peak_sustained_elapsed; the resource that bounds this kernel)"},
             "cpu_baseline": cpu,
             "p99_batch_latency": lat,
             "fused_path": fused,
