@@ -14,9 +14,14 @@
  *
  * Threading: one engine per device.  Calls on different *slots* of one engine may be issued
  * from different host threads concurrently; calls on the same slot must be serialised by the
- * caller.  Configuration (weights / thresholds) is passed by value with every call, so there is
- * no shared mutable config (the reference has a latent race there: scoring/engine.go:304-306
- * vs :498-504).
+ * caller (the synchronous host-buffer calls all use slot 0).  The igs_load_* calls replace device
+ * state: like ONNXModel.Close under its write lock (ml/onnx_model.go:349), they must not run while
+ * a scoring call on the same engine is in flight.  igs_partition_tx_device keeps its counters in
+ * one per-engine scratch buffer: issue one partition at a time per engine (or order them on one
+ * stream).  igs_last_error returns the engine's single message buffer; read it on the thread
+ * that saw the failing status.  Configuration (weights / thresholds) is passed by value with
+ * every call, so there is no shared mutable config (the reference has a latent race there:
+ * scoring/engine.go:304-306 vs :498-504).
  *
  * There is NO CPU fallback behind this ABI: without a CUDA device igs_engine_create() fails.
  */
