@@ -158,6 +158,11 @@ class Engine:
         c = ev.cols()
         self._check(self._lib.igs_load_events(self._h, C.byref(c), len(ev), n_accounts))
 
+    def append_events(self, ev: Events) -> None:
+        """UpdateFeatures for a batch of completed transactions (scoring/engine.go:486-488)."""
+        c = ev.cols()
+        self._check(self._lib.igs_append_events(self._h, C.byref(c), len(ev)))
+
     # -- path A -------------------------------------------------------------------------------
     def score_features(self, cfg: abi.Config, features: np.ndarray, rows: np.ndarray,
                        want_leaves: bool = False, n_trees: int | None = None):
@@ -232,4 +237,12 @@ class Engine:
         self._check(self._lib.igs_ltv_hidden_device(self._h, d_x, n, layer, d_hidden, stream))
 
 
-from . import scoring, sharding  # noqa: E402  (reference-facing mirror: ScoringEngine / ScoreRequest / ScoreResponse)
+from . import scoring, sharding  # noqa: E402  (reference-facing mirror + shard bookkeeping)
+
+
+def __getattr__(name):
+    # grpc / protobuf are only needed by the service shim: import it on first use
+    if name == "grpc_service":
+        import importlib
+        return importlib.import_module(__name__ + ".grpc_service")
+    raise AttributeError(name)

@@ -131,7 +131,7 @@ assert C.sizeof(Config) == 104
 EXPORTS = [
     "igs_default_config", "igs_engine_create", "igs_engine_destroy", "igs_last_error",
     "igs_alloc_pinned", "igs_free_pinned", "igs_load_gbdt", "igs_load_mlp", "igs_load_players",
-    "igs_load_events", "igs_score_features", "igs_score_features_async", "igs_wait",
+    "igs_load_events", "igs_append_events", "igs_score_features", "igs_score_features_async", "igs_wait",
     "igs_score_features_device", "igs_get_velocity", "igs_get_velocity_device", "igs_score_batch",
     "igs_score_batch_async", "igs_score_batch_device", "igs_partition_tx_device", "igs_partition_tx_static",
     "igs_ltv_batch", "igs_ltv_batch_device", "igs_ltv_hidden_device",
@@ -176,6 +176,7 @@ def load_library() -> C.CDLL:
     lib.igs_load_mlp.argtypes = [vp, C.POINTER(MlpDesc)]
     lib.igs_load_players.argtypes = [vp, vp, u64]
     lib.igs_load_events.argtypes = [vp, C.POINTER(EventCols), u64, C.c_uint32]
+    lib.igs_append_events.argtypes = [vp, C.POINTER(EventCols), u64]
     lib.igs_score_features.argtypes = [vp, C.POINTER(Config), vp, vp, u64, vp, vp]
     lib.igs_score_features_async.argtypes = [vp, i32, C.POINTER(Config), vp, vp, u64, vp]
     lib.igs_wait.argtypes = [vp, i32]

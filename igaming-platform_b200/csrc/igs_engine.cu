@@ -265,6 +265,14 @@ int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_
 
 }  // extern "C"
 
+int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, ev != nullptr, "event columns are null");
+    IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_append_event_columns(e, ev, n);
+}
+
 // ------------------------------------------------------------------------------------------------
 // chunk pipeline of the host-buffer calls
 // ------------------------------------------------------------------------------------------------

@@ -86,7 +86,13 @@ struct igs_engine {
     igs_player_row* d_players = nullptr;
     uint64_t n_players = 0;
 
-    // events
+    // events: device-resident raw columns in arrival order (igs_load_events + igs_append_events) and
+    // the index built from them
+    uint32_t* raw_account = nullptr;
+    uint32_t* raw_ts = nullptr;
+    int64_t*  raw_amount = nullptr;
+    uint8_t*  raw_type = nullptr;
+    uint64_t  n_raw = 0, cap_raw = 0;
     igs_event_index ev;
     bool has_events = false;
 
@@ -130,6 +136,7 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
 int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
                         cudaStream_t stream);
 int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts);
+int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n);   // append + rebuild
 void igs_free_event_index(igs_engine* e);
 int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);

@@ -14,6 +14,9 @@
 //      {chain sum with head = new account || gap > 3600, session start with head = new account ||
 //      gap > 1800}.  Three phases (tile reduce, scan of tile aggregates, tile apply).
 // Query (igs_get_velocity*, and inlined into the fused score kernel): velocity.cuh.
+#include <string.h>
+
+#include <algorithm>
 #include <vector>
 
 #include "igs_internal.cuh"
@@ -431,7 +434,16 @@ igs_index_view igs_index_view_of(const igs_engine* e) {
     return v;
 }
 
-void igs_free_event_index(igs_engine* e) {
+static void free_raw_events(igs_engine* e) {
+    if (e->raw_account) cudaFree(e->raw_account);
+    if (e->raw_ts) cudaFree(e->raw_ts);
+    if (e->raw_amount) cudaFree(e->raw_amount);
+    if (e->raw_type) cudaFree(e->raw_type);
+    e->raw_account = e->raw_ts = nullptr; e->raw_amount = nullptr; e->raw_type = nullptr;
+    e->n_raw = e->cap_raw = 0;
+}
+
+static void free_index_arrays(igs_engine* e) {
     igs_event_index& x = e->ev;
     if (x.seg) cudaFree(x.seg);
     if (x.ts) cudaFree(x.ts);
@@ -442,10 +454,84 @@ void igs_free_event_index(igs_engine* e) {
     e->has_events = false;
 }
 
+void igs_free_event_index(igs_engine* e) {
+    free_index_arrays(e);
+    free_raw_events(e);
+}
+
+// Appends n host events to the device-resident raw columns (capacity grows by 1.5x).
+static int append_raw(igs_engine* e, const igs_event_cols* ev, uint64_t n, cudaStream_t st) {
+    const uint64_t need = e->n_raw + n;
+    if (need > e->cap_raw) {
+        const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
+        uint32_t *a = nullptr, *t = nullptr; int64_t* m = nullptr; uint8_t* y = nullptr;
+        IGS_CUDA(e, cudaMalloc(&a, cap * 4));
+        IGS_CUDA(e, cudaMalloc(&t, cap * 4));
+        IGS_CUDA(e, cudaMalloc(&m, cap * 8));
+        IGS_CUDA(e, cudaMalloc(&y, cap));
+        if (e->n_raw) {
+            IGS_CUDA(e, cudaMemcpyAsync(a, e->raw_account, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
+            IGS_CUDA(e, cudaMemcpyAsync(t, e->raw_ts, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
+            IGS_CUDA(e, cudaMemcpyAsync(m, e->raw_amount, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
+            IGS_CUDA(e, cudaMemcpyAsync(y, e->raw_type, e->n_raw, cudaMemcpyDeviceToDevice, st));
+            IGS_CUDA(e, cudaStreamSynchronize(st));
+        }
+        const uint64_t keep = e->n_raw;
+        if (e->raw_account) { cudaFree(e->raw_account); cudaFree(e->raw_ts); cudaFree(e->raw_amount); cudaFree(e->raw_type); }
+        e->raw_account = a; e->raw_ts = t; e->raw_amount = m; e->raw_type = y;
+        e->cap_raw = cap; e->n_raw = keep;
+    }
+    if (n) {
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyHostToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyHostToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyHostToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyHostToDevice, st));
+    }
+    e->n_raw = need;
+    return IGS_OK;
+}
+
+static int build_index_from_raw(igs_engine* e, uint32_t n_accounts);
+
+int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n) {
+    if (!e->has_events) {
+        igs_set_error(e, "igs_append_events needs a loaded history (igs_load_events, possibly with n = 0)");
+        return IGS_ERR_STATE;
+    }
+    if (e->n_raw + n >= 0xFFFFFFFFull) {
+        igs_set_error(e, "at most 2^32-2 events per shard");
+        return IGS_ERR_INVALID;
+    }
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    const uint64_t before = e->n_raw;
+    const uint32_t n_accounts = e->ev.n_accounts;   // the rebuild resets e->ev
+    int rc = append_raw(e, ev, n, e->slot[0].stream);
+    if (rc != IGS_OK) return rc;
+    rc = build_index_from_raw(e, n_accounts);
+    if (rc != IGS_OK) {                      // e.g. an account index out of range: drop the rejected batch
+        char msg[sizeof(e->err)];
+        memcpy(msg, e->err, sizeof(msg));
+        e->n_raw = before;
+        build_index_from_raw(e, n_accounts);
+        memcpy(e->err, msg, sizeof(msg));    // report the rejection, not the recovery
+    }
+    return rc;
+}
+
 int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64, uint32_t n_accounts) {
     IGS_CUDA(e, cudaDeviceSynchronize());
     igs_free_event_index(e);
-    const uint32_t n = (uint32_t)n64;
+    int rc = append_raw(e, ev, n64, e->slot[0].stream);
+    if (rc != IGS_OK) return rc;
+    rc = build_index_from_raw(e, n_accounts);
+    if (rc != IGS_OK) igs_free_event_index(e);
+    return rc;
+}
+
+// (Re)builds the index from the raw columns e->raw_* [0, n_raw).
+static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
+    free_index_arrays(e);
+    const uint32_t n = (uint32_t)e->n_raw;
     cudaStream_t st = e->slot[0].stream;
     igs_event_index& x = e->ev;
     Scratch sc;
@@ -465,17 +551,13 @@ int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64,
         return IGS_OK;
     }
 
-    // ---- upload the columns ---------------------------------------------------------------------
-    uint32_t *d_acct_in, *d_ts_in; int64_t* d_amt_in; uint8_t* d_type_in; uint32_t* d_mm;
-    IGS_CUDA(e, sc.alloc(&d_acct_in, n));
-    IGS_CUDA(e, sc.alloc(&d_ts_in, n));
-    IGS_CUDA(e, sc.alloc(&d_amt_in, n));
-    IGS_CUDA(e, sc.alloc(&d_type_in, n));
+    // ---- the raw columns are already on the device -----------------------------------------------
+    const uint32_t* d_acct_in = e->raw_account;
+    const uint32_t* d_ts_in = e->raw_ts;
+    const int64_t* d_amt_in = e->raw_amount;
+    const uint8_t* d_type_in = e->raw_type;
+    uint32_t* d_mm;
     IGS_CUDA(e, sc.alloc(&d_mm, 4));
-    IGS_CUDA(e, cudaMemcpyAsync(d_acct_in, ev->account, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    IGS_CUDA(e, cudaMemcpyAsync(d_ts_in, ev->ts, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    IGS_CUDA(e, cudaMemcpyAsync(d_amt_in, ev->amount, (size_t)n * 8, cudaMemcpyHostToDevice, st));
-    IGS_CUDA(e, cudaMemcpyAsync(d_type_in, ev->tx_type, (size_t)n, cudaMemcpyHostToDevice, st));
 
     // ---- key range ------------------------------------------------------------------------------
     const uint32_t mm_init[4] = {0xFFFFFFFFu, 0u, 0u, 0u};
@@ -488,7 +570,7 @@ int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64,
     IGS_CUDA(e, cudaStreamSynchronize(st));
     if (mm[2] >= n_accounts) {
         igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
-        igs_free_event_index(e);
+        free_index_arrays(e);
         return IGS_ERR_INVALID;
     }
     const uint32_t ts_min = mm[0];
