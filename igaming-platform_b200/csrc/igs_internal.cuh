@@ -7,6 +7,7 @@
 #include <stdio.h>
 
 #include <mutex>
+#include <vector>
 
 #include "igs.h"
 
@@ -61,6 +62,8 @@ struct igs_tail_rec;
 struct igs_event_index {
     uint64_t n = 0;
     uint32_t n_accounts = 0;
+    uint64_t cap_events = 0;          // capacity of ts / seq / pre / tail (grow-only, 1.5x)
+    uint64_t cap_accounts = 0;        // capacity of seg
     uint32_t* seg = nullptr;          // [n_accounts + 1] first sorted position of each account
     uint32_t* ts = nullptr;           // [n] sorted by (account, ts, arrival)
     uint32_t* seq = nullptr;          // [n] arrival index of the sorted event
@@ -95,6 +98,7 @@ struct igs_engine {
     uint64_t  n_raw = 0, cap_raw = 0;
     igs_event_index ev;
     bool has_events = false;
+    std::vector<igs_buf> build_pool;  // scratch of the index build, kept between igs_append_events calls
 
     // MLP
     void* d_mlp = nullptr;        // see k_ltv.cu

@@ -16,8 +16,8 @@
 //   * Leaves are added to the margin in tree-index order in fp32 — the oracle's order — so the
 //     margin, the logistic (igs_sigmoid), the fp64 blend and the integer score are bit-identical
 //     to the CPU restatement.
-//   * Launch shapes (W x C): 12 x 20 for pre-assembled rows, 16 x 10 for the fused path, where more
-//     warps hide the latency of the velocity lookups.
+//   * Launch shapes (warps x chunk trees x ILP): 12 x 20 x 5 for pre-assembled rows, 16 x 14 x 7 for the
+//     fused path, where more warps hide the latency of the velocity lookups.
 // Two input sources share the kernel body:
 //   kSrcFeatures (path A): pre-assembled normalised 64-float rows + the 48-byte rule sideband.
 //   kSrcTx       (path B): 32-byte tx records; the lane looks its account up in the event index
@@ -35,21 +35,21 @@
 
 namespace {
 
-constexpr int kIlp = 5;
 constexpr int kFeatTileFloats = IGS_NUM_FEATURES * 32;           // per warp
 constexpr int kFeatTileBytes = kFeatTileFloats * 4;              // 8 KB
 
 // Launch shape: W warps per CTA (one tx per lane -> 32 W tx per tile), tree chunks of C trees.
 // smem = W x 8 KB feature tiles + 2 x C x 3 KB chunk buffers.
-template <int W, int C>
+template <int W, int C, int I = 5>
 struct Shape {
+    static constexpr int kIlp = I;        // trees walked at once per lane
     static constexpr int kWarps = W;
     static constexpr int kThreads = W * 32;
     static constexpr int kTileTx = W * 32;
     static constexpr int kChunkTrees = C;
     static constexpr int kChunkBytes = C * IGS_DEV_TREE_BYTES;
     static constexpr int kSmemBytes = W * kFeatTileBytes + 2 * kChunkBytes + 64;
-    static_assert(C % kIlp == 0, "chunk must be a whole number of ILP groups");
+    static_assert(C % I == 0, "chunk must be a whole number of ILP groups");
     static_assert(kSmemBytes <= 227 * 1024, "smem budget");
 };
 
@@ -159,7 +159,7 @@ __device__ __forceinline__ void walk_pair(uint32_t tree_addr, uint32_t tile_lane
 // smem address of this warp's [64][32] fp32 feature tile offset by lane.  Adds leaves to *margin in
 // tree order.  Levels are visited in pairs (igs_internal.cuh): LDS.64 {feats, thr} at the even level,
 // LDS.32 thr at the odd level whose feature came with the parent.
-template <bool kLeaves>
+template <bool kLeaves, int kIlp>
 __device__ __forceinline__ void walk_chunk(uint32_t cb, int trees, uint32_t tile_lane_addr, float* margin,
                                            uint8_t* leaf_out) {
     float m = *margin;
@@ -424,11 +424,11 @@ k_score(const __grid_constant__ ScoreParams p) {
                 mbar_wait(bar0 + 8 * b, (uint32_t)((g >> 1) & 1));
                 if (kLeaves) {
                     uint8_t tmp[kChunkTrees];
-                    walk_chunk<true>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, tmp);
+                    walk_chunk<true, S::kIlp>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, tmp);
                     if (leaf_row)
                         for (int t = 0; t < trees; ++t) leaf_row[c * kChunkTrees + t] = valid ? tmp[t] : 0;
                 } else {
-                    walk_chunk<false>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, nullptr);
+                    walk_chunk<false, S::kIlp>(chunk_addr + b * kChunkBytes, trees, tile_lane_addr, &margin, nullptr);
                 }
                 __syncthreads();   // every lane is done with buffer b
                 if (threadIdx.x == 0 && g + 2 < total_chunks) issue(g + 2);
@@ -475,7 +475,10 @@ static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cud
     case 4: return launch_shape<Shape<12, 25>>(e, src, p, leaves, stream);
     case 5: return launch_shape<Shape<16, 20>>(e, src, p, leaves, stream);
     case 6: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
-    default: return src == kSrcTx ? launch_shape<Shape<16, 10>>(e, src, p, leaves, stream)
+    case 7: return launch_shape<Shape<12, 20, 4>>(e, src, p, leaves, stream);
+    case 8: return launch_shape<Shape<12, 20, 10>>(e, src, p, leaves, stream);
+    case 9: return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
+    default: return src == kSrcTx ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
                                   : launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     }
 }

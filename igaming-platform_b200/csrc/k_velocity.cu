@@ -414,15 +414,35 @@ int bits_for(uint64_t v) {   // number of bits needed to represent v
     return b;
 }
 
+// Scratch of one index build, served from a grow-only pool in the engine: the sequence of requests is
+// the same for every build, so a rebuild after igs_append_events reuses the buffers of the previous one
+// instead of paying a dozen cudaMalloc / cudaFree round trips.
 struct Scratch {
-    std::vector<void*> ptrs;
-    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    igs_engine* e;
+    size_t next = 0;
+    explicit Scratch(igs_engine* eng) : e(eng) {}
     template <typename T> cudaError_t alloc(T** p, size_t count) {
-        cudaError_t st = cudaMalloc((void**)p, (count ? count : 1) * sizeof(T));
-        if (st == cudaSuccess) ptrs.push_back(*p);
-        return st;
+        const size_t bytes = (count ? count : 1) * sizeof(T);
+        if (next == e->build_pool.size()) e->build_pool.emplace_back();
+        igs_buf& b = e->build_pool[next++];
+        if (b.cap < bytes) {
+            if (b.p) cudaFree(b.p);
+            b.p = nullptr; b.cap = 0;
+            const size_t cap = ((bytes + bytes / 4) + 255) & ~(size_t)255;
+            cudaError_t st = cudaMalloc(&b.p, cap);
+            if (st != cudaSuccess) return st;
+            b.cap = cap;
+        }
+        *p = static_cast<T*>(b.p);
+        return cudaSuccess;
     }
 };
+
+static void free_build_pool(igs_engine* e) {
+    for (igs_buf& b : e->build_pool)
+        if (b.p) cudaFree(b.p);
+    e->build_pool.clear();
+}
 
 }  // namespace
 
@@ -443,7 +463,7 @@ static void free_raw_events(igs_engine* e) {
     e->n_raw = e->cap_raw = 0;
 }
 
-static void free_index_arrays(igs_engine* e) {
+static void release_index_arrays(igs_engine* e) {
     igs_event_index& x = e->ev;
     if (x.seg) cudaFree(x.seg);
     if (x.ts) cudaFree(x.ts);
@@ -455,8 +475,9 @@ static void free_index_arrays(igs_engine* e) {
 }
 
 void igs_free_event_index(igs_engine* e) {
-    free_index_arrays(e);
+    release_index_arrays(e);
     free_raw_events(e);
+    free_build_pool(e);
 }
 
 // Appends n host events to the device-resident raw columns (capacity grows by 1.5x).
@@ -525,22 +546,30 @@ int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64,
     if (rc != IGS_OK) return rc;
     rc = build_index_from_raw(e, n_accounts);
     if (rc != IGS_OK) igs_free_event_index(e);
+    else free_build_pool(e);           // a bulk load does not keep ~70 B/event of scratch around
     return rc;
 }
 
 // (Re)builds the index from the raw columns e->raw_* [0, n_raw).
 static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
-    free_index_arrays(e);
     const uint32_t n = (uint32_t)e->n_raw;
     cudaStream_t st = e->slot[0].stream;
     igs_event_index& x = e->ev;
-    Scratch sc;
-
-    IGS_CUDA(e, cudaMalloc(&x.seg, ((size_t)n_accounts + 1) * sizeof(uint32_t)));
-    IGS_CUDA(e, cudaMalloc(&x.ts, (n ? n : 1) * sizeof(uint32_t)));
-    IGS_CUDA(e, cudaMalloc(&x.seq, (n ? n : 1) * sizeof(uint32_t)));
-    IGS_CUDA(e, cudaMalloc(&x.pre, ((size_t)n + 1) * sizeof(igs_prefix_rec)));
-    IGS_CUDA(e, cudaMalloc(&x.tail, (n ? n : 1) * sizeof(igs_tail_rec)));
+    Scratch sc(e);
+    e->has_events = false;
+    if ((uint64_t)n + 1 > x.cap_events || (uint64_t)n_accounts + 1 > x.cap_accounts) {
+        // (re)allocate the index arrays with headroom so that appends rarely come back here
+        const uint64_t ce = std::max<uint64_t>((uint64_t)n + 1, x.cap_events + x.cap_events / 2);
+        const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
+        release_index_arrays(e);
+        IGS_CUDA(e, cudaMalloc(&x.seg, ca * sizeof(uint32_t)));
+        IGS_CUDA(e, cudaMalloc(&x.ts, ce * sizeof(uint32_t)));
+        IGS_CUDA(e, cudaMalloc(&x.seq, ce * sizeof(uint32_t)));
+        IGS_CUDA(e, cudaMalloc(&x.pre, ce * sizeof(igs_prefix_rec)));
+        IGS_CUDA(e, cudaMalloc(&x.tail, ce * sizeof(igs_tail_rec)));
+        x.cap_events = ce;
+        x.cap_accounts = ca;
+    }
     x.n = n;
     x.n_accounts = n_accounts;
     IGS_CUDA(e, cudaMemsetAsync(x.seg, 0, ((size_t)n_accounts + 1) * sizeof(uint32_t), st));
@@ -570,8 +599,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     IGS_CUDA(e, cudaStreamSynchronize(st));
     if (mm[2] >= n_accounts) {
         igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
-        free_index_arrays(e);
-        return IGS_ERR_INVALID;
+        return IGS_ERR_INVALID;          // has_events stays false until a build succeeds
     }
     const uint32_t ts_min = mm[0];
     const int ts_bits = bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1;
