@@ -468,16 +468,10 @@ static int launch_shape(igs_engine* e, int src, const ScoreParams& p, bool leave
 
 static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cudaStream_t stream) {
     static const int variant = getenv("IGS_SCORE_SHAPE") ? atoi(getenv("IGS_SCORE_SHAPE")) : 0;   // tuning knob
-    switch (variant) {
+    switch (variant) {          // alternatives kept for tuning runs (profiles/README.md lists what they measured)
     case 1: return launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
-    case 2: return launch_shape<Shape<16, 15>>(e, src, p, leaves, stream);
-    case 3: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
-    case 4: return launch_shape<Shape<12, 25>>(e, src, p, leaves, stream);
-    case 5: return launch_shape<Shape<16, 20>>(e, src, p, leaves, stream);
-    case 6: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
-    case 7: return launch_shape<Shape<12, 20, 4>>(e, src, p, leaves, stream);
-    case 8: return launch_shape<Shape<12, 20, 10>>(e, src, p, leaves, stream);
-    case 9: return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
+    case 2: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
+    case 3: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
     default: return src == kSrcTx ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
                                   : launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     }
