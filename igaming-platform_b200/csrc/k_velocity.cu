@@ -30,12 +30,14 @@ namespace {
 constexpr int kThreads = 256;
 
 __global__ void k_minmax(const uint32_t* __restrict__ account, const uint32_t* __restrict__ ts,
-                         uint32_t n, uint32_t* __restrict__ out /* ts_min, ts_max, acct_max */) {
-    uint32_t tmin = 0xFFFFFFFFu, tmax = 0, amax = 0;
+                         uint32_t n, uint32_t* __restrict__ out /* ts_min, ts_max, acct_max, unsorted */) {
+    uint32_t tmin = 0xFFFFFFFFu, tmax = 0, amax = 0, unsorted = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t t = __ldg(ts + i), a = __ldg(account + i);
         tmin = min(tmin, t); tmax = max(tmax, t); amax = max(amax, a);
+        if (i > 0 && __ldg(ts + i - 1) > t) unsorted = 1;    // arrival order is not time order
     }
+    if (__any_sync(0xffffffffu, unsorted) && (threadIdx.x & 31) == 0) atomicOr(out + 3, 1u);
     for (int o = 16; o; o >>= 1) {
         tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
         tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
@@ -53,7 +55,8 @@ __global__ void k_make_keys(const uint32_t* __restrict__ account, const uint32_t
                             uint32_t* __restrict__ vals) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    keys[i] = ((uint64_t)__ldg(account + i) << ts_bits) | (uint64_t)(__ldg(ts + i) - ts_min);
+    keys[i] = ts_bits ? ((uint64_t)__ldg(account + i) << ts_bits) | (uint64_t)(__ldg(ts + i) - ts_min)
+                      : (uint64_t)__ldg(account + i);       // time-ordered arrival: a stable sort by account is enough
     vals[i] = i;
 }
 
@@ -210,6 +213,7 @@ int scan_u32(igs_engine* e, uint32_t* data, uint32_t n, uint32_t* scratch, cudaS
 // post-sort columns
 // ------------------------------------------------------------------------------------------------
 __global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ seq,
+                                const uint32_t* __restrict__ ts_in,
                                 const int64_t* __restrict__ amount_in, const uint8_t* __restrict__ type_in,
                                 uint32_t n, uint32_t ts_min, int ts_bits, uint32_t* __restrict__ acct,
                                 uint32_t* __restrict__ ts, int64_t* __restrict__ amount,
@@ -218,8 +222,8 @@ __global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_
     if (i >= n) return;
     const uint64_t k = __ldg(keys + i);
     acct[i] = (uint32_t)(k >> ts_bits);
-    ts[i] = ts_min + (uint32_t)(k & ((1ull << ts_bits) - 1ull));
     const uint32_t s = __ldg(seq + i);
+    ts[i] = ts_bits ? ts_min + (uint32_t)(k & ((1ull << ts_bits) - 1ull)) : __ldg(ts_in + s);
     amount[i] = __ldg(amount_in + s);
     type[i] = __ldg(type_in + s);
 }
@@ -602,7 +606,10 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
         return IGS_ERR_INVALID;          // has_events stays false until a build succeeds
     }
     const uint32_t ts_min = mm[0];
-    const int ts_bits = bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1;
+    // Events that arrive in time order (a log, a queue, appended micro-batches) only need a stable sort by
+    // account: the radix passes over the timestamp bits are skipped.
+    const bool time_ordered = mm[3] == 0;
+    const int ts_bits = time_ordered ? 0 : (bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1);
     const int key_bits = ts_bits + (bits_for(mm[2]) > 0 ? bits_for(mm[2]) : 1);
     const int passes = (key_bits + 9) / 10;
     const int digit_bits = (key_bits + passes - 1) / passes;      // <= 10
@@ -641,7 +648,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     IGS_CUDA(e, sc.alloc(&d_type, n));
     IGS_CUDA(e, sc.alloc(&d_dflag, n));
     IGS_CUDA(e, cudaMemcpyAsync(x.seq, d_vals[cur], (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_amt_in, d_type_in, n, ts_min, ts_bits,
+    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
                                                 d_acct, x.ts, d_amt, d_type);
     IGS_CUDA(e, cudaGetLastError());
     k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, n, n_accounts, x.seg);
