@@ -12,7 +12,7 @@
 //   4. one fused scan over the sorted events producing, per position, the exclusive prefix
 //      {distinct count, per-type count, per-type sum} and, per event, the inclusive segmented
 //      {chain sum with head = new account || gap > 3600, session start with head = new account ||
-//      gap > 1800}.  Three phases (tile reduce, scan of tile aggregates, tile apply).
+//      gap > 1800}.  A 256-ary hierarchy of warp-shuffle passes (reduce up, scan the top, apply down).
 // Query (igs_get_velocity*, and inlined into the fused score kernel): velocity.cuh.
 #include <string.h>
 
@@ -243,17 +243,43 @@ __global__ void k_segments(const uint32_t* __restrict__ acct, uint32_t n, uint32
         for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
 }
 
-// distinct flag: no earlier event of the same (account, ts) group has the same amount
-__global__ void k_distinct(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
-                           const int64_t* __restrict__ amount, uint32_t n, uint8_t* __restrict__ dflag) {
+// head[i] = 1 iff event i is the first of its (account, ts) group in sorted order
+__global__ void k_group_heads(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts, uint32_t n,
+                              uint8_t* __restrict__ head) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t a = __ldg(acct + i), t = __ldg(ts + i);
-    const int64_t m = __ldg(amount + i);
+    head[i] = i == 0 || __ldg(acct + i) != __ldg(acct + i - 1) || __ldg(ts + i) != __ldg(ts + i - 1);
+}
+
+// distinct flag: no earlier event of the same (account, ts) group has the same amount (the ZSET member
+// "ts:amount" dedupe).  Walks back through the group four events at a time; the loads of a step do not
+// depend on each other, so same-second bursts of a hot account (hundreds of events) stay cheap.
+__global__ void k_distinct(const uint8_t* __restrict__ head, const int64_t* __restrict__ amount, uint32_t n,
+                           uint8_t* __restrict__ dflag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
     uint8_t d = 1;
-    for (uint32_t j = i; j-- > 0;) {
-        if (__ldg(acct + j) != a || __ldg(ts + j) != t) break;
-        if (__ldg(amount + j) == m) { d = 0; break; }
+    if (!__ldg(head + i)) {
+        const int64_t m = __ldg(amount + i);
+        uint32_t j = i;                       // candidates are j-1, j-2, ... down to the group head
+        bool done = false;
+        while (!done) {
+            int64_t a[4];
+            uint8_t h[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t jj = j >= (uint32_t)(k + 1) ? j - (k + 1) : 0;
+                a[k] = __ldg(amount + jj);
+                h[k] = j >= (uint32_t)(k + 1) ? __ldg(head + jj) : 1;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (done) break;
+                if (a[k] == m) { d = 0; done = true; }
+                else if (h[k]) done = true;   // reached the first event of the group
+            }
+            j = j >= 4 ? j - 4 : 0;
+        }
     }
     dflag[i] = d;
 }
@@ -303,96 +329,143 @@ __device__ __forceinline__ VScan vs_element(const VCols& c, uint32_t i) {
     return r;
 }
 
-constexpr int kVItems = 8;
-constexpr int kVTile = kThreads * kVItems;   // 2048
+// The scan is a 256-ary hierarchy of warp-level passes (no shared memory, no block barriers): a warp owns
+// 256 consecutive items, reads them 32 at a time (coalesced) and reduces / scans each round with shuffles,
+// carrying the running value in registers.
+//   level 0: elements        -> one aggregate per 256 events        (k_vs_reduce<ElemSrc>)
+//   level 1: those           -> one aggregate per 65 536 events      (k_vs_reduce<AggSrc>)
+//   level 2: a single warp scans the few level-1 aggregates          (k_vs_scan_small)
+//   down   : exclusive scan of the level-0 aggregates with carry-in  (k_vs_apply_aggs),
+//            then of the elements, writing the prefix / tail records (k_vs_apply_elems)
+constexpr int kVTile = 256;
 
-// inclusive block scan of one VScan per thread through shared memory (Hillis-Steele)
-__device__ __forceinline__ VScan vs_block_scan(VScan mine, VScan* sh /* [2][kThreads] */, VScan* block_total) {
-    int cur = 0;
-    sh[threadIdx.x] = mine;
-    __syncthreads();
-    for (int off = 1; off < kThreads; off <<= 1) {
-        VScan v = sh[cur * kThreads + threadIdx.x];
-        if ((int)threadIdx.x >= off) v = vs_combine(sh[cur * kThreads + threadIdx.x - off], v);
-        sh[(cur ^ 1) * kThreads + threadIdx.x] = v;
-        cur ^= 1;
-        __syncthreads();
-    }
-    const VScan inc = sh[cur * kThreads + threadIdx.x];
-    *block_total = sh[cur * kThreads + kThreads - 1];
-    __syncthreads();
-    return inc;
+__device__ __forceinline__ VScan vs_shfl_up(const VScan& v, int o) {
+    VScan r;
+    r.s0 = __shfl_up_sync(0xffffffffu, v.s0, o); r.s1 = __shfl_up_sync(0xffffffffu, v.s1, o);
+    r.chain = __shfl_up_sync(0xffffffffu, v.chain, o);
+    r.d = __shfl_up_sync(0xffffffffu, v.d, o); r.c0 = __shfl_up_sync(0xffffffffu, v.c0, o);
+    r.c1 = __shfl_up_sync(0xffffffffu, v.c1, o); r.st = __shfl_up_sync(0xffffffffu, v.st, o);
+    const uint32_t f = __shfl_up_sync(0xffffffffu, v.cf | (v.sf << 1), o);
+    r.cf = f & 1u; r.sf = f >> 1;
+    return r;
 }
-
-__global__ void __launch_bounds__(kThreads)
-k_vscan_reduce(VCols c, VScan* __restrict__ agg) {
-    __shared__ VScan sh[2 * kThreads];
-    const uint32_t base = blockIdx.x * kVTile + threadIdx.x * kVItems;
-    VScan t = vs_identity();
+__device__ __forceinline__ VScan vs_shfl(const VScan& v, int src) {
+    VScan r;
+    r.s0 = __shfl_sync(0xffffffffu, v.s0, src); r.s1 = __shfl_sync(0xffffffffu, v.s1, src);
+    r.chain = __shfl_sync(0xffffffffu, v.chain, src);
+    r.d = __shfl_sync(0xffffffffu, v.d, src); r.c0 = __shfl_sync(0xffffffffu, v.c0, src);
+    r.c1 = __shfl_sync(0xffffffffu, v.c1, src); r.st = __shfl_sync(0xffffffffu, v.st, src);
+    const uint32_t f = __shfl_sync(0xffffffffu, v.cf | (v.sf << 1), src);
+    r.cf = f & 1u; r.sf = f >> 1;
+    return r;
+}
+// inclusive scan across the 32 lanes (lane order = item order)
+__device__ __forceinline__ VScan vs_warp_scan(VScan v, int lane) {
 #pragma unroll
-    for (int k = 0; k < kVItems; ++k)
-        if (base + k < c.n) t = vs_combine(t, vs_element(c, base + k));
-    VScan total;
-    vs_block_scan(t, sh, &total);
-    if (threadIdx.x == 0) agg[blockIdx.x] = total;
+    for (int o = 1; o < 32; o <<= 1) {
+        const VScan y = vs_shfl_up(v, o);
+        if (lane >= o) v = vs_combine(y, v);
+    }
+    return v;
 }
 
-// exclusive scan of the tile aggregates in place, single block
+struct ElemSrc {
+    VCols c;
+    __device__ __forceinline__ VScan operator()(uint32_t i) const { return vs_element(c, i); }
+    __device__ __forceinline__ uint32_t size() const { return c.n; }
+};
+struct AggSrc {
+    const VScan* a; uint32_t n;
+    __device__ __forceinline__ VScan operator()(uint32_t i) const { return a[i]; }
+    __device__ __forceinline__ uint32_t size() const { return n; }
+};
+
+template <typename Src>
 __global__ void __launch_bounds__(kThreads)
-k_vscan_prefix(VScan* __restrict__ agg, uint32_t nb) {
-    __shared__ VScan sh[2 * kThreads];
+k_vs_reduce(Src src, VScan* __restrict__ agg) {
+    const uint32_t gw = (blockIdx.x * kThreads + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = src.size(), base = gw * kVTile;
+    if (base >= n) return;
     VScan carry = vs_identity();
-    for (uint32_t base = 0; base < nb; base += kThreads) {
-        const uint32_t i = base + threadIdx.x;
-        const VScan mine = i < nb ? agg[i] : vs_identity();
-        VScan total;
-        const VScan inc = vs_block_scan(mine, sh, &total);
-        // exclusive = carry (+) inclusive-of-previous-thread
-        __shared__ VScan prev[kThreads];
-        prev[threadIdx.x] = inc;
-        __syncthreads();
-        VScan ex = carry;
-        if (threadIdx.x > 0) ex = vs_combine(carry, prev[threadIdx.x - 1]);
-        if (i < nb) agg[i] = ex;
-        carry = vs_combine(carry, total);
-        __syncthreads();
+#pragma unroll 1
+    for (int r = 0; r < kVTile / 32; ++r) {
+        const uint32_t i = base + r * 32 + lane;
+        const VScan inc = vs_warp_scan(i < n ? src(i) : vs_identity(), lane);
+        carry = vs_combine(carry, vs_shfl(inc, 31));
+    }
+    if (lane == 0) agg[gw] = carry;
+}
+
+// exclusive scan of a[0..n) in place by one warp (n is a few hundred at most)
+__global__ void __launch_bounds__(32)
+k_vs_scan_small(VScan* __restrict__ a, uint32_t n) {
+    const int lane = threadIdx.x;
+    VScan carry = vs_identity();
+    for (uint32_t base = 0; base < n; base += 32) {
+        const uint32_t i = base + lane;
+        const VScan v = i < n ? a[i] : vs_identity();
+        const VScan inc = vs_warp_scan(v, lane);
+        VScan ex = vs_shfl_up(inc, 1);
+        if (lane == 0) ex = vs_identity();
+        if (i < n) a[i] = vs_combine(carry, ex);
+        carry = vs_combine(carry, vs_shfl(inc, 31));
+    }
+}
+
+// exclusive scan of a[0..n) in place, 256 items per warp, carry-in per warp tile from tile_excl
+__global__ void __launch_bounds__(kThreads)
+k_vs_apply_aggs(VScan* __restrict__ a, uint32_t n, const VScan* __restrict__ tile_excl) {
+    const uint32_t gw = (blockIdx.x * kThreads + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t base = gw * kVTile;
+    if (base >= n) return;
+    VScan carry = tile_excl[gw];
+#pragma unroll 1
+    for (int r = 0; r < kVTile / 32; ++r) {
+        const uint32_t i = base + r * 32 + lane;
+        const VScan v = i < n ? a[i] : vs_identity();
+        const VScan inc = vs_warp_scan(v, lane);
+        VScan ex = vs_shfl_up(inc, 1);
+        if (lane == 0) ex = vs_identity();
+        if (i < n) a[i] = vs_combine(carry, ex);
+        carry = vs_combine(carry, vs_shfl(inc, 31));
     }
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_vscan_apply(VCols c, const VScan* __restrict__ agg, igs_prefix_rec* __restrict__ pre,
-              igs_tail_rec* __restrict__ tail) {
-    __shared__ VScan sh[2 * kThreads];
-    __shared__ VScan prev[kThreads];
-    const uint32_t base = blockIdx.x * kVTile + threadIdx.x * kVItems;
-    VScan el[kVItems];
-    VScan t = vs_identity();
-#pragma unroll
-    for (int k = 0; k < kVItems; ++k) {
-        el[k] = base + k < c.n ? vs_element(c, base + k) : vs_identity();
-        t = vs_combine(t, el[k]);
-    }
-    VScan total;
-    const VScan inc = vs_block_scan(t, sh, &total);
-    prev[threadIdx.x] = inc;
-    __syncthreads();
-    VScan run = agg[blockIdx.x];
-    if (threadIdx.x > 0) run = vs_combine(run, prev[threadIdx.x - 1]);
-#pragma unroll
-    for (int k = 0; k < kVItems; ++k) {
-        const uint32_t i = base + k;
-        if (i <= c.n) {
-            igs_prefix_rec p;
-            p.dcnt = run.d; p.cnt[0] = run.c0; p.cnt[1] = run.c1; p.pad = 0;
-            p.sum[0] = run.s0; p.sum[1] = run.s1;
-            pre[i] = p;
-        }
+k_vs_apply_elems(VCols c, const VScan* __restrict__ tile_excl, igs_prefix_rec* __restrict__ pre,
+                 igs_tail_rec* __restrict__ tail) {
+    const uint32_t gw = (blockIdx.x * kThreads + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t base = gw * kVTile;
+    if (base >= c.n) return;
+    VScan carry = tile_excl[gw];
+#pragma unroll 1
+    for (int r = 0; r < kVTile / 32; ++r) {
+        const uint32_t i = base + r * 32 + lane;
+        const VScan v = i < c.n ? vs_element(c, i) : vs_identity();
+        const VScan inc = vs_warp_scan(v, lane);
+        VScan ex = vs_shfl_up(inc, 1);
+        if (lane == 0) ex = vs_identity();
         if (i < c.n) {
-            run = vs_combine(run, el[k]);
+            const VScan before = vs_combine(carry, ex);          // everything ordered before event i
+            const VScan upto = vs_combine(carry, inc);           // ... including event i
+            igs_prefix_rec p;
+            p.dcnt = before.d; p.cnt[0] = before.c0; p.cnt[1] = before.c1; p.pad = 0;
+            p.sum[0] = before.s0; p.sum[1] = before.s1;
+            pre[i] = p;
             igs_tail_rec tl;
-            tl.chain_sum = run.chain; tl.sess_start = run.st; tl.pad = 0;
+            tl.chain_sum = upto.chain; tl.sess_start = upto.st; tl.pad = 0;
             tail[i] = tl;
+            if (i == c.n - 1) {                                  // pre[n]: totals over the whole history
+                igs_prefix_rec q;
+                q.dcnt = upto.d; q.cnt[0] = upto.c0; q.cnt[1] = upto.c1; q.pad = 0;
+                q.sum[0] = upto.s0; q.sum[1] = upto.s1;
+                pre[c.n] = q;
+            }
         }
+        carry = vs_combine(carry, vs_shfl(inc, 31));
     }
 }
 
@@ -653,23 +726,31 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     IGS_CUDA(e, cudaGetLastError());
     k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, n, n_accounts, x.seg);
     IGS_CUDA(e, cudaGetLastError());
-    k_distinct<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, d_amt, n, d_dflag);
+    uint8_t* d_head;
+    IGS_CUDA(e, sc.alloc(&d_head, n));
+    k_group_heads<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, n, d_head);
+    IGS_CUDA(e, cudaGetLastError());
+    k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag);
     IGS_CUDA(e, cudaGetLastError());
 
-    // ---- fused scan -----------------------------------------------------------------------------
-    const uint32_t nb_v = (n + kVTile - 1) / kVTile;
-    // the apply phase also writes pre[n]; when n is a multiple of the tile that position belongs to
-    // one more (otherwise empty) tile
-    const uint32_t nb_apply = n / kVTile + 1;
-    VScan* d_agg;
-    IGS_CUDA(e, sc.alloc(&d_agg, (size_t)nb_apply + 1));
-    IGS_CUDA(e, cudaMemsetAsync(d_agg, 0, ((size_t)nb_apply + 1) * sizeof(VScan), st));
+    // ---- fused scan: reduce up two levels, scan the top, apply down ---------------------------------
+    const uint32_t n1 = (n + kVTile - 1) / kVTile;            // level-0 aggregates (one per 256 events)
+    const uint32_t n2 = (n1 + kVTile - 1) / kVTile;           // level-1 aggregates (one per 65 536 events)
+    VScan *d_agg1, *d_agg2;
+    IGS_CUDA(e, sc.alloc(&d_agg1, n1));
+    IGS_CUDA(e, sc.alloc(&d_agg2, n2));
     VCols cols{d_acct, x.ts, d_amt, d_type, d_dflag, n};
-    k_vscan_reduce<<<nb_v, kThreads, 0, st>>>(cols, d_agg);
+    const uint32_t warps_per_block = kThreads / 32;
+    const uint32_t g1 = (n1 + warps_per_block - 1) / warps_per_block, g2 = (n2 + warps_per_block - 1) / warps_per_block;
+    k_vs_reduce<ElemSrc><<<g1, kThreads, 0, st>>>(ElemSrc{cols}, d_agg1);
     IGS_CUDA(e, cudaGetLastError());
-    k_vscan_prefix<<<1, kThreads, 0, st>>>(d_agg, nb_apply);
+    k_vs_reduce<AggSrc><<<g2, kThreads, 0, st>>>(AggSrc{d_agg1, n1}, d_agg2);
     IGS_CUDA(e, cudaGetLastError());
-    k_vscan_apply<<<nb_apply, kThreads, 0, st>>>(cols, d_agg, x.pre, x.tail);
+    k_vs_scan_small<<<1, 32, 0, st>>>(d_agg2, n2);
+    IGS_CUDA(e, cudaGetLastError());
+    k_vs_apply_aggs<<<g2, kThreads, 0, st>>>(d_agg1, n1, d_agg2);
+    IGS_CUDA(e, cudaGetLastError());
+    k_vs_apply_elems<<<g1, kThreads, 0, st>>>(cols, d_agg1, x.pre, x.tail);
     IGS_CUDA(e, cudaGetLastError());
     IGS_CUDA(e, cudaStreamSynchronize(st));
     e->has_events = true;
