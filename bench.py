@@ -412,13 +412,27 @@ def main():
         t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        flat = None
+        if not args.skip_latency and rank == 0:
+            nb = LAT_BATCH
+            fl = []
+            for i in range(1020):
+                off = (i * nb) % (n - nb)
+                t0 = time.perf_counter()
+                st = lib.igs_score_batch(eng.handle, C.byref(cfg), h_tx[off:].ctypes.data, nb, h_out[off:].ctypes.data,
+                                         None, None)
+                fl.append(time.perf_counter() - t0)
+                assert st == 0
+            fl = np.array(fl[20:]) * 1e3
+            flat = {"batch": nb, "batches": int(fl.size), "p50_ms": float(np.percentile(fl, 50)),
+                    "p99_ms": float(np.percentile(fl, 99)), "max_ms": float(fl.max())}
         fused = {"workload": f"per GPU: {n} compact tx (32 B) against {n_pl} players + {n_ev}-event index, "
                              "velocity + assembly + rules + 500-tree GBDT + blend in one kernel",
                  "value": n * world / (f_ms * 1e-3), "unit": UNIT, "ms_per_step": f_ms,
                  "e2e": {"value": n * world * e2e_steps / float(t.item()), "unit": UNIT,
                          "h2d_bytes_per_step": int(n * 32), "d2h_bytes_per_step": int(n * 8),
                          "api": "igs_score_batch (pinned host buffers)"},
-                 "index_build_s": load_s, "algorithmic_bytes_per_tx": 136}
+                 "p99_batch_latency": flat, "index_build_s": load_s, "algorithmic_bytes_per_tx": 136}
         lib.igs_free_pinned(p4)
 
     # ---- CPU baseline (oracle port) on rank 0, N=1 only ----------------------------------------

@@ -472,7 +472,13 @@ static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cud
     case 1: return launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     case 2: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
     case 3: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
-    default: return src == kSrcTx ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
+    default:
+        // latency-sized batches: if the 12-warp shape would need a second, nearly empty round of tiles while
+        // the 16-warp shape covers the batch in one round, take the latter
+        if (src == kSrcFeatures && p.n > (unsigned long long)e->sm_count * Shape<12, 20>::kTileTx &&
+            p.n <= (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx)
+            return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
+        return src == kSrcTx ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
                                   : launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     }
 }
