@@ -16,8 +16,8 @@
 //   * Leaves are added to the margin in tree-index order in fp32 — the oracle's order — so the
 //     margin, the logistic (igs_sigmoid), the fp64 blend and the integer score are bit-identical
 //     to the CPU restatement.
-//   * Launch shapes (warps x chunk trees x ILP): 12 x 20 x 5 for pre-assembled rows, 16 x 14 x 7 for the
-//     fused path, where more warps hide the latency of the velocity lookups.
+//   * Launch shapes (warps x chunk trees x ILP [x CTAs per SM]): 12 x 20 x 5 for pre-assembled rows; the fused
+//     path runs two independent 8 x 10 x 5 CTAs per SM so that one CTA's lookup phase overlaps the other's walk.
 // Two input sources share the kernel body:
 //   kSrcFeatures (path A): pre-assembled normalised 64-float rows + the 48-byte rule sideband.
 //   kSrcTx       (path B): 32-byte tx records; the lane looks its account up in the event index
@@ -40,9 +40,10 @@ constexpr int kFeatTileBytes = kFeatTileFloats * 4;              // 8 KB
 
 // Launch shape: W warps per CTA (one tx per lane -> 32 W tx per tile), tree chunks of C trees.
 // smem = W x 8 KB feature tiles + 2 x C x 3 KB chunk buffers.
-template <int W, int C, int I = 5>
+template <int W, int C, int I = 5, int B = 1>
 struct Shape {
     static constexpr int kIlp = I;        // trees walked at once per lane
+    static constexpr int kCtasPerSm = B;  // independent CTAs per SM (their phases interleave)
     static constexpr int kWarps = W;
     static constexpr int kThreads = W * 32;
     static constexpr int kTileTx = W * 32;
@@ -50,7 +51,7 @@ struct Shape {
     static constexpr int kChunkBytes = C * IGS_DEV_TREE_BYTES;
     static constexpr int kSmemBytes = W * kFeatTileBytes + 2 * kChunkBytes + 64;
     static_assert(C % I == 0, "chunk must be a whole number of ILP groups");
-    static_assert(kSmemBytes <= 227 * 1024, "smem budget");
+    static_assert(B * (kSmemBytes + 1024) <= 227 * 1024, "smem budget");
 };
 
 constexpr int kSrcFeatures = 0;
@@ -315,7 +316,7 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
 }
 
 template <int kSrc, bool kLeaves, typename S>
-__global__ void __launch_bounds__(S::kThreads, 1)
+__global__ void __launch_bounds__(S::kThreads, S::kCtasPerSm)
 k_score(const __grid_constant__ ScoreParams p) {
     constexpr int kWarps = S::kWarps, kTileTx = S::kTileTx, kChunkTrees = S::kChunkTrees,
                   kChunkBytes = S::kChunkBytes;
@@ -460,7 +461,8 @@ static int launch_shape(igs_engine* e, int src, const ScoreParams& p, bool leave
     // per-device attribute; a few hundred ns, so simply set on every launch
     IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kSmemBytes));
     const unsigned long long n_tiles = (p.n + S::kTileTx - 1) / S::kTileTx;
-    const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : e->sm_count);
+    const unsigned long long max_ctas = (unsigned long long)e->sm_count * S::kCtasPerSm;
+    const unsigned grid = (unsigned)(n_tiles < max_ctas ? n_tiles : max_ctas);
     kern<<<grid, S::kThreads, S::kSmemBytes, stream>>>(p);
     IGS_CUDA(e, cudaGetLastError());
     return IGS_OK;
@@ -472,14 +474,20 @@ static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cud
     case 1: return launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     case 2: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
     case 3: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
+    case 4: return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
     default:
         // latency-sized batches: if the 12-warp shape would need a second, nearly empty round of tiles while
         // the 16-warp shape covers the batch in one round, take the latter
         if (src == kSrcFeatures && p.n > (unsigned long long)e->sm_count * Shape<12, 20>::kTileTx &&
             p.n <= (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx)
             return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
-        return src == kSrcTx ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
-                                  : launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
+        // fused path: one round of 16-warp tiles when the batch fits in it (lowest latency), else two 8-warp CTAs
+        // per SM (highest throughput)
+        if (src == kSrcTx)
+            return p.n <= (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx
+                       ? launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream)
+                       : launch_shape<Shape<8, 10, 5, 2>>(e, src, p, leaves, stream);
+        return launch_shape<Shape<12, 20>>(e, src, p, leaves, stream);
     }
 }
 
