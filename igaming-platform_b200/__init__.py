@@ -86,6 +86,21 @@ class Events:
     ts: np.ndarray       # uint32
     amount: np.ndarray   # int64
     tx_type: np.ndarray  # uint8
+    device: np.ndarray | None = None   # uint64 ids (igs_hash_id), 0 = empty; igs_event_ids
+    ip: np.ndarray | None = None       # uint64
+
+    def has_ids(self) -> bool:
+        return self.device is not None or self.ip is not None
+
+    def ids(self) -> abi.EventIds:
+        n = len(self)
+        for k in ("device", "ip"):
+            v = getattr(self, k)
+            if v is not None:
+                v = np.ascontiguousarray(v, dtype=np.uint64)
+                assert v.shape == (n,)
+                setattr(self, k, v)
+        return abi.EventIds(abi.ptr(self.device), abi.ptr(self.ip))
 
     def __len__(self) -> int:
         return int(self.account.shape[0])
@@ -155,13 +170,45 @@ class Engine:
         self._check(self._lib.igs_load_players(self._h, abi.ptr(rows), rows.shape[0]))
 
     def load_events(self, ev: Events, n_accounts: int) -> None:
+        """igs_load_events, or igs_load_events_ids when the events carry device / ip columns."""
         c = ev.cols()
-        self._check(self._lib.igs_load_events(self._h, C.byref(c), len(ev), n_accounts))
+        if ev.has_ids():
+            i = ev.ids()
+            self._check(self._lib.igs_load_events_ids(self._h, C.byref(c), C.byref(i), len(ev), n_accounts))
+        else:
+            self._check(self._lib.igs_load_events(self._h, C.byref(c), len(ev), n_accounts))
 
     def append_events(self, ev: Events) -> None:
         """UpdateFeatures for a batch of completed transactions (scoring/engine.go:486-488)."""
         c = ev.cols()
-        self._check(self._lib.igs_append_events(self._h, C.byref(c), len(ev)))
+        if ev.has_ids():
+            i = ev.ids()
+            self._check(self._lib.igs_append_events_ids(self._h, C.byref(c), C.byref(i), len(ev)))
+        else:
+            self._check(self._lib.igs_append_events(self._h, C.byref(c), len(ev)))
+
+    # -- identifiers: uniques + blacklist -----------------------------------------------------
+    def get_uniques(self, queries: np.ndarray) -> np.ndarray:
+        queries = np.ascontiguousarray(queries, dtype=abi.query_dtype)
+        out = np.zeros(queries.shape[0], dtype=abi.uniques_dtype)
+        self._check(self._lib.igs_get_uniques(self._h, abi.ptr(queries), queries.shape[0], abi.ptr(out)))
+        return out
+
+    def blacklist_load(self, kind: int, ids: np.ndarray) -> None:
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        self._check(self._lib.igs_blacklist_load(self._h, kind, abi.ptr(ids), ids.shape[0]))
+
+    def blacklist_add(self, kind: int, ids: np.ndarray) -> None:
+        """AddToBlacklist (features/redis_store.go:251-264) for a batch of ids."""
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        self._check(self._lib.igs_blacklist_add(self._h, kind, abi.ptr(ids), ids.shape[0]))
+
+    def blacklist_check(self, ids: np.ndarray) -> np.ndarray:
+        """CheckBlacklist (features/redis_store.go:267-293) for a batch of identifier triples."""
+        ids = np.ascontiguousarray(ids, dtype=abi.tx_ids_dtype)
+        out = np.zeros(ids.shape[0], dtype=np.uint8)
+        self._check(self._lib.igs_blacklist_check(self._h, abi.ptr(ids), ids.shape[0], abi.ptr(out)))
+        return out
 
     # -- path A -------------------------------------------------------------------------------
     def score_features(self, cfg: abi.Config, features: np.ndarray, rows: np.ndarray,
@@ -194,14 +241,21 @@ class Engine:
 
     # -- path B -------------------------------------------------------------------------------
     def score_batch(self, cfg: abi.Config, tx: np.ndarray, want_features: bool = False,
-                    want_velocity: bool = False):
+                    want_velocity: bool = False, ids: np.ndarray | None = None):
+        """igs_score_batch; with `ids` (tx_ids_dtype, parallel to tx) igs_score_batch_ids."""
         tx = np.ascontiguousarray(tx, dtype=abi.tx_dtype)
         n = tx.shape[0]
         out = np.zeros(n, dtype=abi.result_dtype)
         feats = np.zeros((n, abi.NUM_FEATURES), dtype=np.float32) if want_features else None
         vel = np.zeros(n, dtype=abi.velocity_dtype) if want_velocity else None
-        self._check(self._lib.igs_score_batch(self._h, C.byref(cfg), abi.ptr(tx), n, abi.ptr(out),
-                                              abi.ptr(feats), abi.ptr(vel)))
+        if ids is not None:
+            ids = np.ascontiguousarray(ids, dtype=abi.tx_ids_dtype)
+            assert ids.shape == (n,)
+            self._check(self._lib.igs_score_batch_ids(self._h, C.byref(cfg), abi.ptr(tx), abi.ptr(ids), n,
+                                                      abi.ptr(out), abi.ptr(feats), abi.ptr(vel)))
+        else:
+            self._check(self._lib.igs_score_batch(self._h, C.byref(cfg), abi.ptr(tx), n, abi.ptr(out),
+                                                  abi.ptr(feats), abi.ptr(vel)))
         if want_features or want_velocity:
             return out, feats, vel
         return out
@@ -235,6 +289,12 @@ class Engine:
 
     def ltv_hidden_device(self, d_x: int, n: int, layer: int, d_hidden: int, stream: int = 0) -> None:
         self._check(self._lib.igs_ltv_hidden_device(self._h, d_x, n, layer, d_hidden, stream))
+
+
+def hash_id(s: str | bytes) -> int:
+    """igs_hash_id: the 64-bit id of an identifier string ("" -> 0)."""
+    b = s.encode() if isinstance(s, str) else bytes(s)
+    return int(abi.load_library().igs_hash_id(b, len(b)))
 
 
 from . import scoring, sharding  # noqa: E402  (reference-facing mirror + shard bookkeeping)

@@ -43,6 +43,7 @@ POST_NONE, POST_LOGISTIC = 0, 1
 SEG_VIP, SEG_HIGH, SEG_MEDIUM, SEG_LOW, SEG_CHURNING = 1, 2, 3, 4, 5
 SEQ_ALL = 0xFFFFFFFF
 PARTITION_STATIC_WORDS = 256 * 1024
+BL_DEVICE, BL_FINGERPRINT, BL_IP = 0, 1, 2
 
 rule_row_dtype = np.dtype([
     ("amount", "<i8"), ("total_deposits", "<i8"), ("total_withdrawals", "<i8"),
@@ -70,6 +71,8 @@ velocity_dtype = np.dtype([
     ("time_since_last_tx", "<u4"), ("session_duration", "<u4"), ("n_prior", "<u4"),
     ("win", window_dtype, (2, 3)),
 ])
+tx_ids_dtype = np.dtype([("device", "<u8"), ("fingerprint", "<u8"), ("ip", "<u8")])
+uniques_dtype = np.dtype([("devices_24h", "<u4"), ("ips_24h", "<u4")])
 ltv_row_dtype = np.dtype([
     ("sessions_per_week", "<f8"), ("deposit_frequency", "<f8"), ("total_deposits", "<f8"),
     ("total_withdrawals", "<f8"), ("net_revenue", "<f8"), ("bonus_conversion_rate", "<f8"),
@@ -89,6 +92,7 @@ assert tx_dtype.itemsize == 32
 assert player_row_dtype.itemsize == 96
 assert query_dtype.itemsize == 16
 assert velocity_dtype.itemsize == 128
+assert tx_ids_dtype.itemsize == 24 and uniques_dtype.itemsize == 8
 assert ltv_row_dtype.itemsize == 80
 assert ltv_result_dtype.itemsize == 32
 
@@ -125,6 +129,10 @@ class EventCols(C.Structure):
                 ("tx_type", C.c_void_p)]
 
 
+class EventIds(C.Structure):
+    _fields_ = [("device", C.c_void_p), ("ip", C.c_void_p)]
+
+
 assert C.sizeof(Config) == 104
 
 # Every symbol include/igs.h declares; tests check the built library exports each of them.
@@ -137,6 +145,9 @@ EXPORTS = [
     "igs_ltv_batch", "igs_ltv_batch_device", "igs_ltv_hidden_device",
     "igs_rule_score_from_flags", "igs_reason_codes", "igs_action_name", "igs_ltv_action_name",
     "igs_segment_name", "igs_shard_of", "igs_version",
+    "igs_load_events_ids", "igs_append_events_ids", "igs_get_uniques", "igs_get_uniques_device",
+    "igs_blacklist_load", "igs_blacklist_add", "igs_blacklist_check", "igs_blacklist_check_device",
+    "igs_score_batch_ids", "igs_score_batch_ids_device", "igs_hash_id",
 ]
 
 LIB_NAME = "libigs.so"
@@ -202,6 +213,18 @@ def load_library() -> C.CDLL:
     lib.igs_segment_name.restype = C.c_char_p
     lib.igs_shard_of.argtypes = [u64, u64, C.c_uint32]
     lib.igs_shard_of.restype = C.c_uint32
+    lib.igs_load_events_ids.argtypes = [vp, C.POINTER(EventCols), C.POINTER(EventIds), u64, C.c_uint32]
+    lib.igs_append_events_ids.argtypes = [vp, C.POINTER(EventCols), C.POINTER(EventIds), u64]
+    lib.igs_get_uniques.argtypes = [vp, vp, u64, vp]
+    lib.igs_get_uniques_device.argtypes = [vp, vp, u64, vp, vp]
+    lib.igs_blacklist_load.argtypes = [vp, i32, vp, u64]
+    lib.igs_blacklist_add.argtypes = [vp, i32, vp, u64]
+    lib.igs_blacklist_check.argtypes = [vp, vp, u64, vp]
+    lib.igs_blacklist_check_device.argtypes = [vp, vp, u64, vp, vp]
+    lib.igs_score_batch_ids.argtypes = [vp, C.POINTER(Config), vp, vp, u64, vp, vp, vp]
+    lib.igs_score_batch_ids_device.argtypes = [vp, C.POINTER(Config), vp, vp, u64, vp, vp, vp, vp]
+    lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
+    lib.igs_hash_id.restype = u64
     lib.igs_version.argtypes = []
     lib.igs_version.restype = C.c_char_p
     _lib = lib

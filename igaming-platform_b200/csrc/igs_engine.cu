@@ -146,6 +146,7 @@ void igs_engine_destroy(igs_engine* e) {
     if (e->d_model) cudaFree(e->d_model);
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
+    for (int k = 0; k < 3; ++k) igs_idset_free(&e->bl[k]);
     igs_mlp_free(e);
     delete e;
 }
@@ -260,7 +261,42 @@ int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_
     IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
     IGS_REQUIRE(e, n < 0xFFFFFFFFull, "at most 2^32-2 events per shard");
     std::lock_guard<std::mutex> lk(e->mu);
-    return igs_build_event_index(e, ev, n, n_accounts);
+    return igs_build_event_index(e, ev, nullptr, n, n_accounts);
+}
+
+int igs_load_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
+                        uint32_t n_accounts) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, ev != nullptr && ids != nullptr, "event / identifier columns are null");
+    IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
+    IGS_REQUIRE(e, n < 0xFFFFFFFFull, "at most 2^32-2 events per shard");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_build_event_index(e, ev, ids, n, n_accounts);
+}
+
+int igs_append_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, ev != nullptr && ids != nullptr, "event / identifier columns are null");
+    IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_append_event_columns(e, ev, ids, n);
+}
+
+static int blacklist_update(igs_engine* e, int kind, const uint64_t* ids, uint64_t n, bool replace) {
+    IGS_ENGINE(e);
+    if (kind != IGS_BL_DEVICE && kind != IGS_BL_FINGERPRINT && kind != IGS_BL_IP) {
+        igs_set_error(e, "unknown blacklist type: %d", kind);       // features/redis_store.go:261
+        return IGS_ERR_INVALID;
+    }
+    IGS_REQUIRE(e, n == 0 || ids != nullptr, "ids is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_idset_load(e, &e->bl[kind], ids, n, replace);
+}
+int igs_blacklist_load(igs_engine* e, int kind, const uint64_t* ids, uint64_t n) {
+    return blacklist_update(e, kind, ids, n, true);
+}
+int igs_blacklist_add(igs_engine* e, int kind, const uint64_t* ids, uint64_t n) {
+    return blacklist_update(e, kind, ids, n, false);
 }
 
 }  // extern "C"
@@ -270,7 +306,7 @@ int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n) {
     IGS_REQUIRE(e, ev != nullptr, "event columns are null");
     IGS_REQUIRE(e, n == 0 || (ev->account && ev->ts && ev->amount && ev->tx_type), "an event column is null");
     std::lock_guard<std::mutex> lk(e->mu);
-    return igs_append_event_columns(e, ev, n);
+    return igs_append_event_columns(e, ev, nullptr, n);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -397,13 +433,15 @@ int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs
 // ------------------------------------------------------------------------------------------------
 // path B
 // ------------------------------------------------------------------------------------------------
-static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const igs_tx* tx, uint64_t n,
-                            igs_result* out, float* features_out, igs_velocity* velocity_out) {
+static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const igs_tx* tx, const igs_tx_ids* ids,
+                            uint64_t n, igs_result* out, float* features_out, igs_velocity* velocity_out) {
     IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
     IGS_REQUIRE(e, n == 0 || (tx && out), "tx / out is null");
     if (n == 0) return IGS_OK;
     igs_slot& sl = e->slot[s];
     IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_tx)));
+    if (ids) IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_tx_ids)));
+    igs_tx_ids* d_ids = ids ? (igs_tx_ids*)sl.in1.p : nullptr;
     IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_result)));
     if (features_out) IGS_TRY(igs_reserve(e, &sl.aux0, n * IGS_NUM_FEATURES * sizeof(float)));
     if (velocity_out) IGS_TRY(igs_reserve(e, &sl.aux1, n * sizeof(igs_velocity)));
@@ -413,7 +451,9 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
     igs_velocity* d_vel = velocity_out ? (igs_velocity*)sl.aux1.p : nullptr;
     return run_pipelined(e, sl, n, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
         IGS_CUDA(e, cudaMemcpyAsync(d_tx + off, tx + off, cnt * sizeof(igs_tx), cudaMemcpyHostToDevice, st));
-        IGS_TRY(igs_launch_score_batch(e, cfg, d_tx + off, cnt, d_out + off,
+        if (ids)
+            IGS_CUDA(e, cudaMemcpyAsync(d_ids + off, ids + off, cnt * sizeof(igs_tx_ids), cudaMemcpyHostToDevice, st));
+        IGS_TRY(igs_launch_score_batch(e, cfg, d_tx + off, ids ? d_ids + off : nullptr, cnt, d_out + off,
                                        d_feat ? d_feat + off * IGS_NUM_FEATURES : nullptr,
                                        d_vel ? d_vel + off : nullptr, st));
         IGS_CUDA(e, cudaMemcpyAsync(out + off, d_out + off, cnt * sizeof(igs_result), cudaMemcpyDeviceToHost, st));
@@ -430,7 +470,7 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
 int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n, igs_result* out,
                     float* features_out, igs_velocity* velocity_out) {
     IGS_ENGINE(e);
-    IGS_TRY(score_batch_host(e, 0, cfg, tx, n, out, features_out, velocity_out));
+    IGS_TRY(score_batch_host(e, 0, cfg, tx, nullptr, n, out, features_out, velocity_out));
     IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
     return IGS_OK;
 }
@@ -439,7 +479,7 @@ int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const 
                           igs_result* out) {
     IGS_ENGINE(e);
     IGS_REQUIRE(e, slot >= 0 && slot < IGS_NUM_SLOTS, "slot out of range");
-    return score_batch_host(e, slot, cfg, tx, n, out, nullptr, nullptr);
+    return score_batch_host(e, slot, cfg, tx, nullptr, n, out, nullptr, nullptr);
 }
 
 int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
@@ -448,8 +488,70 @@ int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d
     IGS_ENGINE(e);
     IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
     IGS_REQUIRE(e, n == 0 || (d_tx && d_out), "tx / out is null");
-    return igs_launch_score_batch(e, cfg, d_tx, n, d_out, d_features_out, d_velocity_out,
+    return igs_launch_score_batch(e, cfg, d_tx, nullptr, n, d_out, d_features_out, d_velocity_out,
                                   (cudaStream_t)stream);
+}
+
+int igs_score_batch_ids(igs_engine* e, const igs_config* cfg, const igs_tx* tx, const igs_tx_ids* ids, uint64_t n,
+                        igs_result* out, float* features_out, igs_velocity* velocity_out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || ids != nullptr, "ids is null");
+    IGS_TRY(score_batch_host(e, 0, cfg, tx, ids, n, out, features_out, velocity_out));
+    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
+    return IGS_OK;
+}
+
+int igs_score_batch_ids_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
+                               uint64_t n, igs_result* d_out, float* d_features_out,
+                               igs_velocity* d_velocity_out, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
+    IGS_REQUIRE(e, n == 0 || (d_tx && d_ids && d_out), "tx / ids / out is null");
+    return igs_launch_score_batch(e, cfg, d_tx, d_ids, n, d_out, d_features_out, d_velocity_out,
+                                  (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// identifiers: uniques and blacklist checks
+// ------------------------------------------------------------------------------------------------
+int igs_get_uniques(igs_engine* e, const igs_query* q, uint64_t n, igs_uniques* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (q && out), "q / out is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[0];
+    IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_query)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n * sizeof(igs_uniques)));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, q, n * sizeof(igs_query), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_uniques(e, (const igs_query*)sl.in0.p, n, (igs_uniques*)sl.out0.p, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_uniques), cudaMemcpyDeviceToHost, sl.stream));
+    IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
+    return IGS_OK;
+}
+
+int igs_get_uniques_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (d_q && d_out), "q / out is null");
+    return igs_launch_uniques(e, d_q, n, d_out, (cudaStream_t)stream);
+}
+
+int igs_blacklist_check(igs_engine* e, const igs_tx_ids* ids, uint64_t n, uint8_t* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (ids && out), "ids / out is null");
+    if (n == 0) return IGS_OK;
+    igs_slot& sl = e->slot[0];
+    IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_tx_ids)));
+    IGS_TRY(igs_reserve(e, &sl.out0, n));
+    IGS_CUDA(e, cudaMemcpyAsync(sl.in1.p, ids, n * sizeof(igs_tx_ids), cudaMemcpyHostToDevice, sl.stream));
+    IGS_TRY(igs_launch_blacklist_check(e, (const igs_tx_ids*)sl.in1.p, n, (uint8_t*)sl.out0.p, sl.stream));
+    IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n, cudaMemcpyDeviceToHost, sl.stream));
+    IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
+    return IGS_OK;
+}
+
+int igs_blacklist_check_device(igs_engine* e, const igs_tx_ids* d_ids, uint64_t n, uint8_t* d_out, void* stream) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, n == 0 || (d_ids && d_out), "ids / out is null");
+    return igs_launch_blacklist_check(e, d_ids, n, d_out, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------------

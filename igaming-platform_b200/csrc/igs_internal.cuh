@@ -56,6 +56,13 @@ struct igs_slot {
     igs_buf      in0, in1, out0, aux0, aux1;
 };
 
+// one blacklist set: open-addressing table of 64-bit ids, at most half full
+struct igs_idset {
+    uint64_t* slots = nullptr;
+    uint64_t  cap = 0;        // power of two, 0 = no table
+    uint64_t  count = 0;      // distinct ids stored
+};
+
 // event history index (see velocity.cuh / k_velocity.cu)
 struct igs_prefix_rec;
 struct igs_tail_rec;
@@ -95,10 +102,16 @@ struct igs_engine {
     uint32_t* raw_ts = nullptr;
     int64_t*  raw_amount = nullptr;
     uint8_t*  raw_type = nullptr;
+    uint64_t* raw_device = nullptr;   // identifier columns, only when the history carries identifiers
+    uint64_t* raw_ip = nullptr;
+    bool      has_event_ids = false;
     uint64_t  n_raw = 0, cap_raw = 0;
     igs_event_index ev;
     bool has_events = false;
     std::vector<igs_buf> build_pool;  // scratch of the index build, kept between igs_append_events calls
+
+    // blacklist sets (idset.cuh / k_ids.cu), indexed by IGS_BL_*
+    igs_idset bl[3];
 
     // MLP
     void* d_mlp = nullptr;        // see k_ltv.cu
@@ -134,13 +147,22 @@ int igs_reserve(igs_engine* e, igs_buf* b, size_t bytes);
 int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
                               const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
                               uint8_t* d_leaf_idx, cudaStream_t stream);
-int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
-                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
+                           uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            cudaStream_t stream);
 int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
                         cudaStream_t stream);
-int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts);
-int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n);   // append + rebuild
+int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out, cudaStream_t stream);
+// ids == nullptr: no identifier columns (load) / events without identifiers (append)
+int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
+                          uint32_t n_accounts);
+int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids,
+                             uint64_t n);   // append + rebuild
+// blacklist sets (k_ids.cu)
+int igs_idset_load(igs_engine* e, igs_idset* s, const uint64_t* ids, uint64_t n, bool replace);
+void igs_idset_free(igs_idset* s);
+int igs_launch_blacklist_check(igs_engine* e, const igs_tx_ids* d_ids, uint64_t n, uint8_t* d_out,
+                               cudaStream_t stream);
 void igs_free_event_index(igs_engine* e);
 int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);

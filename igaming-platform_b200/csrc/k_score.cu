@@ -26,6 +26,7 @@
 //                smem tile — the assembled row never touches HBM (SURVEY K3-lookup + K4 fused).
 // Replaces: ScoringEngine.Score (scoring/engine.go:262-323) incl. extractFeatures (:326-417),
 // ONNXModel.PredictBatch (ml/onnx_model.go:311-326), Normalize (:169-184).
+#include "idset.cuh"
 #include "igs_internal.cuh"
 #include "igs_math.cuh"
 #include "velocity.cuh"
@@ -69,6 +70,9 @@ struct ScoreParams {
     igs_index_view ix;
     float* features_out;
     igs_velocity* velocity_out;
+    const igs_tx_ids* tx_ids;      // optional: rule 8 evaluated against the blacklist sets
+    igs_idset_view bl[3];
+    int uniques_from_index;        // the history carries identifiers: ignore the tx's unique counts
     // common
     igs_result* out;
     uint8_t* leaf_idx;
@@ -229,9 +233,22 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
         dst[0] = in_range ? __ldg(src + 0) : z;
         dst[1] = in_range ? __ldg(src + 1) : z;
     }
+    // Blacklist.Check (scoring/engine.go:469-475): the probes are in flight while the velocity lookup runs
+    igs_idset_probe3 blp;
+    const bool check_bl = p.tx_ids != nullptr && in_range;
+    if (check_bl) {
+        const igs_tx_ids id = p.tx_ids[row];
+        igs_idset_probe_begin(p.bl, id.device, id.fingerprint, id.ip, &blp);
+    }
     igs_velocity_a16 vb;
-    igs_velocity_lookup(p.ix, in_range ? t.account : 0xFFFFFFFFu, t.ts, t.seq_limit, &vb.v);
+    igs_uniques uq;
+    igs_velocity_lookup(p.ix, in_range ? t.account : 0xFFFFFFFFu, t.ts, t.seq_limit, &vb.v, &uq);
     const igs_velocity& v = vb.v;
+    // PFCOUNT :80-81 — from the history when it carries identifiers, else the host's counts
+    const unsigned uniq_dev = p.uniques_from_index ? uq.devices_24h : t.unique_devices_24h;
+    const unsigned uniq_ip = p.uniques_from_index ? uq.ips_24h : t.unique_ips_24h;
+    unsigned tbits = t.bits;
+    if (check_bl && igs_idset_probe_end(p.bl, blp)) tbits |= IGS_BIT_BLACKLISTED;
     if (p.velocity_out && in_range) {
         uint4* dst = reinterpret_cast<uint4*>(p.velocity_out + row);
 #pragma unroll
@@ -266,8 +283,8 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
     put(2, igs_min_max(__uint2float_rn(v.tx_count_1h), 200.f));
     put(3, igs_log_transform(__ll2float_rn(v.tx_sum_1h)));
     put(4, avg1h);
-    put(5, igs_min_max(__uint2float_rn(t.unique_devices_24h), 10.f));
-    put(6, igs_min_max(__uint2float_rn(t.unique_ips_24h), 20.f));
+    put(5, igs_min_max(__uint2float_rn(uniq_dev), 10.f));
+    put(6, igs_min_max(__uint2float_rn(uniq_ip), 20.f));
     put(7, 0.f);                                   // IPCountryChanges: never set by the reference
     put(8, 0.f);                                   // DeviceAge: never set
     put(9, igs_min_max(__int2float_rn(account_age), 365.f));
@@ -307,9 +324,9 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
     r->tx_count_1m = v.tx_count_1m;
     r->tslt = v.time_since_last_tx;
     r->deposit_count = (unsigned)pl.r.deposit_count;
-    r->uniq_dev = t.unique_devices_24h;
-    r->uniq_ip = t.unique_ips_24h;
-    r->bits = (t.bits & (IGS_BIT_VPN | IGS_BIT_PROXY | IGS_BIT_TOR | IGS_BIT_BLACKLISTED | IGS_BIT_VALID)) |
+    r->uniq_dev = uniq_dev;
+    r->uniq_ip = uniq_ip;
+    r->bits = (tbits & (IGS_BIT_VPN | IGS_BIT_PROXY | IGS_BIT_TOR | IGS_BIT_BLACKLISTED | IGS_BIT_VALID)) |
               (bonus_only ? IGS_BIT_BONUS_ONLY : 0u);
     r->account_age = account_age;
     r->tx_type = t.tx_type;
@@ -529,8 +546,8 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
     return launch(e, kSrcFeatures, p, leaves, stream);
 }
 
-int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, uint64_t n,
-                           igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
+int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
+                           uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            cudaStream_t stream) {
     if (n == 0) return IGS_OK;
     int rc = check_model(e, cfg);
@@ -543,6 +560,9 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     p.ix = igs_index_view_of(e);       // n_accounts = 0 when no history is loaded: empty velocity
     p.features_out = d_features_out;
     p.velocity_out = d_velocity_out;
+    p.tx_ids = d_ids;
+    igs_blacklist_views(e, p.bl);
+    p.uniques_from_index = e->has_events && e->has_event_ids;
     p.out = d_out;
     p.n = n;
     return launch(e, kSrcTx, p, false, stream);

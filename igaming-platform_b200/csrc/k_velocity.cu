@@ -13,12 +13,19 @@
 //      {distinct count, per-type count, per-type sum} and, per event, the inclusive segmented
 //      {chain sum with head = new account || gap > 3600, session start with head = new account ||
 //      gap > 1800}.  A 256-ary hierarchy of warp-shuffle passes (reduce up, scan the top, apply down).
+//   5. (histories that carry identifiers, igs_load_events_ids) per identifier column — device, IP — the
+//      PFADD + EXPIRE 24h key of :141-152 as of every event: compact the events that carry an identifier,
+//      cut them into chains (gap > 86400 or new account), find each event's previous occurrence of the
+//      same identifier in its chain through a stable radix sort on a 30-bit hash of the identifier
+//      (exact: equal hashes are resolved by comparing the 64-bit ids), and count first occurrences per
+//      chain with a prefix sum.
 // Query (igs_get_velocity*, and inlined into the fused score kernel): velocity.cuh.
 #include <string.h>
 
 #include <algorithm>
 #include <vector>
 
+#include "idset.cuh"
 #include "igs_internal.cuh"
 #include "velocity.cuh"
 
@@ -456,7 +463,8 @@ k_vs_apply_elems(VCols c, const VScan* __restrict__ tile_excl, igs_prefix_rec* _
             p.sum[0] = before.s0; p.sum[1] = before.s1;
             pre[i] = p;
             igs_tail_rec tl;
-            tl.chain_sum = upto.chain; tl.sess_start = upto.st; tl.pad = 0;
+            tl.chain_sum = upto.chain; tl.sess_start = upto.st;
+            tl.dev_ts = tl.ip_ts = 0; tl.dev_cnt = tl.ip_cnt = 0; tl.pad[0] = tl.pad[1] = 0;   // step 5 fills these
             tail[i] = tl;
             if (i == c.n - 1) {                                  // pre[n]: totals over the whole history
                 igs_prefix_rec q;
@@ -483,6 +491,123 @@ k_velocity(igs_index_view ix, const igs_query* __restrict__ q, unsigned long lon
     uint4* dst = reinterpret_cast<uint4*>(out + i);
 #pragma unroll
     for (int k = 0; k < (int)(sizeof(igs_velocity) / 16); ++k) dst[k] = v.q[k];
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_uniques(igs_index_view ix, const igs_query* __restrict__ q, unsigned long long n,
+          igs_uniques* __restrict__ out) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 qq = __ldg(reinterpret_cast<const uint4*>(q + i));
+    igs_velocity_a16 v;
+    igs_uniques u;
+    igs_velocity_lookup(ix, qq.x, qq.y, qq.z, &v.v, &u);
+    out[i] = u;
+}
+
+// ------------------------------------------------------------------------------------------------
+// identifier columns (step 5)
+// ------------------------------------------------------------------------------------------------
+constexpr int kIdKeyBits = 30;       // 3 radix passes of 10 bits
+
+// id_s[p] = identifier of sorted event p; flag[p] = 1 iff it has one
+__global__ void k_id_gather(const uint64_t* __restrict__ raw, const uint32_t* __restrict__ seq, uint32_t n,
+                            uint64_t* __restrict__ id_s, uint32_t* __restrict__ flag) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint64_t v = __ldg(raw + __ldg(seq + p));
+    id_s[p] = v;
+    flag[p] = v != 0;
+}
+
+// compacted sequence k = 0..m-1 of the events that carry an identifier (fex = exclusive scan of flag)
+__global__ void k_id_compact(const uint64_t* __restrict__ id_s, const uint32_t* __restrict__ fex, uint32_t n,
+                             uint32_t* __restrict__ cpos, uint64_t* __restrict__ cid) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint64_t v = __ldg(id_s + p);
+    if (v) {
+        const uint32_t k = __ldg(fex + p);
+        cpos[k] = p;
+        cid[k] = v;
+    }
+}
+
+// chain heads: the key did not exist when event k arrived (new account, or the previous PFADD was more than
+// 24h earlier and the key had expired, :144/:151)
+__global__ void k_id_heads(const uint32_t* __restrict__ cpos, const uint32_t* __restrict__ acct,
+                           const uint32_t* __restrict__ ts, uint32_t m, uint8_t* __restrict__ head,
+                           uint32_t* __restrict__ hsum) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    bool h = k == 0;
+    if (!h) {
+        const uint32_t p = __ldg(cpos + k), q = __ldg(cpos + k - 1);
+        h = __ldg(acct + p) != __ldg(acct + q) ||
+            (long long)__ldg(ts + p) - (long long)__ldg(ts + q) > 86400;
+    }
+    head[k] = h;
+    hsum[k] = h;
+}
+
+// hsum holds the exclusive scan of the head flags on entry and the chain number of k on exit
+__global__ void k_id_chain(const uint8_t* __restrict__ head, uint32_t* __restrict__ hsum,
+                           const uint64_t* __restrict__ cid, uint32_t m, uint32_t* __restrict__ chain_head,
+                           uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    const uint32_t h = __ldg(head + k);
+    const uint32_t g = hsum[k] + h - 1;
+    hsum[k] = g;
+    if (h) chain_head[g] = k;
+    keys[k] = igs_idset_mix(__ldg(cid + k)) >> (64 - kIdKeyBits);
+    vals[k] = k;
+}
+
+// After the stable sort by hash, the entries of one hash value are in event order, so the events of one
+// chain are adjacent; the first earlier entry of the same chain with the same 64-bit id — normally the
+// entry right before — is a previous occurrence.  (Different ids with equal hashes only lengthen the walk.)
+__global__ void k_id_new(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                         const uint32_t* __restrict__ chain, const uint64_t* __restrict__ cid, uint32_t m,
+                         uint8_t* __restrict__ isnew8, uint32_t* __restrict__ isnew32) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= m) return;
+    const uint32_t k = __ldg(vals + r);
+    const uint64_t key = __ldg(keys + r), id = __ldg(cid + k);
+    const uint32_t g = __ldg(chain + k);
+    bool nw = true;
+    for (uint32_t rr = r; rr-- > 0;) {
+        if (__ldg(keys + rr) != key) break;
+        const uint32_t k2 = __ldg(vals + rr);
+        if (__ldg(chain + k2) != g) break;
+        if (__ldg(cid + k2) == id) { nw = false; break; }
+    }
+    isnew8[k] = nw;
+    isnew32[k] = nw;
+}
+
+// state of the key as of every sorted event p (with or without an identifier of its own)
+template <int kCol>
+__global__ void k_id_expand(const uint64_t* __restrict__ id_s, const uint32_t* __restrict__ fex,
+                            const uint32_t* __restrict__ cpos, const uint32_t* __restrict__ chain,
+                            const uint32_t* __restrict__ chain_head, const uint32_t* __restrict__ nex,
+                            const uint8_t* __restrict__ isnew8, const uint32_t* __restrict__ acct,
+                            const uint32_t* __restrict__ ts, uint32_t n, igs_tail_rec* __restrict__ tail) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t kk = __ldg(fex + p) + (__ldg(id_s + p) != 0);   // identifier events at or before p
+    uint32_t cnt = 0, t = 0;
+    if (kk) {
+        const uint32_t k = kk - 1, q = __ldg(cpos + k);
+        if (__ldg(acct + q) == __ldg(acct + p)) {
+            const uint32_t h = __ldg(chain_head + __ldg(chain + k));
+            cnt = __ldg(nex + k) + __ldg(isnew8 + k) - __ldg(nex + h);   // first occurrences in [h, k]
+            t = __ldg(ts + q);
+        }
+    }
+    const uint16_t c16 = (uint16_t)min(cnt, 65535u);
+    if (kCol == 0) { tail[p].dev_ts = t; tail[p].dev_cnt = c16; }
+    else           { tail[p].ip_ts = t;  tail[p].ip_cnt = c16; }
 }
 
 int bits_for(uint64_t v) {   // number of bits needed to represent v
@@ -536,7 +661,11 @@ static void free_raw_events(igs_engine* e) {
     if (e->raw_ts) cudaFree(e->raw_ts);
     if (e->raw_amount) cudaFree(e->raw_amount);
     if (e->raw_type) cudaFree(e->raw_type);
+    if (e->raw_device) cudaFree(e->raw_device);
+    if (e->raw_ip) cudaFree(e->raw_ip);
     e->raw_account = e->raw_ts = nullptr; e->raw_amount = nullptr; e->raw_type = nullptr;
+    e->raw_device = e->raw_ip = nullptr;
+    e->has_event_ids = false;
     e->n_raw = e->cap_raw = 0;
 }
 
@@ -558,7 +687,8 @@ void igs_free_event_index(igs_engine* e) {
 }
 
 // Appends n host events to the device-resident raw columns (capacity grows by 1.5x).
-static int append_raw(igs_engine* e, const igs_event_cols* ev, uint64_t n, cudaStream_t st) {
+static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
+                      cudaStream_t st) {
     const uint64_t need = e->n_raw + n;
     if (need > e->cap_raw) {
         const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
@@ -567,6 +697,18 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, uint64_t n, cudaS
         IGS_CUDA(e, cudaMalloc(&t, cap * 4));
         IGS_CUDA(e, cudaMalloc(&m, cap * 8));
         IGS_CUDA(e, cudaMalloc(&y, cap));
+        if (e->has_event_ids) {
+            uint64_t *d = nullptr, *p = nullptr;
+            IGS_CUDA(e, cudaMalloc(&d, cap * 8));
+            IGS_CUDA(e, cudaMalloc(&p, cap * 8));
+            if (e->n_raw) {
+                IGS_CUDA(e, cudaMemcpyAsync(d, e->raw_device, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
+                IGS_CUDA(e, cudaMemcpyAsync(p, e->raw_ip, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
+                IGS_CUDA(e, cudaStreamSynchronize(st));
+            }
+            if (e->raw_device) { cudaFree(e->raw_device); cudaFree(e->raw_ip); }
+            e->raw_device = d; e->raw_ip = p;
+        }
         if (e->n_raw) {
             IGS_CUDA(e, cudaMemcpyAsync(a, e->raw_account, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
             IGS_CUDA(e, cudaMemcpyAsync(t, e->raw_ts, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
@@ -584,6 +726,16 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, uint64_t n, cudaS
         IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyHostToDevice, st));
         IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyHostToDevice, st));
         IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyHostToDevice, st));
+        if (e->has_event_ids) {       // a missing column = events without that identifier
+            if (ids && ids->device)
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_device + e->n_raw, ids->device, n * 8, cudaMemcpyHostToDevice, st));
+            else
+                IGS_CUDA(e, cudaMemsetAsync(e->raw_device + e->n_raw, 0, n * 8, st));
+            if (ids && ids->ip)
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_ip + e->n_raw, ids->ip, n * 8, cudaMemcpyHostToDevice, st));
+            else
+                IGS_CUDA(e, cudaMemsetAsync(e->raw_ip + e->n_raw, 0, n * 8, st));
+        }
     }
     e->n_raw = need;
     return IGS_OK;
@@ -591,9 +743,13 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, uint64_t n, cudaS
 
 static int build_index_from_raw(igs_engine* e, uint32_t n_accounts);
 
-int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n) {
+int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
     if (!e->has_events) {
         igs_set_error(e, "igs_append_events needs a loaded history (igs_load_events, possibly with n = 0)");
+        return IGS_ERR_STATE;
+    }
+    if (ids && !e->has_event_ids) {
+        igs_set_error(e, "the loaded history carries no identifiers (load it with igs_load_events_ids)");
         return IGS_ERR_STATE;
     }
     if (e->n_raw + n >= 0xFFFFFFFFull) {
@@ -603,7 +759,7 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n
     IGS_CUDA(e, cudaDeviceSynchronize());
     const uint64_t before = e->n_raw;
     const uint32_t n_accounts = e->ev.n_accounts;   // the rebuild resets e->ev
-    int rc = append_raw(e, ev, n, e->slot[0].stream);
+    int rc = append_raw(e, ev, ids, n, e->slot[0].stream);
     if (rc != IGS_OK) return rc;
     rc = build_index_from_raw(e, n_accounts);
     if (rc != IGS_OK) {                      // e.g. an account index out of range: drop the rejected batch
@@ -616,15 +772,86 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, uint64_t n
     return rc;
 }
 
-int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, uint64_t n64, uint32_t n_accounts) {
+int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,
+                          uint32_t n_accounts) {
     IGS_CUDA(e, cudaDeviceSynchronize());
     igs_free_event_index(e);
-    int rc = append_raw(e, ev, n64, e->slot[0].stream);
+    e->has_event_ids = ids != nullptr;
+    int rc = append_raw(e, ev, ids, n64, e->slot[0].stream);
     if (rc != IGS_OK) return rc;
     rc = build_index_from_raw(e, n_accounts);
     if (rc != IGS_OK) igs_free_event_index(e);
     else free_build_pool(e);           // a bulk load does not keep ~70 B/event of scratch around
     return rc;
+}
+
+// stable LSD radix sort of (key, value) pairs on the low passes * digit_bits key bits; returns the index of
+// the buffer pair that holds the result
+static int radix_sort_pairs(igs_engine* e, uint64_t* keys[2], uint32_t* vals[2], uint32_t n, int passes,
+                            int digit_bits, uint32_t* d_hist, uint32_t* d_scan_scratch, cudaStream_t st, int* cur_out) {
+    const uint32_t bins = 1u << digit_bits;
+    const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
+    const uint32_t hist_elems = bins * nb_sort;
+    int cur = 0;
+    for (int p = 0; p < passes; ++p) {
+        const int shift = p * digit_bits;
+        k_radix_hist<<<nb_sort, kThreads, bins * sizeof(uint32_t), st>>>(keys[cur], n, shift, bins, d_hist, nb_sort);
+        IGS_CUDA(e, cudaGetLastError());
+        int rc = scan_u32(e, d_hist, hist_elems, d_scan_scratch, st);
+        if (rc != IGS_OK) return rc;
+        k_radix_scatter<<<nb_sort, kThreads, (size_t)bins * kSortWarps * sizeof(uint32_t), st>>>(
+            keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, bins, d_hist, nb_sort);
+        IGS_CUDA(e, cudaGetLastError());
+        cur ^= 1;
+    }
+    *cur_out = cur;
+    return IGS_OK;
+}
+
+struct IdScratch {
+    uint64_t* keys[2]; uint32_t* vals[2];
+    uint64_t *id_s, *cid;
+    uint32_t *fex, *cpos, *chain, *chain_head, *nex, *hist, *scan_scratch;
+    uint8_t *head, *isnew8;
+};
+
+// Step 5 for one identifier column: fills tail[p].{dev,ip}_{ts,cnt}.  d_acct / e->ev.ts / e->ev.seq are the
+// sorted columns of the build in progress.
+template <int kCol>
+static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, const uint32_t* d_acct, uint32_t n,
+                           cudaStream_t st) {
+    igs_event_index& x = e->ev;
+    const uint32_t nb = (n + kThreads - 1) / kThreads;
+    k_id_gather<<<nb, kThreads, 0, st>>>(raw, x.seq, n, s.id_s, s.fex);
+    IGS_CUDA(e, cudaGetLastError());
+    int rc = scan_u32(e, s.fex, n, s.scan_scratch, st);
+    if (rc != IGS_OK) return rc;
+    uint32_t last_ex = 0; uint64_t last_id = 0;
+    IGS_CUDA(e, cudaMemcpyAsync(&last_ex, s.fex + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+    IGS_CUDA(e, cudaMemcpyAsync(&last_id, s.id_s + (n - 1), 8, cudaMemcpyDeviceToHost, st));
+    IGS_CUDA(e, cudaStreamSynchronize(st));
+    const uint32_t m = last_ex + (last_id != 0);       // events that carry this identifier
+    if (m == 0) return IGS_OK;                         // the tail records already say "no key"
+    const uint32_t mb = (m + kThreads - 1) / kThreads;
+    k_id_compact<<<nb, kThreads, 0, st>>>(s.id_s, s.fex, n, s.cpos, s.cid);
+    IGS_CUDA(e, cudaGetLastError());
+    k_id_heads<<<mb, kThreads, 0, st>>>(s.cpos, d_acct, x.ts, m, s.head, s.chain);
+    IGS_CUDA(e, cudaGetLastError());
+    rc = scan_u32(e, s.chain, m, s.scan_scratch, st);
+    if (rc != IGS_OK) return rc;
+    k_id_chain<<<mb, kThreads, 0, st>>>(s.head, s.chain, s.cid, m, s.chain_head, s.keys[0], s.vals[0]);
+    IGS_CUDA(e, cudaGetLastError());
+    int cur = 0;
+    rc = radix_sort_pairs(e, s.keys, s.vals, m, kIdKeyBits / 10, 10, s.hist, s.scan_scratch, st, &cur);
+    if (rc != IGS_OK) return rc;
+    k_id_new<<<mb, kThreads, 0, st>>>(s.keys[cur], s.vals[cur], s.chain, s.cid, m, s.isnew8, s.nex);
+    IGS_CUDA(e, cudaGetLastError());
+    rc = scan_u32(e, s.nex, m, s.scan_scratch, st);
+    if (rc != IGS_OK) return rc;
+    k_id_expand<kCol><<<nb, kThreads, 0, st>>>(s.id_s, s.fex, s.cpos, s.chain, s.chain_head, s.nex, s.isnew8, d_acct,
+                                               x.ts, n, x.tail);
+    IGS_CUDA(e, cudaGetLastError());
+    return IGS_OK;
 }
 
 // (Re)builds the index from the raw columns e->raw_* [0, n_raw).
@@ -702,16 +929,9 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     k_make_keys<<<nb_el, kThreads, 0, st>>>(d_acct_in, d_ts_in, n, ts_min, ts_bits, d_keys[0], d_vals[0]);
     IGS_CUDA(e, cudaGetLastError());
     int cur = 0;
-    for (int p = 0; p < passes; ++p) {
-        const int shift = p * digit_bits;
-        k_radix_hist<<<nb_sort, kThreads, bins * sizeof(uint32_t), st>>>(d_keys[cur], n, shift, bins, d_hist, nb_sort);
-        IGS_CUDA(e, cudaGetLastError());
-        int rc = scan_u32(e, d_hist, hist_elems, d_scan_scratch, st);
+    {
+        const int rc = radix_sort_pairs(e, d_keys, d_vals, n, passes, digit_bits, d_hist, d_scan_scratch, st, &cur);
         if (rc != IGS_OK) return rc;
-        k_radix_scatter<<<nb_sort, kThreads, (size_t)bins * kSortWarps * sizeof(uint32_t), st>>>(
-            d_keys[cur], d_vals[cur], d_keys[cur ^ 1], d_vals[cur ^ 1], n, shift, bins, d_hist, nb_sort);
-        IGS_CUDA(e, cudaGetLastError());
-        cur ^= 1;
     }
 
     // ---- sorted columns, segments, distinct flags -----------------------------------------------
@@ -752,8 +972,41 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     IGS_CUDA(e, cudaGetLastError());
     k_vs_apply_elems<<<g1, kThreads, 0, st>>>(cols, d_agg1, x.pre, x.tail);
     IGS_CUDA(e, cudaGetLastError());
+
+    // ---- identifier columns ---------------------------------------------------------------------
+    if (e->has_event_ids) {
+        IdScratch is;
+        is.keys[0] = d_keys[0]; is.keys[1] = d_keys[1]; is.vals[0] = d_vals[0]; is.vals[1] = d_vals[1];   // the sort is done with them
+        IGS_CUDA(e, sc.alloc(&is.id_s, n));
+        IGS_CUDA(e, sc.alloc(&is.fex, n));
+        IGS_CUDA(e, sc.alloc(&is.cpos, n));
+        IGS_CUDA(e, sc.alloc(&is.cid, n));
+        IGS_CUDA(e, sc.alloc(&is.head, n));
+        IGS_CUDA(e, sc.alloc(&is.chain, n));
+        IGS_CUDA(e, sc.alloc(&is.chain_head, n));
+        IGS_CUDA(e, sc.alloc(&is.isnew8, n));
+        IGS_CUDA(e, sc.alloc(&is.nex, n));
+        IGS_CUDA(e, sc.alloc(&is.hist, (size_t)(1u << 10) * nb_sort));
+        IGS_CUDA(e, sc.alloc(&is.scan_scratch, scan_u32_scratch_elems(std::max<uint32_t>((1u << 10) * nb_sort, n))));
+        int rc = build_id_column<0>(e, is, e->raw_device, d_acct, n, st);
+        if (rc != IGS_OK) return rc;
+        rc = build_id_column<1>(e, is, e->raw_ip, d_acct, n, st);
+        if (rc != IGS_OK) return rc;
+    }
     IGS_CUDA(e, cudaStreamSynchronize(st));
     e->has_events = true;
+    return IGS_OK;
+}
+
+int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out, cudaStream_t stream) {
+    if (!e->has_events || !e->has_event_ids) {
+        igs_set_error(e, "no event history with identifiers loaded (igs_load_events_ids)");
+        return IGS_ERR_STATE;
+    }
+    if (n == 0) return IGS_OK;
+    const unsigned long long nb = (n + kThreads - 1) / kThreads;
+    k_uniques<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
+    IGS_CUDA(e, cudaGetLastError());
     return IGS_OK;
 }
 

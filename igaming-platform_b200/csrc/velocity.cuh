@@ -13,6 +13,8 @@
 //   last_tx       = L iff t-L <= 7d (:155);  session_start = head of the gap<=1800 chain iff
 //                   t-L <= 1800 (:158-160)
 //   extension     = per-type (bet, deposit) count / sum over [t-W, t], W = 1m, 1h, 24h, multiset
+//   uniques       = distinct identifiers of the trailing chain (gaps <= 86400) of the prior events that
+//                   carried one, iff t - (ts of the last of them) <= 86400   (PFADD/EXPIRE :141-152)
 #pragma once
 
 #include <cuda_runtime.h>
@@ -29,12 +31,19 @@ struct __align__(32) igs_prefix_rec {
     uint32_t pad;
     int64_t  sum[2];    // their amounts
 };
-// inclusive chain columns of sorted event i
-struct __align__(16) igs_tail_rec {
+// inclusive chain columns of sorted event i — one 32-byte sector, so the identifier columns ride
+// along with the load the chain columns need anyway
+struct __align__(32) igs_tail_rec {
     int64_t  chain_sum;   // sum over the maximal chain (consecutive gaps <= 3600) ending at i
     uint32_t sess_start;  // ts of the first event of the gap<=1800 chain ending at i
-    uint32_t pad;
+    // PFADD + EXPIRE 24h keys (features/redis_store.go:141-152) as of event i, per key: ts of the
+    // account's last event <= i that carried an identifier, and the number of distinct identifiers in
+    // its chain (gaps <= 86400 between consecutive such events).  cnt == 0: no such event.
+    uint32_t dev_ts, ip_ts;
+    uint16_t dev_cnt, ip_cnt;
+    uint32_t pad[2];
 };
+static_assert(sizeof(igs_tail_rec) == 32, "one sector per tail record");
 
 // a velocity block that can be moved with 16-byte loads/stores
 union __align__(16) igs_velocity_a16 {
@@ -67,7 +76,9 @@ __device__ __forceinline__ uint32_t igs_lower_ts(const uint32_t* __restrict__ ts
 }
 
 __device__ __forceinline__ void igs_velocity_lookup(const igs_index_view& ix, uint32_t account,
-                                                    uint32_t t, uint32_t seq_limit, igs_velocity* v) {
+                                                    uint32_t t, uint32_t seq_limit, igs_velocity* v,
+                                                    igs_uniques* uq = nullptr) {
+    if (uq) uq->devices_24h = uq->ips_24h = 0;
     v->tx_sum_1h = 0;
     v->tx_count_1m = v->tx_count_5m = v->tx_count_1h = 0;
     v->time_since_last_tx = v->session_duration = v->n_prior = 0;
@@ -114,7 +125,17 @@ __device__ __forceinline__ void igs_velocity_lookup(const igs_index_view& ix, ui
         v->win[ty][2].sum = pu.sum[ty] - p86400.sum[ty];
     }
     const long long gap = now - L;
-    const igs_tail_rec tl = ix.tail[u - 1];
+    union __align__(16) { igs_tail_rec r; uint4 q[2]; } tlu;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(ix.tail + (u - 1));
+        tlu.q[0] = __ldg(src);
+        if (uq) tlu.q[1] = __ldg(src + 1);
+    }
+    const igs_tail_rec& tl = tlu.r;
+    if (uq) {
+        if (tl.dev_cnt && now - (long long)tl.dev_ts <= 86400) uq->devices_24h = tl.dev_cnt;
+        if (tl.ip_cnt && now - (long long)tl.ip_ts <= 86400) uq->ips_24h = tl.ip_cnt;
+    }
     if (gap <= 3600) v->tx_sum_1h = tl.chain_sum;
     if (gap <= 7 * 24 * 3600) v->time_since_last_tx = (uint32_t)gap;
     if (gap <= 1800) v->session_duration = (uint32_t)(now - (long long)tl.sess_start);

@@ -226,6 +226,30 @@ typedef struct igs_velocity {
     igs_window win[2][3];          /* [IGS_TX_BET|IGS_TX_DEPOSIT][1m,1h,24h]                     */
 } igs_velocity;
 
+/* Identifiers — device id, browser fingerprint, IP (ScoreRequest.DeviceID / Fingerprint / IP,
+ * scoring/engine.go:45-47; TransactionEvent.DeviceID / IP, features/redis_store.go:52-55) — cross
+ * this ABI as 64-bit ids: igs_hash_id() of the string.  Id 0 is the empty string, which the
+ * reference skips everywhere (`if event.DeviceID != ""` redis_store.go:141,148; :271-279).
+ * Distinct strings are told apart by their 64-bit ids only (collision odds 2^-64 per pair).     */
+typedef struct igs_event_ids {      /* columns parallel to igs_event_cols; a NULL column = all empty */
+    const uint64_t* device;
+    const uint64_t* ip;
+} igs_event_ids;
+typedef struct igs_tx_ids {         /* one per scored tx, parallel to igs_tx                      */
+    uint64_t device;
+    uint64_t fingerprint;
+    uint64_t ip;
+} igs_tx_ids;
+/* RealTimeFeatures.UniqueDevices24h / UniqueIPs24h (features/redis_store.go:44-45).              */
+typedef struct igs_uniques {
+    uint32_t devices_24h;
+    uint32_t ips_24h;
+} igs_uniques;
+/* The three blacklist sets, features/redis_store.go:245-247.                                     */
+#define IGS_BL_DEVICE      0
+#define IGS_BL_FINGERPRINT 1
+#define IGS_BL_IP          2
+
 /* Tree ensemble: n_trees complete depth-8 trees in implicit heap order (node i has children
  * 2i+1 / 2i+2; leaf j of the bottom level follows internal node 127+j/2).  Branch rule =
  * ONNX BRANCH_LEQ: go left iff x[feat] <= thr; NaN goes right.  margin = base_score +
@@ -368,6 +392,56 @@ int igs_score_batch_device(igs_engine* e, const igs_config* cfg, const igs_tx* d
                            igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            void* stream);
 
+/* ------------------------------------------------------------------------------------------ */
+/* identifiers on the device: exact unique devices / IPs per account and the      */
+/* blacklist sets, so that R3, R4 and R8 need no host-side lookups                               */
+/* ------------------------------------------------------------------------------------------ */
+
+/* igs_load_events / igs_append_events with the events' device and IP identifiers — the PFADD +
+ * EXPIRE 24h pair of UpdateRealTimeFeatures (features/redis_store.go:141-152).  A history loaded
+ * through igs_load_events_ids "carries identifiers": from then on every scoring call on this
+ * engine takes UniqueDevices24h / UniqueIPs24h from the history and ignores
+ * igs_tx.unique_devices_24h / unique_ips_24h; plain igs_append_events on such a history appends
+ * events without identifiers.  igs_append_events_ids on a history without identifiers fails with
+ * IGS_ERR_STATE.
+ * Semantics (per account, per key): an event with a non-empty identifier adds it to the key and
+ * renews the key's 24h TTL, so the events that carried one form chains with consecutive gaps
+ * <= 86400 s; a query at time t sees the distinct identifiers of the trailing chain of its prior
+ * events iff t - (ts of the last of them) <= 86400, else 0.  Counts are EXACT where Redis answers
+ * PFCOUNT from a HyperLogLog (0.81 % standard error): a deliberate deviation — the approximate
+ * registers cannot be reproduced without Redis itself.  Counts saturate at 65 535.               */
+int igs_load_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
+                        uint32_t n_accounts);
+int igs_append_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n);
+/* The PFCOUNT pair of GetRealTimeFeatures (features/redis_store.go:80-81,102-107) for n queries.
+ * Needs a history that carries identifiers.                                                     */
+int igs_get_uniques(igs_engine* e, const igs_query* q, uint64_t n, igs_uniques* out);
+int igs_get_uniques_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out,
+                           void* stream);
+
+/* Replaces the blacklist sets of the feature store.  igs_blacklist_load = DEL + SADD of all n ids
+ * (n = 0 empties the set); igs_blacklist_add = AddToBlacklist (features/redis_store.go:251-264)
+ * for n ids.  kind = IGS_BL_*; an unknown kind fails with IGS_ERR_INVALID like the reference's
+ * "unknown blacklist type" (:261).  Id 0 is ignored.  Like the other loads, not concurrent with
+ * scoring calls on the same engine.                                                              */
+int igs_blacklist_load(igs_engine* e, int kind, const uint64_t* ids, uint64_t n);
+int igs_blacklist_add(igs_engine* e, int kind, const uint64_t* ids, uint64_t n);
+/* Replaces Blacklist.Check (scoring/engine.go:174-176) = CheckBlacklist
+ * (features/redis_store.go:267-293) for n identifier triples: out[i] = 1 iff any non-empty
+ * identifier of ids[i] is in its set.                                                           */
+int igs_blacklist_check(igs_engine* e, const igs_tx_ids* ids, uint64_t n, uint8_t* out);
+int igs_blacklist_check_device(igs_engine* e, const igs_tx_ids* d_ids, uint64_t n, uint8_t* d_out,
+                               void* stream);
+
+/* igs_score_batch with rule 8 evaluated on the device (scoring/engine.go:468-475): the tx is
+ * KNOWN_FRAUDSTER iff its IGS_BIT_BLACKLISTED is set or igs_blacklist_check(ids[i]) hits.  ids is
+ * parallel to tx.  Everything else is igs_score_batch.                                          */
+int igs_score_batch_ids(igs_engine* e, const igs_config* cfg, const igs_tx* tx, const igs_tx_ids* ids,
+                        uint64_t n, igs_result* out, float* features_out, igs_velocity* velocity_out);
+int igs_score_batch_ids_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx,
+                               const igs_tx_ids* d_ids, uint64_t n, igs_result* d_out,
+                               float* d_features_out, igs_velocity* d_velocity_out, void* stream);
+
 /* Shard partition (device buffers): groups n tx records by shard = splitmix64(account) % n_shards
  * (n_shards <= 256), keeping arrival order inside a shard.  The reference has no batch partition;
  * the key is the one its feature store is addressed by (AccountID, features/redis_store.go:61,
@@ -432,6 +506,10 @@ const char* igs_segment_name(int seg);         /* prediction/ltv.go:17-23       
 /* shard = splitmix64(lo ^ hi) % n_shards for a 16-byte account uuid (ScoreRequest.AccountID);
  * igs_shard_of(account, 0, n) is the shard igs_partition_tx_device assigns to a dense index.     */
 uint32_t igs_shard_of(uint64_t uuid_lo, uint64_t uuid_hi, uint32_t n_shards);
+/* Id of an identifier string (device id, fingerprint, IP text): FNV-1a 64 over the bytes followed
+ * by the splitmix64 finaliser; len 0 -> 0, a non-empty string never maps to 0.  No reference
+ * counterpart (Redis keys the strings themselves).                                              */
+uint64_t igs_hash_id(const char* s, size_t len);
 /* Library / build identification, e.g. "igs 0.1 sm_100a".                                       */
 const char* igs_version(void);
 

@@ -367,16 +367,21 @@ struct orc_redis_account {
     int64_t sum, sum_expire;     /* tx_sum:1h  INCRBY + EXPIRE 1h :136-138 */
     int64_t last, last_expire;   /* last_tx    SET EX 7d :155 */
     int64_t sess, sess_expire;   /* session_start SETNX + EXPIRE 30m :158-160 */
+    /* unique_devices / unique_ips: PFADD + EXPIRE 24h :141-152.  Exact sets stand in for the
+     * HyperLogLog registers (PFCOUNT is approximate; the deviation is documented in the header). */
+    uint64_t* dev; size_t dev_n, dev_cap; int64_t dev_expire;
+    uint64_t* ip;  size_t ip_n,  ip_cap;  int64_t ip_expire;
 };
 
 orc_redis_account* orc_redis_new(void) {
     orc_redis_account* a = (orc_redis_account*)calloc(1, sizeof(*a));
     a->z_expire = a->sum_expire = a->last_expire = a->sess_expire = -1;
+    a->dev_expire = a->ip_expire = -1;
     return a;
 }
 void orc_redis_free(orc_redis_account* a) {
     if (!a) return;
-    free(a->z_ts); free(a->z_amt); free(a);
+    free(a->z_ts); free(a->z_amt); free(a->dev); free(a->ip); free(a);
 }
 /* Redis expires a key when now > when (keyIsExpired); at now == when it is still alive. */
 static int alive(int64_t expire, int64_t now) { return expire >= 0 && !(now > expire); }
@@ -386,6 +391,8 @@ static void redis_expire_keys(orc_redis_account* a, int64_t now) {
     if (!alive(a->sum_expire, now)) { a->sum = 0; a->sum_expire = -1; }
     if (!alive(a->last_expire, now)) { a->last = 0; a->last_expire = -1; }
     if (!alive(a->sess_expire, now)) { a->sess = 0; a->sess_expire = -1; }
+    if (!alive(a->dev_expire, now)) { a->dev_n = 0; a->dev_expire = -1; }
+    if (!alive(a->ip_expire, now)) { a->ip_n = 0; a->ip_expire = -1; }
 }
 
 /* GetRealTimeFeatures, features/redis_store.go:60-116. */
@@ -401,6 +408,8 @@ void orc_redis_get(orc_redis_account* a, int64_t now, orc_realtime* out) {
     if (a->sum_expire >= 0) out->tx_sum_1h = a->sum;                  /* :99-101 */
     if (a->last_expire >= 0) out->last_tx_timestamp = a->last;        /* :108-110 */
     if (a->sess_expire >= 0) out->session_start = a->sess;            /* :111-113 */
+    out->unique_devices_24h = (int64_t)a->dev_n;                      /* PFCOUNT :80, :102-104 */
+    out->unique_ips_24h = (int64_t)a->ip_n;                           /* PFCOUNT :81, :105-107 */
 }
 
 /* UpdateRealTimeFeatures, features/redis_store.go:119-168; wall clock == event ts. */
@@ -428,6 +437,56 @@ void orc_redis_update(orc_redis_account* a, int64_t ts, int64_t amount) {
     a->last = ts; a->last_expire = ts + 7 * 24 * 3600;                /* :155 */
     if (a->sess_expire < 0) a->sess = ts;                             /* SETNX :159 */
     a->sess_expire = ts + 1800;                                       /* :160 */
+}
+
+static void set_add(uint64_t** v, size_t* n, size_t* cap, uint64_t id) {
+    for (size_t i = 0; i < *n; ++i)
+        if ((*v)[i] == id) return;
+    if (*n == *cap) {
+        *cap = *cap ? *cap * 2 : 8;
+        *v = (uint64_t*)realloc(*v, *cap * sizeof(uint64_t));
+    }
+    (*v)[(*n)++] = id;
+}
+
+/* UpdateRealTimeFeatures with the event's identifiers: id 0 = empty string, which the reference
+ * skips (`if event.DeviceID != ""` :141, `if event.IP != ""` :148). */
+void orc_redis_update_ids(orc_redis_account* a, int64_t ts, int64_t amount, uint64_t device,
+                          uint64_t ip) {
+    orc_redis_update(a, ts, amount);
+    if (device) { set_add(&a->dev, &a->dev_n, &a->dev_cap, device); a->dev_expire = ts + 86400; } /* :143-144 */
+    if (ip) { set_add(&a->ip, &a->ip_n, &a->ip_cap, ip); a->ip_expire = ts + 86400; }             /* :150-151 */
+}
+
+static int u64_cmp(const void* a, const void* b) {
+    const uint64_t x = *(const uint64_t*)a, y = *(const uint64_t*)b;
+    return x < y ? -1 : x > y;
+}
+
+/* Closed form of one PFADD/EXPIRE-24h key: the events that carried an identifier form chains with
+ * consecutive gaps <= 86400 (each PFADD refreshes the TTL); the key holds the distinct identifiers
+ * of the trailing chain and is alive iff now - (ts of the last such event) <= 86400. */
+uint32_t orc_uniques_closed_form(const uint32_t* ts, const uint64_t* id, uint32_t n, uint32_t now_u) {
+    const int64_t now = now_u;
+    uint32_t j = n;
+    while (j > 0 && id[j - 1] == 0) --j;
+    if (j == 0) return 0;
+    int64_t last = ts[j - 1];
+    if (now - last > 86400) return 0;
+    uint64_t* chain = (uint64_t*)malloc((size_t)j * sizeof(uint64_t));
+    size_t m = 0;
+    for (uint32_t k = j; k-- > 0;) {
+        if (id[k] == 0) continue;
+        if (last - (int64_t)ts[k] > 86400) break;
+        chain[m++] = id[k];
+        last = ts[k];
+    }
+    qsort(chain, m, sizeof(uint64_t), u64_cmp);
+    uint32_t distinct = 0;
+    for (size_t k = 0; k < m; ++k)
+        if (k == 0 || chain[k] != chain[k - 1]) ++distinct;
+    free(chain);
+    return distinct;
 }
 
 /* Closed form.  Prior events ordered by (ts, arrival). */
@@ -486,11 +545,13 @@ static int ev_cmp(const void* a, const void* b) {
 typedef struct {
     ev_key* keys; uint64_t* seg;          /* seg[a]..seg[a+1] = events of account a */
     uint32_t* ts; int64_t* amt; uint8_t* ty; uint32_t* seq;
+    uint64_t* dev; uint64_t* ip;          /* NULL when the history has no identifier columns */
     uint64_t n; uint32_t n_accounts;
 } ev_index;
 
 static void ev_index_build(ev_index* ix, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts) {
     ix->n = n; ix->n_accounts = n_accounts;
+    ix->dev = ix->ip = NULL;
     ix->keys = (ev_key*)malloc((n ? n : 1) * sizeof(ev_key));
     for (uint64_t i = 0; i < n; ++i) ix->keys[i] = (ev_key){ev->account[i], ev->ts[i], (uint32_t)i};
     qsort(ix->keys, n, sizeof(ev_key), ev_cmp);
@@ -506,8 +567,36 @@ static void ev_index_build(ev_index* ix, const igs_event_cols* ev, uint64_t n, u
     }
     for (uint32_t a = 0; a < n_accounts; ++a) ix->seg[a + 1] += ix->seg[a];
 }
+static void ev_index_add_ids(ev_index* ix, const igs_event_ids* ids) {
+    const uint64_t n = ix->n;
+    ix->dev = (uint64_t*)calloc(n ? n : 1, 8);
+    ix->ip = (uint64_t*)calloc(n ? n : 1, 8);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (ids->device) ix->dev[i] = ids->device[ix->seq[i]];
+        if (ids->ip) ix->ip[i] = ids->ip[ix->seq[i]];
+    }
+}
 static void ev_index_free(ev_index* ix) {
     free(ix->keys); free(ix->seg); free(ix->ts); free(ix->amt); free(ix->ty); free(ix->seq);
+    free(ix->dev); free(ix->ip);
+}
+/* number of events of `account` ordered before (ts, seq_limit); *start = first sorted position */
+static uint64_t ev_index_prior(const ev_index* ix, uint32_t account, uint32_t ts, uint32_t seq_limit,
+                               uint64_t* start) {
+    *start = 0;
+    if (account >= ix->n_accounts) return 0;
+    uint64_t s = ix->seg[account], e = ix->seg[account + 1];
+    uint64_t u = s;
+    while (u < e && (ix->ts[u] < ts || (ix->ts[u] == ts && ix->seq[u] < seq_limit))) ++u;
+    *start = s;
+    return u - s;
+}
+static void ev_index_uniques(const ev_index* ix, uint32_t account, uint32_t ts, uint32_t seq_limit,
+                             igs_uniques* out) {
+    uint64_t s;
+    const uint32_t n = (uint32_t)ev_index_prior(ix, account, ts, seq_limit, &s);
+    out->devices_24h = ix->dev ? orc_uniques_closed_form(ix->ts + s, ix->dev + s, n, ts) : 0;
+    out->ips_24h = ix->ip ? orc_uniques_closed_form(ix->ts + s, ix->ip + s, n, ts) : 0;
 }
 static void ev_index_query(const ev_index* ix, uint32_t account, uint32_t ts, uint32_t seq_limit,
                            igs_velocity* out) {
@@ -525,6 +614,41 @@ void orc_velocity_batch(const igs_event_cols* ev, uint64_t n_events, uint32_t n_
     for (uint64_t i = 0; i < n_q; ++i)
         ev_index_query(&ix, q[i].account, q[i].ts, q[i].seq_limit, out + i);
     ev_index_free(&ix);
+}
+
+void orc_uniques_batch(const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n_events,
+                       uint32_t n_accounts, const igs_query* q, uint64_t n_q, igs_uniques* out) {
+    ev_index ix;
+    ev_index_build(&ix, ev, n_events, n_accounts);
+    ev_index_add_ids(&ix, ids);
+    for (uint64_t i = 0; i < n_q; ++i)
+        ev_index_uniques(&ix, q[i].account, q[i].ts, q[i].seq_limit, out + i);
+    ev_index_free(&ix);
+}
+
+/* The id of an identifier string (spec of igs_hash_id, include/igs.h): FNV-1a 64 over the bytes,
+ * then the splitmix64 finaliser; "" -> 0 and a non-empty string never maps to 0. */
+uint64_t orc_hash_id(const char* s, size_t len) {
+    if (len == 0) return 0;
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (size_t i = 0; i < len; ++i) { h ^= (uint8_t)s[i]; h *= 0x100000001b3ull; }
+    h ^= h >> 30; h *= 0xbf58476d1ce4e5b9ull;
+    h ^= h >> 27; h *= 0x94d049bb133111ebull;
+    h ^= h >> 31;
+    return h ? h : 1;
+}
+
+/* CheckBlacklist, features/redis_store.go:267-293: SISMEMBER per non-empty identifier, any hit. */
+static int set_has(const uint64_t* v, uint64_t n, uint64_t id) {
+    if (!id) return 0;                               /* `if deviceID != ""` :271, :274, :277 */
+    for (uint64_t i = 0; i < n; ++i)
+        if (v[i] == id) return 1;
+    return 0;
+}
+int orc_blacklist_check(const orc_blacklist* bl, const igs_tx_ids* id) {
+    return set_has(bl->device, bl->n_device, id->device) ||
+           set_has(bl->fingerprint, bl->n_fingerprint, id->fingerprint) ||
+           set_has(bl->ip, bl->n_ip, id->ip);
 }
 
 /* ========================================================================================== */
@@ -588,6 +712,37 @@ void orc_score_batch(const igs_config* c, const igs_gbdt_desc* m, const igs_play
         to_result(&s, out + i);
         if (features_out) memcpy(features_out + i * 64, x, sizeof(x));
         if (velocity_out) velocity_out[i] = v;
+    }
+    ev_index_free(&ix);
+}
+
+/* Path B with the identifier inputs computed here instead of arriving with the tx: uniques from
+ * the history's identifier columns (when ev_ids != NULL), R8 from the blacklist sets (when
+ * tx_ids != NULL; OR-ed with the tx's own IGS_BIT_BLACKLISTED). */
+void orc_score_batch_ids(const igs_config* c, const igs_gbdt_desc* m, const igs_player_row* players,
+                         uint64_t n_players, const igs_event_cols* ev, const igs_event_ids* ev_ids,
+                         uint64_t n_events, const orc_blacklist* bl, const igs_tx* tx,
+                         const igs_tx_ids* tx_ids, uint64_t n, igs_result* out, float* features_out) {
+    ev_index ix;
+    ev_index_build(&ix, ev, n_events, (uint32_t)n_players);
+    if (ev_ids) ev_index_add_ids(&ix, ev_ids);
+    for (uint64_t i = 0; i < n; ++i) {
+        igs_tx t = tx[i];
+        igs_velocity v;
+        ev_index_query(&ix, t.account, t.ts, t.seq_limit, &v);
+        if (ev_ids) {
+            igs_uniques u;
+            ev_index_uniques(&ix, t.account, t.ts, t.seq_limit, &u);
+            t.unique_devices_24h = (uint16_t)(u.devices_24h > 65535 ? 65535 : u.devices_24h);
+            t.unique_ips_24h = (uint16_t)(u.ips_24h > 65535 ? 65535 : u.ips_24h);
+        }
+        if (tx_ids && bl && orc_blacklist_check(bl, tx_ids + i)) t.bits |= IGS_BIT_BLACKLISTED;
+        orc_features fv; float x[64]; igs_rule_row row; orc_score s;
+        const igs_player_row* p = t.account < n_players ? players + t.account : NULL;
+        orc_assemble(&t, &v, p, &fv, x, &row);
+        orc_score_features_row(c, m, x, &row, &s, NULL);
+        to_result(&s, out + i);
+        if (features_out) memcpy(features_out + i * 64, x, sizeof(x));
     }
     ev_index_free(&ix);
 }

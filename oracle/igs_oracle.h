@@ -21,7 +21,11 @@
  * not vendored) and ships neither model.  The tree-ensemble and MLP evaluation orders, the
  * sigmoid and the bf16 rounding points below are DEFINED here (ONNX TreeEnsemble BRANCH_LEQ
  * semantics, leaves summed in tree order in fp32), not copied from anything.
- * Also unpinned: Redis PFCOUNT (HyperLogLog) — uniques are an input here, not computed.
+ * Also unpinned: Redis PFCOUNT (HyperLogLog, approximate).  Where uniques are computed here
+ * (orc_redis_update_ids, orc_uniques_*) they are EXACT distinct counts over the PFADD / EXPIRE-24h
+ * key life time — a deliberate deviation: HLL registers cannot be restated bit for bit without
+ * Redis's hash (MurmurHash64A with its seed) and sparse/dense encodings, none of which is under
+ * /root/reference.
  */
 #ifndef IGS_ORACLE_H_
 #define IGS_ORACLE_H_
@@ -114,10 +118,27 @@ void orc_score_features_batch(const igs_config* cfg, const igs_gbdt_desc* m, con
 typedef struct orc_redis_account orc_redis_account;
 orc_redis_account* orc_redis_new(void);
 void orc_redis_free(orc_redis_account* a);
-/* GetRealTimeFeatures :60-116 at wall clock `now` (unix s).  Uniques are not emulated (0).      */
+/* GetRealTimeFeatures :60-116 at wall clock `now` (unix s).  Uniques: exact set sizes.           */
 void orc_redis_get(orc_redis_account* a, int64_t now, orc_realtime* out);
 /* UpdateRealTimeFeatures :119-168 for an event at ts; wall clock == ts.                         */
 void orc_redis_update(orc_redis_account* a, int64_t ts, int64_t amount);
+
+/* Same with the event's device / IP identifiers (0 = empty string, skipped :141,:148).           */
+void orc_redis_update_ids(orc_redis_account* a, int64_t ts, int64_t amount, uint64_t device,
+                          uint64_t ip);
+/* Closed form of one PFADD + EXPIRE-24h key against the account's n prior events.               */
+uint32_t orc_uniques_closed_form(const uint32_t* ts, const uint64_t* id, uint32_t n_prior,
+                                 uint32_t now);
+void orc_uniques_batch(const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n_events,
+                       uint32_t n_accounts, const igs_query* q, uint64_t n_q, igs_uniques* out);
+uint64_t orc_hash_id(const char* s, size_t len);                         /* spec of igs_hash_id */
+/* Blacklist sets (SADD :251-264) and CheckBlacklist :267-293.                                   */
+typedef struct orc_blacklist {
+    const uint64_t* device; uint64_t n_device;
+    const uint64_t* fingerprint; uint64_t n_fingerprint;
+    const uint64_t* ip; uint64_t n_ip;
+} orc_blacklist;
+int orc_blacklist_check(const orc_blacklist* bl, const igs_tx_ids* id);
 
 /* Closed form of the same + the extension windows, for one query against the account's events
  * already ordered by (ts, arrival): ts[], amount[], type[] of the n_prior events that precede
@@ -135,6 +156,11 @@ void orc_score_batch(const igs_config* cfg, const igs_gbdt_desc* m, const igs_pl
                      uint64_t n_players, const igs_event_cols* ev, uint64_t n_events,
                      const igs_tx* tx, uint64_t n, igs_result* out, float* features_out,
                      igs_velocity* velocity_out);
+
+void orc_score_batch_ids(const igs_config* cfg, const igs_gbdt_desc* m, const igs_player_row* players,
+                         uint64_t n_players, const igs_event_cols* ev, const igs_event_ids* ev_ids,
+                         uint64_t n_events, const orc_blacklist* bl, const igs_tx* tx,
+                         const igs_tx_ids* tx_ids, uint64_t n, igs_result* out, float* features_out);
 
 /* ------------------------------------------------------------------------------------------ */
 /* prediction/ltv.go + the MLP spec                                                            */

@@ -48,6 +48,12 @@ class Realtime(C.Structure):
         "unique_ips_24h", "last_tx_timestamp", "session_start")]
 
 
+class Blacklist(C.Structure):
+    _fields_ = [("device", C.c_void_p), ("n_device", C.c_uint64),
+                ("fingerprint", C.c_void_p), ("n_fingerprint", C.c_uint64),
+                ("ip", C.c_void_p), ("n_ip", C.c_uint64)]
+
+
 class Score(C.Structure):
     _fields_ = [("score", C.c_int32), ("rule_score", C.c_int32), ("ml_score", C.c_double),
                 ("flags", C.c_uint32), ("action", C.c_int32)]
@@ -109,6 +115,21 @@ def lib() -> C.CDLL:
     L.orc_score_batch.argtypes = [C.POINTER(abi.Config), C.POINTER(abi.GbdtDesc), vp, u64,
                                   C.POINTER(abi.EventCols), u64, vp, u64, vp, vp, vp]
     L.orc_score_batch.restype = None
+    L.orc_redis_update_ids.argtypes = [vp, C.c_int64, C.c_int64, u64, u64]
+    L.orc_redis_update_ids.restype = None
+    L.orc_uniques_closed_form.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
+    L.orc_uniques_closed_form.restype = C.c_uint32
+    L.orc_uniques_batch.argtypes = [C.POINTER(abi.EventCols), C.POINTER(abi.EventIds), u64, C.c_uint32,
+                                    vp, u64, vp]
+    L.orc_uniques_batch.restype = None
+    L.orc_hash_id.argtypes = [C.c_char_p, C.c_size_t]
+    L.orc_hash_id.restype = u64
+    L.orc_blacklist_check.argtypes = [C.POINTER(Blacklist), vp]
+    L.orc_blacklist_check.restype = C.c_int
+    L.orc_score_batch_ids.argtypes = [C.POINTER(abi.Config), C.POINTER(abi.GbdtDesc), vp, u64,
+                                      C.POINTER(abi.EventCols), C.POINTER(abi.EventIds), u64,
+                                      C.POINTER(Blacklist), vp, vp, u64, vp, vp]
+    L.orc_score_batch_ids.restype = None
     for f in ("orc_ltv_engagement", "orc_ltv_heuristic", "orc_ltv_churn"):
         getattr(L, f).argtypes = [vp]
         getattr(L, f).restype = C.c_double
@@ -193,6 +214,54 @@ def score_batch(cfg, model, players, ev, tx, want_features=False, want_velocity=
     if want_features or want_velocity:
         return out, feats, vel
     return out
+
+
+def uniques_batch(ev, n_accounts: int, queries: np.ndarray) -> np.ndarray:
+    queries = np.ascontiguousarray(queries, dtype=abi.query_dtype)
+    out = np.zeros(queries.shape[0], dtype=abi.uniques_dtype)
+    c, i = ev.cols(), ev.ids()
+    lib().orc_uniques_batch(C.byref(c), C.byref(i), len(ev), n_accounts, abi.ptr(queries),
+                            queries.shape[0], abi.ptr(out))
+    return out
+
+
+def hash_id(s) -> int:
+    b = s.encode() if isinstance(s, str) else bytes(s)
+    return int(lib().orc_hash_id(b, len(b)))
+
+
+def make_blacklist(device=None, fingerprint=None, ip=None):
+    """-> (Blacklist struct, keep-alive arrays)"""
+    arrs = [np.ascontiguousarray(a if a is not None else [], dtype=np.uint64) for a in (device, fingerprint, ip)]
+    bl = Blacklist(abi.ptr(arrs[0]), arrs[0].shape[0], abi.ptr(arrs[1]), arrs[1].shape[0],
+                   abi.ptr(arrs[2]), arrs[2].shape[0])
+    return bl, arrs
+
+
+def blacklist_check(bl: Blacklist, ids: np.ndarray) -> np.ndarray:
+    ids = np.ascontiguousarray(ids, dtype=abi.tx_ids_dtype)
+    L = lib()
+    return np.array([L.orc_blacklist_check(C.byref(bl), ids[i:i + 1].ctypes.data) for i in range(ids.shape[0])],
+                    dtype=np.uint8)
+
+
+def score_batch_ids(cfg, model, players, ev, tx, bl=None, tx_ids=None, want_features=False):
+    """Path B with uniques from the history's identifier columns (when ev has them) and R8 from bl."""
+    players = np.ascontiguousarray(players, dtype=abi.player_row_dtype)
+    tx = np.ascontiguousarray(tx, dtype=abi.tx_dtype)
+    n = tx.shape[0]
+    out = np.zeros(n, dtype=abi.result_dtype)
+    feats = np.zeros((n, abi.NUM_FEATURES), dtype=np.float32) if want_features else None
+    d = model.desc() if model is not None else None
+    c = ev.cols()
+    i = ev.ids() if ev.has_ids() else None
+    if tx_ids is not None:
+        tx_ids = np.ascontiguousarray(tx_ids, dtype=abi.tx_ids_dtype)
+    lib().orc_score_batch_ids(C.byref(cfg), C.byref(d) if d is not None else None, abi.ptr(players),
+                              players.shape[0], C.byref(c), C.byref(i) if i is not None else None, len(ev),
+                              C.byref(bl) if bl is not None else None, abi.ptr(tx), abi.ptr(tx_ids), n,
+                              abi.ptr(out), abi.ptr(feats))
+    return (out, feats) if want_features else out
 
 
 def ltv_epilogue(rows: np.ndarray, ltv: np.ndarray) -> np.ndarray:

@@ -272,6 +272,55 @@ def make_events(n_events: int, n_accounts: int, seed: int = MASTER_SEED, zipf_s:
     return pkg.Events(acct.astype(np.uint32), (T0 + ts).astype(np.uint32), amt.astype(np.int64), ty)
 
 
+def mix64(x: np.ndarray) -> np.ndarray:
+    """splitmix64 finaliser, vectorised (the mix igs_hash_id ends with)."""
+    x = x.astype(np.uint64).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(30); x *= np.uint64(0xbf58476d1ce4e5b9)
+        x ^= x >> np.uint64(27); x *= np.uint64(0x94d049bb133111eb)
+        x ^= x >> np.uint64(31)
+    return x
+
+
+def colliding_ids(count: int = 4, seed: int = 1) -> np.ndarray:
+    """`count` distinct non-zero 64-bit ids whose mix64 values share their top 30 bits pairwise with a
+    partner (birthday search) — they land in the same radix-sort key of the index build and must still
+    be counted as different identifiers."""
+    cand = splitmix64(seed, 99, 400_000) | np.uint64(1)
+    key = mix64(cand) >> np.uint64(34)
+    order = np.argsort(key, kind="stable")
+    k = key[order]
+    dup = np.nonzero(k[1:] == k[:-1])[0]
+    out = []
+    for d in dup:
+        a, b = cand[order[d]], cand[order[d + 1]]
+        if a != b:
+            out += [a, b]
+        if len(out) >= count:
+            break
+    assert len(out) >= count, "no hash collisions found"
+    return np.array(out[:count], dtype=np.uint64)
+
+
+def make_event_ids(ev, seed: int = MASTER_SEED, empty_rate: float = 0.1, shared_rate: float = 0.05,
+                   devices_per_account: float = 1.2, ips_per_account: float = 2.5):
+    """Device / IP ids for an event history: each account draws from its own small pools (so R3 / R4
+    thresholds are straddled), some events carry no identifier, some devices are shared across accounts."""
+    n = len(ev)
+    s = seed + 404
+    U = lambda k: uniform(s, k, n)  # noqa: E731
+    acct = ev.account.astype(np.uint64)
+    kd = geometric(U(1), devices_per_account).astype(np.uint64)
+    ki = geometric(U(2), ips_per_account).astype(np.uint64)
+    dev = mix64(acct * np.uint64(1_000_003) + kd + np.uint64(17)) | np.uint64(1)
+    ip = mix64(acct * np.uint64(7_000_003) + ki + np.uint64(0xABCDEF)) | np.uint64(1)
+    shared = U(3) < shared_rate
+    dev = np.where(shared, mix64((splitmix64(s, 4, n) % np.uint64(50)) + np.uint64(5)) | np.uint64(1), dev)
+    dev = np.where(U(5) < empty_rate, np.uint64(0), dev)
+    ip = np.where(U(6) < empty_rate, np.uint64(0), ip)
+    return pkg.Events(ev.account, ev.ts, ev.amount, ev.tx_type, device=dev.astype(np.uint64), ip=ip.astype(np.uint64))
+
+
 def make_tx(n: int, n_accounts: int, seed: int = MASTER_SEED, zipf_s: float = 1.1,
             t_lo: int = T0 + 24 * 3600, t_hi: int = T0 + 48 * 3600, invalid_rate: float = 0.0) -> np.ndarray:
     """Compact tx records (queries) with C1 marginals; ts uniform in [t_lo, t_hi)."""
