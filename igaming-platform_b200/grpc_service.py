@@ -2,11 +2,12 @@
 
 The reference registers its handler with `riskv1.RegisterRiskServiceServer(grpcServer, NewRiskGRPCHandler(...))`
 (services/risk/cmd/main.go:141-142) but ships neither the handler nor generated code.  This module is that
-handler's body for the RPCs on the scoring path — `ScoreTransaction`, `ScoreBatch`, `GetThresholds`,
-`UpdateThresholds` (proto/risk/v1/risk.proto:12-13,30-31) — speaking the same wire format.  There is no
-`protoc` in this image, so the message descriptors are built by hand from the .proto (same package, message
-names, field names, numbers and types; risk.proto:38-89,197-257); the other RPCs of the service (LTV,
-bonus abuse, blacklist management, feature inspection) answer UNIMPLEMENTED.
+handler's body for the RPCs the engine can answer — `ScoreTransaction`, `ScoreBatch`, `GetThresholds`,
+`UpdateThresholds` (proto/risk/v1/risk.proto:12-13,30-31), `AddToBlacklist`, `CheckBlacklist` (:23-24, on the
+device-side sets) and `PredictLTV`, `GetPlayerSegment` (:16-17, on the LTV model) — speaking the same wire
+format.  There is no `protoc` in this image, so the message descriptors are built by hand from the .proto (same
+package, message names, field names, numbers and types; risk.proto:38-257); `CheckBonusAbuse` and
+`GetFeatures` answer UNIMPLEMENTED.
 
 Marshalling only: every score in a response was computed by the CUDA library through `scoring.ScoringEngine`.
 """
@@ -18,7 +19,7 @@ from concurrent import futures
 from typing import Optional
 
 import numpy as np
-from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+from google.protobuf import descriptor_pb2, descriptor_pool, message_factory, timestamp_pb2
 
 from . import abi, scoring
 
@@ -61,6 +62,13 @@ def build_file_descriptor() -> descriptor_pb2.FileDescriptorProto:
     fd.name = "risk/v1/risk_scoring_subset.proto"
     fd.package = PACKAGE
     fd.syntax = "proto3"
+    fd.dependency.append("google/protobuf/timestamp.proto")           # risk.proto:7
+    seg = fd.enum_type.add()
+    seg.name = "Segment"                                               # risk.proto:122-129
+    for nm, num in (("SEGMENT_UNSPECIFIED", 0), ("SEGMENT_VIP", 1), ("SEGMENT_HIGH", 2), ("SEGMENT_MEDIUM", 3),
+                    ("SEGMENT_LOW", 4), ("SEGMENT_CHURNING", 5)):
+        v = seg.value.add()
+        v.name, v.number = nm, num
     en = fd.enum_type.add()
     en.name = "Action"
     for nm, num in (("ACTION_UNSPECIFIED", 0), ("ACTION_APPROVE", 1), ("ACTION_REVIEW", 2), ("ACTION_BLOCK", 3)):
@@ -89,10 +97,32 @@ def build_file_descriptor() -> descriptor_pb2.FileDescriptorProto:
                                           ("review_threshold", 3, _T.TYPE_INT32)])
     _msg(fd, "GetThresholdsRequest", [])
     _msg(fd, "GetThresholdsResponse", [("block_threshold", 1, _T.TYPE_INT32), ("review_threshold", 2, _T.TYPE_INT32)])
+    ts = ".google.protobuf.Timestamp"
+    # blacklist management, risk.proto:148-182
+    _msg(fd, "AddToBlacklistRequest", [("type", 1, _T.TYPE_STRING), ("value", 2, _T.TYPE_STRING), ("reason", 3, _T.TYPE_STRING),
+                                       ("created_by", 4, _T.TYPE_STRING), ("expires_at", 5, _T.TYPE_MESSAGE, ts)])
+    _msg(fd, "AddToBlacklistResponse", [("success", 1, _T.TYPE_BOOL), ("id", 2, _T.TYPE_STRING)])
+    _msg(fd, "CheckBlacklistRequest", [("device_id", 1, _T.TYPE_STRING), ("fingerprint", 2, _T.TYPE_STRING),
+                                       ("ip_address", 3, _T.TYPE_STRING), ("email", 4, _T.TYPE_STRING)])
+    _msg(fd, "BlacklistMatch", [("type", 1, _T.TYPE_STRING), ("value", 2, _T.TYPE_STRING), ("reason", 3, _T.TYPE_STRING),
+                                ("created_at", 4, _T.TYPE_MESSAGE, ts)])
+    _msg(fd, "CheckBlacklistResponse", [("is_blacklisted", 1, _T.TYPE_BOOL),
+                                        ("matches", 2, _T.TYPE_MESSAGE, f".{PACKAGE}.BlacklistMatch", _T.LABEL_REPEATED)])
+    # LTV & segmentation, risk.proto:94-120
+    _msg(fd, "PredictLTVRequest", [("account_id", 1, _T.TYPE_STRING)])
+    _msg(fd, "PredictLTVResponse", [("account_id", 1, _T.TYPE_STRING), ("predicted_ltv", 2, _T.TYPE_FLOAT),
+                                    ("segment", 3, _T.TYPE_ENUM, f".{PACKAGE}.Segment"), ("churn_risk", 4, _T.TYPE_FLOAT),
+                                    ("predicted_active_days", 5, _T.TYPE_INT32), ("confidence", 6, _T.TYPE_FLOAT),
+                                    ("next_best_action", 7, _T.TYPE_STRING), ("predicted_at", 8, _T.TYPE_MESSAGE, ts)])
+    _msg(fd, "GetPlayerSegmentRequest", [("account_id", 1, _T.TYPE_STRING)])
+    _msg(fd, "GetPlayerSegmentResponse", [("account_id", 1, _T.TYPE_STRING), ("segment", 2, _T.TYPE_ENUM, f".{PACKAGE}.Segment"),
+                                          ("ltv", 3, _T.TYPE_FLOAT), ("churn_risk", 4, _T.TYPE_FLOAT),
+                                          ("recommended_actions", 5, _T.TYPE_STRING, None, _T.LABEL_REPEATED)])
     return fd
 
 
 _pool = descriptor_pool.DescriptorPool()
+_pool.AddSerializedFile(timestamp_pb2.DESCRIPTOR.serialized_pb)
 _pool.Add(build_file_descriptor())
 
 
@@ -109,14 +139,27 @@ UpdateThresholdsRequest = message_class("UpdateThresholdsRequest")
 UpdateThresholdsResponse = message_class("UpdateThresholdsResponse")
 GetThresholdsRequest = message_class("GetThresholdsRequest")
 GetThresholdsResponse = message_class("GetThresholdsResponse")
+AddToBlacklistRequest = message_class("AddToBlacklistRequest")
+AddToBlacklistResponse = message_class("AddToBlacklistResponse")
+CheckBlacklistRequest = message_class("CheckBlacklistRequest")
+CheckBlacklistResponse = message_class("CheckBlacklistResponse")
+BlacklistMatch = message_class("BlacklistMatch")
+PredictLTVRequest = message_class("PredictLTVRequest")
+PredictLTVResponse = message_class("PredictLTVResponse")
+GetPlayerSegmentRequest = message_class("GetPlayerSegmentRequest")
+GetPlayerSegmentResponse = message_class("GetPlayerSegmentResponse")
 
 _METHODS = {
     "ScoreTransaction": (ScoreTransactionRequest, ScoreTransactionResponse),
     "ScoreBatch": (ScoreBatchRequest, ScoreBatchResponse),
     "UpdateThresholds": (UpdateThresholdsRequest, UpdateThresholdsResponse),
     "GetThresholds": (GetThresholdsRequest, GetThresholdsResponse),
+    "AddToBlacklist": (AddToBlacklistRequest, AddToBlacklistResponse),
+    "CheckBlacklist": (CheckBlacklistRequest, CheckBlacklistResponse),
+    "PredictLTV": (PredictLTVRequest, PredictLTVResponse),
+    "GetPlayerSegment": (GetPlayerSegmentRequest, GetPlayerSegmentResponse),
 }
-_UNIMPLEMENTED = ["PredictLTV", "GetPlayerSegment", "CheckBonusAbuse", "AddToBlacklist", "CheckBlacklist", "GetFeatures"]
+_UNIMPLEMENTED = ["CheckBonusAbuse", "GetFeatures"]
 _ACTION_ENUM = {"approve": 1, "review": 2, "block": 3}
 
 
@@ -158,17 +201,29 @@ def fill_features(fv, tx_row, vel, player) -> None:
 
 class RiskServicer:
     """Handler body for the scoring RPCs.  `players` (optional host copy of the BatchFeatures table)
-    enables the 26-field `features` echo of ScoreTransactionResponse."""
+    enables the 26-field `features` echo of ScoreTransactionResponse; `ltv_inputs` (optional host copy of
+    the per-player LTV model input: n x 256 bf16 bit patterns + igs_ltv_row sideband, indexed like the
+    directory) enables PredictLTV / GetPlayerSegment."""
 
-    def __init__(self, engine: scoring.ScoringEngine, players: Optional[np.ndarray] = None):
+    def __init__(self, engine: scoring.ScoringEngine, players: Optional[np.ndarray] = None, ltv_inputs=None):
         self.engine = engine
         self.players = players
+        self.ltv_inputs = ltv_inputs
 
     def _score(self, reqs, now: Optional[int] = None):
         t0 = time.perf_counter()
         sreqs = [to_score_request(m) for m in reqs]
         tx = self.engine.marshal(sreqs, now=now)
-        out, _, vel = self.engine.engine.score_batch(self.engine.config, tx, want_velocity=True)
+        if self.engine.device_identifiers:      # rule 8 on the device; echo the uniques the engine used
+            out, _, vel = self.engine.engine.score_batch(self.engine.config, tx, want_velocity=True,
+                                                         ids=self.engine.marshal_ids(sreqs))
+            try:
+                uq = self.engine.engine.get_uniques(scoring.queries_of(tx))
+                tx["unique_devices_24h"], tx["unique_ips_24h"] = uq["devices_24h"], uq["ips_24h"]
+            except Exception:                   # history without identifiers: the tx's own counts were used
+                pass
+        else:
+            out, _, vel = self.engine.engine.score_batch(self.engine.config, tx, want_velocity=True)
         res = self.engine.unmarshal(out, int((time.perf_counter() - t0) * 1000))
         msgs = []
         for i, r in enumerate(res):
@@ -195,6 +250,58 @@ class RiskServicer:
         self.engine.SetThresholds(request.block_threshold, request.review_threshold)
         b, r = self.engine.GetThresholds()
         return UpdateThresholdsResponse(success=True, block_threshold=b, review_threshold=r)
+
+
+    # -- blacklist management (risk.proto:23-24) on the device-side sets -----------------------------
+    def AddToBlacklist(self, request, context):
+        try:
+            self.engine.AddToBlacklist(request.type, request.value)
+        except ValueError:                       # "unknown blacklist type" (redis_store.go:261), e.g. email
+            return AddToBlacklistResponse(success=False, id="")
+        return AddToBlacklistResponse(success=True, id=f"{request.type}:{self.engine._hash(request.value):016x}")
+
+    def CheckBlacklist(self, request, context):
+        h = self.engine._hash
+        ids = np.zeros(3, dtype=abi.tx_ids_dtype)            # one single-identifier probe per list type
+        ids["device"][0], ids["fingerprint"][1], ids["ip"][2] = h(request.device_id), h(request.fingerprint), h(request.ip_address)
+        hit = self.engine.engine.blacklist_check(ids)
+        resp = CheckBlacklistResponse(is_blacklisted=bool(hit.any()))
+        for k, (typ, val) in enumerate((("device", request.device_id), ("fingerprint", request.fingerprint),
+                                        ("ip", request.ip_address))):
+            if hit[k]:
+                resp.matches.add(type=typ, value=val)
+        return resp
+
+    # -- LTV & segmentation (risk.proto:16-17) on the LTV model --------------------------------------
+    def _ltv(self, account_id: str, context):
+        import grpc
+        if self.ltv_inputs is None:
+            context.abort(grpc.StatusCode.FAILED_PRECONDITION, "no LTV inputs loaded")
+        try:
+            idx = self.engine.directory.get(_uuid.UUID(account_id))
+        except ValueError:
+            idx = 0xFFFFFFFE
+        x, rows = self.ltv_inputs
+        if idx >= rows.shape[0]:
+            context.abort(grpc.StatusCode.NOT_FOUND, "unknown account")       # GetPlayerFeatures error, ltv.go:115-118
+        return self.engine.engine.ltv_batch(x[idx:idx + 1], rows[idx:idx + 1])[0]
+
+    def PredictLTV(self, request, context):
+        r = self._ltv(request.account_id, context)
+        lib = abi.load_library()
+        resp = PredictLTVResponse(account_id=request.account_id, predicted_ltv=float(r["predicted_ltv"]),
+                                  segment=int(r["segment"]), churn_risk=float(r["churn_risk"]),
+                                  predicted_active_days=int(r["days_survival"]), confidence=float(r["confidence"]),
+                                  next_best_action=lib.igs_ltv_action_name(int(r["next_best_action"])).decode())
+        resp.predicted_at.GetCurrentTime()
+        return resp
+
+    def GetPlayerSegment(self, request, context):
+        r = self._ltv(request.account_id, context)
+        lib = abi.load_library()
+        return GetPlayerSegmentResponse(account_id=request.account_id, segment=int(r["segment"]),
+                                        ltv=float(r["predicted_ltv"]), churn_risk=float(r["churn_risk"]),
+                                        recommended_actions=[lib.igs_ltv_action_name(int(r["next_best_action"])).decode()])
 
 
 def add_to_server(servicer: RiskServicer, server) -> None:

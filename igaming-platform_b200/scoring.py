@@ -1,9 +1,9 @@
 """Host-side mirror of the reference's operator interface for the scoring path.
 
 Same names, argument meaning and error behaviour as `services/risk/internal/scoring/engine.go`
-(`ScoreRequest` :40-53, `ScoreResponse` :56-64, `ScoringEngine.Score` :262-323, `SetThresholds` /
-`GetThresholds` :491-504, `ScoreWithExplanation` :507-543), but a batch goes to the GPU in one C-ABI
-call (`igs_score_batch`).  This is marshalling only — requests to `igs_tx` records, result records
+(`ScoreRequest` :40-53, `ScoreResponse` :56-64, `ScoringEngine.Score` :262-323, `UpdateFeatures`
+:486-488, `SetThresholds` / `GetThresholds` :491-504, `ScoreWithExplanation` :507-543), but a batch
+goes to the GPU in one C-ABI call (`igs_score_batch` / `igs_score_batch_ids`).  This is marshalling only — requests to `igs_tx` records, result records
 to responses; every number in a response was computed by the CUDA library.
 """
 from __future__ import annotations
@@ -37,6 +37,17 @@ class ScoreRequest:
     fingerprint: str = ""
     user_agent: str = ""
     session_id: str = ""
+    timestamp: int = 0
+
+
+@dataclass
+class TransactionEvent:
+    """scoring.TransactionEvent (= features.TransactionEvent, features/redis_store.go:49-56)."""
+    account_id: _uuid.UUID
+    amount: int = 0
+    tx_type: str = "bet"
+    ip: str = ""
+    device_id: str = ""
     timestamp: int = 0
 
 
@@ -75,6 +86,13 @@ class PlayerDirectory:
         return len(self._idx)
 
 
+def queries_of(tx: np.ndarray) -> np.ndarray:
+    """The igs_query records of a batch of igs_tx records."""
+    q = np.zeros(tx.shape[0], dtype=abi.query_dtype)
+    q["account"], q["ts"], q["seq_limit"] = tx["account"], tx["ts"], tx["seq_limit"]
+    return q
+
+
 IPIntel = Callable[[str], Tuple[bool, bool, bool]]          # ip -> (vpn, proxy, tor)   engine.go:158-171
 Blacklist = Callable[[str, str, str], bool]                  # (device, fingerprint, ip) engine.go:174-176
 Uniques = Callable[[_uuid.UUID], Tuple[int, int]]            # account -> (devices24h, ips24h) redis_store.go:80-81
@@ -82,17 +100,58 @@ Uniques = Callable[[_uuid.UUID], Tuple[int, int]]            # account -> (devic
 
 class ScoringEngine:
     """scoring.ScoringEngine over one `Engine` (one GPU).  `ip_intel`, `blacklist` and `uniques`
-    may be None, exactly as the reference tolerates nil (engine.go:394, :469)."""
+    may be None, exactly as the reference tolerates nil (engine.go:394, :469).
+
+    `device_identifiers=True` moves the identifier work to the GPU: requests and events carry
+    `igs_hash_id` of their device / fingerprint / ip strings, rule 8 is evaluated against the
+    engine's blacklist sets (`AddToBlacklist`) and — when the history was loaded with identifiers —
+    the unique device / IP counts come from the event index.  The host-side `blacklist` / `uniques`
+    callables are then optional extras (a host verdict still ORs into rule 8)."""
 
     def __init__(self, engine, directory: PlayerDirectory, config: Optional[abi.Config] = None,
                  ip_intel: Optional[IPIntel] = None, blacklist: Optional[Blacklist] = None,
-                 uniques: Optional[Uniques] = None):
+                 uniques: Optional[Uniques] = None, device_identifiers: bool = False):
         from . import default_config
         self.engine = engine
         self.directory = directory
         self.config = config if config is not None else default_config()
         self.ip_intel, self.blacklist, self.uniques = ip_intel, blacklist, uniques
+        self.device_identifiers = device_identifiers
         self._lib = abi.load_library()
+
+    def _hash(self, s: str) -> int:
+        b = s.encode()
+        return int(self._lib.igs_hash_id(b, len(b)))
+
+    def marshal_ids(self, reqs: Sequence[ScoreRequest]) -> np.ndarray:
+        """The identifier triples of a batch (igs_tx_ids); "" -> 0 = not checked (redis_store.go:271-279)."""
+        ids = np.zeros(len(reqs), dtype=abi.tx_ids_dtype)
+        for i, r in enumerate(reqs):
+            ids[i] = (self._hash(r.device_id), self._hash(r.fingerprint), self._hash(r.ip))
+        return ids
+
+    def AddToBlacklist(self, list_type: str, value: str) -> None:
+        """RedisFeatureStore.AddToBlacklist (features/redis_store.go:251-264) on the device sets."""
+        kinds = {"device": abi.BL_DEVICE, "ip": abi.BL_IP, "fingerprint": abi.BL_FINGERPRINT}
+        if list_type not in kinds:
+            raise ValueError(f"unknown blacklist type: {list_type}")           # :261
+        self.engine.blacklist_add(kinds[list_type], np.array([self._hash(value)], np.uint64))
+
+    def UpdateFeatures(self, events: Sequence[TransactionEvent]) -> None:
+        """ScoringEngine.UpdateFeatures (engine.go:486-488) for a micro-batch of completed transactions:
+        one igs_append_events(_ids) call.  Events of accounts the directory does not know are dropped
+        (the device tables are dense)."""
+        from . import Events
+        known = [e for e in events if self.directory.get(e.account_id) != 0xFFFFFFFE]
+        now = int(time.time())
+        ev = Events(np.array([self.directory.get(e.account_id) for e in known], np.uint32),
+                    np.array([e.timestamp or now for e in known], np.uint32),
+                    np.array([e.amount for e in known], np.int64),
+                    np.array([_TX_TYPES.get(e.tx_type, abi.TX_OTHER) for e in known], np.uint8))
+        if self.device_identifiers:
+            ev.device = np.array([self._hash(e.device_id) for e in known], np.uint64)
+            ev.ip = np.array([self._hash(e.ip) for e in known], np.uint64)
+        self.engine.append_events(ev)
 
     # -- marshalling (pure host logic; unit-tested without a GPU) ---------------------------------
     def marshal(self, reqs: Sequence[ScoreRequest], now: Optional[int] = None) -> np.ndarray:
@@ -132,10 +191,11 @@ class ScoringEngine:
         """rpc ScoreBatch (risk.proto:13): never raises for data reasons (engine.go:314-322)."""
         t0 = time.perf_counter()
         tx = self.marshal(reqs)
+        ids = self.marshal_ids(reqs) if self.device_identifiers else None
         if with_features:
-            out, feats, _ = self.engine.score_batch(self.config, tx, want_features=True)
+            out, feats, _ = self.engine.score_batch(self.config, tx, want_features=True, ids=ids)
         else:
-            out, feats = self.engine.score_batch(self.config, tx), None
+            out, feats = self.engine.score_batch(self.config, tx, ids=ids), None
         return self.unmarshal(out, int((time.perf_counter() - t0) * 1000), feats)
 
     def Score(self, req: ScoreRequest) -> ScoreResponse:

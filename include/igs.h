@@ -164,8 +164,8 @@ typedef struct igs_tx {
     uint32_t ts;                 /* unix seconds; plays the role of time.Now() (engine.go:350)   */
     uint32_t seq_limit;          /* the query sees events of its account ordered before
                                     (ts, seq_limit); UINT32_MAX = every event with ts' <= ts     */
-    uint16_t unique_devices_24h;
-    uint16_t unique_ips_24h;
+    uint16_t unique_devices_24h; /* host-supplied PFCOUNTs (redis_store.go:80-81); ignored when the */
+    uint16_t unique_ips_24h;     /* history carries identifiers (igs_load_events_ids)            */
     uint8_t  tx_type;            /* IGS_TX_*                                                    */
     uint8_t  bits;               /* IGS_BIT_VPN|PROXY|TOR|BLACKLISTED|VALID                      */
     uint8_t  pad[6];

@@ -114,6 +114,41 @@ public:
     void LoadGBDT(const igs_gbdt_desc& d) { check(igs_load_gbdt(e_, &d)); }
     void LoadPlayers(const igs_player_row* rows, uint64_t n) { check(igs_load_players(e_, rows, n)); }
     void LoadEvents(const igs_event_cols& ev, uint64_t n, uint32_t n_accounts) { check(igs_load_events(e_, &ev, n, n_accounts)); }
+    // History with device / IP identifier columns: from then on UniqueDevices24h / UniqueIPs24h come from the
+    // event index, and ScoreBatch evaluates rule 8 against the device-side blacklist sets.
+    void LoadEvents(const igs_event_cols& ev, const igs_event_ids& ids, uint64_t n, uint32_t n_accounts) {
+        check(igs_load_events_ids(e_, &ev, &ids, n, n_accounts));
+        device_ids_ = true;
+    }
+    static uint64_t HashId(const std::string& s) { return igs_hash_id(s.data(), s.size()); }
+    // RedisFeatureStore.AddToBlacklist, features/redis_store.go:251-264
+    void AddToBlacklist(const std::string& list_type, const std::string& value) {
+        const int kind = list_type == "device" ? IGS_BL_DEVICE : list_type == "ip" ? IGS_BL_IP
+                       : list_type == "fingerprint" ? IGS_BL_FINGERPRINT : -1;
+        if (kind < 0) throw Error(IGS_ERR_INVALID, "unknown blacklist type: " + list_type);   // :261
+        const uint64_t id = HashId(value);
+        check(igs_blacklist_add(e_, kind, &id, 1));
+        device_ids_ = true;
+    }
+    // ScoringEngine.UpdateFeatures (engine.go:486-488) for a micro-batch of completed transactions.
+    struct TransactionEvent {      // features.TransactionEvent, features/redis_store.go:49-56
+        std::array<uint8_t, 16> account_id{};
+        int64_t amount = 0;
+        std::string tx_type = "bet", ip, device_id;
+        int64_t timestamp = 0;
+    };
+    void UpdateFeatures(const std::vector<TransactionEvent>& events) {
+        std::vector<uint32_t> acct, ts; std::vector<int64_t> amt; std::vector<uint8_t> ty; std::vector<uint64_t> dev, ip;
+        for (const TransactionEvent& ev : events) {
+            const uint32_t a = dir_ ? dir_->Get(ev.account_id) : 0xFFFFFFFEu;
+            if (a == 0xFFFFFFFEu) continue;              // unknown account: the device tables are dense
+            acct.push_back(a); ts.push_back((uint32_t)ev.timestamp); amt.push_back(ev.amount);
+            ty.push_back(TxType(ev.tx_type)); dev.push_back(HashId(ev.device_id)); ip.push_back(HashId(ev.ip));
+        }
+        const igs_event_cols cols{acct.data(), ts.data(), amt.data(), ty.data()};
+        const igs_event_ids ids{dev.data(), ip.data()};
+        check(device_ids_ ? igs_append_events_ids(e_, &cols, &ids, acct.size()) : igs_append_events(e_, &cols, acct.size()));
+    }
 
     std::vector<igs_tx> Marshal(const std::vector<ScoreRequest>& reqs) const {
         const int64_t now = std::chrono::duration_cast<std::chrono::seconds>(
@@ -126,8 +161,7 @@ public:
             t.account = dir_ ? dir_->Get(r.account_id) : 0xFFFFFFFEu;
             t.ts = (uint32_t)(r.timestamp ? r.timestamp : now);
             t.seq_limit = 0xFFFFFFFFu;
-            t.tx_type = r.tx_type == "bet" ? IGS_TX_BET : r.tx_type == "deposit" ? IGS_TX_DEPOSIT
-                      : r.tx_type == "withdraw" ? IGS_TX_WITHDRAW : IGS_TX_OTHER;
+            t.tx_type = TxType(r.tx_type);
             uint8_t bits = IGS_BIT_VALID;
             if (ip_ && !r.ip.empty()) {                                   // engine.go:394-405
                 auto [vpn, proxy, tor] = ip_(r.ip);
@@ -153,7 +187,14 @@ public:
         igs_tx* h_tx = tx_.reserve(n);
         igs_result* h_out = out_.reserve(n);
         std::copy(tx.begin(), tx.end(), h_tx);
-        check(igs_score_batch(e_, &cfg_, h_tx, n, h_out, nullptr, nullptr));
+        if (device_ids_) {                  // rule 8 on the device: identifiers travel as 64-bit ids
+            igs_tx_ids* h_ids = ids_.reserve(n);
+            for (size_t i = 0; i < n; ++i)
+                h_ids[i] = igs_tx_ids{HashId(reqs[i].device_id), HashId(reqs[i].fingerprint), HashId(reqs[i].ip)};
+            check(igs_score_batch_ids(e_, &cfg_, h_tx, h_ids, n, h_out, nullptr, nullptr));
+        } else {
+            check(igs_score_batch(e_, &cfg_, h_tx, n, h_out, nullptr, nullptr));
+        }
         const int64_t ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
         std::vector<ScoreResponse> res(n);
         const char* names[IGS_NUM_REASONS];
@@ -191,6 +232,9 @@ public:
     }
 
 private:
+    static uint8_t TxType(const std::string& t) {
+        return t == "bet" ? IGS_TX_BET : t == "deposit" ? IGS_TX_DEPOSIT : t == "withdraw" ? IGS_TX_WITHDRAW : IGS_TX_OTHER;
+    }
     void check(int rc) const {
         if (rc != IGS_OK) throw Error(rc, igs_last_error(e_));
     }
@@ -201,7 +245,9 @@ private:
     Blacklist bl_;
     Uniques uq_;
     Pinned<igs_tx> tx_;
+    Pinned<igs_tx_ids> ids_;
     Pinned<igs_result> out_;
+    bool device_ids_ = false;
 };
 
 }  // namespace igs

@@ -127,6 +127,51 @@ int main(int argc, char** argv) {
         threw = e.status == IGS_ERR_STATE;
     }
     REQUIRE(threw);
+
+    // Identifiers on the device: the reference's real-time loop — Score, then UpdateFeatures — with the unique
+    // device / IP counts coming from the event index and rule 8 from AddToBlacklist, checked against the oracle's
+    // command-level Redis emulation of the same stream.
+    {
+        igs_config c0 = cfg;
+        c0.model_kind = IGS_MODEL_NONE;
+        igs::ScoringEngine e3(0, c0, &dir);
+        e3.LoadPlayers(players.data(), players.size());
+        const igs_event_cols none{nullptr, nullptr, nullptr, nullptr};
+        const igs_event_ids no_ids{nullptr, nullptr};
+        e3.LoadEvents(none, no_ids, 0, n_players);
+        e3.AddToBlacklist("ip", "203.0.113.66");
+        bool bad_type = false;
+        try { e3.AddToBlacklist("email", "x"); } catch (const igs::Error& e) { bad_type = e.status == IGS_ERR_INVALID; }
+        REQUIRE(bad_type);
+        orc_redis_account* redis = orc_redis_new();
+        uint32_t fired = 0;
+        for (int step = 0; step < 8; ++step) {
+            igs::ScoreRequest r;
+            r.account_id = make_id(3);
+            r.amount = 700; r.tx_type = "bet"; r.timestamp = now + 5 * step;
+            r.device_id = "dev-" + std::to_string(step % 5);
+            r.ip = step == 7 ? "203.0.113.66" : "198.51.100." + std::to_string(step);
+            const igs::ScoreResponse got = e3.Score(r);
+            orc_realtime rt;
+            orc_redis_get(redis, r.timestamp, &rt);
+            std::vector<std::string> want_codes;
+            if (rt.unique_devices_24h > 3) want_codes.push_back("MULTIPLE_DEVICES");
+            if (rt.unique_ips_24h > 5) want_codes.push_back("IP_COUNTRY_MISMATCH");
+            if (step == 7) want_codes.push_back("KNOWN_FRAUDSTER");
+            std::vector<std::string> got_codes;
+            for (const std::string& code : got.reason_codes)
+                if (code == "MULTIPLE_DEVICES" || code == "IP_COUNTRY_MISMATCH" || code == "KNOWN_FRAUDSTER") got_codes.push_back(code);
+            REQUIRE(got_codes == want_codes);
+            fired |= (uint32_t)want_codes.size();
+            igs::ScoringEngine::TransactionEvent te;
+            te.account_id = r.account_id; te.amount = r.amount; te.ip = r.ip; te.device_id = r.device_id; te.timestamp = r.timestamp;
+            e3.UpdateFeatures({te});
+            orc_redis_update_ids(redis, r.timestamp, r.amount, orc_hash_id(r.device_id.data(), r.device_id.size()),
+                                 orc_hash_id(r.ip.data(), r.ip.size()));
+        }
+        orc_redis_free(redis);
+        REQUIRE(fired == 3);      // some step fired one rule, the last one all three
+    }
     std::printf("test_scoring_engine: %zu requests, flags seen 0x%x: ok\n", res.size(), seen);
     return 0;
 }

@@ -31,6 +31,19 @@ def test_descriptors_match_the_reference_proto(pkg):
     assert fv.fields_by_name["tx_sum_1h"].number == 4 and fv.fields_by_name["time_since_last_tx_sec"].number == 16
     assert gs.ScoreBatchRequest.DESCRIPTOR.fields_by_name["transactions"].number == 1
     assert gs.ScoreBatchResponse.DESCRIPTOR.fields_by_name["results"].number == 1
+    # blacklist + LTV messages (risk.proto:94-182)
+    a = gs.AddToBlacklistRequest.DESCRIPTOR
+    assert {f.name: f.number for f in a.fields} == {"type": 1, "value": 2, "reason": 3, "created_by": 4, "expires_at": 5}
+    assert a.fields_by_name["expires_at"].message_type.full_name == "google.protobuf.Timestamp"
+    c = gs.CheckBlacklistRequest.DESCRIPTOR
+    assert {f.name: f.number for f in c.fields} == {"device_id": 1, "fingerprint": 2, "ip_address": 3, "email": 4}
+    assert {f.name: f.number for f in gs.BlacklistMatch.DESCRIPTOR.fields} == {"type": 1, "value": 2, "reason": 3, "created_at": 4}
+    l = gs.PredictLTVResponse.DESCRIPTOR
+    assert {f.name: f.number for f in l.fields} == {"account_id": 1, "predicted_ltv": 2, "segment": 3, "churn_risk": 4,
+                                                    "predicted_active_days": 5, "confidence": 6, "next_best_action": 7,
+                                                    "predicted_at": 8}
+    assert l.fields_by_name["segment"].enum_type.values_by_name["SEGMENT_CHURNING"].number == 5
+    assert gs.GetPlayerSegmentResponse.DESCRIPTOR.fields_by_name["recommended_actions"].is_repeated
 
 
 def test_wire_bytes_are_plain_proto3(pkg):
@@ -58,6 +71,21 @@ class FakeDeviceEngine:
         self.abi = abi
         self.calls = []
 
+    def blacklist_add(self, kind, ids):
+        self.sets = getattr(self, "sets", {0: set(), 1: set(), 2: set()})
+        self.sets[kind] |= set(int(x) for x in ids)
+
+    def blacklist_check(self, ids):
+        sets = getattr(self, "sets", {0: set(), 1: set(), 2: set()})
+        return np.array([int(r["device"]) in sets[0] or int(r["fingerprint"]) in sets[1] or int(r["ip"]) in sets[2]
+                         for r in ids], dtype=np.uint8)
+
+    def ltv_batch(self, x, rows):
+        out = np.zeros(rows.shape[0], dtype=self.abi.ltv_result_dtype)
+        out["predicted_ltv"], out["churn_risk"], out["confidence"] = 1234.5, 0.25, 0.5
+        out["days_survival"], out["segment"], out["next_best_action"] = 77, self.abi.SEG_HIGH, 0
+        return out
+
     def score_batch(self, cfg, tx, want_features=False, want_velocity=False):
         n = tx.shape[0]
         self.calls.append(tx.copy())
@@ -81,7 +109,8 @@ def make_service(pkg, device_engine, players=None):
         d.add(u)
     eng = sc.ScoringEngine(device_engine, d, config=pkg.default_config(),
                            ip_intel=lambda ip: (False, False, ip == "tor"))
-    return gs.RiskServicer(eng, players=players), ids
+    x, rows = synth.make_ltv_inputs(8, seed=4)
+    return gs.RiskServicer(eng, players=players, ltv_inputs=(x, rows)), ids
 
 
 def test_grpc_round_trip_with_stand_in_engine(pkg, built_lib):
@@ -114,7 +143,24 @@ def test_grpc_round_trip_with_stand_in_engine(pkg, built_lib):
         assert up.success and up.block_threshold == 50
         assert client.ScoreTransaction(req.transactions[1]).action == 3
         import grpc
-        raw = client.channel.unary_unary(f"/{gs.SERVICE}/PredictLTV", request_serializer=lambda b: b,
+        # blacklist management on the (stand-in) device sets
+        assert client.AddToBlacklist(gs.AddToBlacklistRequest(type="device", value="dev-9", reason="chargeback")).success
+        assert not client.AddToBlacklist(gs.AddToBlacklistRequest(type="email", value="a@b.c")).success    # redis_store.go:261
+        cb = client.CheckBlacklist(gs.CheckBlacklistRequest(device_id="dev-9", fingerprint="dev-9", ip_address="dev-9"))
+        assert cb.is_blacklisted and [(m.type, m.value) for m in cb.matches] == [("device", "dev-9")]
+        assert not client.CheckBlacklist(gs.CheckBlacklistRequest(device_id="dev-8")).is_blacklisted
+        assert not client.CheckBlacklist(gs.CheckBlacklistRequest()).is_blacklisted
+        # LTV
+        lt = client.PredictLTV(gs.PredictLTVRequest(account_id=str(ids[2])))
+        assert (lt.account_id, lt.segment, lt.predicted_active_days) == (str(ids[2]), 2, 77)
+        assert lt.predicted_ltv == 1234.5 and lt.predicted_at.seconds > 0 and lt.next_best_action
+        sg = client.GetPlayerSegment(gs.GetPlayerSegmentRequest(account_id=str(ids[2])))
+        assert sg.segment == 2 and list(sg.recommended_actions) == [lt.next_best_action]
+        import grpc
+        with pytest.raises(grpc.RpcError) as ei:
+            client.PredictLTV(gs.PredictLTVRequest(account_id=str(uuid.UUID(int=1))))
+        assert ei.value.code() == grpc.StatusCode.NOT_FOUND
+        raw = client.channel.unary_unary(f"/{gs.SERVICE}/CheckBonusAbuse", request_serializer=lambda b: b,
                                          response_deserializer=lambda b: b)
         with pytest.raises(grpc.RpcError) as ei:
             raw(b"")
@@ -164,3 +210,55 @@ def test_grpc_score_batch_on_the_gpu(engine, orc, pkg):
     finally:
         client.close()
         server.stop(0)
+
+
+@pytest.mark.gpu
+def test_grpc_blacklist_and_ltv_on_the_gpu(engine, orc, pkg):
+    """AddToBlacklist -> ScoreTransaction fires KNOWN_FRAUDSTER through the device-side sets; CheckBlacklist
+    names the matching list; PredictLTV / GetPlayerSegment return the LTV model's result for the account."""
+    sc, gs, abi = pkg.scoring, pkg.grpc_service, pkg.abi
+    n_players = 20
+    now = int(__import__("time").time())
+    players = synth.make_players(n_players, seed=71, now=now)
+    engine.load_players(players)
+    engine.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64), np.zeros(0, np.uint8),
+                                  device=np.zeros(0, np.uint64), ip=np.zeros(0, np.uint64)), n_players)
+    mlp = synth.make_mlp(seed=72)
+    engine.load_mlp(mlp)
+    x, rows = synth.make_ltv_inputs(n_players, seed=73)
+    d = sc.PlayerDirectory()
+    ids = [uuid.UUID(int=8000 + i) for i in range(n_players)]
+    for u in ids:
+        d.add(u)
+    eng = sc.ScoringEngine(engine, d, config=pkg.default_config(model_kind=abi.MODEL_NONE), device_identifiers=True)
+    server = gs.serve(gs.RiskServicer(eng, players=players, ltv_inputs=(x, rows)), "127.0.0.1:0")
+    client = gs.RiskClient(f"127.0.0.1:{server.bound_port}")
+    try:
+        req = gs.ScoreTransactionRequest(account_id=str(ids[3]), amount=500, transaction_type="bet", device_id="phone-1",
+                                         fingerprint="fp-1", ip_address="198.51.100.9")
+        assert "KNOWN_FRAUDSTER" not in client.ScoreTransaction(req).reason_codes
+        assert client.AddToBlacklist(gs.AddToBlacklistRequest(type="fingerprint", value="fp-1")).success
+        r = client.ScoreTransaction(req)
+        assert "KNOWN_FRAUDSTER" in r.reason_codes and r.rule_score >= 50
+        cb = client.CheckBlacklist(gs.CheckBlacklistRequest(device_id="phone-1", fingerprint="fp-1", ip_address="198.51.100.9"))
+        assert cb.is_blacklisted and [(m.type, m.value) for m in cb.matches] == [("fingerprint", "fp-1")]
+        assert not client.CheckBlacklist(gs.CheckBlacklistRequest(device_id="fp-1")).is_blacklisted   # wrong list
+        # uniques echo: after two completed transactions with different devices the next score sees 2 devices
+        for k in range(2):
+            eng.UpdateFeatures([sc.TransactionEvent(ids[3], 100, "bet", ip="198.51.100.9", device_id=f"phone-{k}", timestamp=now - 5)])
+        f = client.ScoreTransaction(req).features
+        assert (f.unique_devices_24h, f.unique_ips_24h, f.tx_count_1m) == (2, 1, 1)   # equal (ts, amount): one ZSET member
+        # LTV for one account == the batch call for that row
+        want = engine.ltv_batch(x[5:6], rows[5:6])[0]
+        lt = client.PredictLTV(gs.PredictLTVRequest(account_id=str(ids[5])))
+        assert lt.predicted_ltv == np.float32(want["predicted_ltv"]) and lt.segment == int(want["segment"])
+        assert lt.churn_risk == np.float32(want["churn_risk"]) and lt.predicted_active_days == int(want["days_survival"])
+        sg = client.GetPlayerSegment(gs.GetPlayerSegmentRequest(account_id=str(ids[5])))
+        assert sg.segment == lt.segment and list(sg.recommended_actions) == [lt.next_best_action]
+    finally:
+        client.close()
+        server.stop(0)
+        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+            engine.blacklist_load(kind, np.zeros(0, np.uint64))
+        engine.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64),
+                                      np.zeros(0, np.uint8)), 1)

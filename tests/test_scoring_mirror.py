@@ -85,3 +85,61 @@ def test_score_and_score_batch_like_the_reference(engine, orc, pkg):
     s.SetThresholds(80, 50)
     text = s.ScoreWithExplanation(reqs[0])
     assert "Final Score:" in text and "KNOWN_FRAUDSTER (+50)" in text
+
+
+@pytest.mark.gpu
+def test_device_identifiers_stream_like_the_reference(engine, orc, pkg):
+    """The reference's real-time loop with every identifier input on the device: Score a tx, then
+    UpdateFeatures with it (main.go:219-224).  Devices / IPs accumulate per account until R3 / R4
+    fire; AddToBlacklist makes R8 fire for a fingerprint.  Checked against the oracle's command-level
+    Redis emulation of the same stream."""
+    sc, abi = pkg.scoring, pkg.abi
+    now = synth.T0 + 1000
+    players = synth.make_players(4, seed=93, now=now)
+    players["account_created_at"][:] = now - 400 * 86400
+    engine.load_players(players)
+    empty = pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64), np.zeros(0, np.uint8),
+                       device=np.zeros(0, np.uint64), ip=np.zeros(0, np.uint64))
+    engine.load_events(empty, 4)
+    d = sc.PlayerDirectory()
+    accts = [uuid.UUID(int=7000 + i) for i in range(4)]
+    for u in accts:
+        d.add(u)
+    s = sc.ScoringEngine(engine, d, config=pkg.default_config(model_kind=abi.MODEL_NONE), device_identifiers=True)
+    try:
+        s.AddToBlacklist("fingerprint", "fp-bad")
+        with pytest.raises(ValueError):
+            s.AddToBlacklist("email", "x")
+        L = orc.lib()
+        redis = [L.orc_redis_new() for _ in accts]
+        import ctypes as C
+        fired = set()
+        for step in range(9):
+            t = now + 10 * step
+            a = step % 2                                       # two accounts alternate
+            dev, ip = f"dev-{a}-{step // 2}", f"10.0.{a}.{step}"
+            fp = "fp-bad" if step == 8 else "fp-ok"
+            r = s.Score(sc.ScoreRequest(accts[a], 500, "bet", ip=ip, device_id=dev, fingerprint=fp, timestamp=t))
+            rt = orc.Realtime()
+            L.orc_redis_get(redis[a], t, C.byref(rt))
+            want = []
+            if rt.unique_devices_24h > 3:
+                want.append("MULTIPLE_DEVICES")
+            if rt.unique_ips_24h > 5:
+                want.append("IP_COUNTRY_MISMATCH")
+            if fp == "fp-bad":
+                want.append("KNOWN_FRAUDSTER")
+            assert [c for c in r.reason_codes if c in ("MULTIPLE_DEVICES", "IP_COUNTRY_MISMATCH", "KNOWN_FRAUDSTER")] == want, step
+            # features idx 5 / 6 = minmax(uniques) exactly as the emulation counts them
+            assert r.features[5] == np.float32(min(rt.unique_devices_24h, 10)) / np.float32(10)
+            fired |= set(want)
+            s.UpdateFeatures([sc.TransactionEvent(accts[a], 500, "bet", ip=ip, device_id=dev, timestamp=t)])
+            L.orc_redis_update_ids(redis[a], t, 500, orc.hash_id(dev), orc.hash_id(ip))
+        assert fired == {"MULTIPLE_DEVICES", "KNOWN_FRAUDSTER"}
+        for h in redis:
+            L.orc_redis_free(h)
+    finally:
+        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+            engine.blacklist_load(kind, np.zeros(0, np.uint64))
+        engine.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64),
+                                      np.zeros(0, np.uint8)), 1)
