@@ -259,18 +259,23 @@ __global__ void k_group_heads(const uint32_t* __restrict__ acct, const uint32_t*
 }
 
 // distinct flag: no earlier event of the same (account, ts) group has the same amount (the ZSET member
-// "ts:amount" dedupe).  Walks back through the group four events at a time; the loads of a step do not
-// depend on each other, so same-second bursts of a hot account (hundreds of events) stay cheap.
+// "ts:amount" dedupe).  Walks back through the group four events at a time (the loads of a step do not
+// depend on each other), at most kDistinctWalk events: groups of up to kDistinctWalk + 1 events — all of
+// them in ordinary traffic — are settled here.  An event that is deeper in its group and found no equal
+// amount on the way is marked kUnresolved and counted; the hash pass below settles those groups, so a
+// same-second burst of any size (a bot, a replayed queue) costs linear, not quadratic, work.
+constexpr uint32_t kDistinctWalk = 32;
+constexpr uint8_t kUnresolved = 2;
+
 __global__ void k_distinct(const uint8_t* __restrict__ head, const int64_t* __restrict__ amount, uint32_t n,
-                           uint8_t* __restrict__ dflag) {
+                           uint8_t* __restrict__ dflag, uint32_t* __restrict__ n_unresolved) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
     uint8_t d = 1;
-    if (!__ldg(head + i)) {
+    if (i < n && !__ldg(head + i)) {
         const int64_t m = __ldg(amount + i);
         uint32_t j = i;                       // candidates are j-1, j-2, ... down to the group head
         bool done = false;
-        while (!done) {
+        for (uint32_t step = 0; step < kDistinctWalk / 4 && !done; ++step) {
             int64_t a[4];
             uint8_t h[4];
 #pragma unroll
@@ -287,8 +292,79 @@ __global__ void k_distinct(const uint8_t* __restrict__ head, const int64_t* __re
             }
             j = j >= 4 ? j - 4 : 0;
         }
+        if (!done) d = kUnresolved;
     }
-    dflag[i] = d;
+    const unsigned unres = __ballot_sync(0xffffffffu, d == kUnresolved);
+    if (unres && (threadIdx.x & 31) == 0) atomicAdd(n_unresolved, (uint32_t)__popc(unres));
+    if (i < n) dflag[i] = d;
+}
+
+// ---- hash pass for the groups k_distinct could not settle (rare) ---------------------------------
+// Every (account, ts) group with more than kDistinctWalk + 1 events gets its own open-addressing table
+// (capacity = power of two >= 2 x group size): key = amount, value = smallest sorted position that carries
+// it.  An event is distinct iff it is that smallest position.  The amount INT64_MIN would collide with the
+// empty-slot marker and is tracked in a per-group word instead.
+__global__ void k_dg_heads_u32(const uint8_t* __restrict__ head, uint32_t n, uint32_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __ldg(head + i);
+}
+// gid = exclusive scan of the head flags on entry; group of event i = gid[i] + head[i] - 1
+__global__ void k_dg_starts(const uint8_t* __restrict__ head, uint32_t* __restrict__ gid, uint32_t n,
+                            uint32_t* __restrict__ gstart, uint32_t n_groups) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t h = __ldg(head + i);
+    const uint32_t g = gid[i] + h - 1;
+    gid[i] = g;
+    if (h) gstart[g] = i;
+    if (i == n - 1) gstart[n_groups] = n;
+}
+__global__ void k_dg_caps(const uint32_t* __restrict__ gstart, uint32_t n_groups, uint32_t* __restrict__ cap) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_groups) return;
+    const uint32_t size = __ldg(gstart + g + 1) - __ldg(gstart + g);
+    uint32_t c = 0;
+    if (size > kDistinctWalk + 1) {
+        c = 64;
+        while (c < 2 * size) c <<= 1;
+    }
+    cap[g] = c;
+}
+__device__ __forceinline__ uint32_t dg_slot(uint64_t key, uint32_t mask) {
+    return (uint32_t)(igs_idset_mix(key) & mask);
+}
+__global__ void k_dg_insert(const uint32_t* __restrict__ gid, const uint32_t* __restrict__ gstart,
+                            const uint32_t* __restrict__ toff /* exclusive scan of cap, [n_groups + 1] */,
+                            const int64_t* __restrict__ amount, uint32_t n, unsigned long long* __restrict__ keys,
+                            uint32_t* __restrict__ minpos, uint32_t* __restrict__ special) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = __ldg(gid + i);
+    const uint32_t base = __ldg(toff + g), cap = __ldg(toff + g + 1) - base;
+    if (cap == 0) return;                                   // small group: settled by k_distinct
+    const uint64_t key = (uint64_t)__ldg(amount + i) ^ 0x8000000000000000ull;
+    if (key == 0) { atomicMin(special + g, i); return; }
+    uint32_t h = dg_slot(key, cap - 1);
+    for (;;) {
+        const unsigned long long prev = atomicCAS(keys + base + h, 0ull, (unsigned long long)key);
+        if (prev == 0ull || prev == key) { atomicMin(minpos + base + h, i); return; }
+        h = (h + 1) & (cap - 1);
+    }
+}
+__global__ void k_dg_resolve(const uint32_t* __restrict__ gid, const uint32_t* __restrict__ toff,
+                             const int64_t* __restrict__ amount, uint32_t n,
+                             const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ minpos,
+                             const uint32_t* __restrict__ special, uint8_t* __restrict__ dflag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = __ldg(gid + i);
+    const uint32_t base = __ldg(toff + g), cap = __ldg(toff + g + 1) - base;
+    if (cap == 0) return;
+    const uint64_t key = (uint64_t)__ldg(amount + i) ^ 0x8000000000000000ull;
+    if (key == 0) { dflag[i] = __ldg(special + g) == i; return; }
+    uint32_t h = dg_slot(key, cap - 1);
+    while (keys[base + h] != key) h = (h + 1) & (cap - 1);  // present: inserted by k_dg_insert
+    dflag[i] = minpos[base + h] == i;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -808,6 +884,59 @@ static int radix_sort_pairs(igs_engine* e, uint64_t* keys[2], uint32_t* vals[2],
     return IGS_OK;
 }
 
+// Settles the distinct flags of the (account, ts) groups that are too long for k_distinct's bounded walk.
+// Its buffers come from the build pool like everything else; they are requested on every build, in the same
+// order (one element each when there is nothing to settle), so that the pool's request sequence stays fixed
+// and rebuilds after igs_append_events reuse them.
+static int resolve_big_groups(igs_engine* e, Scratch& sc, bool needed, const uint8_t* d_head, const int64_t* d_amt,
+                              uint32_t n, uint8_t* d_dflag, uint32_t* d_scan_scratch, cudaStream_t st) {
+    const uint32_t nb = (n + kThreads - 1) / kThreads;
+    uint32_t *gid, *gstart, *cap, *minpos, *special, *scr;
+    unsigned long long* keys;
+    IGS_CUDA(e, sc.alloc(&gid, needed ? n : 1));
+    uint32_t n_groups = 0;
+    if (needed) {
+        k_dg_heads_u32<<<nb, kThreads, 0, st>>>(d_head, n, gid);
+        IGS_CUDA(e, cudaGetLastError());
+        const int rc = scan_u32(e, gid, n, d_scan_scratch, st);
+        if (rc != IGS_OK) return rc;
+        uint32_t last_ex = 0; uint8_t last_head = 0;
+        IGS_CUDA(e, cudaMemcpyAsync(&last_ex, gid + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaMemcpyAsync(&last_head, d_head + (n - 1), 1, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+        n_groups = last_ex + last_head;
+    }
+    IGS_CUDA(e, sc.alloc(&gstart, (size_t)n_groups + 1));
+    IGS_CUDA(e, sc.alloc(&cap, (size_t)n_groups + 1));
+    IGS_CUDA(e, sc.alloc(&special, n_groups));
+    IGS_CUDA(e, sc.alloc(&scr, scan_u32_scratch_elems(n_groups + 1)));
+    uint32_t total = 0;
+    if (needed) {
+        IGS_CUDA(e, cudaMemsetAsync(special, 0xFF, (size_t)n_groups * 4, st));
+        IGS_CUDA(e, cudaMemsetAsync(cap + n_groups, 0, 4, st));
+        k_dg_starts<<<nb, kThreads, 0, st>>>(d_head, gid, n, gstart, n_groups);
+        IGS_CUDA(e, cudaGetLastError());
+        k_dg_caps<<<(n_groups + kThreads - 1) / kThreads, kThreads, 0, st>>>(gstart, n_groups, cap);
+        IGS_CUDA(e, cudaGetLastError());
+        // exclusive scan over n_groups + 1 entries: cap[n_groups] becomes the total table size
+        const int rc = scan_u32(e, cap, n_groups + 1, scr, st);
+        if (rc != IGS_OK) return rc;
+        IGS_CUDA(e, cudaMemcpyAsync(&total, cap + n_groups, 4, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+    }
+    IGS_CUDA(e, sc.alloc(&keys, total));
+    IGS_CUDA(e, sc.alloc(&minpos, total));
+    if (needed) {
+        IGS_CUDA(e, cudaMemsetAsync(keys, 0, (size_t)total * 8, st));
+        IGS_CUDA(e, cudaMemsetAsync(minpos, 0xFF, (size_t)total * 4, st));
+        k_dg_insert<<<nb, kThreads, 0, st>>>(gid, gstart, cap, d_amt, n, keys, minpos, special);
+        IGS_CUDA(e, cudaGetLastError());
+        k_dg_resolve<<<nb, kThreads, 0, st>>>(gid, cap, d_amt, n, keys, minpos, special, d_dflag);
+        IGS_CUDA(e, cudaGetLastError());
+    }
+    return IGS_OK;
+}
+
 struct IdScratch {
     uint64_t* keys[2]; uint32_t* vals[2];
     uint64_t *id_s, *cid;
@@ -948,10 +1077,20 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     IGS_CUDA(e, cudaGetLastError());
     uint8_t* d_head;
     IGS_CUDA(e, sc.alloc(&d_head, n));
+    uint32_t* d_scan_scratch_n;                                        // scratch of an n-element u32 scan
+    IGS_CUDA(e, sc.alloc(&d_scan_scratch_n, scan_u32_scratch_elems(n + 1)));
     k_group_heads<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, n, d_head);
     IGS_CUDA(e, cudaGetLastError());
-    k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag);
+    IGS_CUDA(e, cudaMemsetAsync(d_mm, 0, 4, st));                     // d_mm[0] is free again: unresolved counter
+    k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_mm);
     IGS_CUDA(e, cudaGetLastError());
+    {
+        uint32_t n_unres = 0;
+        IGS_CUDA(e, cudaMemcpyAsync(&n_unres, d_mm, 4, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+        const int rc = resolve_big_groups(e, sc, n_unres != 0, d_head, d_amt, n, d_dflag, d_scan_scratch_n, st);
+        if (rc != IGS_OK) return rc;
+    }
 
     // ---- fused scan: reduce up two levels, scan the top, apply down ---------------------------------
     const uint32_t n1 = (n + kVTile - 1) / kVTile;            // level-0 aggregates (one per 256 events)

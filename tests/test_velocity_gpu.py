@@ -101,6 +101,51 @@ def test_dedupe_and_ties_stress(engine, orc, pkg):
     assert int(want["tx_count_1m"].max()) <= 10      # at most 5 amounts x 2 seconds
 
 
+def test_same_second_bursts_of_any_size(engine, orc, pkg):
+    """Groups of events sharing (account, second) that are longer than the kernel's bounded backward walk
+    (33 events) go through the per-group hash tables: sizes right at the boundary, thousands of events with
+    few / many distinct amounts, the amount INT64_MIN (the tables' empty-slot marker), appended in pieces."""
+    abi = pkg.abi
+    rng = np.random.default_rng(17)
+    I64_MIN = np.iinfo(np.int64).min
+    parts = []          # (account, ts offset, amounts)
+    parts.append((0, 100, rng.integers(1, 300, 6000)))                      # 6000 events, ~300 distinct amounts
+    parts.append((0, 101, np.arange(5000, dtype=np.int64)))                 # all distinct
+    parts.append((1, 100, np.full(4000, 77, np.int64)))                     # all equal
+    parts.append((2, 50, np.concatenate([np.arange(33), [5]])))             # 34 events: dup is 29 back
+    parts.append((3, 50, np.concatenate([[5], np.arange(100, 132), [5]])))  # 34 events: dup is 33 back (beyond the walk)
+    parts.append((4, 50, np.arange(33)))                                    # 33 events: exactly the walk
+    parts.append((5, 60, np.array([I64_MIN, 3, I64_MIN] + list(range(10, 50)) + [I64_MIN, 3], dtype=np.int64)))
+    parts.append((6, 10, rng.integers(1, 50, 3000)))                        # plus ordinary traffic around it
+    acct = np.concatenate([np.full(len(a), k, np.uint32) for k, _, a in parts] + [rng.integers(0, 8, 5000).astype(np.uint32)])
+    ts = np.concatenate([np.full(len(a), synth.T0 + t, np.uint32) for _, t, a in parts]
+                        + [(synth.T0 + rng.integers(0, 200, 5000)).astype(np.uint32)])
+    amt = np.concatenate([np.asarray(a, np.int64) for _, _, a in parts] + [rng.integers(1, 20, 5000).astype(np.int64)])
+    perm = rng.permutation(len(acct))                                       # arrival order is arbitrary
+    ev = pkg.Events(acct[perm], ts[perm], amt[perm], np.zeros(len(acct), np.uint8))
+    n_acc = 8
+    engine.load_events(ev, n_acc)
+    q = np.zeros(8 * 6, dtype=abi.query_dtype)
+    q["account"] = np.repeat(np.arange(8), 6)
+    q["ts"] = synth.T0 + np.tile([49, 50, 100, 101, 150, 3000], 8)
+    q["seq_limit"] = abi.SEQ_ALL
+    mid = np.zeros(64, dtype=abi.query_dtype)                               # queries that see part of a burst
+    mid["account"] = rng.integers(0, 7, 64)
+    mid["ts"] = synth.T0 + rng.choice([50, 60, 100, 101], 64)
+    mid["seq_limit"] = rng.integers(0, len(acct), 64)
+    q = np.concatenate([q, mid])
+    want = orc.velocity_batch(ev, n_acc, q)
+    assert_velocity_equal(engine.get_velocity(q), want)
+    assert want["tx_count_1m"].max() >= 5000
+    # the same history arriving in three appends
+    cuts = [0, 7000, 7001, len(acct)]
+    first = pkg.Events(ev.account[:cuts[1]], ev.ts[:cuts[1]], ev.amount[:cuts[1]], ev.tx_type[:cuts[1]])
+    engine.load_events(first, n_acc)
+    for a, b in zip(cuts[1:-1], cuts[2:]):
+        engine.append_events(pkg.Events(ev.account[a:b], ev.ts[a:b], ev.amount[a:b], ev.tx_type[a:b]))
+    assert_velocity_equal(engine.get_velocity(q), want)
+
+
 def test_unsorted_arrival_and_wide_keys(engine, orc, pkg):
     """Events arrive in random time order over a 400-day span with sparse account ids (the sort
     must order by (account, ts) and keep arrival order among equal keys)."""
