@@ -210,6 +210,37 @@ class Engine:
         self._check(self._lib.igs_blacklist_check(self._h, abi.ptr(ids), ids.shape[0], abi.ptr(out)))
         return out
 
+    # -- linked accounts / bonus abuse (stages; links.build_links drives them) ------------------
+    def links_pairs(self, shard: int, n_shards: int):
+        """Stage 1 -> (device pointer to the grouped igs_link_pair records, per-shard counts)."""
+        p = C.c_void_p()
+        counts = (C.c_uint64 * n_shards)()
+        self._check(self._lib.igs_links_pairs(self._h, shard, n_shards, C.byref(p), counts))
+        return p.value or 0, np.array(list(counts), dtype=np.uint64)
+
+    def links_group(self, d_pairs: int, n: int, n_shards: int):
+        """Stage 2 -> (device pointer to the grouped igs_link records, per-shard counts)."""
+        p = C.c_void_p()
+        counts = (C.c_uint64 * n_shards)()
+        self._check(self._lib.igs_links_group(self._h, d_pairs, n, n_shards, C.byref(p), counts))
+        return p.value or 0, np.array(list(counts), dtype=np.uint64)
+
+    def links_finish(self, d_links: int, n: int, shard: int) -> None:
+        self._check(self._lib.igs_links_finish(self._h, d_links, n, shard))
+
+    def get_links(self, accounts: np.ndarray) -> np.ndarray:
+        accounts = np.ascontiguousarray(accounts, dtype=np.uint32)
+        out = np.zeros(accounts.shape[0], dtype=abi.links_row_dtype)
+        self._check(self._lib.igs_get_links(self._h, abi.ptr(accounts), accounts.shape[0], abi.ptr(out)))
+        return out
+
+    def check_bonus_abuse(self, accounts: np.ndarray) -> np.ndarray:
+        """RiskChecker.CheckBonusAbuse (bonus_engine.go:139-141) for a batch of dense account indices."""
+        accounts = np.ascontiguousarray(accounts, dtype=np.uint32)
+        out = np.zeros(accounts.shape[0], dtype=abi.abuse_dtype)
+        self._check(self._lib.igs_check_bonus_abuse(self._h, abi.ptr(accounts), accounts.shape[0], abi.ptr(out)))
+        return out
+
     # -- path A -------------------------------------------------------------------------------
     def score_features(self, cfg: abi.Config, features: np.ndarray, rows: np.ndarray,
                        want_leaves: bool = False, n_trees: int | None = None):
@@ -297,7 +328,7 @@ def hash_id(s: str | bytes) -> int:
     return int(abi.load_library().igs_hash_id(b, len(b)))
 
 
-from . import scoring, sharding  # noqa: E402  (reference-facing mirror + shard bookkeeping)
+from . import links, scoring, sharding  # noqa: E402  (reference-facing mirror + shard bookkeeping)
 
 
 def __getattr__(name):

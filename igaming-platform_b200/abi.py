@@ -44,6 +44,8 @@ SEG_VIP, SEG_HIGH, SEG_MEDIUM, SEG_LOW, SEG_CHURNING = 1, 2, 3, 4, 5
 SEQ_ALL = 0xFFFFFFFF
 PARTITION_STATIC_WORDS = 256 * 1024
 BL_DEVICE, BL_FINGERPRINT, BL_IP = 0, 1, 2
+LINK_MAX_ACCOUNTS = 64
+ABUSE_BONUS_ONLY, ABUSE_MULTI_ACCOUNT, ABUSE_ACCOUNT_RING = 1, 2, 4
 
 rule_row_dtype = np.dtype([
     ("amount", "<i8"), ("total_deposits", "<i8"), ("total_withdrawals", "<i8"),
@@ -73,6 +75,11 @@ velocity_dtype = np.dtype([
 ])
 tx_ids_dtype = np.dtype([("device", "<u8"), ("fingerprint", "<u8"), ("ip", "<u8")])
 uniques_dtype = np.dtype([("devices_24h", "<u4"), ("ips_24h", "<u4")])
+link_pair_dtype = np.dtype([("device", "<u8"), ("account", "<u8")])
+link_dtype = np.dtype([("account", "<u8"), ("other", "<u8")])
+links_row_dtype = np.dtype([("n_linked", "<u4"), ("reserved", "<u4"), ("linked", "<u8", (3,))])
+abuse_dtype = np.dtype([("abuse_score", "<f4"), ("n_linked", "<u4"), ("is_abuser", "u1"), ("signals", "u1"),
+                        ("pad", "u1", (6,))])
 ltv_row_dtype = np.dtype([
     ("sessions_per_week", "<f8"), ("deposit_frequency", "<f8"), ("total_deposits", "<f8"),
     ("total_withdrawals", "<f8"), ("net_revenue", "<f8"), ("bonus_conversion_rate", "<f8"),
@@ -93,6 +100,7 @@ assert player_row_dtype.itemsize == 96
 assert query_dtype.itemsize == 16
 assert velocity_dtype.itemsize == 128
 assert tx_ids_dtype.itemsize == 24 and uniques_dtype.itemsize == 8
+assert link_pair_dtype.itemsize == 16 and link_dtype.itemsize == 16 and links_row_dtype.itemsize == 32 and abuse_dtype.itemsize == 16
 assert ltv_row_dtype.itemsize == 80
 assert ltv_result_dtype.itemsize == 32
 
@@ -148,6 +156,8 @@ EXPORTS = [
     "igs_load_events_ids", "igs_append_events_ids", "igs_get_uniques", "igs_get_uniques_device",
     "igs_blacklist_load", "igs_blacklist_add", "igs_blacklist_check", "igs_blacklist_check_device",
     "igs_score_batch_ids", "igs_score_batch_ids_device", "igs_hash_id",
+    "igs_links_pairs", "igs_links_group", "igs_links_finish", "igs_get_links", "igs_check_bonus_abuse",
+    "igs_abuse_signals",
 ]
 
 LIB_NAME = "libigs.so"
@@ -223,6 +233,12 @@ def load_library() -> C.CDLL:
     lib.igs_blacklist_check_device.argtypes = [vp, vp, u64, vp, vp]
     lib.igs_score_batch_ids.argtypes = [vp, C.POINTER(Config), vp, vp, u64, vp, vp, vp]
     lib.igs_score_batch_ids_device.argtypes = [vp, C.POINTER(Config), vp, vp, u64, vp, vp, vp, vp]
+    lib.igs_links_pairs.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(vp), C.POINTER(u64)]
+    lib.igs_links_group.argtypes = [vp, vp, u64, C.c_uint32, C.POINTER(vp), C.POINTER(u64)]
+    lib.igs_links_finish.argtypes = [vp, vp, u64, C.c_uint32]
+    lib.igs_get_links.argtypes = [vp, vp, u64, vp]
+    lib.igs_check_bonus_abuse.argtypes = [vp, vp, u64, vp]
+    lib.igs_abuse_signals.argtypes = [C.c_uint32, C.POINTER(C.c_char_p * 3)]
     lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
     lib.igs_hash_id.restype = u64
     lib.igs_version.argtypes = []

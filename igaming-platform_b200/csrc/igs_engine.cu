@@ -147,6 +147,7 @@ void igs_engine_destroy(igs_engine* e) {
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
     for (int k = 0; k < 3; ++k) igs_idset_free(&e->bl[k]);
+    igs_links_free(e);
     igs_mlp_free(e);
     delete e;
 }

@@ -113,6 +113,11 @@ struct igs_engine {
     // blacklist sets (idset.cuh / k_ids.cu), indexed by IGS_BL_*
     igs_idset bl[3];
 
+    // linked accounts (k_links.cu): stage scratch + the per-account table built by igs_links_finish
+    std::vector<igs_buf> links_pool;
+    igs_links_row* d_links_rows = nullptr;
+    uint64_t n_links_rows = 0;
+
     // MLP
     void* d_mlp = nullptr;        // see k_ltv.cu
     bool  has_mlp = false;
@@ -158,6 +163,8 @@ int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_eve
                           uint32_t n_accounts);
 int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids,
                              uint64_t n);   // append + rebuild
+// linked accounts (k_links.cu)
+void igs_links_free(igs_engine* e);
 // blacklist sets (k_ids.cu)
 int igs_idset_load(igs_engine* e, igs_idset* s, const uint64_t* ids, uint64_t n, bool replace);
 void igs_idset_free(igs_idset* s);

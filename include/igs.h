@@ -442,6 +442,67 @@ int igs_score_batch_ids_device(igs_engine* e, const igs_config* cfg, const igs_t
                                const igs_tx_ids* d_ids, uint64_t n, igs_result* d_out,
                                float* d_features_out, igs_velocity* d_velocity_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------ */
+/* linked accounts / bonus abuse — the one step of the path that crosses shards    */
+/* ------------------------------------------------------------------------------------------ */
+/* Serves RiskChecker.CheckBonusAbuse (services/bonus/internal/service/bonus_engine.go:139-141, called at
+ * :268-275) and rpc CheckBonusAbuse (proto/risk/v1/risk.proto:20,135-145: is_abuser, abuse_score,
+ * signals, linked_accounts).  The reference declares these interfaces and the MULTI_ACCOUNT reason
+ * ("Linked to other accounts", risk.proto:274) but contains no implementation, so the semantics below
+ * are DEFINED HERE (parity unpinned; the oracle restates them on the CPU):
+ *   - two accounts are linked iff some device id occurs in the histories of both; a device seen on
+ *     more than IGS_LINK_MAX_ACCOUNTS accounts is treated as public (a kiosk, an emulator image) and
+ *     links nobody;
+ *   - per account: n_linked = number of distinct linked accounts, linked[] = the three smallest of
+ *     their global ids;
+ *   - signals: IGS_ABUSE_BONUS_ONLY = FeatureVector.BonusOnlyPlayer (scoring/engine.go:384-386),
+ *     IGS_ABUSE_MULTI_ACCOUNT = n_linked >= 1, IGS_ABUSE_ACCOUNT_RING = n_linked >= 3;
+ *     abuse_score = (5*bonus_only + 3*multi_account + 2*account_ring) / 10; is_abuser = score >= 0.5.
+ * Accounts live on the shard igs_shard_of picks, devices do not: the links are found in three stages
+ * with an exchange between them.  A global account id is (shard << 32) | dense index.
+ *   stage 1, every shard:  igs_links_pairs   -> (device, account) pairs of the local history, grouped
+ *                                              by the shard that owns the device
+ *                                              (owner = igs_shard_of(device, 0, n_shards))
+ *   exchange 1:            all-to-all of the groups (the caller's collective: NCCL all_to_all over
+ *                          NVLink in igaming-platform_b200/links.py; nothing to do for one shard)
+ *   stage 2, device owner: igs_links_group   -> directed links (account, other), grouped by the shard
+ *                                              that owns `account`
+ *   exchange 2:            all-to-all of the groups
+ *   stage 3, account owner: igs_links_finish -> the per-account table, resident on the device
+ * Stage outputs are device buffers owned by the engine, valid until the next igs_links_* call;
+ * counts[n_shards] (host) receives the group sizes, groups are contiguous in shard order.          */
+#define IGS_LINK_MAX_ACCOUNTS 64
+typedef struct igs_link_pair { uint64_t device; uint64_t account; } igs_link_pair;
+typedef struct igs_link { uint64_t account; uint64_t other; } igs_link;
+typedef struct igs_links_row {
+    uint32_t n_linked;
+    uint32_t reserved;
+    uint64_t linked[3];        /* smallest global ids of the linked accounts, 0-filled              */
+} igs_links_row;
+#define IGS_ABUSE_BONUS_ONLY    (1u << 0)
+#define IGS_ABUSE_MULTI_ACCOUNT (1u << 1)
+#define IGS_ABUSE_ACCOUNT_RING  (1u << 2)
+typedef struct igs_abuse {
+    float    abuse_score;      /* CheckBonusAbuseResponse.abuse_score, 0..1                         */
+    uint32_t n_linked;
+    uint8_t  is_abuser;        /* RiskChecker.CheckBonusAbuse's bool                                */
+    uint8_t  signals;          /* IGS_ABUSE_*                                                       */
+    uint8_t  pad[6];
+} igs_abuse;
+int igs_links_pairs(igs_engine* e, uint32_t shard, uint32_t n_shards, const igs_link_pair** d_pairs,
+                    uint64_t* counts);
+int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n, uint32_t n_shards,
+                    const igs_link** d_links, uint64_t* counts);
+int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n, uint32_t shard);
+/* Rows of the table built by igs_links_finish for n dense account indices of this shard (host
+ * buffers).  An index beyond the table yields a zero row.                                          */
+int igs_get_links(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_links_row* out);
+/* CheckBonusAbuse for n dense account indices (host buffers): needs igs_load_players and a links
+ * table (igs_links_finish; without one every account has n_linked = 0).                            */
+int igs_check_bonus_abuse(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_abuse* out);
+/* Signal strings in bit order: writes up to 3 pointers to static strings, returns how many.        */
+int igs_abuse_signals(uint32_t signals, const char* out[3]);
+
 /* Shard partition (device buffers): groups n tx records by shard = splitmix64(account) % n_shards
  * (n_shards <= 256), keeping arrival order inside a shard.  The reference has no batch partition;
  * the key is the one its feature store is addressed by (AccountID, features/redis_store.go:61,

@@ -748,6 +748,79 @@ void orc_score_batch_ids(const igs_config* c, const igs_gbdt_desc* m, const igs_
 }
 
 /* ========================================================================================== */
+/* linked accounts / bonus abuse.  The reference only declares the interfaces     */
+/* (bonus_engine.go:139-141, risk.proto:135-145,274); the semantics are the spec in igs.h,        */
+/* restated here the slow and obvious way: sort, unique, enumerate.  PARITY UNPINNED.             */
+/* ========================================================================================== */
+typedef struct { uint64_t a, b; } u64pair;
+static int pair_cmp(const void* x, const void* y) {
+    const u64pair* p = (const u64pair*)x; const u64pair* q = (const u64pair*)y;
+    if (p->a != q->a) return p->a < q->a ? -1 : 1;
+    if (p->b != q->b) return p->b < q->b ? -1 : 1;
+    return 0;
+}
+static uint64_t pair_unique(u64pair* v, uint64_t n) {
+    uint64_t w = 0;
+    for (uint64_t i = 0; i < n; ++i)
+        if (w == 0 || v[i].a != v[w - 1].a || v[i].b != v[w - 1].b) v[w++] = v[i];
+    return w;
+}
+
+void orc_links(const uint64_t* device, const uint64_t* account, uint64_t n_events,
+               const uint64_t* query, uint64_t n_q, igs_links_row* out) {
+    u64pair* pr = (u64pair*)malloc((n_events ? n_events : 1) * sizeof(u64pair));
+    uint64_t np = 0;
+    for (uint64_t i = 0; i < n_events; ++i)
+        if (device[i]) { pr[np].a = device[i]; pr[np].b = account[i]; np++; }   /* empty identifier: skipped */
+    qsort(pr, np, sizeof(u64pair), pair_cmp);
+    np = pair_unique(pr, np);
+    uint64_t cap = 16, nl = 0;
+    u64pair* lk = (u64pair*)malloc(cap * sizeof(u64pair));
+    for (uint64_t s = 0; s < np;) {
+        uint64_t e = s;
+        while (e < np && pr[e].a == pr[s].a) ++e;
+        const uint64_t k = e - s;                       /* accounts seen with this device */
+        if (k >= 2 && k <= IGS_LINK_MAX_ACCOUNTS)
+            for (uint64_t i = s; i < e; ++i)
+                for (uint64_t j = s; j < e; ++j) {
+                    if (i == j) continue;
+                    if (nl == cap) { cap *= 2; lk = (u64pair*)realloc(lk, cap * sizeof(u64pair)); }
+                    lk[nl].a = pr[i].b; lk[nl].b = pr[j].b; nl++;
+                }
+        s = e;
+    }
+    qsort(lk, nl, sizeof(u64pair), pair_cmp);
+    nl = pair_unique(lk, nl);
+    for (uint64_t q = 0; q < n_q; ++q) {
+        igs_links_row r;
+        memset(&r, 0, sizeof(r));
+        uint64_t lo = 0, hi = nl;                       /* first link of query[q] */
+        while (lo < hi) { uint64_t mid = (lo + hi) / 2; if (lk[mid].a < query[q]) lo = mid + 1; else hi = mid; }
+        for (uint64_t i = lo; i < nl && lk[i].a == query[q]; ++i) {
+            if (r.n_linked < 3) r.linked[r.n_linked] = lk[i].b;          /* sorted: the three smallest */
+            r.n_linked++;
+        }
+        out[q] = r;
+    }
+    free(pr); free(lk);
+}
+
+void orc_check_bonus_abuse(const igs_player_row* p, const igs_links_row* l, igs_abuse* out) {
+    memset(out, 0, sizeof(*out));
+    const int bonus_only = p && p->bonus_claim_count > 3 && p->total_deposits < 5000;   /* engine.go:384-386 */
+    const uint32_t nl = l ? l->n_linked : 0;
+    uint32_t sig = 0;
+    if (bonus_only) sig |= IGS_ABUSE_BONUS_ONLY;
+    if (nl >= 1) sig |= IGS_ABUSE_MULTI_ACCOUNT;
+    if (nl >= 3) sig |= IGS_ABUSE_ACCOUNT_RING;
+    const int tenths = 5 * bonus_only + 3 * (nl >= 1) + 2 * (nl >= 3);
+    out->abuse_score = (float)tenths / 10.0f;
+    out->n_linked = nl;
+    out->is_abuser = tenths >= 5;
+    out->signals = (uint8_t)sig;
+}
+
+/* ========================================================================================== */
 /* prediction/ltv.go                                                                           */
 /* ========================================================================================== */
 

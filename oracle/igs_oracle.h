@@ -162,6 +162,13 @@ void orc_score_batch_ids(const igs_config* cfg, const igs_gbdt_desc* m, const ig
                          uint64_t n_events, const orc_blacklist* bl, const igs_tx* tx,
                          const igs_tx_ids* tx_ids, uint64_t n, igs_result* out, float* features_out);
 
+/* Linked accounts over ALL shards at once (spec in igs.h, §8f-4): device[i] / account[i] = the
+ * identifier and the global account id of event i; out[q] = row of query[q].  PARITY UNPINNED: the
+ * reference declares CheckBonusAbuse (bonus_engine.go:139-141, risk.proto:135-145) without a body.  */
+void orc_links(const uint64_t* device, const uint64_t* account, uint64_t n_events,
+               const uint64_t* query, uint64_t n_q, igs_links_row* out);
+void orc_check_bonus_abuse(const igs_player_row* p, const igs_links_row* l, igs_abuse* out);
+
 /* ------------------------------------------------------------------------------------------ */
 /* prediction/ltv.go + the MLP spec                                                            */
 /* ------------------------------------------------------------------------------------------ */

@@ -130,6 +130,10 @@ def lib() -> C.CDLL:
                                       C.POINTER(abi.EventCols), C.POINTER(abi.EventIds), u64,
                                       C.POINTER(Blacklist), vp, vp, u64, vp, vp]
     L.orc_score_batch_ids.restype = None
+    L.orc_links.argtypes = [vp, vp, u64, vp, u64, vp]
+    L.orc_links.restype = None
+    L.orc_check_bonus_abuse.argtypes = [vp, vp, vp]
+    L.orc_check_bonus_abuse.restype = None
     for f in ("orc_ltv_engagement", "orc_ltv_heuristic", "orc_ltv_churn"):
         getattr(L, f).argtypes = [vp]
         getattr(L, f).restype = C.c_double
@@ -262,6 +266,27 @@ def score_batch_ids(cfg, model, players, ev, tx, bl=None, tx_ids=None, want_feat
                               C.byref(bl) if bl is not None else None, abi.ptr(tx), abi.ptr(tx_ids), n,
                               abi.ptr(out), abi.ptr(feats))
     return (out, feats) if want_features else out
+
+
+def links(device: np.ndarray, account: np.ndarray, query: np.ndarray) -> np.ndarray:
+    """Linked accounts over all shards at once: device / global account id per event -> rows of `query`."""
+    device = np.ascontiguousarray(device, dtype=np.uint64)
+    account = np.ascontiguousarray(account, dtype=np.uint64)
+    query = np.ascontiguousarray(query, dtype=np.uint64)
+    out = np.zeros(query.shape[0], dtype=abi.links_row_dtype)
+    lib().orc_links(abi.ptr(device), abi.ptr(account), device.shape[0], abi.ptr(query), query.shape[0], abi.ptr(out))
+    return out
+
+
+def check_bonus_abuse(players, rows: np.ndarray, accounts: np.ndarray) -> np.ndarray:
+    """players: BatchFeatures table (or None); rows[i] = links row of accounts[i]."""
+    rows = np.ascontiguousarray(rows, dtype=abi.links_row_dtype)
+    out = np.zeros(rows.shape[0], dtype=abi.abuse_dtype)
+    L = lib()
+    for i, a in enumerate(accounts):
+        p = players[int(a):int(a) + 1].ctypes.data if players is not None and int(a) < players.shape[0] else None
+        L.orc_check_bonus_abuse(p, rows[i:i + 1].ctypes.data, out[i:i + 1].ctypes.data)
+    return out
 
 
 def ltv_epilogue(rows: np.ndarray, ltv: np.ndarray) -> np.ndarray:
