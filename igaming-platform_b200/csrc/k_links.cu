@@ -25,6 +25,11 @@ namespace {
 constexpr int kKeyBits = 40;          // 4 radix passes of 10 bits
 constexpr int kKeyPasses = 4;
 constexpr int kMaxShards = 256;
+// Slots of the engine's links pool: every stage makes the same requests in the same order on every run and
+// owns a fixed range, so a rerun reuses its buffers and a stage never overwrites the previous stage's output
+// (with one shard the caller hands stage N's output straight to stage N + 1).
+constexpr size_t kStage2First = 2;      // stage 1: counters, pairs
+constexpr size_t kStage3First = 40;     // stage 2 uses fewer than 38 slots
 
 __host__ __device__ __forceinline__ uint32_t shard_of(uint64_t x, uint32_t n_shards) {   // = igs_shard_of(x, 0, n)
     return (uint32_t)(igs_idset_mix(x + 0x9E3779B97F4A7C15ull) % n_shards);
@@ -342,7 +347,7 @@ int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, u
     cudaStream_t st = e->slot[0].stream;
     const uint32_t n = (uint32_t)n64;
     Scratch sc(e->links_pool);
-    sc.next = 2;                                        // keep stage 1's output alive (one shard: d_pairs is it)
+    sc.next = kStage2First;                             // keep stage 1's output alive (one shard: d_pairs is it)
     Rec* d_distinct; uint32_t m = 0;
     int rc = distinct_records(e, sc, reinterpret_cast<const Rec*>(d_pairs), n, &d_distinct, &m, st);
     if (rc != IGS_OK) return rc;
@@ -370,6 +375,10 @@ int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, u
     }
     igs_link* d_out;
     IGS_CUDA(e, sc.alloc(&d_out, total));
+    if (sc.next > kStage3First) {
+        igs_set_error(e, "internal: stage 2 outgrew its scratch slots");
+        return IGS_ERR_STATE;
+    }
     if (total) {
         IGS_CUDA(e, cudaMemcpyAsync(d_counts, h_starts, n_shards * 8, cudaMemcpyHostToDevice, st));
         k_lg_emit<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_counts, d_out);
@@ -402,7 +411,8 @@ int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n64, uint3
     IGS_CUDA(e, cudaGetLastError());
     // The links buffer may be stage 2's output (one shard), which lives in the pool: take scratch behind it.
     Scratch sc(e->links_pool);
-    sc.next = e->links_pool.size();
+    if (e->links_pool.size() < kStage3First) e->links_pool.resize(kStage3First);
+    sc.next = kStage3First;
     Rec* d_distinct; uint32_t m = 0;
     int rc = distinct_records(e, sc, reinterpret_cast<const Rec*>(d_links), n, &d_distinct, &m, st);
     if (rc != IGS_OK) return rc;
@@ -417,11 +427,7 @@ int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n64, uint3
     IGS_CUDA(e, cudaGetLastError());
     IGS_CUDA(e, cudaStreamSynchronize(st));
     e->n_links_rows = n_rows;
-    // stage scratch is not needed between runs of this periodic job
-    for (igs_buf& b : e->links_pool)
-        if (b.p) cudaFree(b.p);
-    e->links_pool.clear();
-    return IGS_OK;
+    return IGS_OK;     // the stage scratch stays in the pool for the next run of this periodic job
 }
 
 int igs_get_links(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_links_row* out) {

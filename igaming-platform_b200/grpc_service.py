@@ -4,10 +4,10 @@ The reference registers its handler with `riskv1.RegisterRiskServiceServer(grpcS
 (services/risk/cmd/main.go:141-142) but ships neither the handler nor generated code.  This module is that
 handler's body for the RPCs the engine can answer — `ScoreTransaction`, `ScoreBatch`, `GetThresholds`,
 `UpdateThresholds` (proto/risk/v1/risk.proto:12-13,30-31), `AddToBlacklist`, `CheckBlacklist` (:23-24, on the
-device-side sets) and `PredictLTV`, `GetPlayerSegment` (:16-17, on the LTV model) — speaking the same wire
-format.  There is no `protoc` in this image, so the message descriptors are built by hand from the .proto (same
-package, message names, field names, numbers and types; risk.proto:38-257); `CheckBonusAbuse` and
-`GetFeatures` answer UNIMPLEMENTED.
+device-side sets), `CheckBonusAbuse` (:20, on the links table) and `PredictLTV`, `GetPlayerSegment` (:16-17,
+on the LTV model) — speaking the same wire format.  There is no `protoc` in this image, so the message descriptors are built by hand from the .proto (same
+package, message names, field names, numbers and types; risk.proto:38-257); `GetFeatures` answers
+UNIMPLEMENTED.
 
 Marshalling only: every score in a response was computed by the CUDA library through `scoring.ScoringEngine`.
 """
@@ -108,6 +108,11 @@ def build_file_descriptor() -> descriptor_pb2.FileDescriptorProto:
                                 ("created_at", 4, _T.TYPE_MESSAGE, ts)])
     _msg(fd, "CheckBlacklistResponse", [("is_blacklisted", 1, _T.TYPE_BOOL),
                                         ("matches", 2, _T.TYPE_MESSAGE, f".{PACKAGE}.BlacklistMatch", _T.LABEL_REPEATED)])
+    # bonus abuse, risk.proto:135-145
+    _msg(fd, "CheckBonusAbuseRequest", [("account_id", 1, _T.TYPE_STRING), ("bonus_id", 2, _T.TYPE_STRING)])
+    _msg(fd, "CheckBonusAbuseResponse", [("is_abuser", 1, _T.TYPE_BOOL), ("abuse_score", 2, _T.TYPE_FLOAT),
+                                         ("signals", 3, _T.TYPE_STRING, None, _T.LABEL_REPEATED),
+                                         ("linked_accounts", 4, _T.TYPE_STRING, None, _T.LABEL_REPEATED)])
     # LTV & segmentation, risk.proto:94-120
     _msg(fd, "PredictLTVRequest", [("account_id", 1, _T.TYPE_STRING)])
     _msg(fd, "PredictLTVResponse", [("account_id", 1, _T.TYPE_STRING), ("predicted_ltv", 2, _T.TYPE_FLOAT),
@@ -144,6 +149,8 @@ AddToBlacklistResponse = message_class("AddToBlacklistResponse")
 CheckBlacklistRequest = message_class("CheckBlacklistRequest")
 CheckBlacklistResponse = message_class("CheckBlacklistResponse")
 BlacklistMatch = message_class("BlacklistMatch")
+CheckBonusAbuseRequest = message_class("CheckBonusAbuseRequest")
+CheckBonusAbuseResponse = message_class("CheckBonusAbuseResponse")
 PredictLTVRequest = message_class("PredictLTVRequest")
 PredictLTVResponse = message_class("PredictLTVResponse")
 GetPlayerSegmentRequest = message_class("GetPlayerSegmentRequest")
@@ -156,10 +163,11 @@ _METHODS = {
     "GetThresholds": (GetThresholdsRequest, GetThresholdsResponse),
     "AddToBlacklist": (AddToBlacklistRequest, AddToBlacklistResponse),
     "CheckBlacklist": (CheckBlacklistRequest, CheckBlacklistResponse),
+    "CheckBonusAbuse": (CheckBonusAbuseRequest, CheckBonusAbuseResponse),
     "PredictLTV": (PredictLTVRequest, PredictLTVResponse),
     "GetPlayerSegment": (GetPlayerSegmentRequest, GetPlayerSegmentResponse),
 }
-_UNIMPLEMENTED = ["CheckBonusAbuse", "GetFeatures"]
+_UNIMPLEMENTED = ["GetFeatures"]
 _ACTION_ENUM = {"approve": 1, "review": 2, "block": 3}
 
 
@@ -271,6 +279,15 @@ class RiskServicer:
             if hit[k]:
                 resp.matches.add(type=typ, value=val)
         return resp
+
+    # -- bonus abuse (risk.proto:20) on the links table + player rows -------------------------------
+    def CheckBonusAbuse(self, request, context):
+        try:
+            acc = _uuid.UUID(request.account_id)
+        except ValueError:
+            acc = _uuid.UUID(int=0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFF)
+        is_abuser, score, signals, linked = self.engine.CheckBonusAbuse(acc)
+        return CheckBonusAbuseResponse(is_abuser=is_abuser, abuse_score=score, signals=signals, linked_accounts=linked)
 
     # -- LTV & segmentation (risk.proto:16-17) on the LTV model --------------------------------------
     def _ltv(self, account_id: str, context):

@@ -82,6 +82,12 @@ class PlayerDirectory:
         # velocity features, as the reference does when the feature store errors (engine.go:338-366)
         return self._idx.get(account_id, 0xFFFFFFFE)
 
+    def uuid_of(self, index: int) -> Optional[_uuid.UUID]:
+        """Reverse lookup (dense index -> account uuid) for reporting linked accounts."""
+        if not hasattr(self, "_rev") or len(self._rev) != len(self._idx):
+            self._rev = {i: u for u, i in self._idx.items()}
+        return self._rev.get(index)
+
     def __len__(self) -> int:
         return len(self._idx)
 
@@ -152,6 +158,22 @@ class ScoringEngine:
             ev.device = np.array([self._hash(e.device_id) for e in known], np.uint64)
             ev.ip = np.array([self._hash(e.ip) for e in known], np.uint64)
         self.engine.append_events(ev)
+
+    def CheckBonusAbuse(self, account_id: _uuid.UUID) -> Tuple[bool, float, List[str], List[str]]:
+        """RiskChecker.CheckBonusAbuse (services/bonus/internal/service/bonus_engine.go:139-141) with the
+        detail of rpc CheckBonusAbuse (risk.proto:140-145): (is_abuser, abuse_score, signals, linked accounts).
+        Linked accounts of this shard are reported by uuid, those of other shards as "shard:index"."""
+        idx = np.array([self.directory.get(account_id)], np.uint32)
+        a = self.engine.check_bonus_abuse(idx)[0]
+        row = self.engine.get_links(idx)[0]
+        names = (C.c_char_p * 3)()
+        k = self._lib.igs_abuse_signals(int(a["signals"]), C.byref(names))
+        linked = []
+        for g in row["linked"][:min(int(row["n_linked"]), 3)]:
+            shard, i = int(g) >> 32, int(g) & 0xFFFFFFFF
+            u = self.directory.uuid_of(i) if shard == self.directory.shard else None
+            linked.append(str(u) if u is not None else f"{shard}:{i}")
+        return bool(a["is_abuser"]), float(a["abuse_score"]), [names[j].decode() for j in range(k)], linked
 
     # -- marshalling (pure host logic; unit-tested without a GPU) ---------------------------------
     def marshal(self, reqs: Sequence[ScoreRequest], now: Optional[int] = None) -> np.ndarray:

@@ -130,6 +130,23 @@ public:
         check(igs_blacklist_add(e_, kind, &id, 1));
         device_ids_ = true;
     }
+    // Rebuilds the linked-accounts table of a single-shard deployment from the loaded history (a periodic job;
+    // with several shards the three igs_links_* stages are driven with an all-to-all between them).
+    void BuildLinks() {
+        const igs_link_pair* pairs = nullptr; const igs_link* links = nullptr;
+        uint64_t n_pairs = 0, n_links = 0;
+        check(igs_links_pairs(e_, 0, 1, &pairs, &n_pairs));
+        check(igs_links_group(e_, pairs, n_pairs, 1, &links, &n_links));
+        check(igs_links_finish(e_, links, n_links, 0));
+    }
+    // RiskChecker.CheckBonusAbuse, services/bonus/internal/service/bonus_engine.go:139-141
+    bool CheckBonusAbuse(const AccountID& account_id, igs_abuse* detail = nullptr) {
+        const uint32_t idx = dir_ ? dir_->Get(account_id) : 0xFFFFFFFEu;
+        igs_abuse a{};
+        check(igs_check_bonus_abuse(e_, &idx, 1, &a));
+        if (detail) *detail = a;
+        return a.is_abuser != 0;
+    }
     // ScoringEngine.UpdateFeatures (engine.go:486-488) for a micro-batch of completed transactions.
     struct TransactionEvent {      // features.TransactionEvent, features/redis_store.go:49-56
         std::array<uint8_t, 16> account_id{};

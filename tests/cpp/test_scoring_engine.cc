@@ -171,6 +171,30 @@ int main(int argc, char** argv) {
         }
         orc_redis_free(redis);
         REQUIRE(fired == 3);      // some step fired one rule, the last one all three
+
+        // RiskChecker.CheckBonusAbuse: accounts 3 and 7 share "dev-2" -> MULTI_ACCOUNT for both, checked against
+        // the oracle's table over the same history
+        igs::ScoringEngine::TransactionEvent te;
+        te.account_id = make_id(7); te.amount = 5; te.device_id = "dev-2"; te.ip = "198.51.100.77"; te.timestamp = now + 100;
+        e3.UpdateFeatures({te});
+        e3.BuildLinks();
+        std::vector<uint64_t> hd, ha;
+        for (int step = 0; step < 8; ++step) {
+            const std::string dv = "dev-" + std::to_string(step % 5);
+            hd.push_back(orc_hash_id(dv.data(), dv.size())); ha.push_back(3);
+        }
+        hd.push_back(orc_hash_id("dev-2", 5)); ha.push_back(7);
+        const uint64_t q[3] = {3, 7, 9};
+        igs_links_row want_rows[3];
+        orc_links(hd.data(), ha.data(), hd.size(), q, 3, want_rows);
+        for (int k = 0; k < 3; ++k) {
+            igs_abuse got{}, want_abuse{};
+            const bool is_abuser = e3.CheckBonusAbuse(make_id((uint32_t)q[k]), &got);
+            orc_check_bonus_abuse(&players[q[k]], &want_rows[k], &want_abuse);
+            REQUIRE(got.n_linked == want_abuse.n_linked && got.signals == want_abuse.signals);
+            REQUIRE(got.abuse_score == want_abuse.abuse_score && is_abuser == (want_abuse.is_abuser != 0));
+        }
+        REQUIRE(want_rows[0].n_linked == 1 && want_rows[0].linked[0] == 7 && want_rows[2].n_linked == 0);
     }
     std::printf("test_scoring_engine: %zu requests, flags seen 0x%x: ok\n", res.size(), seen);
     return 0;

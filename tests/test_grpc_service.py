@@ -38,6 +38,9 @@ def test_descriptors_match_the_reference_proto(pkg):
     c = gs.CheckBlacklistRequest.DESCRIPTOR
     assert {f.name: f.number for f in c.fields} == {"device_id": 1, "fingerprint": 2, "ip_address": 3, "email": 4}
     assert {f.name: f.number for f in gs.BlacklistMatch.DESCRIPTOR.fields} == {"type": 1, "value": 2, "reason": 3, "created_at": 4}
+    b = gs.CheckBonusAbuseResponse.DESCRIPTOR
+    assert {f.name: f.number for f in b.fields} == {"is_abuser": 1, "abuse_score": 2, "signals": 3, "linked_accounts": 4}
+    assert {f.name: f.number for f in gs.CheckBonusAbuseRequest.DESCRIPTOR.fields} == {"account_id": 1, "bonus_id": 2}
     l = gs.PredictLTVResponse.DESCRIPTOR
     assert {f.name: f.number for f in l.fields} == {"account_id": 1, "predicted_ltv": 2, "segment": 3, "churn_risk": 4,
                                                     "predicted_active_days": 5, "confidence": 6, "next_best_action": 7,
@@ -79,6 +82,18 @@ class FakeDeviceEngine:
         sets = getattr(self, "sets", {0: set(), 1: set(), 2: set()})
         return np.array([int(r["device"]) in sets[0] or int(r["fingerprint"]) in sets[1] or int(r["ip"]) in sets[2]
                          for r in ids], dtype=np.uint8)
+
+    def check_bonus_abuse(self, accounts):
+        out = np.zeros(accounts.shape[0], dtype=self.abi.abuse_dtype)
+        out["abuse_score"], out["n_linked"], out["is_abuser"] = 0.8, 2, 1
+        out["signals"] = self.abi.ABUSE_BONUS_ONLY | self.abi.ABUSE_MULTI_ACCOUNT
+        return out
+
+    def get_links(self, accounts):
+        out = np.zeros(accounts.shape[0], dtype=self.abi.links_row_dtype)
+        out["n_linked"] = 2
+        out["linked"][:, 0], out["linked"][:, 1] = 4, (3 << 32) | 9      # one on this shard, one on shard 3
+        return out
 
     def ltv_batch(self, x, rows):
         out = np.zeros(rows.shape[0], dtype=self.abi.ltv_result_dtype)
@@ -160,7 +175,10 @@ def test_grpc_round_trip_with_stand_in_engine(pkg, built_lib):
         with pytest.raises(grpc.RpcError) as ei:
             client.PredictLTV(gs.PredictLTVRequest(account_id=str(uuid.UUID(int=1))))
         assert ei.value.code() == grpc.StatusCode.NOT_FOUND
-        raw = client.channel.unary_unary(f"/{gs.SERVICE}/CheckBonusAbuse", request_serializer=lambda b: b,
+        ba = client.CheckBonusAbuse(gs.CheckBonusAbuseRequest(account_id=str(ids[1])))
+        assert ba.is_abuser and abs(ba.abuse_score - 0.8) < 1e-6
+        assert list(ba.signals) == ["BONUS_ONLY_PLAYER", "MULTI_ACCOUNT"] and list(ba.linked_accounts) == [str(ids[4]), "3:9"]
+        raw = client.channel.unary_unary(f"/{gs.SERVICE}/GetFeatures", request_serializer=lambda b: b,
                                          response_deserializer=lambda b: b)
         with pytest.raises(grpc.RpcError) as ei:
             raw(b"")

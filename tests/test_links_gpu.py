@@ -49,6 +49,20 @@ def test_single_shard_links_match_oracle(engine, orc, pkg):
     assert ab.tobytes() == orc.check_bonus_abuse(players, want, q).tobytes()
     assert ab["is_abuser"].any() and not ab["is_abuser"].all()
     assert set(np.unique(ab["signals"])) >= {0, abi.ABUSE_MULTI_ACCOUNT}
+    # the reference-facing mirror: RiskChecker.CheckBonusAbuse by account uuid
+    import uuid
+    sc = pkg.scoring
+    d = sc.PlayerDirectory()
+    uu = [uuid.UUID(int=30_000 + i) for i in range(n_acc)]
+    for u in uu:
+        d.add(u)
+    mirror = sc.ScoringEngine(engine, d)
+    ring = int(np.nonzero(want["n_linked"] >= 3)[0][0])
+    is_abuser, score, signals, linked = mirror.CheckBonusAbuse(uu[ring])
+    assert (is_abuser, np.float32(score)) == (bool(ab["is_abuser"][ring]), ab["abuse_score"][ring])
+    assert "MULTI_ACCOUNT" in signals and "ACCOUNT_RING" in signals
+    assert linked == [str(uu[int(g)]) for g in want["linked"][ring]]
+    assert mirror.CheckBonusAbuse(uuid.UUID(int=1)) == (False, 0.0, [], [])      # unknown account
     names = (__import__("ctypes").c_char_p * 3)()
     k = abi.load_library().igs_abuse_signals(7, names)
     assert [names[i].decode() for i in range(k)] == ["BONUS_ONLY_PLAYER", "MULTI_ACCOUNT", "ACCOUNT_RING"]
