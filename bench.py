@@ -108,6 +108,16 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def shard_skew(world, synth, pkg):
+    """max / mean shard size when a C5-style batch (Zipf(1.1) accounts) is partitioned by
+    splitmix64(account) % n_shards — the only scaling risk of a path without a collective."""
+    if world == 1:
+        return {"n_shards": 1, "max_over_mean": 1.0}
+    tx = synth.make_tx(2_000_000, 4_000_000, seed=synth.MASTER_SEED)
+    sizes = np.bincount(pkg.sharding.shard_of(tx["account"], world), minlength=world)
+    return {"n_shards": world, "max_over_mean": float(sizes.max() / sizes.mean()), "sample_tx": int(tx.shape[0])}
+
+
 def pinned_array(lib, shape, dtype):
     dtype = np.dtype(dtype)
     nbytes = int(np.prod(shape)) * dtype.itemsize
@@ -435,6 +445,47 @@ def main():
                  "p99_batch_latency": flat, "index_build_s": load_s, "algorithmic_bytes_per_tx": 136}
         lib.igs_free_pinned(p4)
 
+        # the same path with the identifier inputs on the device: unique devices / IPs from
+        # the event index, rule 8 from three 100k-member blacklist sets, 24 B/tx of identifiers in
+        ev_ids = synth.make_event_ids(events, seed=synth.MASTER_SEED + rank)
+        t0 = time.perf_counter()
+        eng.load_events(ev_ids, n_pl)
+        load_ids_s = time.perf_counter() - t0
+        rng = np.random.default_rng(synth.MASTER_SEED + rank)
+        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+            eng.blacklist_load(kind, rng.integers(1, 1 << 63, 100_000, dtype=np.uint64))
+        ids = np.zeros(n, dtype=abi.tx_ids_dtype)
+        ids["device"] = ev_ids.device[rng.integers(0, n_ev, n)]
+        ids["fingerprint"] = rng.integers(1, 1 << 63, n, dtype=np.uint64)
+        ids["ip"] = ev_ids.ip[rng.integers(0, n_ev, n)]
+        d_ids = torch.from_numpy(ids.view(np.uint8).reshape(n, -1)).to(dev)
+
+        def istep():
+            st = lib.igs_score_batch_ids_device(eng.handle, C.byref(cfg), d_tx.data_ptr(), d_ids.data_ptr(), n,
+                                                d_out.data_ptr(), None, None, stream)
+            assert st == 0, lib.igs_last_error(eng.handle).decode()
+
+        for _ in range(args.warmup):
+            istep()
+        barrier()
+        i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        i0.record()
+        for _ in range(args.steps):
+            istep()
+        i1.record()
+        barrier()
+        t = torch.tensor([i0.elapsed_time(i1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        i_ms = float(t.item()) / args.steps
+        fused["with_identifiers"] = {
+            "workload": "same, history with device / IP columns (exact uniques from the index) + 3 x 100k-member "
+                        "blacklist sets probed per tx (igs_score_batch_ids_device)",
+            "value": n * world / (i_ms * 1e-3), "unit": UNIT, "ms_per_step": i_ms, "index_build_s": load_ids_s,
+            "algorithmic_bytes_per_tx": 160}
+        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+            eng.blacklist_load(kind, np.zeros(0, np.uint64))
+
     # ---- CPU baseline (oracle port) on rank 0, N=1 only ----------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
@@ -464,6 +515,7 @@ def main():
             "config": {"workload": "C2: 1M tx x 64 f32 features, 500-tree depth-8 GBDT + 8 rules + blend, per GPU",
                        "tx_per_gpu": n, "n_trees": N_TREES, "n_features": 64, "depth": 8,
                        "sharding": f"player-hash shards x{world}, no collective",
+                       "shard_skew": shard_skew(world, synth, pkg),
                        "l2": "inputs 312 MB per step > 126 MB L2, no flush needed"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT,

@@ -4,10 +4,10 @@ The reference registers its handler with `riskv1.RegisterRiskServiceServer(grpcS
 (services/risk/cmd/main.go:141-142) but ships neither the handler nor generated code.  This module is that
 handler's body for the RPCs the engine can answer — `ScoreTransaction`, `ScoreBatch`, `GetThresholds`,
 `UpdateThresholds` (proto/risk/v1/risk.proto:12-13,30-31), `AddToBlacklist`, `CheckBlacklist` (:23-24, on the
-device-side sets), `CheckBonusAbuse` (:20, on the links table) and `PredictLTV`, `GetPlayerSegment` (:16-17,
+device-side sets), `CheckBonusAbuse` (:20, on the links table), `GetFeatures` (:27) and `PredictLTV`, `GetPlayerSegment` (:16-17,
 on the LTV model) — speaking the same wire format.  There is no `protoc` in this image, so the message descriptors are built by hand from the .proto (same
-package, message names, field names, numbers and types; risk.proto:38-257); `GetFeatures` answers
-UNIMPLEMENTED.
+package, message names, field names, numbers and types; risk.proto:38-257).  `GetFeatures` (:27) echoes
+what extractFeatures would see for the account right now.  All ten RPCs of the service are answered.
 
 Marshalling only: every score in a response was computed by the CUDA library through `scoring.ScoringEngine`.
 """
@@ -108,6 +108,10 @@ def build_file_descriptor() -> descriptor_pb2.FileDescriptorProto:
                                 ("created_at", 4, _T.TYPE_MESSAGE, ts)])
     _msg(fd, "CheckBlacklistResponse", [("is_blacklisted", 1, _T.TYPE_BOOL),
                                         ("matches", 2, _T.TYPE_MESSAGE, f".{PACKAGE}.BlacklistMatch", _T.LABEL_REPEATED)])
+    # feature inspection, risk.proto:188-195
+    _msg(fd, "GetFeaturesRequest", [("account_id", 1, _T.TYPE_STRING)])
+    _msg(fd, "GetFeaturesResponse", [("account_id", 1, _T.TYPE_STRING), ("features", 2, _T.TYPE_MESSAGE, f".{PACKAGE}.FeatureVector"),
+                                     ("computed_at", 3, _T.TYPE_MESSAGE, ts)])
     # bonus abuse, risk.proto:135-145
     _msg(fd, "CheckBonusAbuseRequest", [("account_id", 1, _T.TYPE_STRING), ("bonus_id", 2, _T.TYPE_STRING)])
     _msg(fd, "CheckBonusAbuseResponse", [("is_abuser", 1, _T.TYPE_BOOL), ("abuse_score", 2, _T.TYPE_FLOAT),
@@ -149,6 +153,8 @@ AddToBlacklistResponse = message_class("AddToBlacklistResponse")
 CheckBlacklistRequest = message_class("CheckBlacklistRequest")
 CheckBlacklistResponse = message_class("CheckBlacklistResponse")
 BlacklistMatch = message_class("BlacklistMatch")
+GetFeaturesRequest = message_class("GetFeaturesRequest")
+GetFeaturesResponse = message_class("GetFeaturesResponse")
 CheckBonusAbuseRequest = message_class("CheckBonusAbuseRequest")
 CheckBonusAbuseResponse = message_class("CheckBonusAbuseResponse")
 PredictLTVRequest = message_class("PredictLTVRequest")
@@ -164,10 +170,11 @@ _METHODS = {
     "AddToBlacklist": (AddToBlacklistRequest, AddToBlacklistResponse),
     "CheckBlacklist": (CheckBlacklistRequest, CheckBlacklistResponse),
     "CheckBonusAbuse": (CheckBonusAbuseRequest, CheckBonusAbuseResponse),
+    "GetFeatures": (GetFeaturesRequest, GetFeaturesResponse),
     "PredictLTV": (PredictLTVRequest, PredictLTVResponse),
     "GetPlayerSegment": (GetPlayerSegmentRequest, GetPlayerSegmentResponse),
 }
-_UNIMPLEMENTED = ["GetFeatures"]
+_UNIMPLEMENTED = []
 _ACTION_ENUM = {"approve": 1, "review": 2, "block": 3}
 
 
@@ -278,6 +285,14 @@ class RiskServicer:
                                         ("ip", request.ip_address))):
             if hit[k]:
                 resp.matches.add(type=typ, value=val)
+        return resp
+
+    # -- feature inspection (risk.proto:27): extractFeatures for the account at wall-clock now, no tx ---
+    def GetFeatures(self, request, context):
+        probe = ScoreTransactionRequest(account_id=request.account_id)          # amount 0, no identifiers
+        resp = GetFeaturesResponse(account_id=request.account_id)
+        resp.features.CopyFrom(self._score([probe])[0].features)
+        resp.computed_at.GetCurrentTime()
         return resp
 
     # -- bonus abuse (risk.proto:20) on the links table + player rows -------------------------------

@@ -178,7 +178,11 @@ def test_grpc_round_trip_with_stand_in_engine(pkg, built_lib):
         ba = client.CheckBonusAbuse(gs.CheckBonusAbuseRequest(account_id=str(ids[1])))
         assert ba.is_abuser and abs(ba.abuse_score - 0.8) < 1e-6
         assert list(ba.signals) == ["BONUS_ONLY_PLAYER", "MULTI_ACCOUNT"] and list(ba.linked_accounts) == [str(ids[4]), "3:9"]
-        raw = client.channel.unary_unary(f"/{gs.SERVICE}/GetFeatures", request_serializer=lambda b: b,
+        gf = client.GetFeatures(gs.GetFeaturesRequest(account_id=str(ids[0])))
+        assert gf.account_id == str(ids[0]) and gf.computed_at.seconds > 0
+        assert (gf.features.tx_count_1h, gf.features.time_since_last_tx_sec) == (4, 17)
+        assert gf.features.total_deposits == int(players["total_deposits"][0])
+        raw = client.channel.unary_unary(f"/{gs.SERVICE}/NoSuchMethod", request_serializer=lambda b: b,
                                          response_deserializer=lambda b: b)
         with pytest.raises(grpc.RpcError) as ei:
             raw(b"")
