@@ -228,6 +228,33 @@ class Engine:
     def links_finish(self, d_links: int, n: int, shard: int) -> None:
         self._check(self._lib.igs_links_finish(self._h, d_links, n, shard))
 
+    # peer-memory exchange (links.build_links_peer drives these)
+    def links_window_create(self, cap_pairs: int, cap_links: int):
+        """-> (64-byte IPC handle, device address of this shard's receive window)."""
+        h = (C.c_uint8 * abi.IPC_HANDLE_BYTES)()
+        p = C.c_void_p()
+        self._check(self._lib.igs_links_window_create(self._h, cap_pairs, cap_links, h, C.byref(p)))
+        return bytes(h), p.value
+
+    def links_window_open(self, peer_shard: int, handle: bytes) -> None:
+        buf = (C.c_uint8 * abi.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+        self._check(self._lib.igs_links_window_open(self._h, peer_shard, buf))
+
+    def links_window_attach(self, peer_shard: int, d_window: int) -> None:
+        self._check(self._lib.igs_links_window_attach(self._h, peer_shard, d_window))
+
+    def links_window_reset(self) -> None:
+        self._check(self._lib.igs_links_window_reset(self._h))
+
+    def links_pairs_peer(self, shard: int, n_shards: int) -> None:
+        self._check(self._lib.igs_links_pairs_peer(self._h, shard, n_shards))
+
+    def links_group_peer(self, shard: int, n_shards: int) -> None:
+        self._check(self._lib.igs_links_group_peer(self._h, shard, n_shards))
+
+    def links_finish_peer(self, shard: int) -> None:
+        self._check(self._lib.igs_links_finish_peer(self._h, shard))
+
     def get_links(self, accounts: np.ndarray) -> np.ndarray:
         accounts = np.ascontiguousarray(accounts, dtype=np.uint32)
         out = np.zeros(accounts.shape[0], dtype=abi.links_row_dtype)

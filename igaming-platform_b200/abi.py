@@ -45,6 +45,7 @@ SEQ_ALL = 0xFFFFFFFF
 PARTITION_STATIC_WORDS = 256 * 1024
 BL_DEVICE, BL_FINGERPRINT, BL_IP = 0, 1, 2
 LINK_MAX_ACCOUNTS = 64
+IPC_HANDLE_BYTES = 64
 ABUSE_BONUS_ONLY, ABUSE_MULTI_ACCOUNT, ABUSE_ACCOUNT_RING = 1, 2, 4
 
 rule_row_dtype = np.dtype([
@@ -157,7 +158,8 @@ EXPORTS = [
     "igs_blacklist_load", "igs_blacklist_add", "igs_blacklist_check", "igs_blacklist_check_device",
     "igs_score_batch_ids", "igs_score_batch_ids_device", "igs_hash_id",
     "igs_links_pairs", "igs_links_group", "igs_links_finish", "igs_get_links", "igs_check_bonus_abuse",
-    "igs_abuse_signals",
+    "igs_abuse_signals", "igs_links_window_create", "igs_links_window_open", "igs_links_window_attach",
+    "igs_links_window_reset", "igs_links_pairs_peer", "igs_links_group_peer", "igs_links_finish_peer",
 ]
 
 LIB_NAME = "libigs.so"
@@ -239,6 +241,13 @@ def load_library() -> C.CDLL:
     lib.igs_get_links.argtypes = [vp, vp, u64, vp]
     lib.igs_check_bonus_abuse.argtypes = [vp, vp, u64, vp]
     lib.igs_abuse_signals.argtypes = [C.c_uint32, C.POINTER(C.c_char_p * 3)]
+    lib.igs_links_window_create.argtypes = [vp, u64, u64, vp, C.POINTER(vp)]
+    lib.igs_links_window_open.argtypes = [vp, C.c_uint32, vp]
+    lib.igs_links_window_attach.argtypes = [vp, C.c_uint32, vp]
+    lib.igs_links_window_reset.argtypes = [vp]
+    lib.igs_links_pairs_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
+    lib.igs_links_group_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
+    lib.igs_links_finish_peer.argtypes = [vp, C.c_uint32]
     lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
     lib.igs_hash_id.restype = u64
     lib.igs_version.argtypes = []

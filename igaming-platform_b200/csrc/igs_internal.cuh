@@ -117,6 +117,11 @@ struct igs_engine {
     std::vector<igs_buf> links_pool;
     igs_links_row* d_links_rows = nullptr;
     uint64_t n_links_rows = 0;
+    // peer-memory exchange: this shard's receive window, and every shard's window as seen from here
+    void*    links_window = nullptr;          // [cursor block][cap_pairs pairs][cap_links links]
+    uint64_t links_cap_pairs = 0, links_cap_links = 0;
+    void*    links_peer[256] = {nullptr};     // indexed by shard; own entry = links_window
+    bool     links_peer_ipc[256] = {false};   // opened through an IPC handle (to be closed)
 
     // MLP
     void* d_mlp = nullptr;        // see k_ltv.cu

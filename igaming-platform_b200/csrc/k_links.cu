@@ -167,6 +167,72 @@ __global__ void k_lg_emit(const uint64_t* __restrict__ keys, const Rec* __restri
     }
 }
 
+// ---- peer-memory variants: the exchange is part of the producing kernel ----------------------------------
+// A shard's receive window as its peers see it.  cursors[0] / cursors[1] count the pair / link slots claimed
+// so far (they keep counting past the capacity, so an overflow reports the size that was needed).
+struct PeerWin {
+    unsigned long long* cursors;
+    Rec* pairs;
+    Rec* links;
+};
+constexpr size_t kWindowHeader = 256;
+__host__ PeerWin window_view(void* base, uint64_t cap_pairs) {
+    PeerWin w;
+    w.cursors = static_cast<unsigned long long*>(base);
+    w.pairs = reinterpret_cast<Rec*>(static_cast<char*>(base) + kWindowHeader);
+    w.links = w.pairs + cap_pairs;
+    return w;
+}
+
+// stage 1 + exchange 1: each pair goes straight into the window of the shard that owns its device — over
+// NVLink when that shard is another GPU.  One remote atomic per warp and destination claims the slots.
+__global__ void __launch_bounds__(kThreads)
+k_lp_scatter_peer(const uint64_t* __restrict__ device, const uint32_t* __restrict__ account, uint32_t n,
+                  uint32_t shard, uint32_t n_shards, const PeerWin* __restrict__ wins, unsigned long long cap_pairs) {
+    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    const uint64_t d = i < n ? __ldg(device + i) : 0;
+    const uint32_t dest = d ? shard_of(d, n_shards) : 0xFFFFFFFFu;
+    const unsigned peers = __match_any_sync(0xffffffffu, dest);
+    if (!d) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+    const PeerWin w = wins[dest];
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd_system(w.cursors + 0, (unsigned long long)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    const unsigned long long slot = base + __popc(peers & ((1u << lane) - 1u));
+    if (slot < cap_pairs) {
+        Rec p;
+        p.a = d;
+        p.b = ((uint64_t)shard << 32) | __ldg(account + i);
+        w.pairs[slot] = p;
+    }
+}
+
+// stage 2's emit + exchange 2: the links of a pair go straight into the window of the account's shard
+__global__ void k_lg_emit_peer(const uint64_t* __restrict__ keys, const Rec* __restrict__ pairs, uint32_t n,
+                               uint32_t n_shards, const uint32_t* __restrict__ links_of,
+                               const PeerWin* __restrict__ wins, unsigned long long cap_links) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const uint32_t cnt = __ldg(links_of + r);
+    if (!cnt) return;
+    const Rec me = pairs[r];
+    const PeerWin w = wins[min((uint32_t)(me.b >> 32), n_shards - 1)];
+    unsigned long long pos = atomicAdd_system(w.cursors + 1, (unsigned long long)cnt);
+    if (pos + cnt > cap_links) return;                        // the consumer reports the overflow
+    const uint64_t key = __ldg(keys + r);
+    for (uint32_t rr = r; rr-- > 0;) {
+        if (__ldg(keys + rr) != key) break;
+        const Rec o = pairs[rr];
+        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; w.links[pos++] = l; }
+    }
+    for (uint32_t rr = r + 1; rr < n; ++rr) {
+        if (__ldg(keys + rr) != key) break;
+        const Rec o = pairs[rr];
+        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; w.links[pos++] = l; }
+    }
+}
+
 // ---- stage 3 ------------------------------------------------------------------------------------
 __global__ void k_lf_init(igs_links_row* __restrict__ rows, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -295,6 +361,13 @@ void igs_links_free(igs_engine* e) {
     if (e->d_links_rows) cudaFree(e->d_links_rows);
     e->d_links_rows = nullptr;
     e->n_links_rows = 0;
+    for (int s = 0; s < kMaxShards; ++s) {
+        if (e->links_peer[s] && e->links_peer_ipc[s]) cudaIpcCloseMemHandle(e->links_peer[s]);
+        e->links_peer[s] = nullptr;
+        e->links_peer_ipc[s] = false;
+    }
+    if (e->links_window) cudaFree(e->links_window);
+    e->links_window = nullptr;
 }
 
 extern "C" {
@@ -335,18 +408,17 @@ int igs_links_pairs(igs_engine* e, uint32_t shard, uint32_t n_shards, const igs_
     return IGS_OK;
 }
 
-int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, uint32_t n_shards,
-                    const igs_link** d_links, uint64_t* counts) {
-    if (!e) return IGS_ERR_INVALID;
-    IGS_REQUIRE(e, d_links && counts, "d_links / counts is null");
+// Stage 2.  d_wins == nullptr: links into an engine-owned buffer grouped by shard (*d_links, counts);
+// else: links straight into the account owners' windows.
+static int links_group_impl(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, uint32_t n_shards,
+                            const igs_link** d_links, uint64_t* counts, const PeerWin* d_wins) {
     IGS_REQUIRE(e, n64 == 0 || d_pairs, "d_pairs is null");
     IGS_REQUIRE(e, n_shards >= 1 && n_shards <= kMaxShards, "n_shards out of range");
     IGS_REQUIRE(e, n64 < 0xFFFFFFFFull, "at most 2^32-2 pairs per stage");
-    IGS_CUDA(e, cudaSetDevice(e->device));
-    std::lock_guard<std::mutex> lk(e->mu);
     cudaStream_t st = e->slot[0].stream;
     const uint32_t n = (uint32_t)n64;
     Scratch sc(e->links_pool);
+    if (e->links_pool.size() < kStage2First) e->links_pool.resize(kStage2First);
     sc.next = kStage2First;                             // keep stage 1's output alive (one shard: d_pairs is it)
     Rec* d_distinct; uint32_t m = 0;
     int rc = distinct_records(e, sc, reinterpret_cast<const Rec*>(d_pairs), n, &d_distinct, &m, st);
@@ -369,10 +441,18 @@ int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, u
         IGS_CUDA(e, cudaGetLastError());
         k_lg_count<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_counts);
         IGS_CUDA(e, cudaGetLastError());
+        if (d_wins) {
+            k_lg_emit_peer<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_wins,
+                                                    (unsigned long long)e->links_cap_links);
+            IGS_CUDA(e, cudaGetLastError());
+        }
         IGS_CUDA(e, cudaMemcpyAsync(h_counts, d_counts, n_shards * 8, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
         total = offsets_of(h_counts, n_shards, h_starts);
     }
+    if (counts)
+        for (uint32_t s = 0; s < n_shards; ++s) counts[s] = h_counts[s];
+    if (d_wins) return IGS_OK;
     igs_link* d_out;
     IGS_CUDA(e, sc.alloc(&d_out, total));
     if (sc.next > kStage3First) {
@@ -385,21 +465,26 @@ int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, u
         IGS_CUDA(e, cudaGetLastError());
         IGS_CUDA(e, cudaStreamSynchronize(st));
     }
-    for (uint32_t s = 0; s < n_shards; ++s) counts[s] = h_counts[s];
     *d_links = d_out;
     return IGS_OK;
 }
 
-int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n64, uint32_t shard) {
+int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n64, uint32_t n_shards,
+                    const igs_link** d_links, uint64_t* counts) {
     if (!e) return IGS_ERR_INVALID;
+    IGS_REQUIRE(e, d_links && counts, "d_links / counts is null");
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    return links_group_impl(e, d_pairs, n64, n_shards, d_links, counts, nullptr);
+}
+
+static int links_finish_impl(igs_engine* e, const igs_link* d_links, uint64_t n64, uint32_t shard) {
     IGS_REQUIRE(e, n64 == 0 || d_links, "d_links is null");
     IGS_REQUIRE(e, n64 < 0xFFFFFFFFull, "at most 2^32-2 links per stage");
     if (!e->has_events) {
         igs_set_error(e, "no event history loaded: the account index space is unknown (igs_load_events_ids)");
         return IGS_ERR_STATE;
     }
-    IGS_CUDA(e, cudaSetDevice(e->device));
-    std::lock_guard<std::mutex> lk(e->mu);
     cudaStream_t st = e->slot[0].stream;
     const uint32_t n = (uint32_t)n64;
     const uint32_t n_rows = e->ev.n_accounts;
@@ -428,6 +513,169 @@ int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n64, uint3
     IGS_CUDA(e, cudaStreamSynchronize(st));
     e->n_links_rows = n_rows;
     return IGS_OK;     // the stage scratch stays in the pool for the next run of this periodic job
+}
+
+int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n64, uint32_t shard) {
+    if (!e) return IGS_ERR_INVALID;
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    return links_finish_impl(e, d_links, n64, shard);
+}
+
+// ------------------------------------------------------------------------------------------------
+// peer-memory exchange
+// ------------------------------------------------------------------------------------------------
+static void close_peer_windows(igs_engine* e) {
+    for (int s = 0; s < kMaxShards; ++s) {
+        if (e->links_peer[s] && e->links_peer_ipc[s]) cudaIpcCloseMemHandle(e->links_peer[s]);
+        e->links_peer[s] = nullptr;
+        e->links_peer_ipc[s] = false;
+    }
+}
+
+int igs_links_window_create(igs_engine* e, uint64_t cap_pairs, uint64_t cap_links,
+                            uint8_t handle_out[IGS_IPC_HANDLE_BYTES], void** d_window) {
+    if (!e) return IGS_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == IGS_IPC_HANDLE_BYTES, "handle size");
+    IGS_REQUIRE(e, cap_pairs < 0xFFFFFFFFull && cap_links < 0xFFFFFFFFull, "window capacities are limited to 2^32-2 records");
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    close_peer_windows(e);
+    if (e->links_window) cudaFree(e->links_window);
+    e->links_window = nullptr;
+    const size_t bytes = kWindowHeader + (size_t)(cap_pairs + cap_links) * sizeof(Rec);
+    cudaError_t st = cudaMalloc(&e->links_window, bytes);
+    if (st != cudaSuccess) {
+        igs_set_error(e, "cudaMalloc(%zu) for the links window failed: %s", bytes, cudaGetErrorString(st));
+        return IGS_ERR_NOMEM;
+    }
+    IGS_CUDA(e, cudaMemset(e->links_window, 0, kWindowHeader));
+    e->links_cap_pairs = cap_pairs;
+    e->links_cap_links = cap_links;
+    if (handle_out) {
+        cudaIpcMemHandle_t h;
+        IGS_CUDA(e, cudaIpcGetMemHandle(&h, e->links_window));
+        memcpy(handle_out, &h, sizeof(h));
+    }
+    if (d_window) *d_window = e->links_window;
+    return IGS_OK;
+}
+
+int igs_links_window_open(igs_engine* e, uint32_t peer_shard, const uint8_t handle[IGS_IPC_HANDLE_BYTES]) {
+    if (!e) return IGS_ERR_INVALID;
+    IGS_REQUIRE(e, peer_shard < kMaxShards && handle, "peer shard out of range / handle is null");
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    IGS_CUDA(e, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    if (e->links_peer[peer_shard] && e->links_peer_ipc[peer_shard]) cudaIpcCloseMemHandle(e->links_peer[peer_shard]);
+    e->links_peer[peer_shard] = p;
+    e->links_peer_ipc[peer_shard] = true;
+    return IGS_OK;
+}
+
+int igs_links_window_attach(igs_engine* e, uint32_t peer_shard, void* d_window) {
+    if (!e) return IGS_ERR_INVALID;
+    IGS_REQUIRE(e, peer_shard < kMaxShards && d_window, "peer shard out of range / window is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (e->links_peer[peer_shard] && e->links_peer_ipc[peer_shard]) cudaIpcCloseMemHandle(e->links_peer[peer_shard]);
+    e->links_peer[peer_shard] = d_window;
+    e->links_peer_ipc[peer_shard] = false;
+    return IGS_OK;
+}
+
+int igs_links_window_reset(igs_engine* e) {
+    if (!e) return IGS_ERR_INVALID;
+    if (!e->links_window) { igs_set_error(e, "no links window (igs_links_window_create)"); return IGS_ERR_STATE; }
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    IGS_CUDA(e, cudaMemsetAsync(e->links_window, 0, kWindowHeader, e->slot[0].stream));
+    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
+    return IGS_OK;
+}
+
+// the n_shards windows as a device table (scratch slot 0 of the links pool)
+static int upload_windows(igs_engine* e, Scratch& sc, uint32_t n_shards, PeerWin** d_wins, cudaStream_t st) {
+    PeerWin h[kMaxShards];
+    for (uint32_t s = 0; s < n_shards; ++s) {
+        if (!e->links_peer[s]) {
+            igs_set_error(e, "the window of shard %u is not attached / opened", s);
+            return IGS_ERR_STATE;
+        }
+        h[s] = window_view(e->links_peer[s], e->links_cap_pairs);
+    }
+    IGS_CUDA(e, sc.alloc(d_wins, kMaxShards));
+    IGS_CUDA(e, cudaMemcpyAsync(*d_wins, h, n_shards * sizeof(PeerWin), cudaMemcpyHostToDevice, st));
+    return IGS_OK;
+}
+
+int igs_links_pairs_peer(igs_engine* e, uint32_t shard, uint32_t n_shards) {
+    if (!e) return IGS_ERR_INVALID;
+    IGS_REQUIRE(e, n_shards >= 1 && n_shards <= kMaxShards && shard < n_shards, "shard / n_shards out of range");
+    if (!e->has_events || !e->has_event_ids) {
+        igs_set_error(e, "no event history with identifiers loaded (igs_load_events_ids)");
+        return IGS_ERR_STATE;
+    }
+    if (!e->links_window) { igs_set_error(e, "no links window (igs_links_window_create)"); return IGS_ERR_STATE; }
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    cudaStream_t st = e->slot[0].stream;
+    Scratch sc(e->links_pool);
+    PeerWin* d_wins;
+    int rc = upload_windows(e, sc, n_shards, &d_wins, st);
+    if (rc != IGS_OK) return rc;
+    const uint32_t n = (uint32_t)e->n_raw;
+    if (n) {
+        k_lp_scatter_peer<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(
+            e->raw_device, e->raw_account, n, shard, n_shards, d_wins, (unsigned long long)e->links_cap_pairs);
+        IGS_CUDA(e, cudaGetLastError());
+    }
+    IGS_CUDA(e, cudaStreamSynchronize(st));
+    return IGS_OK;
+}
+
+// number of records the peers have put into this shard's window (which = 0 pairs, 1 links)
+static int window_fill(igs_engine* e, int which, uint64_t cap, uint64_t* n_out) {
+    unsigned long long cur[2] = {0, 0};
+    IGS_CUDA(e, cudaMemcpy(cur, e->links_window, sizeof(cur), cudaMemcpyDeviceToHost));
+    if (cur[which] > cap) {
+        igs_set_error(e, "links window too small: %llu %s arrived, capacity %llu (igs_links_window_create)",
+                      cur[which], which ? "links" : "pairs", (unsigned long long)cap);
+        return IGS_ERR_NOMEM;
+    }
+    *n_out = cur[which];
+    return IGS_OK;
+}
+
+int igs_links_group_peer(igs_engine* e, uint32_t shard, uint32_t n_shards) {
+    if (!e) return IGS_ERR_INVALID;
+    IGS_REQUIRE(e, n_shards >= 1 && n_shards <= kMaxShards && shard < n_shards, "shard / n_shards out of range");
+    if (!e->links_window) { igs_set_error(e, "no links window (igs_links_window_create)"); return IGS_ERR_STATE; }
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    uint64_t n = 0;
+    int rc = window_fill(e, 0, e->links_cap_pairs, &n);
+    if (rc != IGS_OK) return rc;
+    Scratch sc(e->links_pool);
+    PeerWin* d_wins;
+    rc = upload_windows(e, sc, n_shards, &d_wins, e->slot[0].stream);
+    if (rc != IGS_OK) return rc;
+    const PeerWin mine = window_view(e->links_window, e->links_cap_pairs);
+    return links_group_impl(e, reinterpret_cast<const igs_link_pair*>(mine.pairs), n, n_shards, nullptr, nullptr, d_wins);
+}
+
+int igs_links_finish_peer(igs_engine* e, uint32_t shard) {
+    if (!e) return IGS_ERR_INVALID;
+    if (!e->links_window) { igs_set_error(e, "no links window (igs_links_window_create)"); return IGS_ERR_STATE; }
+    IGS_CUDA(e, cudaSetDevice(e->device));
+    std::lock_guard<std::mutex> lk(e->mu);
+    uint64_t n = 0;
+    int rc = window_fill(e, 1, e->links_cap_links, &n);
+    if (rc != IGS_OK) return rc;
+    const PeerWin mine = window_view(e->links_window, e->links_cap_pairs);
+    return links_finish_impl(e, reinterpret_cast<const igs_link*>(mine.links), n, shard);
 }
 
 int igs_get_links(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_links_row* out) {

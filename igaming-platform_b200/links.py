@@ -67,6 +67,39 @@ def build_links(engine, shard: int = 0, n_shards: int = 1, group=None, exchange=
             "links_sent": int(link_counts.sum()), "links_received": n_links}
 
 
+def setup_peer_windows(engine, shard: int, n_shards: int, cap_pairs: int, cap_links: int, group=None) -> None:
+    """Collective, once: every shard allocates its receive window and maps every peer's (CUDA IPC handles
+    travel through torch.distributed; NVLink / NVSwitch carries the stores and atomics afterwards)."""
+    handle, ptr = engine.links_window_create(cap_pairs, cap_links)
+    if n_shards > 1:
+        import torch.distributed as dist
+        handles = [None] * n_shards
+        dist.all_gather_object(handles, handle, group=group)
+        for s in range(n_shards):
+            if s != shard:
+                engine.links_window_open(s, handles[s])
+    engine.links_window_attach(shard, ptr)
+
+
+def build_links_peer(engine, shard: int = 0, n_shards: int = 1, group=None, barrier=None) -> None:
+    """build_links with both exchanges fused into the producing kernels over peer memory (no NCCL on the
+    data, no staging, no host-side counts).  Needs setup_peer_windows.  No kernel waits for another GPU: the
+    steps are separated by host barriers."""
+    if barrier is None:
+        if n_shards == 1:
+            barrier = lambda: None                                           # noqa: E731
+        else:
+            import torch.distributed as dist
+            barrier = lambda: dist.barrier(group=group)                      # noqa: E731
+    engine.links_window_reset()
+    barrier()
+    engine.links_pairs_peer(shard, n_shards)
+    barrier()
+    engine.links_group_peer(shard, n_shards)
+    barrier()
+    engine.links_finish_peer(shard)
+
+
 def global_account_id(shard: int, index) -> np.ndarray:
     """(shard << 32) | dense index — the account ids the links table reports."""
     return (np.uint64(shard) << np.uint64(32)) | np.asarray(index, dtype=np.uint64)

@@ -494,6 +494,34 @@ int igs_links_pairs(igs_engine* e, uint32_t shard, uint32_t n_shards, const igs_
 int igs_links_group(igs_engine* e, const igs_link_pair* d_pairs, uint64_t n, uint32_t n_shards,
                     const igs_link** d_links, uint64_t* counts);
 int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n, uint32_t shard);
+
+/* The same job with the two exchanges fused into the producing kernels over peer memory (NVLink /
+ * NVSwitch): every shard owns a receive WINDOW — one device allocation holding a cursor block, room
+ * for cap_pairs pairs and cap_links links — that its peers map and write into directly.  Stage 1's
+ * scatter and stage 2's emit claim slots in the destination's window with one remote atomic per warp /
+ * per pair and store the records straight into it; nothing is staged, counted on the host or copied by
+ * a collective.  No kernel waits for another GPU: the caller separates the steps with a barrier of
+ * its own (torch.distributed.barrier in links.py), in this order on every shard:
+ *     igs_links_window_reset -> barrier -> igs_links_pairs_peer -> barrier ->
+ *     igs_links_group_peer   -> barrier -> igs_links_finish_peer
+ * Every call returns after its kernels have completed.  A window that is too small loses nothing
+ * silently: the cursor keeps counting, the consuming call fails with IGS_ERR_NOMEM and names the
+ * capacity that would have sufficed.  No counterpart in the reference.
+ * igs_links_window_create: allocates this shard's window and returns the 64-byte inter-process handle
+ * (cudaIpcMemHandle_t) peers open; igs_links_window_open maps a peer's window from its handle (other
+ * process / other GPU); igs_links_window_attach registers a window by address (this shard's own, or a
+ * peer engine in the same process).  All n_shards windows, the own one included, must be attached /
+ * opened before the first *_peer call; capacities must be the same on every shard.                  */
+#define IGS_IPC_HANDLE_BYTES 64
+int igs_links_window_create(igs_engine* e, uint64_t cap_pairs, uint64_t cap_links,
+                            uint8_t handle_out[IGS_IPC_HANDLE_BYTES], void** d_window);
+int igs_links_window_open(igs_engine* e, uint32_t peer_shard, const uint8_t handle[IGS_IPC_HANDLE_BYTES]);
+int igs_links_window_attach(igs_engine* e, uint32_t peer_shard, void* d_window);
+int igs_links_window_reset(igs_engine* e);
+int igs_links_pairs_peer(igs_engine* e, uint32_t shard, uint32_t n_shards);
+int igs_links_group_peer(igs_engine* e, uint32_t shard, uint32_t n_shards);
+int igs_links_finish_peer(igs_engine* e, uint32_t shard);
+
 /* Rows of the table built by igs_links_finish for n dense account indices of this shard (host
  * buffers).  An index beyond the table yields a zero row.                                          */
 int igs_get_links(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_links_row* out);

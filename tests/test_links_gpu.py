@@ -149,6 +149,81 @@ def test_simulated_shards_match_oracle(orc, pkg, built_lib, n_shards):
             eng.close()
 
 
+def test_peer_window_single_shard_and_overflow(engine, orc, pkg):
+    """The peer-memory path with one shard (its own window is the only destination), and a window that is too
+    small: nothing is lost silently, the consuming stage names the capacity that was needed."""
+    abi, links = pkg.abi, pkg.links
+    n_acc, n_ev = 2000, 40000
+    ev = make_history(pkg, n_ev, n_acc, seed=83)
+    engine.load_events(ev, n_acc)
+    links.setup_peer_windows(engine, 0, 1, cap_pairs=n_ev, cap_links=400_000)
+    for _ in range(2):                                                   # a rerun reuses the window
+        links.build_links_peer(engine)
+        q = np.arange(n_acc, dtype=np.uint32)
+        want = orc.links(ev.device, ev.account.astype(np.uint64), q.astype(np.uint64))
+        assert engine.get_links(q).tobytes() == want.tobytes()
+    n_pairs = int((ev.device != 0).sum())
+    links.setup_peer_windows(engine, 0, 1, cap_pairs=n_pairs - 1, cap_links=400_000)
+    with pytest.raises(pkg.IgsError) as ei:
+        links.build_links_peer(engine)
+    assert ei.value.status == abi.ERR_NOMEM and f"{n_pairs} pairs arrived" in str(ei.value)
+    links.setup_peer_windows(engine, 0, 1, cap_pairs=n_pairs, cap_links=10)
+    with pytest.raises(pkg.IgsError) as ei:
+        links.build_links_peer(engine)
+    assert ei.value.status == abi.ERR_NOMEM and "links arrived" in str(ei.value)
+    engine.load_events(synth.make_events(10, 10, seed=1), 10)           # no identifiers
+    with pytest.raises(pkg.IgsError) as ei:
+        engine.links_pairs_peer(0, 1)
+    assert ei.value.status == abi.ERR_STATE
+
+
+@pytest.mark.parametrize("n_shards", [2, 4])
+def test_peer_windows_between_simulated_shards(orc, pkg, built_lib, n_shards):
+    """Several engines on one GPU write straight into each other's windows (attached by address: same
+    process) — the kernels and the slot claiming are those of the multi-GPU job, only the wire is missing."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    abi, links = pkg.abi, pkg.links
+    lib = abi.load_library()
+    n_acc_total, n_ev = 3000, 60000
+    ev = make_history(pkg, n_ev, n_acc_total, seed=95, shared_rate=0.1)
+    shard_of = np.array([lib.igs_shard_of(int(g), 0, n_shards) for g in range(n_acc_total)], dtype=np.uint32)
+    dense = np.zeros(n_acc_total, dtype=np.uint32)
+    sizes = []
+    for s in range(n_shards):
+        idx = np.nonzero(shard_of == s)[0]
+        dense[idx] = np.arange(idx.size)
+        sizes.append(idx.size)
+    gid = (shard_of.astype(np.uint64) << np.uint64(32)) | dense.astype(np.uint64)
+    engines = [pkg.Engine(0) for _ in range(n_shards)]
+    try:
+        ptrs = []
+        for s, eng in enumerate(engines):
+            m = shard_of[ev.account] == s
+            eng.load_events(pkg.Events(dense[ev.account[m]], ev.ts[m], ev.amount[m], ev.tx_type[m],
+                                       device=ev.device[m], ip=ev.ip[m]), sizes[s])
+            ptrs.append(eng.links_window_create(n_ev, 600_000)[1])
+        for eng in engines:
+            for s, p in enumerate(ptrs):
+                eng.links_window_attach(s, p)
+        for step in ("links_window_reset", "links_pairs_peer", "links_group_peer", "links_finish_peer"):
+            for s, eng in enumerate(engines):                            # every shard finishes a step before the next
+                if step == "links_window_reset":
+                    eng.links_window_reset()
+                elif step == "links_finish_peer":
+                    eng.links_finish_peer(s)
+                else:
+                    getattr(eng, step)(s, n_shards)
+        want_all = orc.links(ev.device, gid[ev.account], gid)
+        for s, eng in enumerate(engines):
+            idx = np.nonzero(shard_of == s)[0]
+            assert eng.get_links(np.arange(idx.size, dtype=np.uint32)).tobytes() == want_all[idx].tobytes(), f"shard {s}"
+    finally:
+        for eng in engines:
+            eng.close()
+
+
 def test_links_need_identifiers(engine, pkg):
     engine.load_events(synth.make_events(100, 10, seed=1), 10)
     with pytest.raises(pkg.IgsError) as ei:

@@ -26,6 +26,9 @@ def main():
     ap.add_argument("--accounts", type=int, default=1_000_000, help="global account count")
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--peer", action="store_true",
+                    help="exchange through peer-memory windows (stores + atomics over NVLink from inside the "
+                         "producing kernels) instead of NCCL all-to-all")
     args = ap.parse_args()
 
     import torch
@@ -59,14 +62,20 @@ def main():
     eng = pkg.Engine(local)
     eng.load_events(pkg.Events(dense[ev.account[m]], ev.ts[m], ev.amount[m], ev.tx_type[m], device=ev.device[m],
                                ip=ev.ip[m]), mine.size)
-    times, stats = [], None
+    if args.peer:
+        # capacity: every event could carry a device owned by one shard; links bounded generously
+        links.setup_peer_windows(eng, rank, world, cap_pairs=n_ev, cap_links=4 * n_ev)
+    times, stats = [], {"pairs_sent": 0, "links_sent": 0}
     for _ in range(args.reps):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        stats = links.build_links(eng, rank, world)
+        if args.peer:
+            links.build_links_peer(eng, rank, world)
+        else:
+            stats = links.build_links(eng, rank, world)
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -91,7 +100,8 @@ def main():
     if rank == 0:
         best = min(times)
         print(json.dumps({"job": "linked accounts (igs_links_pairs -> all-to-all -> igs_links_group -> all-to-all -> "
-                                 "igs_links_finish)", "n_gpus": world, "events": int(tot[2].item()),
+                                 "igs_links_finish)", "exchange": "peer-memory windows (fused into the kernels)" if args.peer
+                          else "NCCL all_to_all_single", "n_gpus": world, "events": int(tot[2].item()),
                           "accounts": args.accounts, "pairs_exchanged": int(tot[0].item()),
                           "links_exchanged": int(tot[1].item()), "ms_best": best, "ms_all": times,
                           "events_per_s": int(tot[2].item()) / (best * 1e-3),
