@@ -185,51 +185,82 @@ __host__ PeerWin window_view(void* base, uint64_t cap_pairs) {
 }
 
 // stage 1 + exchange 1: each pair goes straight into the window of the shard that owns its device — over
-// NVLink when that shard is another GPU.  One remote atomic per warp and destination claims the slots.
+// NVLink when that shard is another GPU.  A block first ranks its 1024 events per destination in shared
+// memory, then claims each destination's slots with ONE system-scope atomic, so the remote cursors see a
+// few atomics per thousand records.
+constexpr int kPeerItems = 4;
 __global__ void __launch_bounds__(kThreads)
 k_lp_scatter_peer(const uint64_t* __restrict__ device, const uint32_t* __restrict__ account, uint32_t n,
                   uint32_t shard, uint32_t n_shards, const PeerWin* __restrict__ wins, unsigned long long cap_pairs) {
-    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
-    const uint64_t d = i < n ? __ldg(device + i) : 0;
-    const uint32_t dest = d ? shard_of(d, n_shards) : 0xFFFFFFFFu;
-    const unsigned peers = __match_any_sync(0xffffffffu, dest);
-    if (!d) return;
-    const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
-    const PeerWin w = wins[dest];
-    unsigned long long base = 0;
-    if (lane == leader) base = atomicAdd_system(w.cursors + 0, (unsigned long long)__popc(peers));
-    base = __shfl_sync(peers, base, leader);
-    const unsigned long long slot = base + __popc(peers & ((1u << lane) - 1u));
-    if (slot < cap_pairs) {
-        Rec p;
-        p.a = d;
-        p.b = ((uint64_t)shard << 32) | __ldg(account + i);
-        w.pairs[slot] = p;
+    __shared__ uint32_t sh_cnt[kMaxShards];
+    __shared__ unsigned long long sh_base[kMaxShards];
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) sh_cnt[s] = 0;
+    __syncthreads();
+    uint64_t d[kPeerItems];
+    uint32_t dest[kPeerItems], rank[kPeerItems];
+    const uint32_t base_i = blockIdx.x * (kThreads * kPeerItems) + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < kPeerItems; ++k) {
+        const uint32_t i = base_i + k * kThreads;
+        d[k] = i < n ? __ldg(device + i) : 0;
+        dest[k] = d[k] ? shard_of(d[k], n_shards) : 0;
+        rank[k] = d[k] ? atomicAdd(&sh_cnt[dest[k]], 1u) : 0;
+    }
+    __syncthreads();
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads)
+        sh_base[s] = sh_cnt[s] ? atomicAdd_system(wins[s].cursors + 0, (unsigned long long)sh_cnt[s]) : 0ull;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kPeerItems; ++k) {
+        if (!d[k]) continue;
+        const unsigned long long slot = sh_base[dest[k]] + rank[k];
+        if (slot < cap_pairs) {
+            Rec p;
+            p.a = d[k];
+            p.b = ((uint64_t)shard << 32) | __ldg(account + base_i + k * kThreads);
+            wins[dest[k]].pairs[slot] = p;
+        }
     }
 }
 
-// stage 2's emit + exchange 2: the links of a pair go straight into the window of the account's shard
-__global__ void k_lg_emit_peer(const uint64_t* __restrict__ keys, const Rec* __restrict__ pairs, uint32_t n,
-                               uint32_t n_shards, const uint32_t* __restrict__ links_of,
-                               const PeerWin* __restrict__ wins, unsigned long long cap_links) {
+// stage 2's emit + exchange 2: the links of a pair go straight into the window of the account's shard; the
+// block sums its link counts per destination and claims them with one system-scope atomic each
+__global__ void __launch_bounds__(kThreads)
+k_lg_emit_peer(const uint64_t* __restrict__ keys, const Rec* __restrict__ pairs, uint32_t n,
+               uint32_t n_shards, const uint32_t* __restrict__ links_of,
+               const PeerWin* __restrict__ wins, unsigned long long cap_links) {
+    __shared__ uint32_t sh_cnt[kMaxShards];
+    __shared__ unsigned long long sh_base[kMaxShards];
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) sh_cnt[s] = 0;
+    __syncthreads();
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n) return;
-    const uint32_t cnt = __ldg(links_of + r);
+    const uint32_t cnt = r < n ? __ldg(links_of + r) : 0;
+    Rec me;
+    me.a = me.b = 0;
+    uint32_t dst = 0, off = 0;
+    if (cnt) {
+        me = pairs[r];
+        dst = min((uint32_t)(me.b >> 32), n_shards - 1);
+        off = atomicAdd(&sh_cnt[dst], cnt);
+    }
+    __syncthreads();
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads)
+        sh_base[s] = sh_cnt[s] ? atomicAdd_system(wins[s].cursors + 1, (unsigned long long)sh_cnt[s]) : 0ull;
+    __syncthreads();
     if (!cnt) return;
-    const Rec me = pairs[r];
-    const PeerWin w = wins[min((uint32_t)(me.b >> 32), n_shards - 1)];
-    unsigned long long pos = atomicAdd_system(w.cursors + 1, (unsigned long long)cnt);
+    unsigned long long pos = sh_base[dst] + off;
     if (pos + cnt > cap_links) return;                        // the consumer reports the overflow
+    Rec* out = wins[dst].links;
     const uint64_t key = __ldg(keys + r);
     for (uint32_t rr = r; rr-- > 0;) {
         if (__ldg(keys + rr) != key) break;
         const Rec o = pairs[rr];
-        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; w.links[pos++] = l; }
+        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; out[pos++] = l; }
     }
     for (uint32_t rr = r + 1; rr < n; ++rr) {
         if (__ldg(keys + rr) != key) break;
         const Rec o = pairs[rr];
-        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; w.links[pos++] = l; }
+        if (o.a == me.a) { Rec l; l.a = me.b; l.b = o.b; out[pos++] = l; }
     }
 }
 
@@ -628,7 +659,7 @@ int igs_links_pairs_peer(igs_engine* e, uint32_t shard, uint32_t n_shards) {
     if (rc != IGS_OK) return rc;
     const uint32_t n = (uint32_t)e->n_raw;
     if (n) {
-        k_lp_scatter_peer<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(
+        k_lp_scatter_peer<<<(n + kThreads * kPeerItems - 1) / (kThreads * kPeerItems), kThreads, 0, st>>>(
             e->raw_device, e->raw_account, n, shard, n_shards, d_wins, (unsigned long long)e->links_cap_pairs);
         IGS_CUDA(e, cudaGetLastError());
     }

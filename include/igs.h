@@ -498,8 +498,8 @@ int igs_links_finish(igs_engine* e, const igs_link* d_links, uint64_t n, uint32_
 /* The same job with the two exchanges fused into the producing kernels over peer memory (NVLink /
  * NVSwitch): every shard owns a receive WINDOW — one device allocation holding a cursor block, room
  * for cap_pairs pairs and cap_links links — that its peers map and write into directly.  Stage 1's
- * scatter and stage 2's emit claim slots in the destination's window with one remote atomic per warp /
- * per pair and store the records straight into it; nothing is staged, counted on the host or copied by
+ * scatter and stage 2's emit claim slots in the destination's window with one remote atomic per block
+ * and destination and store the records straight into it; nothing is staged, counted on the host or copied by
  * a collective.  No kernel waits for another GPU: the caller separates the steps with a barrier of
  * its own (torch.distributed.barrier in links.py), in this order on every shard:
  *     igs_links_window_reset -> barrier -> igs_links_pairs_peer -> barrier ->
