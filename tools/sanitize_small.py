@@ -51,5 +51,31 @@ torch.cuda.synchronize()
 eng.load_mlp(synth.make_mlp(seed=8))
 x, lrows = synth.make_ltv_inputs(300, seed=9)
 o, raw = eng.ltv_batch(x, lrows, want_raw=True)
+# identifiers: uniques in the index, blacklist sets, fused path with ids; linked accounts (both exchanges)
+evi = synth.make_event_ids(ev, seed=10)
+eng.load_events(evi, 300)
+eng.append_events(synth.make_event_ids(synth.make_events(700, 300, seed=11, span=3600), seed=12))
+u = eng.get_uniques(synth.queries_of(tx))
+for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+    eng.blacklist_load(kind, evi.device[:50] if kind == abi.BL_DEVICE else np.arange(1, 40, dtype=np.uint64))
+    eng.blacklist_add(kind, np.arange(100, 3000, dtype=np.uint64))
+ids = np.zeros(tx.shape[0], dtype=abi.tx_ids_dtype)
+ids["device"], ids["fingerprint"], ids["ip"] = evi.device[:tx.shape[0]], 7, evi.ip[:tx.shape[0]]
+hit = eng.blacklist_check(ids)
+r2 = eng.score_batch(pkg.default_config(model_kind=abi.MODEL_GBDT), tx, ids=ids)
+pkg.links.build_links(eng)
+rows0 = eng.get_links(np.arange(310, dtype=np.uint32))
+pkg.links.setup_peer_windows(eng, 0, 1, cap_pairs=6000, cap_links=200_000)
+pkg.links.build_links_peer(eng)
+assert eng.get_links(np.arange(310, dtype=np.uint32)).tobytes() == rows0.tobytes()
+ab = eng.check_bonus_abuse(np.arange(310, dtype=np.uint32))
+for n0 in (0, 1):                                   # degenerate sizes
+    eng.get_uniques(synth.queries_of(tx[:n0])); eng.blacklist_check(ids[:n0]); eng.get_links(np.arange(n0, dtype=np.uint32))
+    eng.score_batch(pkg.default_config(model_kind=abi.MODEL_MOCK), tx[:n0], ids=ids[:n0])
+eng.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64), np.zeros(0, np.uint8),
+                           device=np.zeros(0, np.uint64), ip=np.zeros(0, np.uint64)), 5)
+pkg.links.build_links(eng)                          # empty history
+pkg.links.build_links_peer(eng)
 eng.close()
-print("sanitize_small: all entry points ran;", int(out["score"].sum()), int(v["n_prior"].sum()), float(raw.sum()))
+print("sanitize_small: all entry points ran;", int(u["devices_24h"].sum()), int(hit.sum()), int(rows0["n_linked"].sum()),
+      int(ab["is_abuser"].sum()), int(out["score"].sum()), int(v["n_prior"].sum()), float(raw.sum()))
