@@ -47,7 +47,9 @@ def test_struct_sizes_match_header(pkg):
     src = r'''
 #include <stdio.h>
 #include "igs.h"
-int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(igs_config),
+int main(void){printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(igs_event_ids), sizeof(igs_tx_ids), sizeof(igs_uniques),
+ sizeof(igs_link_pair), sizeof(igs_link), sizeof(igs_links_row), sizeof(igs_abuse));
+ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(igs_config),
  sizeof(igs_rule_row), sizeof(igs_result), sizeof(igs_tx), sizeof(igs_player_row), sizeof(igs_query),
  sizeof(igs_velocity), sizeof(igs_ltv_row), sizeof(igs_ltv_result), sizeof(igs_gbdt_desc),
  sizeof(igs_mlp_desc), sizeof(igs_event_cols));return 0;}'''
@@ -57,7 +59,9 @@ int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeo
                                os.path.join(d, "s.c")])
         got = [int(x) for x in subprocess.check_output([os.path.join(d, "s")]).split()]
     abi = pkg.abi
-    want = [C.sizeof(abi.Config), abi.rule_row_dtype.itemsize, abi.result_dtype.itemsize,
+    want = [C.sizeof(abi.EventIds), abi.tx_ids_dtype.itemsize, abi.uniques_dtype.itemsize, abi.link_pair_dtype.itemsize,
+            abi.link_dtype.itemsize, abi.links_row_dtype.itemsize, abi.abuse_dtype.itemsize,
+            C.sizeof(abi.Config), abi.rule_row_dtype.itemsize, abi.result_dtype.itemsize,
             abi.tx_dtype.itemsize, abi.player_row_dtype.itemsize, abi.query_dtype.itemsize,
             abi.velocity_dtype.itemsize, abi.ltv_row_dtype.itemsize, abi.ltv_result_dtype.itemsize,
             C.sizeof(abi.GbdtDesc), C.sizeof(abi.MlpDesc), C.sizeof(abi.EventCols)]
