@@ -9,7 +9,7 @@
 //   stage 2  igs_links_group   owner: distinct pairs, per-device account sets, directed links (account, other)
 //                              grouped by the account's shard
 //   stage 3  igs_links_finish  account owner: distinct links -> per-account {count, three smallest ids}
-// All of it is HBM-streaming integer work: hash-keyed stable radix sorts (40-bit keys, 4 passes) where equal
+// All of it is HBM-streaming integer work: hash-keyed stable radix sorts (40-bit keys, 5 passes) where equal
 // hashes are resolved by comparing the full 128-bit records, so the results are exact.
 #include <string.h>
 
@@ -22,8 +22,8 @@
 
 namespace {
 
-constexpr int kKeyBits = 40;          // 4 radix passes of 10 bits
-constexpr int kKeyPasses = 4;
+constexpr int kKeyBits = 40;          // 5 radix passes of 8 bits
+constexpr int kKeyPasses = 5;
 constexpr int kMaxShards = 256;
 // Slots of the engine's links pool: every stage makes the same requests in the same order on every run and
 // owns a fixed range, so a rerun reuses its buffers and a stage never overwrites the previous stage's output
@@ -344,8 +344,8 @@ int sort_records(igs_engine* e, Scratch& sc, const Rec* d_rec, uint32_t n, int b
     IGS_CUDA(e, sc.alloc(&keys[1], n));
     IGS_CUDA(e, sc.alloc(&vals[0], n));
     IGS_CUDA(e, sc.alloc(&vals[1], n));
-    IGS_CUDA(e, sc.alloc(&d_hist, (size_t)1024 * nb_sort));
-    IGS_CUDA(e, sc.alloc(&d_scr, scan_u32_scratch_elems(std::max<uint32_t>(1024u * nb_sort, n + 1))));
+    IGS_CUDA(e, sc.alloc(&d_hist, (size_t)kSortBins * nb_sort));
+    IGS_CUDA(e, sc.alloc(&d_scr, scan_u32_scratch_elems(std::max<uint32_t>((uint32_t)kSortBins * nb_sort, n + 1))));
     *cur = 0;
     if (n == 0) return IGS_OK;
     k_rec_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(d_rec, n, by_first_only, keys[0], vals[0]);

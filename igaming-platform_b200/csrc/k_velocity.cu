@@ -4,7 +4,7 @@
 // Build (igs_load_events), replaces the Redis state of UpdateRealTimeFeatures
 // (features/redis_store.go:119-168):
 //   1. key = (account << ts_bits) | (ts - ts_min), value = arrival index; LSD radix sort, stable,
-//      <= 10-bit digits sized so that the key's significant bits take the fewest passes
+//      <= 8-bit digits sized so that the key's significant bits take the fewest passes
 //      (ZSET ordering by score, :127-130).
 //   2. gather amount / type by the sorted arrival index; CSR `seg` of account boundaries.
 //   3. distinct flag per event: first occurrence of (account, ts, amount) — the ZSET member
@@ -16,7 +16,7 @@
 //   5. (histories that carry identifiers, igs_load_events_ids) per identifier column — device, IP — the
 //      PFADD + EXPIRE 24h key of :141-152 as of every event: compact the events that carry an identifier,
 //      cut them into chains (gap > 86400 or new account), find each event's previous occurrence of the
-//      same identifier in its chain through a stable radix sort on a 30-bit hash of the identifier
+//      same identifier in its chain through a stable radix sort on a 32-bit hash of the identifier
 //      (exact: equal hashes are resolved by comparing the 64-bit ids), and count first occurrences per
 //      chain with a prefix sum.
 // Query (igs_get_velocity*, and inlined into the fused score kernel): velocity.cuh.
@@ -435,7 +435,7 @@ k_uniques(igs_index_view ix, const igs_query* __restrict__ q, unsigned long long
 // ------------------------------------------------------------------------------------------------
 // identifier columns (step 5)
 // ------------------------------------------------------------------------------------------------
-constexpr int kIdKeyBits = 30;       // 3 radix passes of 10 bits
+constexpr int kIdKeyBits = 32;       // 4 radix passes of 8 bits
 
 // id_s[p] = identifier of sorted event p; flag[p] = 1 iff it has one
 __global__ void k_id_gather(const uint64_t* __restrict__ raw, const uint32_t* __restrict__ seq, uint32_t n,
@@ -775,7 +775,7 @@ static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, con
     k_id_chain<<<mb, kThreads, 0, st>>>(s.head, s.chain, s.cid, m, s.chain_head, s.keys[0], s.vals[0]);
     IGS_CUDA(e, cudaGetLastError());
     int cur = 0;
-    rc = radix_sort_pairs(e, s.keys, s.vals, m, kIdKeyBits / 10, 10, s.hist, s.scan_scratch, st, &cur);
+    rc = radix_sort_pairs(e, s.keys, s.vals, m, kIdKeyBits / kSortMaxBits, kSortMaxBits, s.hist, s.scan_scratch, st, &cur);
     if (rc != IGS_OK) return rc;
     k_id_new<<<mb, kThreads, 0, st>>>(s.keys[cur], s.vals[cur], s.chain, s.cid, m, s.isnew8, s.nex);
     IGS_CUDA(e, cudaGetLastError());
@@ -844,8 +844,8 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     const bool time_ordered = mm[3] == 0;
     const int ts_bits = time_ordered ? 0 : (bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1);
     const int key_bits = ts_bits + (bits_for(mm[2]) > 0 ? bits_for(mm[2]) : 1);
-    const int passes = (key_bits + 9) / 10;
-    const int digit_bits = (key_bits + passes - 1) / passes;      // <= 10
+    const int passes = (key_bits + kSortMaxBits - 1) / kSortMaxBits;
+    const int digit_bits = (key_bits + passes - 1) / passes;      // <= 8
     const uint32_t bins = 1u << digit_bits;
 
     // ---- radix sort -----------------------------------------------------------------------------
@@ -929,8 +929,8 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
         IGS_CUDA(e, sc.alloc(&is.chain_head, n));
         IGS_CUDA(e, sc.alloc(&is.isnew8, n));
         IGS_CUDA(e, sc.alloc(&is.nex, n));
-        IGS_CUDA(e, sc.alloc(&is.hist, (size_t)(1u << 10) * nb_sort));
-        IGS_CUDA(e, sc.alloc(&is.scan_scratch, scan_u32_scratch_elems(std::max<uint32_t>((1u << 10) * nb_sort, n))));
+        IGS_CUDA(e, sc.alloc(&is.hist, (size_t)kSortBins * nb_sort));
+        IGS_CUDA(e, sc.alloc(&is.scan_scratch, scan_u32_scratch_elems(std::max<uint32_t>((uint32_t)kSortBins * nb_sort, n))));
         int rc = build_id_column<0>(e, is, e->raw_device, d_acct, n, st);
         if (rc != IGS_OK) return rc;
         rc = build_id_column<1>(e, is, e->raw_ip, d_acct, n, st);

@@ -15,39 +15,63 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------------------------------------
 // LSD radix sort pass: histogram -> exclusive scan (bin-major) -> stable scatter
 // ------------------------------------------------------------------------------------------------
-constexpr int kSortItems = 8;
-constexpr int kSortTile = kThreads * kSortItems;   // 2048 keys per block
+// Digits of at most 8 bits and tiles of 4096 keys: a tile then holds ~16 keys per digit value, so after the
+// tile has been ordered by digit in shared memory, neighbouring threads write neighbouring global addresses
+// (runs of ~128 bytes) instead of one 32-byte sector per key.  (10-bit digits on 2048-key tiles — the first
+// version — scattered every warp's 32 keys to ~32 different sectors and ran at a quarter of the HBM roofline.)
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kThreads * kSortItems;   // 4096 keys per block
 constexpr int kSortWarps = kThreads / 32;
+constexpr int kSortMaxBits = 8;
+constexpr int kSortBins = 1 << kSortMaxBits;
+constexpr int kSortSpan = kSortItems * 32;         // keys per warp
 
 __global__ void __launch_bounds__(kThreads)
 k_radix_hist(const uint64_t* __restrict__ keys, uint32_t n, int shift, uint32_t bins,
              uint32_t* __restrict__ hist_g, uint32_t nblocks) {
-    extern __shared__ uint32_t sh_hist[];
-    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) sh_hist[d] = 0;
+    __shared__ uint32_t sh_hist[kSortWarps][kSortBins];     // per-warp tables: less contention on hot digits
+    for (uint32_t d = threadIdx.x; d < kSortWarps * kSortBins; d += kThreads) (&sh_hist[0][0])[d] = 0;
     __syncthreads();
+    const int warp = threadIdx.x >> 5;
     const uint32_t base = blockIdx.x * kSortTile;
 #pragma unroll
     for (int r = 0; r < kSortItems; ++r) {
         const uint32_t i = base + r * kThreads + threadIdx.x;
-        if (i < n) atomicAdd(&sh_hist[(uint32_t)(__ldg(keys + i) >> shift) & (bins - 1)], 1u);
+        if (i < n) atomicAdd(&sh_hist[warp][(uint32_t)(__ldg(keys + i) >> shift) & (bins - 1)], 1u);
     }
     __syncthreads();
-    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) hist_g[(size_t)d * nblocks + blockIdx.x] = sh_hist[d];
+    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w) t += sh_hist[w][d];
+        hist_g[(size_t)d * nblocks + blockIdx.x] = t;
+    }
 }
 
-// Stable scatter.  Warp w owns the contiguous span [base + w*256, +256) of the tile and walks it in
-// 8 rounds of 32 keys; __match_any_sync ranks equal digits inside a round, a per-warp counter table
-// carries the rank across rounds, and a per-digit scan over the 8 warps orders the warps.
+struct SortSmem {
+    uint64_t keys[kSortTile];
+    uint32_t vals[kSortTile];
+    uint32_t cnt[kSortWarps][kSortBins];   // per warp and digit: count, then start inside the digit's run
+    uint32_t tile_base[kSortBins];         // start of the digit's run inside the tile
+    uint32_t gbase[kSortBins];             // start of this tile's part of the digit's run in the output
+};
+
+// Stable scatter.  Warp w owns the contiguous span [w*512, +512) of the tile and walks it in 16 rounds of
+// 32 keys; __match_any_sync ranks equal digits inside a round, a per-warp counter table carries the rank
+// across rounds, a per-digit scan over the 8 warps orders the warps.  The tile is then laid out by digit in
+// shared memory and written out with consecutive threads on consecutive slots.
 __global__ void __launch_bounds__(kThreads)
 k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
                 uint32_t bins, const uint32_t* __restrict__ hist_scan_g, uint32_t nblocks) {
-    extern __shared__ uint32_t sh_cnt[];   // [kSortWarps][bins]
+    extern __shared__ __align__(16) unsigned char sort_smem_raw[];
+    SortSmem& s = *reinterpret_cast<SortSmem*>(sort_smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (uint32_t d = threadIdx.x; d < bins * kSortWarps; d += kThreads) sh_cnt[d] = 0;
+    for (uint32_t d = threadIdx.x; d < kSortWarps * kSortBins; d += kThreads) (&s.cnt[0][0])[d] = 0;
     __syncthreads();
-    uint32_t* my_cnt = sh_cnt + warp * bins;
-    const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32);
+    uint32_t* my_cnt = s.cnt[warp];
+    const uint32_t tile0 = blockIdx.x * kSortTile;
+    const uint32_t wbase = tile0 + warp * kSortSpan;
     uint64_t key[kSortItems];
     uint32_t rank[kSortItems];
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -56,7 +80,7 @@ k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict
         const uint32_t i = wbase + r * 32 + lane;
         const bool valid = i < n;
         key[r] = valid ? __ldg(keys_in + i) : 0;
-        const uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & (bins - 1)) : (bins + lane);
+        const uint32_t digit = valid ? ((uint32_t)(key[r] >> shift) & (bins - 1)) : (kSortBins + lane);
         const uint32_t peers = __match_any_sync(0xffffffffu, digit);
         const uint32_t before = valid ? my_cnt[digit] : 0;
         __syncwarp();
@@ -65,15 +89,33 @@ k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict
         rank[r] = before + __popc(peers & lt_mask);
     }
     __syncthreads();
-    // per digit: exclusive scan over warps + global base of this (digit, block)
-    for (uint32_t d = threadIdx.x; d < bins; d += kThreads) {
-        uint32_t run = __ldg(hist_scan_g + (size_t)d * nblocks + blockIdx.x);
+    // per digit: exclusive scan over the warps, the tile total, this tile's base in the output
+    {
+        const uint32_t d = threadIdx.x;            // kThreads == kSortBins
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < kSortWarps; ++w) {
-            const uint32_t c = sh_cnt[w * bins + d];
-            sh_cnt[w * bins + d] = run;
+            const uint32_t c = s.cnt[w][d];
+            s.cnt[w][d] = run;
             run += c;
         }
+        s.tile_base[d] = run;                      // totals; scanned below
+        s.gbase[d] = d < bins ? __ldg(hist_scan_g + (size_t)d * nblocks + blockIdx.x) : 0;
+    }
+    __syncthreads();
+    if (warp == 0) {                               // exclusive scan of the 256 totals by one warp
+        uint32_t v[kSortBins / 32], sum = 0;
+#pragma unroll
+        for (int k = 0; k < kSortBins / 32; ++k) { v[k] = sum; sum += s.tile_base[lane * (kSortBins / 32) + k]; }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += y;
+        }
+        const uint32_t excl = inc - sum;
+#pragma unroll
+        for (int k = 0; k < kSortBins / 32; ++k) s.tile_base[lane * (kSortBins / 32) + k] = v[k] + excl;
     }
     __syncthreads();
 #pragma unroll
@@ -81,12 +123,22 @@ k_radix_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict
         const uint32_t i = wbase + r * 32 + lane;
         if (i < n) {
             const uint32_t digit = (uint32_t)(key[r] >> shift) & (bins - 1);
-            const uint32_t pos = my_cnt[digit] + rank[r];
-            keys_out[pos] = key[r];
-            vals_out[pos] = __ldg(vals_in + i);
+            const uint32_t pos = s.tile_base[digit] + my_cnt[digit] + rank[r];
+            s.keys[pos] = key[r];
+            s.vals[pos] = __ldg(vals_in + i);
         }
     }
+    __syncthreads();
+    const uint32_t tile_n = min((uint32_t)kSortTile, n - tile0);
+    for (uint32_t j = threadIdx.x; j < tile_n; j += kThreads) {
+        const uint64_t k = s.keys[j];
+        const uint32_t digit = (uint32_t)(k >> shift) & (bins - 1);
+        const uint32_t out = s.gbase[digit] + (j - s.tile_base[digit]);
+        keys_out[out] = k;
+        vals_out[out] = s.vals[j];
+    }
 }
+static_assert(kThreads == kSortBins, "one thread per digit value in the scatter's scan step");
 
 // ------------------------------------------------------------------------------------------------
 // u32 exclusive scan (in place), 3 phases, recursive on the tile sums
@@ -192,17 +244,26 @@ struct Scratch {
 // the buffer pair that holds the result
 static int radix_sort_pairs(igs_engine* e, uint64_t* keys[2], uint32_t* vals[2], uint32_t n, int passes,
                             int digit_bits, uint32_t* d_hist, uint32_t* d_scan_scratch, cudaStream_t st, int* cur_out) {
+    if (digit_bits > kSortMaxBits) {
+        igs_set_error(e, "internal: radix digits are at most %d bits", kSortMaxBits);
+        return IGS_ERR_INVALID;
+    }
     const uint32_t bins = 1u << digit_bits;
     const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
     const uint32_t hist_elems = bins * nb_sort;
+    static bool smem_opt_in = false;       // per process; the attribute is per function and device-independent here
+    if (!smem_opt_in) {
+        IGS_CUDA(e, cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
+        smem_opt_in = true;
+    }
     int cur = 0;
     for (int p = 0; p < passes; ++p) {
         const int shift = p * digit_bits;
-        k_radix_hist<<<nb_sort, kThreads, bins * sizeof(uint32_t), st>>>(keys[cur], n, shift, bins, d_hist, nb_sort);
+        k_radix_hist<<<nb_sort, kThreads, 0, st>>>(keys[cur], n, shift, bins, d_hist, nb_sort);
         IGS_CUDA(e, cudaGetLastError());
         int rc = scan_u32(e, d_hist, hist_elems, d_scan_scratch, st);
         if (rc != IGS_OK) return rc;
-        k_radix_scatter<<<nb_sort, kThreads, (size_t)bins * kSortWarps * sizeof(uint32_t), st>>>(
+        k_radix_scatter<<<nb_sort, kThreads, sizeof(SortSmem), st>>>(
             keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, bins, d_hist, nb_sort);
         IGS_CUDA(e, cudaGetLastError());
         cur ^= 1;

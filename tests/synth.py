@@ -283,11 +283,11 @@ def mix64(x: np.ndarray) -> np.ndarray:
 
 
 def colliding_ids(count: int = 4, seed: int = 1) -> np.ndarray:
-    """`count` distinct non-zero 64-bit ids whose mix64 values share their top 30 bits pairwise with a
+    """`count` distinct non-zero 64-bit ids whose mix64 values share their top 32 bits pairwise with a
     partner (birthday search) — they land in the same radix-sort key of the index build and must still
     be counted as different identifiers."""
     cand = splitmix64(seed, 99, 400_000) | np.uint64(1)
-    key = mix64(cand) >> np.uint64(34)
+    key = mix64(cand) >> np.uint64(32)
     order = np.argsort(key, kind="stable")
     k = key[order]
     dup = np.nonzero(k[1:] == k[:-1])[0]
