@@ -15,12 +15,14 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------------------------------------
 // LSD radix sort pass: histogram -> exclusive scan (bin-major) -> stable scatter
 // ------------------------------------------------------------------------------------------------
-// Digits of at most 8 bits and tiles of 4096 keys: a tile then holds ~16 keys per digit value, so after the
+// Digits of at most 8 bits on tiles of 2048 keys: a tile then holds ~8 keys per digit value, so after the
 // tile has been ordered by digit in shared memory, neighbouring threads write neighbouring global addresses
-// (runs of ~128 bytes) instead of one 32-byte sector per key.  (10-bit digits on 2048-key tiles — the first
-// version — scattered every warp's 32 keys to ~32 different sectors and ran at a quarter of the HBM roofline.)
-constexpr int kSortItems = 16;
-constexpr int kSortTile = kThreads * kSortItems;   // 4096 keys per block
+// (runs of ~64 bytes of keys: whole 32-byte sectors) instead of one sector per key.  (10-bit digits scattered
+// straight from registers — the first version — sent every warp's 32 keys to ~32 different sectors and ran at
+// a quarter of the HBM roofline.  4096-key tiles coalesce even better but fit only 3 blocks per SM: 104 us per
+// pass against 82 us; 1024-key tiles: 84 us and a costlier histogram.)
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kThreads * kSortItems;   // keys per block
 constexpr int kSortWarps = kThreads / 32;
 constexpr int kSortMaxBits = 8;
 constexpr int kSortBins = 1 << kSortMaxBits;
@@ -56,7 +58,7 @@ struct SortSmem {
     uint32_t gbase[kSortBins];             // start of this tile's part of the digit's run in the output
 };
 
-// Stable scatter.  Warp w owns the contiguous span [w*512, +512) of the tile and walks it in 16 rounds of
+// Stable scatter.  Warp w owns a contiguous span of the tile (kSortSpan keys) and walks it in rounds of
 // 32 keys; __match_any_sync ranks equal digits inside a round, a per-warp counter table carries the rank
 // across rounds, a per-digit scan over the 8 warps orders the warps.  The tile is then laid out by digit in
 // shared memory and written out with consecutive threads on consecutive slots.
