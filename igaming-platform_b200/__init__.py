@@ -187,6 +187,12 @@ class Engine:
         else:
             self._check(self._lib.igs_append_events(self._h, C.byref(c), len(ev)))
 
+    def evict_events(self, now: int) -> int:
+        """igs_evict_events: drop what can no longer influence a query at t >= now; -> events dropped."""
+        n = C.c_uint64(0)
+        self._check(self._lib.igs_evict_events(self._h, now, C.byref(n)))
+        return int(n.value)
+
     # -- identifiers: uniques + blacklist -----------------------------------------------------
     def get_uniques(self, queries: np.ndarray) -> np.ndarray:
         queries = np.ascontiguousarray(queries, dtype=abi.query_dtype)

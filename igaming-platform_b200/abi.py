@@ -160,6 +160,7 @@ EXPORTS = [
     "igs_links_pairs", "igs_links_group", "igs_links_finish", "igs_get_links", "igs_check_bonus_abuse",
     "igs_abuse_signals", "igs_links_window_create", "igs_links_window_open", "igs_links_window_attach",
     "igs_links_window_reset", "igs_links_pairs_peer", "igs_links_group_peer", "igs_links_finish_peer",
+    "igs_evict_events",
 ]
 
 LIB_NAME = "libigs.so"
@@ -248,6 +249,7 @@ def load_library() -> C.CDLL:
     lib.igs_links_pairs_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.igs_links_group_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.igs_links_finish_peer.argtypes = [vp, C.c_uint32]
+    lib.igs_evict_events.argtypes = [vp, C.c_uint32, C.POINTER(u64)]
     lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
     lib.igs_hash_id.restype = u64
     lib.igs_version.argtypes = []

@@ -283,6 +283,12 @@ int igs_append_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_eve
     return igs_append_event_columns(e, ev, ids, n);
 }
 
+int igs_evict_events(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
+    IGS_ENGINE(e);
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_evict_event_history(e, now, n_evicted);
+}
+
 static int blacklist_update(igs_engine* e, int kind, const uint64_t* ids, uint64_t n, bool replace) {
     IGS_ENGINE(e);
     if (kind != IGS_BL_DEVICE && kind != IGS_BL_FINGERPRINT && kind != IGS_BL_IP) {

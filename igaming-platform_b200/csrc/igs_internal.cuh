@@ -176,6 +176,7 @@ void igs_idset_free(igs_idset* s);
 int igs_launch_blacklist_check(igs_engine* e, const igs_tx_ids* d_ids, uint64_t n, uint8_t* d_out,
                                cudaStream_t stream);
 void igs_free_event_index(igs_engine* e);
+int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted);
 int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);
 int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,

@@ -537,6 +537,62 @@ __global__ void k_id_expand(const uint64_t* __restrict__ id_s, const uint32_t* _
     else           { tail[p].ip_ts = t;  tail[p].ip_cnt = c16; }
 }
 
+// ------------------------------------------------------------------------------------------------
+// eviction (igs_evict_events)
+// ------------------------------------------------------------------------------------------------
+// account of sorted position j = the segment that contains it
+__device__ __forceinline__ uint32_t account_of(const uint32_t* __restrict__ seg, uint32_t n_accounts, uint32_t j) {
+    uint32_t lo = 0, hi = n_accounts;                 // first a with seg[a + 1] > j
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (__ldg(seg + mid + 1) <= j) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+// keep_from[a] = first sorted position of account a that can still influence a query at t >= now: the start of
+// the trailing chain of events with consecutive gaps <= 86400 (the longest key life among the chains: tx_sum 1h,
+// session 30m, identifier keys 24h; windows reach back 24h), or the end of the segment when even last_tx (7d,
+// the longest TTL of all, redis_store.go:155) has expired.
+__global__ void k_ev_breaks(const uint32_t* __restrict__ seg, const uint32_t* __restrict__ ts, uint32_t n,
+                            uint32_t n_accounts, uint32_t* __restrict__ keep_from) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t t = __ldg(ts + j);
+    const bool maybe = j == 0 || t < __ldg(ts + j - 1) || (long long)t - (long long)__ldg(ts + j - 1) > 86400;
+    if (!maybe) return;                               // same account, gap <= 24h: not a break
+    const uint32_t a = account_of(seg, n_accounts, j);
+    const bool brk = j == __ldg(seg + a) || (long long)t - (long long)__ldg(ts + j - 1) > 86400;
+    if (brk) atomicMax(keep_from + a, j);
+}
+__global__ void k_ev_dead(const uint32_t* __restrict__ seg, const uint32_t* __restrict__ ts, uint32_t n_accounts,
+                          uint32_t now, uint32_t* __restrict__ keep_from) {
+    const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n_accounts) return;
+    const uint32_t s = __ldg(seg + a), e = __ldg(seg + a + 1);
+    if (e == s) return;
+    if ((long long)now - (long long)__ldg(ts + e - 1) > 7 * 86400) keep_from[a] = e;
+}
+// keep flag per ARRIVAL index (the raw columns are in arrival order)
+__global__ void k_ev_keep(const uint32_t* __restrict__ seg, const uint32_t* __restrict__ seq, uint32_t n,
+                          uint32_t n_accounts, const uint32_t* __restrict__ keep_from, uint32_t* __restrict__ keep) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t a = account_of(seg, n_accounts, j);
+    keep[__ldg(seq + j)] = j >= __ldg(keep_from + a);
+}
+__global__ void k_save_last_u32(const uint32_t* __restrict__ flag, uint32_t n, uint32_t* __restrict__ out) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *out = flag[n - 1];
+}
+template <typename T>
+__global__ void k_ev_compact(const T* __restrict__ in, const uint32_t* __restrict__ keep_ex,
+                             const uint32_t* __restrict__ last_keep, uint32_t n, T* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t ex = __ldg(keep_ex + i);
+    const bool kept = i + 1 < n ? __ldg(keep_ex + i + 1) != ex : *last_keep != 0;
+    if (kept) out[ex] = in[i];
+}
+
 int bits_for(uint64_t v) {   // number of bits needed to represent v
     int b = 0;
     while (v) { ++b; v >>= 1; }
@@ -964,4 +1020,81 @@ int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_vel
     k_velocity<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
     IGS_CUDA(e, cudaGetLastError());
     return IGS_OK;
+}
+
+// Drops the events that can no longer influence any query at t >= now and rebuilds the index.  Stable
+// compaction of the raw columns: the survivors keep their relative arrival order but are renumbered.
+int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
+    if (n_evicted) *n_evicted = 0;
+    if (!e->has_events) {
+        igs_set_error(e, "no event history loaded (igs_load_events)");
+        return IGS_ERR_STATE;
+    }
+    const uint32_t n = (uint32_t)e->n_raw;
+    const uint32_t n_accounts = e->ev.n_accounts;
+    if (n == 0) return IGS_OK;
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    cudaStream_t st = e->slot[0].stream;
+    const igs_event_index& x = e->ev;
+    const uint32_t nb = (n + kThreads - 1) / kThreads;
+    uint32_t *keep_from = nullptr, *keep = nullptr, *scr = nullptr, *last_keep = nullptr;
+    void* fresh[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int rc = IGS_OK;
+    auto bail = [&](cudaError_t err, const char* what) {
+        igs_set_error(e, "%s failed: %s", what, cudaGetErrorString(err));
+        rc = err == cudaErrorMemoryAllocation ? IGS_ERR_NOMEM : IGS_ERR_CUDA;
+    };
+    uint32_t kept = 0;
+    do {
+        cudaError_t err;
+        if ((err = cudaMalloc(&keep_from, ((size_t)n_accounts + 1) * 4)) != cudaSuccess) { bail(err, "cudaMalloc"); break; }
+        if ((err = cudaMalloc(&keep, (size_t)n * 4 + 4)) != cudaSuccess) { bail(err, "cudaMalloc"); break; }
+        if ((err = cudaMalloc(&scr, scan_u32_scratch_elems(n) * 4)) != cudaSuccess) { bail(err, "cudaMalloc"); break; }
+        last_keep = keep + n;
+        cudaMemsetAsync(keep_from, 0, ((size_t)n_accounts + 1) * 4, st);
+        k_ev_breaks<<<nb, kThreads, 0, st>>>(x.seg, x.ts, n, n_accounts, keep_from);
+        k_ev_dead<<<(n_accounts + kThreads - 1) / kThreads, kThreads, 0, st>>>(x.seg, x.ts, n_accounts, now, keep_from);
+        k_ev_keep<<<nb, kThreads, 0, st>>>(x.seg, x.seq, n, n_accounts, keep_from, keep);
+        k_save_last_u32<<<1, 32, 0, st>>>(keep, n, last_keep);
+        if ((err = cudaGetLastError()) != cudaSuccess) { bail(err, "eviction kernels"); break; }
+        if ((rc = scan_u32(e, keep, n, scr, st)) != IGS_OK) break;
+        uint32_t ex = 0, lk = 0;
+        cudaMemcpyAsync(&ex, keep + (n - 1), 4, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(&lk, last_keep, 4, cudaMemcpyDeviceToHost, st);
+        if ((err = cudaStreamSynchronize(st)) != cudaSuccess) { bail(err, "eviction count"); break; }
+        kept = ex + lk;
+        if (kept == n) break;                                     // nothing to drop
+        const size_t cap = std::max<size_t>(kept, 1024);
+        const size_t widths[6] = {4, 4, 8, 1, 8, 8};
+        const int cols = e->has_event_ids ? 6 : 4;
+        bool ok = true;
+        for (int c = 0; c < cols && ok; ++c)
+            if ((err = cudaMalloc(&fresh[c], cap * widths[c])) != cudaSuccess) { bail(err, "cudaMalloc"); ok = false; }
+        if (!ok) break;
+        k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_account, keep, last_keep, n, (uint32_t*)fresh[0]);
+        k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_ts, keep, last_keep, n, (uint32_t*)fresh[1]);
+        k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_amount, keep, last_keep, n, (int64_t*)fresh[2]);
+        k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_type, keep, last_keep, n, (uint8_t*)fresh[3]);
+        if (cols == 6) {
+            k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_device, keep, last_keep, n, (uint64_t*)fresh[4]);
+            k_ev_compact<<<nb, kThreads, 0, st>>>(e->raw_ip, keep, last_keep, n, (uint64_t*)fresh[5]);
+        }
+        if ((err = cudaGetLastError()) != cudaSuccess) { bail(err, "compaction"); break; }
+        if ((err = cudaStreamSynchronize(st)) != cudaSuccess) { bail(err, "compaction"); break; }
+        cudaFree(e->raw_account); cudaFree(e->raw_ts); cudaFree(e->raw_amount); cudaFree(e->raw_type);
+        e->raw_account = (uint32_t*)fresh[0]; e->raw_ts = (uint32_t*)fresh[1];
+        e->raw_amount = (int64_t*)fresh[2]; e->raw_type = (uint8_t*)fresh[3];
+        if (cols == 6) {
+            cudaFree(e->raw_device); cudaFree(e->raw_ip);
+            e->raw_device = (uint64_t*)fresh[4]; e->raw_ip = (uint64_t*)fresh[5];
+        }
+        for (void*& f : fresh) f = nullptr;
+        e->n_raw = kept;
+        e->cap_raw = cap;
+        rc = build_index_from_raw(e, n_accounts);
+    } while (false);
+    for (void* f : fresh) if (f) cudaFree(f);
+    cudaFree(keep_from); cudaFree(keep); cudaFree(scr);
+    if (rc == IGS_OK && n_evicted) *n_evicted = n - kept;
+    return rc;
 }

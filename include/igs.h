@@ -351,6 +351,18 @@ int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_
  * account is rejected as a whole and the history is left as it was.                                  */
 int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n);
 
+/* Replaces the key expiry Redis does on its own (the TTLs of features/redis_store.go:133,138,144,151,
+ * 155,160): drops from the resident history every event that cannot influence any query at
+ * t >= now, and refreshes the index.  What is dropped, per account: everything before the trailing
+ * chain of events with consecutive gaps <= 86400 s (the longest-lived chain key; the windows reach
+ * back 24 h too), and the whole account once now - (its last event) > 7 d (last_tx, the longest TTL).
+ * Queries at t >= now return exactly what they returned before; queries in the past may not.  An
+ * account that never pauses for a day keeps its whole history — as its tx_sum / unique-identifier keys
+ * never expire in Redis either.  The survivors keep their arrival order but are renumbered: pass
+ * seq_limit = UINT32_MAX in queries afterwards.  *n_evicted (optional) receives the number of events
+ * dropped.  Like the loads, not concurrent with scoring calls on the same engine.                  */
+int igs_evict_events(igs_engine* e, uint32_t now, uint64_t* n_evicted);
+
 /* ------------------------------------------------------------------------------------------ */
 /* scoring — replaces ScoringEngine.Score (scoring/engine.go:262-323) applied to a batch, i.e.   */
 /* rpc ScoreBatch (proto/risk/v1/risk.proto:13,76-82) and ONNXModel.PredictBatch                 */

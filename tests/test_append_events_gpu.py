@@ -82,3 +82,72 @@ def test_append_errors(engine, pkg):
         assert fresh.get_velocity(q)["n_prior"].tolist() == [1, 0, 0]      # the rejected batch left no trace
         fresh.append_events(pkg.Events(np.array([1], np.uint32), np.array([6], np.uint32), np.array([1], np.int64), np.zeros(1, np.uint8)))
         assert fresh.get_velocity(q)["n_prior"].tolist() == [1, 1, 0]
+
+
+def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg):
+    """igs_evict_events(now) = the TTLs of the Redis keys: what it drops cannot influence any query at
+    t >= now.  History with dormant accounts (dead for more than 7 days), accounts that paused for more than a
+    day and came back, and accounts that never pause; with identifier columns.  Velocity blocks and unique
+    counts at t >= now are bit-identical before / after eviction and equal to the oracle on the FULL history;
+    appends afterwards still behave like the full history."""
+    abi = pkg.abi
+    rng = np.random.default_rng(23)
+    n_acc = 600
+    day = 86400
+    now = synth.T0 + 30 * day
+    rows = []
+    for a in range(n_acc):
+        kind = a % 4
+        if kind == 0:      # dormant: last event more than 7 days before now
+            ts = now - rng.integers(8 * day, 25 * day) - np.sort(rng.integers(0, 2 * day, rng.integers(1, 30)))
+        elif kind == 1:    # old burst, pause of more than a day, recent chain
+            old = now - rng.integers(5 * day, 20 * day) - rng.integers(0, 3600, rng.integers(1, 40))
+            new = now - rng.integers(0, 20 * 3600, rng.integers(1, 40))
+            ts = np.concatenate([old, new])
+        elif kind == 2:    # active every few hours for weeks: one long 24h-gap chain
+            ts = now - np.cumsum(rng.integers(600, 20 * 3600, rng.integers(20, 120)))
+        else:              # last seen 2-6 days ago: chain keys dead, last_tx alive
+            ts = now - rng.integers(2 * day, 6 * day) - rng.integers(0, 7200, rng.integers(1, 10))
+        rows.append((np.full(ts.size, a), ts))
+    acct = np.concatenate([r[0] for r in rows]).astype(np.uint32)
+    ts = np.concatenate([r[1] for r in rows]).astype(np.uint32)
+    perm = rng.permutation(acct.size)
+    acct, ts = acct[perm], ts[perm]
+    n = acct.size
+    ev = pkg.Events(acct, ts, rng.integers(1, 50, n).astype(np.int64) * 100, rng.integers(0, 3, n).astype(np.uint8),
+                    device=rng.integers(0, 6, n).astype(np.uint64), ip=rng.integers(0, 9, n).astype(np.uint64))
+    engine.load_events(ev, n_acc)
+    q = np.zeros(6000, dtype=abi.query_dtype)
+    q["account"] = rng.integers(0, n_acc, q.shape[0])
+    q["ts"] = now + rng.choice([0, 1, 60, 3600, day, 3 * day, 7 * day, 8 * day], q.shape[0]) + rng.integers(0, 100, q.shape[0])
+    q["ts"][:50] = now
+    q["seq_limit"] = abi.SEQ_ALL
+    v0, u0 = engine.get_velocity(q), engine.get_uniques(q)
+    assert v0.tobytes() == orc.velocity_batch(ev, n_acc, q).tobytes()
+    dropped = engine.evict_events(now)
+    assert 0.2 * n < dropped < 0.9 * n, dropped
+    v1, u1 = engine.get_velocity(q), engine.get_uniques(q)
+    same = v0.copy()
+    same["n_prior"] = v1["n_prior"]                       # the number of prior events is the one thing that shrinks
+    assert v1.tobytes() == same.tobytes()
+    assert (v1["n_prior"] <= v0["n_prior"]).all() and (v1["n_prior"] < v0["n_prior"]).any()
+    assert u1.tobytes() == u0.tobytes()
+    assert engine.evict_events(now) == 0                 # idempotent
+    # appends after the eviction: as if nothing had been dropped
+    m = 3000
+    more = pkg.Events(rng.integers(0, n_acc, m).astype(np.uint32), (now + np.sort(rng.integers(0, 3 * day, m))).astype(np.uint32),
+                      rng.integers(1, 50, m).astype(np.int64) * 100, rng.integers(0, 3, m).astype(np.uint8),
+                      device=rng.integers(0, 6, m).astype(np.uint64), ip=rng.integers(0, 9, m).astype(np.uint64))
+    engine.append_events(more)
+    full = pkg.Events(np.concatenate([ev.account, more.account]), np.concatenate([ev.ts, more.ts]),
+                      np.concatenate([ev.amount, more.amount]), np.concatenate([ev.tx_type, more.tx_type]),
+                      device=np.concatenate([ev.device, more.device]), ip=np.concatenate([ev.ip, more.ip]))
+    q2 = q.copy()
+    q2["ts"] = now + 3 * day + rng.integers(0, 5 * day, q.shape[0])
+    want = orc.velocity_batch(full, n_acc, q2)
+    got = engine.get_velocity(q2)
+    want["n_prior"] = got["n_prior"]
+    assert got.tobytes() == want.tobytes()
+    assert engine.get_uniques(q2).tobytes() == orc.uniques_batch(full, n_acc, q2).tobytes()
+    # a later eviction drops the accounts that went quiet meanwhile
+    assert engine.evict_events(now + 20 * day) > 0
