@@ -14,9 +14,10 @@
  *
  * Threading: one engine per device.  Calls on different *slots* of one engine may be issued
  * from different host threads concurrently; calls on the same slot must be serialised by the
- * caller (the synchronous host-buffer calls all use slot 0).  The igs_load_* calls replace device
- * state: like ONNXModel.Close under its write lock (ml/onnx_model.go:349), they must not run while
- * a scoring call on the same engine is in flight.  igs_partition_tx_device keeps its counters in
+ * caller (the synchronous host-buffer calls all use slot 0).  The calls that replace device state —
+ * igs_load_*, igs_append_events*, igs_evict_events, igs_blacklist_load / _add, igs_links_* — are
+ * like ONNXModel.Close under its write lock (ml/onnx_model.go:349): they must not run while a
+ * scoring or query call on the same engine is in flight.  igs_partition_tx_device keeps its counters in
  * one per-engine scratch buffer: issue one partition at a time per engine (or order them on one
  * stream).  igs_last_error returns the engine's single message buffer; read it on the thread
  * that saw the failing status.  Configuration (weights / thresholds) is passed by value with
