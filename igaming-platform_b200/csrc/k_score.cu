@@ -29,9 +29,11 @@
 #include "idset.cuh"
 #include "igs_internal.cuh"
 #include "igs_math.cuh"
+#include "sortscan.cuh"
 #include "velocity.cuh"
 
 #include <stdlib.h>
+#include <algorithm>
 #include <string.h>
 
 namespace {
@@ -70,6 +72,7 @@ struct ScoreParams {
     igs_index_view ix;
     float* features_out;
     igs_velocity* velocity_out;
+    const uint32_t* perm;          // optional: slot -> row, the batch visited in account order (see launch)
     const igs_tx_ids* tx_ids;      // optional: rule 8 evaluated against the blacklist sets
     igs_idset_view bl[3];
     int uniques_from_index;        // the history carries identifiers: ignore the tx's unique counts
@@ -380,8 +383,11 @@ k_score(const __grid_constant__ ScoreParams p) {
     unsigned long long g = 0;
 
     for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const unsigned long long row = tile * kTileTx + threadIdx.x;
-        const bool in_range = row < p.n;
+        const unsigned long long slot = tile * kTileTx + threadIdx.x;
+        const bool in_range = slot < p.n;
+        // path B may visit the batch in account order: neighbouring lanes then gather neighbouring (often the
+        // same) index records.  Every read and write of the row goes through the permutation.
+        const unsigned long long row = (kSrc == kSrcTx && p.perm != nullptr && in_range) ? __ldg(p.perm + slot) : slot;
 
         RuleIn ri;
         if (kSrc == kSrcFeatures) {
@@ -546,6 +552,46 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
     return launch(e, kSrcFeatures, p, leaves, stream);
 }
 
+// ---- account-ordered visiting of large fused batches -----------------------------------------------------
+// The index gathers of the fused path are bound by random 32-byte sector reads.  Visiting the batch in
+// account order makes neighbouring lanes read neighbouring records (the same ones for a hot account): one or
+// three radix passes over (account, row) cost less than they save once the batch is large (1M tx: 1.85 -> 1.76
+// ms including the sort; one pass — locality without adjacency — gains nothing).  The scratch is stream-ordered
+// (cudaMallocAsync), so concurrent calls on different streams do not share it.
+constexpr unsigned long long kVisitSortMin = 262144;
+__global__ void k_visit_keys(const igs_tx* __restrict__ tx, uint32_t n, int drop_bits, uint64_t* __restrict__ keys,
+                             uint32_t* __restrict__ vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = (uint64_t)(__ldg(&tx[i].account) >> drop_bits);
+    vals[i] = i;
+}
+static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, int passes, cudaStream_t stream, void** scratch,
+                       const uint32_t** perm) {
+    const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
+    const size_t hist_elems = (size_t)kSortBins * nb_sort;
+    const size_t b_keys = ((size_t)n * 8 + 255) & ~(size_t)255, b_vals = ((size_t)n * 4 + 255) & ~(size_t)255;
+    const size_t b_hist = (hist_elems * 4 + 255) & ~(size_t)255;
+    const size_t b_scr = (scan_u32_scratch_elems((uint32_t)hist_elems) * 4 + 255) & ~(size_t)255;
+    char* base = nullptr;
+    IGS_CUDA(e, cudaMallocAsync((void**)&base, 2 * b_keys + 2 * b_vals + b_hist + b_scr, stream));
+    *scratch = base;
+    uint64_t* keys[2] = {(uint64_t*)base, (uint64_t*)(base + b_keys)};
+    uint32_t* vals[2] = {(uint32_t*)(base + 2 * b_keys), (uint32_t*)(base + 2 * b_keys + b_vals)};
+    uint32_t* hist = (uint32_t*)(base + 2 * b_keys + 2 * b_vals);
+    uint32_t* scr = (uint32_t*)(base + 2 * b_keys + 2 * b_vals + b_hist);
+    int acct_bits = 1;
+    while (acct_bits < 32 && (e->ev.n_accounts >> acct_bits)) ++acct_bits;
+    const int drop = std::max(0, acct_bits - passes * kSortMaxBits);
+    k_visit_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, stream>>>(d_tx, n, drop, keys[0], vals[0]);
+    IGS_CUDA(e, cudaGetLastError());
+    int cur = 0;
+    const int rc = radix_sort_pairs(e, keys, vals, n, passes, kSortMaxBits, hist, scr, stream, &cur);
+    if (rc != IGS_OK) return rc;
+    *perm = vals[cur];
+    return IGS_OK;
+}
+
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            cudaStream_t stream) {
@@ -565,5 +611,13 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     p.uniques_from_index = e->has_events && e->has_event_ids;
     p.out = d_out;
     p.n = n;
-    return launch(e, kSrcTx, p, false, stream);
+    static const int visit_passes = getenv("IGS_VISIT_SORT_PASSES") ? atoi(getenv("IGS_VISIT_SORT_PASSES")) : 3;   // tuning knob (0 = off)
+    void* scratch = nullptr;
+    if (visit_passes > 0 && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
+        rc = visit_order(e, d_tx, (uint32_t)n, std::min(visit_passes, 4), stream, &scratch, &p.perm);
+        if (rc != IGS_OK) { if (scratch) cudaFreeAsync(scratch, stream); return rc; }
+    }
+    rc = launch(e, kSrcTx, p, false, stream);
+    if (scratch) cudaFreeAsync(scratch, stream);
+    return rc;
 }

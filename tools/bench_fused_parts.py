@@ -31,5 +31,10 @@ for label, load_pl, load_ev in (("nothing_loaded", False, False), ("players_only
     if load_pl: eng.load_players(synth.make_players(n_pl))
     if load_ev: eng.load_events(synth.make_events(n_ev, n_pl), n_pl)
     res[label] = timed(lambda: lib.igs_score_batch_device(eng.handle, C.byref(cfg), d_tx.data_ptr(), n, d_out.data_ptr(), None, None, stream))
+    if load_ev:      # the same batch ordered by account: what an account-sorted batch would buy (locality of the index gathers)
+        d_sorted = torch.from_numpy(tx[np.argsort(tx["account"], kind="stable")].view(np.uint8).reshape(n, -1)).to(dev)
+        res["players_and_events_batch_sorted_by_account"] = timed(lambda: lib.igs_score_batch_device(
+            eng.handle, C.byref(cfg), d_sorted.data_ptr(), n, d_out.data_ptr(), None, None, stream))
+        res["distinct_accounts_in_batch"] = int(np.unique(tx["account"]).size)
     eng.close()
 print(json.dumps(res))
