@@ -222,3 +222,60 @@ def test_fused_path_with_identifiers_matches_oracle(clean_engine, orc, pkg, kind
     want2 = orc.score_batch_ids(cfg, model, players, ev, tx)
     assert got2.tobytes() == want2.tobytes()
     assert (got2["flags"] & abi.R_KNOWN_FRAUDSTER != 0).sum() < (got["flags"] & abi.R_KNOWN_FRAUDSTER != 0).sum()
+
+
+def test_large_batch_is_visited_in_account_order_with_identical_results(clean_engine, orc, pkg):
+    """Batches of >= 262 144 tx go through the device-side account sort + row permutation: results, assembled
+    features and velocity blocks must land in the caller's row order, bit-identical to the oracle (and to the
+    same rows scored in a small, unsorted batch)."""
+    abi = pkg.abi
+    n_players, n_events, n = 4000, 60000, 300_000
+    now = synth.T0 + 12 * 3600
+    players = synth.make_players(n_players, seed=61, now=now)
+    ev = synth.make_event_ids(synth.make_events(n_events, n_players, seed=62, span=12 * 3600), seed=63)
+    tx = synth.make_tx(n, n_players, seed=64, t_lo=synth.T0 + 3600, t_hi=now, invalid_rate=0.01)
+    tx["account"][::4999] = n_players + 7                    # beyond the tables
+    rng = np.random.default_rng(65)
+    ids = np.zeros(n, dtype=abi.tx_ids_dtype)
+    ids["device"] = ev.device[rng.integers(0, n_events, n)]
+    ids["fingerprint"] = rng.integers(1, 3000, n).astype(np.uint64)
+    ids["ip"] = ev.ip[rng.integers(0, n_events, n)]
+    bl_fp = np.arange(1, 40, dtype=np.uint64)
+    clean_engine.load_players(players)
+    clean_engine.load_events(ev, n_players)
+    clean_engine.blacklist_load(abi.BL_FINGERPRINT, bl_fp)
+    model = synth.make_gbdt(n_trees=40, seed=66)
+    clean_engine.load_gbdt(model)
+    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    # device-buffer entry point: the whole batch in one launch (the host-buffer call would cut it into chunks
+    # below the sorting threshold)
+    import ctypes as C
+    import torch
+    lib = abi.load_library()
+    dev = torch.device("cuda", 0)
+    d_tx = torch.from_numpy(tx.view(np.uint8).reshape(n, -1)).to(dev)
+    d_ids = torch.from_numpy(ids.view(np.uint8).reshape(n, -1)).to(dev)
+    d_out = torch.zeros((n, 8), dtype=torch.uint8, device=dev)
+    d_f = torch.zeros((n, abi.NUM_FEATURES), dtype=torch.float32, device=dev)
+    d_v = torch.zeros((n, 128), dtype=torch.uint8, device=dev)
+    st = lib.igs_score_batch_ids_device(clean_engine.handle, C.byref(cfg), d_tx.data_ptr(), d_ids.data_ptr(), n,
+                                        d_out.data_ptr(), d_f.data_ptr(), d_v.data_ptr(),
+                                        torch.cuda.current_stream().cuda_stream)
+    assert st == 0, lib.igs_last_error(clean_engine.handle).decode()
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy().view(abi.result_dtype).reshape(n)
+    gf = d_f.cpu().numpy()
+    gv = d_v.cpu().numpy().view(abi.velocity_dtype).reshape(n)
+    # oracle on a sample of rows (the oracle scores a row from the row alone, so a sub-batch is a fair check)
+    pick = np.sort(rng.choice(n, 6000, replace=False))
+    bl, keep = orc.make_blacklist(None, bl_fp, None)
+    want, wf = orc.score_batch_ids(cfg, model, players, ev, tx[pick], bl=bl, tx_ids=ids[pick], want_features=True)
+    assert got[pick].tobytes() == want.tobytes()
+    assert np.array_equal(gf[pick].view(np.uint32), wf.view(np.uint32))
+    # every row against the unsorted small-batch path of the library itself
+    for a in range(0, n, 100_000):
+        small, sf, sv = clean_engine.score_batch(cfg, tx[a:a + 100_000], want_features=True, want_velocity=True,
+                                                 ids=ids[a:a + 100_000])
+        assert got[a:a + 100_000].tobytes() == small.tobytes()
+        assert gv[a:a + 100_000].tobytes() == sv.tobytes()
+        assert np.array_equal(gf[a:a + 100_000].view(np.uint32), sf.view(np.uint32))
