@@ -158,6 +158,7 @@ __device__ __forceinline__ void ltv_epilogue(const igs_ltv_row& f, double ltv, i
 // GEMM layer
 // ------------------------------------------------------------------------------------------------
 constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 4;
+constexpr uint32_t kSwizzleBytes = BK * 2;          // one k-block row = one swizzle atom row (64 or 128 bytes)
 constexpr int kNonEpiWarps = 4;   // TMA producer, MMA issuer, TMEM allocator, spare
 constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
 constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
@@ -172,7 +173,7 @@ constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN 
 // between 8-row groups, descriptor version 1 (sm_100), layout type 2
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
     const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
-    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    const uint32_t hi = ((8u * kSwizzleBytes) >> 4) | (1u << 14) | ((kSwizzleBytes == 128 ? 2u : 4u) << 29);
     return ((uint64_t)hi << 32) | lo;
 }
 
@@ -389,7 +390,8 @@ int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, ui
     const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, kSwizzleBytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         igs_set_error(e, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
