@@ -5,13 +5,14 @@
 // k_mlp_gemm — one layer, out[M,N] = relu(A[M,K] * W[N,K]^T + bias) rounded to bf16.
 //   Persistent, one CTA per SM, 128 x 256 output tiles, warp-specialised:
 //     warp 0 (one lane)  TMA producer: cp.async.bulk.tensor 2D loads of the A (128 x 64) and W
-//                        (256 x 64) k-blocks into a 4-stage 128B-swizzled smem ring (SASS UTMALDG)
+//                        (256 x 64) k-blocks into a 3-stage 128B-swizzled smem ring (SASS UTMALDG)
 //     warp 1 (one lane)  MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M=128 N=256 K=16, smem
 //                        descriptors advanced 32 B per K step, accumulators in TMEM (2 x 256 columns,
 //                        double buffered so the epilogue of tile i overlaps the MMAs of tile i+1);
 //                        tcgen05.commit releases smem stages / publishes the accumulator (SASS UTCHMMA)
 //     warp 2             TMEM allocation (512 columns) and release
-//     warps 4-7          epilogue: tcgen05.ld 32x32b.x32 (SASS LDTM) -> +bias, ReLU, bf16 -> global
+//     warps 4-7 (4-11)   epilogue: tcgen05.ld 32x32b.x32 (SASS LDTM) -> +bias, ReLU, bf16 -> swizzled smem
+//                        staging -> cp.async.bulk.tensor store of 64-column x 32-row boxes (SASS UTMASTG)
 //   Synchronisation is mbarrier-only inside the tile loop (full/empty per smem stage, full/empty per
 //   TMEM accumulator).
 //   Layer 3 runs the kHead variant: a CTA owns whole 128-row tiles and walks their 4 column tiles in order;
@@ -61,6 +62,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
         ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tm), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -157,14 +167,19 @@ __device__ __forceinline__ void ltv_epilogue(const igs_ltv_row& f, double ltv, i
 // ------------------------------------------------------------------------------------------------
 // GEMM layer
 // ------------------------------------------------------------------------------------------------
-constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 4;
+constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16, STAGES = 3;
 constexpr uint32_t kSwizzleBytes = BK * 2;          // one k-block row = one swizzle atom row (64 or 128 bytes)
 constexpr int kNonEpiWarps = 4;   // TMA producer, MMA issuer, TMEM allocator, spare
 constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
 constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
 constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kTmemCols = 512;           // 2 accumulators x 256 fp32 columns
-constexpr uint32_t kGemmSmem = STAGES * kStageBytes + 1024 /* alignment slack */ + 256 /* barriers */ +
+// output staging for the TMA store: the bf16 tile as 64-column x 32-row boxes (4 KB, 128B-swizzled), one set per
+// epilogue warp — 128 x 256 x 2 B = 64 KB.  (Three smem stages feed the MMAs as well as four did: the fourth
+// stage's 48 KB went here.)
+constexpr uint32_t kOutBoxCols = 64, kOutBoxRows = 32, kOutBoxBytes = kOutBoxCols * kOutBoxRows * 2;
+constexpr uint32_t kOutStageBytes = BM * BN * 2;
+constexpr uint32_t kGemmSmem = STAGES * kStageBytes + kOutStageBytes + 1024 /* alignment slack */ + 256 /* barriers */ +
                                4096 /* w4 as fp32 */ + 4096 /* bias */;
 // instruction descriptor, kind::f16: D=F32 (bit 4), A=BF16 (bit 7), B=BF16 (bit 10), both K-major,
 // N>>3 at bit 17, M>>4 at bit 24
@@ -180,6 +195,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
 struct GemmParams {
     CUtensorMap tm_a;     // A  [M, K] bf16, K contiguous; box 64 x 128
     CUtensorMap tm_b;     // W  [N, K] bf16, K contiguous; box 64 x 256
+    CUtensorMap tm_out;   // out [M, N] bf16; box 64 x 32 (store)
     const float* bias;    // [N]
     uint16_t* out;        // [M, N] bf16 (null when the head is fused and nobody wants the activations)
     uint32_t M, N, K;
@@ -210,13 +226,14 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
     uint8_t* smem = smem_raw + (base - raw);
     const uint32_t a_base = base;
     const uint32_t b_base = base + STAGES * kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+    const uint32_t out_base = base + STAGES * kStageBytes;          // 1024-aligned: stages are multiples of 1 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes + kOutStageBytes);
     const uint32_t bar_full = smem_u32(bars);             // [STAGES]
     const uint32_t bar_empty = bar_full + 8 * STAGES;     // [STAGES]
     const uint32_t bar_tfull = bar_empty + 8 * STAGES;    // [2]
     const uint32_t bar_tempty = bar_tfull + 16;           // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-    float* w4s = reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256);
+    float* w4s = reinterpret_cast<float*>(smem + STAGES * kStageBytes + kOutStageBytes + 256);
     float* bias_s = w4s + IGS_MLP_HIDDEN;
     if (kHead)
         for (int i = threadIdx.x; i < IGS_MLP_HIDDEN; i += kGemmThreads) w4s[i] = bf16_bits_to_f32(__ldg(p.w4 + i));
@@ -300,7 +317,13 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
             tc_fence_after();
             const uint32_t row = m0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-            uint16_t* orow = p.out ? p.out + (size_t)row * p.N + n0 : nullptr;
+            // this warp's staging: kCols / 64 boxes of 32 rows x 64 columns
+            const uint32_t my_out = out_base + (uint32_t)(warp - kNonEpiWarps) * (kCols / kOutBoxCols) * kOutBoxBytes;
+            const bool store = p.out != nullptr;
+            if (store) {                                                   // the previous tile's store has read the staging
+                if (lane == 0) bulk_wait_read0();
+                __syncwarp();
+            }
 #pragma unroll 1
             for (int c = c0; c < c0 + kCols; c += 32) {
                 uint32_t r[32];
@@ -321,16 +344,33 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
                         dot = __fmaf_rn(bf16_bits_to_f32(packed[j] >> 16), w4s[n0 + c + 2 * j + 1], dot);
                     }
                 }
-                if (orow && row < p.M) {
-                    uint4* dst = reinterpret_cast<uint4*>(orow + c);
+                if (store) {
+                    // row `lane` of box (c - c0) / 64, 16-byte chunks (c % 64) / 8 .. +3, 128B swizzle: chunk ^ (row & 7)
+                    const uint32_t box = my_out + (uint32_t)((c - c0) / (int)kOutBoxCols) * kOutBoxBytes + (uint32_t)lane * 128u;
+                    const uint32_t j0 = (uint32_t)(c % (int)kOutBoxCols) / 8u;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+                    for (uint32_t j = 0; j < 4; ++j) {
+                        const uint32_t addr = box + (((j0 + j) ^ ((uint32_t)lane & 7u)) << 4);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(packed[4 * j]),
+                                     "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
+                                     : "memory");
+                    }
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+            if (store) {                                                   // whole lines to global, off the LSU path
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+#pragma unroll
+                    for (int b = 0; b < kCols / (int)kOutBoxCols; ++b)
+                        tma_store_2d(&p.tm_out, my_out + (uint32_t)b * kOutBoxBytes, (int)(n0 + c0 + b * (int)kOutBoxCols),
+                                     (int)(m0 + q * 32));
+                    bulk_commit();
+                }
+            }
             if (kHead && (t % n_blks) == n_blks - 1) {                        // row complete: model output + epilogue
                 if (row < p.M) {
                     const float y = __fadd_rn(dot, p.b4);
@@ -344,6 +384,7 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
             }
         }
     }
+    if (warp >= kNonEpiWarps && lane == 0) bulk_wait0();                   // outstanding output stores
     tc_fence_before();
     __syncthreads();
     if (warp == 2) {
@@ -379,7 +420,9 @@ EncodeTiledFn get_encode_fn() {
 }
 
 // 2D bf16 row-major [rows, cols] tensor map with a (64 x box_rows) box and 128B swizzle
-int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows,
+              uint32_t box_cols = BK, CUtensorMapSwizzle swz = kSwizzleBytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                                                                     : CU_TENSOR_MAP_SWIZZLE_64B) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) {
         igs_set_error(e, "cuTensorMapEncodeTiled is not available from the driver");
@@ -387,10 +430,10 @@ int make_tmap(igs_engine* e, CUtensorMap* tm, const void* ptr, uint64_t rows, ui
     }
     const cuuint64_t gdim[2] = {cols, rows};
     const cuuint64_t gstride[1] = {cols * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+    const cuuint32_t box[2] = {(cuuint32_t)box_cols, box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, kSwizzleBytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -416,6 +459,10 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
     if (rc != IGS_OK) return rc;
     rc = make_tmap(e, &p.tm_b, w, N, K, BN);
     if (rc != IGS_OK) return rc;
+    if (out) {
+        rc = make_tmap(e, &p.tm_out, out, M, N, kOutBoxRows, kOutBoxCols, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != IGS_OK) return rc;
+    }
     p.bias = bias; p.out = out; p.M = M; p.N = N; p.K = K;
     if (head) { p.w4 = head->w4; p.b4 = head->b4; p.rows = head->rows; p.res = head->res; p.raw = head->raw; }
     // the short-K layer gets 8 epilogue warps; long-K layers hide a 4-warp epilogue behind their MMAs
