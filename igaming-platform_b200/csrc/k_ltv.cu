@@ -487,7 +487,8 @@ constexpr uint64_t kLtvChunkRows = 256 * 1024;   // 512 MB of bf16 activations p
 int launch_fused(igs_engine* e, MlpDevice* m, const uint16_t* d_x, const igs_ltv_row* d_rows, uint32_t n,
                  igs_ltv_result* d_out, float* d_raw, cudaStream_t st) {
     const uint32_t H = IGS_MLP_HIDDEN;
-    const uint32_t m_blks = (n + BM - 1) / BM, n_pairs = (m_blks + 1) / 2;
+    static const bool single = getenv("IGS_MLP_FUSED") && atoi(getenv("IGS_MLP_FUSED")) == 2;
+    const uint32_t m_blks = (n + BM - 1) / BM, n_pairs = single ? m_blks : (m_blks + 1) / 2;
     const uint32_t grid = n_pairs < (uint32_t)e->sm_count ? n_pairs : (uint32_t)e->sm_count;
     const uint64_t scratch_rows = (uint64_t)e->sm_count * 3 * BM;
     int rc = igs_reserve(e, &m->scratch, scratch_rows * H * 2);
@@ -502,7 +503,7 @@ int launch_fused(igs_engine* e, MlpDevice* m, const uint16_t* d_x, const igs_ltv
     if ((rc = make_tmap(e, &p.tm_s_st, m->scratch.p, scratch_rows, H, kOutBoxRows, kOutBoxCols,
                         CU_TENSOR_MAP_SWIZZLE_128B)) != IGS_OK) return rc;
     p.bias[0] = m->b1; p.bias[1] = m->b2; p.bias[2] = m->b3;
-    p.w4 = m->w4; p.b4 = m->b4; p.M = n; p.rows = d_rows; p.res = d_out; p.raw = d_raw;
+    p.w4 = m->w4; p.b4 = m->b4; p.M = n; p.single = single ? 1u : 0u; p.rows = d_rows; p.res = d_out; p.raw = d_raw;
     IGS_CUDA(e, cudaFuncSetAttribute(k_mlp_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
     k_mlp_fused<<<grid, kFusedThreads, kFusedSmem, st>>>(p);
     IGS_CUDA(e, cudaGetLastError());

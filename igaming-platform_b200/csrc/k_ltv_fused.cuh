@@ -29,6 +29,7 @@ struct FusedParams {
     const uint16_t* w4;
     float b4;
     uint32_t M;
+    uint32_t single;         // 1: groups of one row tile (consumer phase follows its producer directly)
     const igs_ltv_row* rows;
     igs_ltv_result* res;
     float* raw;
@@ -80,10 +81,14 @@ k_mlp_fused(const __grid_constant__ FusedParams p) {
     const uint32_t tmem_base = *tmem_slot;
 
     const uint32_t m_blks = (p.M + BM - 1) / BM;
-    const uint32_t n_pairs = (m_blks + 1) / 2;
+    const uint32_t n_pairs = p.single ? m_blks : (m_blks + 1) / 2;
     const uint32_t my_pairs = n_pairs > blockIdx.x ? (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     // row tile of (pair i of this CTA, phase ph); >= m_blks: the pair's second tile does not exist
-    auto tile_of = [&](uint32_t i, int ph) -> uint32_t { return (blockIdx.x + i * gridDim.x) * 2 + (uint32_t)(ph & 1); };
+    auto tile_of = [&](uint32_t i, int ph) -> uint32_t {
+        const uint32_t g = blockIdx.x + i * gridDim.x;
+        if (p.single) return (ph & 1) ? m_blks : g;          // one row tile per group: the B phases do not exist
+        return g * 2 + (uint32_t)(ph & 1);
+    };
     const int scratch_row0 = (int)(blockIdx.x * 3 * BM);   // this CTA's X, Y, Z in the scratch tensor
 
     if (warp == 0) {
