@@ -7,6 +7,8 @@ compute path is the CUDA library: importing works anywhere, creating an Engine n
 from __future__ import annotations
 
 import ctypes as C
+import functools
+import threading
 from dataclasses import dataclass
 
 import numpy as np
@@ -128,6 +130,10 @@ class Engine:
         self._h = h
         self.device = device
         self._n_trees = 0
+        # The synchronous host-buffer calls all stage through slot 0 and the loads replace device state
+        # (include/igs.h, Threading): ctypes drops the GIL during a call, so a multi-threaded host (the gRPC
+        # shim's worker pool) must not let two of them overlap.  They are serialised here.
+        self._lock = threading.RLock()
 
     # -- life cycle ---------------------------------------------------------------------------
     def close(self) -> None:
@@ -186,6 +192,17 @@ class Engine:
             self._check(self._lib.igs_append_events_ids(self._h, C.byref(c), C.byref(i), len(ev)))
         else:
             self._check(self._lib.igs_append_events(self._h, C.byref(c), len(ev)))
+
+    def set_late_policy(self, policy: int) -> None:
+        """abi.LATE_REJECT (default): igs_append_events refuses batches with late events; abi.LATE_REORDER accepts
+        them and orders by timestamp (see include/igs.h, LATE EVENTS)."""
+        self._check(self._lib.igs_set_late_policy(self._h, policy))
+
+    def history_info(self) -> dict:
+        info = abi.HistoryInfo()
+        self._check(self._lib.igs_get_history_info(self._h, C.byref(info)))
+        return {"n_events": int(info.n_events), "late_events": int(info.late_events),
+                "n_accounts": int(info.n_accounts), "has_identifiers": bool(info.has_identifiers)}
 
     def evict_events(self, now: int) -> int:
         """igs_evict_events: drop what can no longer influence a query at t >= now; -> events dropped."""
@@ -351,8 +368,42 @@ class Engine:
                                             abi.ptr(out), abi.ptr(raw)))
         return (out, raw) if want_raw else out
 
+    def ltv_predict_batch(self, rows: np.ndarray, want_raw: bool = False):
+        """LTVPredictor.BatchPredict (prediction/ltv.go:385-398) with the reference's own calculateLTV."""
+        rows = np.ascontiguousarray(rows, dtype=abi.ltv_row_dtype)
+        n = rows.shape[0]
+        out = np.zeros(n, dtype=abi.ltv_result_dtype)
+        raw = np.zeros(n, dtype=np.float64) if want_raw else None
+        self._check(self._lib.igs_ltv_predict_batch(self._h, abi.ptr(rows), n, abi.ptr(out), abi.ptr(raw)))
+        return (out, raw) if want_raw else out
+
+    def ltv_mock_predict(self, feats: np.ndarray) -> np.ndarray:
+        """ml.LTVModel.Predict (ml/onnx_model.go:405-432) per ml.LTVFeatures row."""
+        feats = np.ascontiguousarray(feats, dtype=abi.ltv_features_dtype)
+        out = np.zeros(feats.shape[0], dtype=np.float64)
+        self._check(self._lib.igs_ltv_mock_predict(self._h, abi.ptr(feats), feats.shape[0], abi.ptr(out)))
+        return out
+
     def ltv_hidden_device(self, d_x: int, n: int, layer: int, d_hidden: int, stream: int = 0) -> None:
         self._check(self._lib.igs_ltv_hidden_device(self._h, d_x, n, layer, d_hidden, stream))
+
+
+def _serialised(fn):
+    @functools.wraps(fn)
+    def call(self, *a, **k):
+        with self._lock:
+            return fn(self, *a, **k)
+    return call
+
+
+# every method that uses slot 0's staging or replaces device state; the *_device methods are ordered by the
+# caller's streams and stay lock-free
+for _name in ("load_gbdt", "load_mlp", "load_players", "load_events", "append_events", "set_late_policy",
+              "history_info", "evict_events", "get_uniques", "blacklist_load", "blacklist_add", "blacklist_check",
+              "links_pairs", "links_group", "links_finish", "get_links", "check_bonus_abuse", "score_features",
+              "get_velocity", "score_batch", "ltv_batch", "ltv_predict_batch", "ltv_mock_predict"):
+    setattr(Engine, _name, _serialised(getattr(Engine, _name)))
+del _name
 
 
 def hash_id(s: str | bytes) -> int:

@@ -44,6 +44,7 @@ SEG_VIP, SEG_HIGH, SEG_MEDIUM, SEG_LOW, SEG_CHURNING = 1, 2, 3, 4, 5
 SEQ_ALL = 0xFFFFFFFF
 PARTITION_STATIC_WORDS = 256 * 1024
 BL_DEVICE, BL_FINGERPRINT, BL_IP = 0, 1, 2
+LATE_REJECT, LATE_REORDER = 0, 1
 LINK_MAX_ACCOUNTS = 64
 IPC_HANDLE_BYTES = 64
 ABUSE_BONUS_ONLY, ABUSE_MULTI_ACCOUNT, ABUSE_ACCOUNT_RING = 1, 2, 4
@@ -94,6 +95,14 @@ ltv_result_dtype = np.dtype([
     ("segment", "u1"), ("next_best_action", "u1"), ("pad", "u1", (6,)),
 ])
 
+# ml.LTVFeatures, ml/onnx_model.go:375-393 (declaration order)
+ltv_features_dtype = np.dtype([(k, "<f4") for k in (
+    "days_since_registration", "days_since_last_deposit", "days_since_last_bet", "total_active_days",
+    "sessions_per_week", "total_deposits", "total_withdrawals", "net_revenue", "avg_deposit_amount",
+    "deposit_frequency", "total_bets", "bet_count", "win_rate", "avg_bet_size", "games_played",
+    "bonuses_claimed", "bonus_conversion_rate")])
+
+assert ltv_features_dtype.itemsize == 68
 assert rule_row_dtype.itemsize == 48
 assert result_dtype.itemsize == 8
 assert tx_dtype.itemsize == 32
@@ -142,7 +151,12 @@ class EventIds(C.Structure):
     _fields_ = [("device", C.c_void_p), ("ip", C.c_void_p)]
 
 
-assert C.sizeof(Config) == 104
+class HistoryInfo(C.Structure):
+    _fields_ = [("n_events", C.c_uint64), ("late_events", C.c_uint64), ("n_accounts", C.c_uint32),
+                ("has_identifiers", C.c_uint32), ("reserved", C.c_uint64 * 4)]
+
+
+assert C.sizeof(Config) == 104 and C.sizeof(HistoryInfo) == 56
 
 # Every symbol include/igs.h declares; tests check the built library exports each of them.
 EXPORTS = [
@@ -161,6 +175,8 @@ EXPORTS = [
     "igs_abuse_signals", "igs_links_window_create", "igs_links_window_open", "igs_links_window_attach",
     "igs_links_window_reset", "igs_links_pairs_peer", "igs_links_group_peer", "igs_links_finish_peer",
     "igs_evict_events",
+    "igs_set_late_policy", "igs_get_history_info",
+    "igs_ltv_predict_batch", "igs_ltv_predict_batch_device", "igs_ltv_mock_predict", "igs_ltv_mock_predict_device",
 ]
 
 LIB_NAME = "libigs.so"
@@ -249,6 +265,12 @@ def load_library() -> C.CDLL:
     lib.igs_links_pairs_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.igs_links_group_peer.argtypes = [vp, C.c_uint32, C.c_uint32]
     lib.igs_links_finish_peer.argtypes = [vp, C.c_uint32]
+    lib.igs_ltv_predict_batch.argtypes = [vp, vp, u64, vp, vp]
+    lib.igs_ltv_predict_batch_device.argtypes = [vp, vp, u64, vp, vp, vp]
+    lib.igs_ltv_mock_predict.argtypes = [vp, vp, u64, vp]
+    lib.igs_ltv_mock_predict_device.argtypes = [vp, vp, u64, vp, vp]
+    lib.igs_set_late_policy.argtypes = [vp, i32]
+    lib.igs_get_history_info.argtypes = [vp, C.POINTER(HistoryInfo)]
     lib.igs_evict_events.argtypes = [vp, C.c_uint32, C.POINTER(u64)]
     lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
     lib.igs_hash_id.restype = u64

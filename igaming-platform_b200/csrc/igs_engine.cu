@@ -289,6 +289,27 @@ int igs_evict_events(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
     return igs_evict_event_history(e, now, n_evicted);
 }
 
+int igs_set_late_policy(igs_engine* e, int policy) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, policy == IGS_LATE_REJECT || policy == IGS_LATE_REORDER, "policy must be IGS_LATE_REJECT or IGS_LATE_REORDER");
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->late_policy = policy;
+    return IGS_OK;
+}
+
+int igs_get_history_info(igs_engine* e, igs_history_info* out) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, out != nullptr, "out is null");
+    std::lock_guard<std::mutex> lk(e->mu);
+    memset(out, 0, sizeof(*out));
+    if (!e->has_events) return IGS_OK;
+    out->n_events = e->n_raw;
+    out->late_events = e->late_events;
+    out->n_accounts = e->ev.n_accounts;
+    out->has_identifiers = e->has_event_ids ? 1u : 0u;
+    return IGS_OK;
+}
+
 static int blacklist_update(igs_engine* e, int kind, const uint64_t* ids, uint64_t n, bool replace) {
     IGS_ENGINE(e);
     if (kind != IGS_BL_DEVICE && kind != IGS_BL_FINGERPRINT && kind != IGS_BL_IP) {
@@ -330,14 +351,35 @@ static int run_pipelined(igs_engine* e, igs_slot& sl, uint64_t n, Body&& body /*
     if (n <= 2 * kPipeChunkRows) return body(sl.stream, (uint64_t)0, n);
     IGS_CUDA(e, cudaEventRecord(sl.ev_fork, sl.stream));
     for (int k = 0; k < IGS_PIPE_STREAMS; ++k) IGS_CUDA(e, cudaStreamWaitEvent(sl.pipe[k], sl.ev_fork, 0));
-    int k = 0;
-    for (uint64_t off = 0; off < n; off += kPipeChunkRows, k = (k + 1) % IGS_PIPE_STREAMS) {
+    int k = 0, rc = IGS_OK;
+    for (uint64_t off = 0; off < n && rc == IGS_OK; off += kPipeChunkRows, k = (k + 1) % IGS_PIPE_STREAMS) {
         const uint64_t cnt = std::min(kPipeChunkRows, n - off);
-        IGS_TRY(body(sl.pipe[k], off, cnt));
+        rc = body(sl.pipe[k], off, cnt);
     }
+    // Join the workers into the slot's stream whether or not a chunk failed: chunks already queued keep copying
+    // into the caller's buffers, and igs_wait / the synchronous wrappers must cover them.
     for (int j = 0; j < IGS_PIPE_STREAMS; ++j) {
-        IGS_CUDA(e, cudaEventRecord(sl.ev_join[j], sl.pipe[j]));
-        IGS_CUDA(e, cudaStreamWaitEvent(sl.stream, sl.ev_join[j], 0));
+        const cudaError_t a = cudaEventRecord(sl.ev_join[j], sl.pipe[j]);
+        const cudaError_t b = a == cudaSuccess ? cudaStreamWaitEvent(sl.stream, sl.ev_join[j], 0) : a;
+        if (b != cudaSuccess) {
+            cudaStreamSynchronize(sl.pipe[j]);          // could not order it: wait for it here
+            if (rc == IGS_OK) {
+                igs_set_error(e, "joining the chunk pipeline failed: %s", cudaGetErrorString(b));
+                rc = IGS_ERR_CUDA;
+            }
+        }
+    }
+    return rc;
+}
+
+// Synchronous wrappers: wait for the slot's stream even when queueing failed half way, so that nothing is still
+// writing into the caller's buffers when the call returns; the first error wins.
+static int finish_sync(igs_engine* e, int slot, int rc) {
+    const cudaError_t st = cudaStreamSynchronize(e->slot[slot].stream);
+    if (rc != IGS_OK) return rc;
+    if (st != cudaSuccess) {
+        igs_set_error(e, "cudaStreamSynchronize failed: %s", cudaGetErrorString(st));
+        return IGS_ERR_CUDA;
     }
     return IGS_OK;
 }
@@ -386,9 +428,7 @@ static int score_features_host(igs_engine* e, int s, const igs_config* cfg, cons
 int igs_score_features(igs_engine* e, const igs_config* cfg, const float* features,
                        const igs_rule_row* rows, uint64_t n, igs_result* out, uint8_t* leaf_idx) {
     IGS_ENGINE(e);
-    IGS_TRY(score_features_host(e, 0, cfg, features, rows, n, out, leaf_idx));
-    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
-    return IGS_OK;
+    return finish_sync(e, 0, score_features_host(e, 0, cfg, features, rows, n, out, leaf_idx));
 }
 
 int igs_score_features_async(igs_engine* e, int slot, const igs_config* cfg, const float* features,
@@ -477,9 +517,7 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
 int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n, igs_result* out,
                     float* features_out, igs_velocity* velocity_out) {
     IGS_ENGINE(e);
-    IGS_TRY(score_batch_host(e, 0, cfg, tx, nullptr, n, out, features_out, velocity_out));
-    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
-    return IGS_OK;
+    return finish_sync(e, 0, score_batch_host(e, 0, cfg, tx, nullptr, n, out, features_out, velocity_out));
 }
 
 int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const igs_tx* tx, uint64_t n,
@@ -503,9 +541,7 @@ int igs_score_batch_ids(igs_engine* e, const igs_config* cfg, const igs_tx* tx, 
                         igs_result* out, float* features_out, igs_velocity* velocity_out) {
     IGS_ENGINE(e);
     IGS_REQUIRE(e, n == 0 || ids != nullptr, "ids is null");
-    IGS_TRY(score_batch_host(e, 0, cfg, tx, ids, n, out, features_out, velocity_out));
-    IGS_CUDA(e, cudaStreamSynchronize(e->slot[0].stream));
-    return IGS_OK;
+    return finish_sync(e, 0, score_batch_host(e, 0, cfg, tx, ids, n, out, features_out, velocity_out));
 }
 
 int igs_score_batch_ids_device(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,

@@ -109,6 +109,8 @@ struct igs_engine {
     igs_event_index ev;
     bool has_events = false;
     std::vector<igs_buf> build_pool;  // scratch of the index build, kept between igs_append_events calls
+    int      late_policy = IGS_LATE_REJECT;   // igs_set_late_policy
+    uint64_t late_events = 0;                 // late pairs in the resident history (igs_history_info)
 
     // blacklist sets (idset.cuh / k_ids.cu), indexed by IGS_BL_*
     igs_idset bl[3];

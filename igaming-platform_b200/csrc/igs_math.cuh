@@ -96,10 +96,13 @@ __device__ __forceinline__ void igs_blend(const igs_config& c, int rule_score, u
     double s = __dadd_rn(a, b);
     long long fs = __double2ll_rz(s);
     if (fs > 100) fs = 100;                                                        // :297-299
+    // The reference would return a negative int for a negative blend (negative weights): below every
+    // threshold, i.e. approve.  The result byte cannot hold it; the action is taken first, then the score is
+    // clamped at 0.
     int action = fs >= c.block_threshold ? IGS_ACTION_BLOCK
                : fs >= c.review_threshold ? IGS_ACTION_REVIEW : IGS_ACTION_APPROVE; // :303-310
     out->ml_score = (float)ml;
     out->flags = (uint16_t)fl;
-    out->score = (uint8_t)fs;
+    out->score = (uint8_t)(fs < 0 ? 0 : fs);
     out->action = (uint8_t)action;
 }

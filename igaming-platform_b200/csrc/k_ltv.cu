@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "igs_internal.cuh"
+#include "ltv_math.cuh"
 
 namespace {
 
@@ -99,71 +100,7 @@ __device__ __forceinline__ void tc_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[3
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// ------------------------------------------------------------------------------------------------
-// fp64 epilogue helpers (prediction/ltv.go)
-// ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float bf16_bits_to_f32(uint32_t b) { return __uint_as_float(b << 16); }
-
-// calculateEngagementScore, prediction/ltv.go:181-225
-__device__ __forceinline__ double ltv_engagement(const igs_ltv_row& f) {
-    double s = 0.0;
-    if (f.days_since_last_bet < 3) s += 0.3; else if (f.days_since_last_bet < 7) s += 0.2;
-    else if (f.days_since_last_bet < 14) s += 0.1;
-    if (f.sessions_per_week >= 5) s += 0.2; else if (f.sessions_per_week >= 3) s += 0.15;
-    else if (f.sessions_per_week >= 1) s += 0.1;
-    if (f.deposit_frequency >= 4) s += 0.2; else if (f.deposit_frequency >= 2) s += 0.15;
-    else if (f.deposit_frequency >= 1) s += 0.1;
-    if (f.push_enabled) s += 0.1;
-    if (f.email_opt_in) s += 0.1;
-    if (f.has_vip_manager) s += 0.1;
-    return s < 1.0 ? s : 1.0;
-}
-// calculateChurnRisk, :228-262
-__device__ __forceinline__ double ltv_churn(const igs_ltv_row& f) {
-    double r = 0.0;
-    if (f.days_since_last_bet > 30) r += 0.5; else if (f.days_since_last_bet > 14) r += 0.3;
-    else if (f.days_since_last_bet > 7) r += 0.15;
-    if (f.sessions_per_week < 1 && f.days_since_registration > 30) r += 0.2;
-    if (f.days_since_last_deposit > 30) r += 0.2;
-    if (f.support_tickets > 3) r += 0.1;
-    if (f.total_withdrawals > f.total_deposits) r += 0.1;
-    return r < 1.0 ? r : 1.0;
-}
-// Predict after the model output, :124-139 (+ :265-382)
-__device__ __forceinline__ void ltv_epilogue(const igs_ltv_row& f, double ltv, igs_ltv_result* out) {
-    const double churn = ltv_churn(f);
-    const double adjusted = __dmul_rn(ltv, __dsub_rn(1.0, __dmul_rn(churn, 0.5)));          // :127
-    int seg;
-    if (churn > 0.7) seg = IGS_SEG_CHURNING;                                                // :267
-    else if (adjusted >= 10000) seg = IGS_SEG_VIP;
-    else if (adjusted >= 1000) seg = IGS_SEG_HIGH;
-    else if (adjusted >= 100) seg = IGS_SEG_MEDIUM;
-    else seg = IGS_SEG_LOW;
-    double surv = __dmul_rn(__dmul_rn(90.0, __dadd_rn(1.0, ltv_engagement(f))), __dsub_rn(1.0, churn));  // :286-294
-    if (!(surv > 0)) surv = 0;
-    int act = 0;                                                                            // :300-343
-    switch (seg) {
-    case IGS_SEG_CHURNING: act = f.net_revenue > 0 ? 1 : 2; break;
-    case IGS_SEG_VIP: act = f.days_since_last_deposit > 7 ? 3 : 4; break;
-    case IGS_SEG_HIGH: act = !f.has_vip_manager ? 5 : (churn > 0.3 ? 6 : 7); break;
-    case IGS_SEG_MEDIUM: act = f.bonuses_claimed < 3 ? 8 : (f.games_played < 5 ? 9 : 10); break;
-    case IGS_SEG_LOW: act = f.days_since_registration < 7 ? 11 : (f.bonus_conversion_rate > 0.8 ? 0 : 12); break;
-    }
-    double conf = 0.0;                                                                      // :346-382
-    if (f.days_since_registration > 90) conf += 0.3; else if (f.days_since_registration > 30) conf += 0.2;
-    else conf += 0.1;
-    if (f.bet_count > 100) conf += 0.3; else if (f.bet_count > 20) conf += 0.2; else conf += 0.1;
-    if (f.deposit_frequency > 2) conf += 0.2; else if (f.deposit_frequency > 0) conf += 0.1;
-    if (f.days_since_last_bet < 7) conf += 0.2; else if (f.days_since_last_bet < 30) conf += 0.1;
-    if (conf > 1.0) conf = 1.0;
-    out->predicted_ltv = adjusted;
-    out->churn_risk = churn;
-    out->confidence = (float)conf;
-    out->days_survival = (int32_t)surv;
-    out->segment = (uint8_t)seg;
-    out->next_best_action = (uint8_t)act;
-    for (int i = 0; i < 6; ++i) out->pad[i] = 0;
-}
 
 // ------------------------------------------------------------------------------------------------
 // GEMM layer

@@ -139,7 +139,7 @@ k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
 int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t n_shards, uint32_t* counts,
                       igs_tx* d_tx_out, uint32_t* d_perm, uint32_t* d_offsets, cudaStream_t stream) {
     const uint32_t n = (uint32_t)n64;
-    const uint32_t nblocks = (n + kTile - 1) / kTile;
+    const uint32_t nblocks = (uint32_t)((n64 + kTile - 1) / kTile);    // 64-bit: n + kTile - 1 wraps near 2^32
     if (n == 0) {
         IGS_CUDA(e, cudaMemsetAsync(d_offsets, 0, ((size_t)n_shards + 1) * sizeof(uint32_t), stream));
         return IGS_OK;
@@ -190,8 +190,8 @@ extern "C" int igs_partition_tx_static(igs_engine* e, const igs_tx* d_tx, uint64
         igs_set_error(nullptr, "engine handle is null");
         return IGS_ERR_INVALID;
     }
-    IGS_CUDA(e, cudaSetDevice(e->device));
     IGS_REQUIRE(e, e->device >= 0 && e->device < kMaxDevices, "device ordinal beyond 63");
+    IGS_CUDA(e, cudaSetDevice(e->device));
     IGS_REQUIRE(e, n_shards >= 1 && n_shards <= 256, "n_shards must be 1..256");
     IGS_REQUIRE(e, n < (1ull << 32), "at most 2^32-1 records per call");
     IGS_REQUIRE(e, d_offsets != nullptr, "offsets is null");

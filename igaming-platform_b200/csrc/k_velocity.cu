@@ -86,19 +86,35 @@ __global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_
     type[i] = __ldg(type_in + s);
 }
 
-__global__ void k_segments(const uint32_t* __restrict__ acct, uint32_t n, uint32_t n_accounts,
-                           uint32_t* __restrict__ seg) {
+// Also counts LATE events: sorted neighbours of one account whose arrival order is the reverse of their time
+// order — the earlier-timestamped one arrived later.  Redis would have applied it on arrival, with its old
+// timestamp as "now" (features/redis_store.go:121,132,155); the index files it where its timestamp says.
+// late[0] = such pairs in the whole history, late[1] = those whose late event has arrival index >= n_before
+// (the batch being appended).
+__global__ void k_segments(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ seq, uint32_t n,
+                           uint32_t n_accounts, uint32_t n_before, uint32_t* __restrict__ seg,
+                           uint32_t* __restrict__ late) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t a = __ldg(acct + i);
-    if (i == 0) {
-        for (uint32_t x = 0; x <= a; ++x) seg[x] = 0;
-    } else {
-        const uint32_t p = __ldg(acct + i - 1);
-        for (uint32_t x = p + 1; x <= a; ++x) seg[x] = i;
+    bool is_late = false, is_new = false;
+    if (i < n) {
+        const uint32_t a = __ldg(acct + i);
+        if (i == 0) {
+            for (uint32_t x = 0; x <= a; ++x) seg[x] = 0;
+        } else {
+            const uint32_t p = __ldg(acct + i - 1);
+            for (uint32_t x = p + 1; x <= a; ++x) seg[x] = i;
+            const uint32_t sp = __ldg(seq + i - 1);
+            is_late = p == a && sp > __ldg(seq + i);
+            is_new = is_late && sp >= n_before;
+        }
+        if (i == n - 1)
+            for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
     }
-    if (i == n - 1)
-        for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
+    const unsigned m0 = __ballot_sync(0xffffffffu, is_late), m1 = __ballot_sync(0xffffffffu, is_new);
+    if ((threadIdx.x & 31) == 0) {
+        if (m0) atomicAdd(late + 0, (uint32_t)__popc(m0));
+        if (m1) atomicAdd(late + 1, (uint32_t)__popc(m1));
+    }
 }
 
 // head[i] = 1 iff event i is the first of its (account, ts) group in sorted order
@@ -553,11 +569,15 @@ __device__ __forceinline__ uint32_t account_of(const uint32_t* __restrict__ seg,
 // the trailing chain of events with consecutive gaps <= 86400 (the longest key life among the chains: tx_sum 1h,
 // session 30m, identifier keys 24h; windows reach back 24h), or the end of the segment when even last_tx (7d,
 // the longest TTL of all, redis_store.go:155) has expired.
+// A break after which the account's later events all lie in the future of `now` (future-dated events, a caller
+// whose clock is behind the ingest clock) must not drop what precedes it: queries at now <= t < ts(break event)
+// still see those events.  Only breaks whose later event has ts <= now count.
 __global__ void k_ev_breaks(const uint32_t* __restrict__ seg, const uint32_t* __restrict__ ts, uint32_t n,
-                            uint32_t n_accounts, uint32_t* __restrict__ keep_from) {
+                            uint32_t n_accounts, uint32_t now, uint32_t* __restrict__ keep_from) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     const uint32_t t = __ldg(ts + j);
+    if (t > now) return;
     const bool maybe = j == 0 || t < __ldg(ts + j - 1) || (long long)t - (long long)__ldg(ts + j - 1) > 86400;
     if (!maybe) return;                               // same account, gap <= 24h: not a break
     const uint32_t a = account_of(seg, n_accounts, j);
@@ -652,14 +672,23 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
     if (need > e->cap_raw) {
         const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
         uint32_t *a = nullptr, *t = nullptr; int64_t* m = nullptr; uint8_t* y = nullptr;
-        IGS_CUDA(e, cudaMalloc(&a, cap * 4));
-        IGS_CUDA(e, cudaMalloc(&t, cap * 4));
-        IGS_CUDA(e, cudaMalloc(&m, cap * 8));
-        IGS_CUDA(e, cudaMalloc(&y, cap));
+        uint64_t *d = nullptr, *p = nullptr;
+        {
+            cudaError_t err = cudaMalloc(&a, cap * 4);
+            if (err == cudaSuccess) err = cudaMalloc(&t, cap * 4);
+            if (err == cudaSuccess) err = cudaMalloc(&m, cap * 8);
+            if (err == cudaSuccess) err = cudaMalloc(&y, cap);
+            if (err == cudaSuccess && e->has_event_ids) err = cudaMalloc(&d, cap * 8);
+            if (err == cudaSuccess && e->has_event_ids) err = cudaMalloc(&p, cap * 8);
+            if (err != cudaSuccess) {                 // give back what was obtained; the old columns are untouched
+                for (void* q : {(void*)a, (void*)t, (void*)m, (void*)y, (void*)d, (void*)p})
+                    if (q) cudaFree(q);
+                igs_set_error(e, "growing the event columns to %llu events failed: %s", (unsigned long long)cap,
+                              cudaGetErrorString(err));
+                return err == cudaErrorMemoryAllocation ? IGS_ERR_NOMEM : IGS_ERR_CUDA;
+            }
+        }
         if (e->has_event_ids) {
-            uint64_t *d = nullptr, *p = nullptr;
-            IGS_CUDA(e, cudaMalloc(&d, cap * 8));
-            IGS_CUDA(e, cudaMalloc(&p, cap * 8));
             if (e->n_raw) {
                 IGS_CUDA(e, cudaMemcpyAsync(d, e->raw_device, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
                 IGS_CUDA(e, cudaMemcpyAsync(p, e->raw_ip, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
@@ -700,7 +729,9 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
     return IGS_OK;
 }
 
-static int build_index_from_raw(igs_engine* e, uint32_t n_accounts);
+// n_before: arrival indices >= n_before are the batch being appended (late events among them are subject to the
+// late policy); a bulk load or an eviction passes "none"
+static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_before = 0xFFFFFFFFull);
 
 int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
     if (!e->has_events) {
@@ -720,8 +751,8 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_
     const uint32_t n_accounts = e->ev.n_accounts;   // the rebuild resets e->ev
     int rc = append_raw(e, ev, ids, n, e->slot[0].stream);
     if (rc != IGS_OK) return rc;
-    rc = build_index_from_raw(e, n_accounts);
-    if (rc != IGS_OK) {                      // e.g. an account index out of range: drop the rejected batch
+    rc = build_index_from_raw(e, n_accounts, before);
+    if (rc != IGS_OK) {                      // an account index out of range, late events: drop the rejected batch
         char msg[sizeof(e->err)];
         memcpy(msg, e->err, sizeof(msg));
         e->n_raw = before;
@@ -844,7 +875,7 @@ static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, con
 }
 
 // (Re)builds the index from the raw columns e->raw_* [0, n_raw).
-static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
+static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_before) {
     const uint32_t n = (uint32_t)e->n_raw;
     cudaStream_t st = e->slot[0].stream;
     igs_event_index& x = e->ev;
@@ -879,10 +910,10 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     const int64_t* d_amt_in = e->raw_amount;
     const uint8_t* d_type_in = e->raw_type;
     uint32_t* d_mm;
-    IGS_CUDA(e, sc.alloc(&d_mm, 4));
+    IGS_CUDA(e, sc.alloc(&d_mm, 8));            // [0..3] key range, [4..5] late-event counters
 
     // ---- key range ------------------------------------------------------------------------------
-    const uint32_t mm_init[4] = {0xFFFFFFFFu, 0u, 0u, 0u};
+    const uint32_t mm_init[8] = {0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     IGS_CUDA(e, cudaMemcpyAsync(d_mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, st));
     const uint32_t nb_el = (n + kThreads - 1) / kThreads;
     k_minmax<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct_in, d_ts_in, n, d_mm);
@@ -933,7 +964,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
                                                 d_acct, x.ts, d_amt, d_type);
     IGS_CUDA(e, cudaGetLastError());
-    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, n, n_accounts, x.seg);
+    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, x.seq, n, n_accounts, (uint32_t)n_before, x.seg, d_mm + 4);
     IGS_CUDA(e, cudaGetLastError());
     uint8_t* d_head;
     IGS_CUDA(e, sc.alloc(&d_head, n));
@@ -945,9 +976,17 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts) {
     k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_mm);
     IGS_CUDA(e, cudaGetLastError());
     {
-        uint32_t n_unres = 0;
+        uint32_t n_unres = 0, late[2] = {0, 0};
         IGS_CUDA(e, cudaMemcpyAsync(&n_unres, d_mm, 4, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaMemcpyAsync(late, d_mm + 4, 8, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
+        e->late_events = late[0];
+        if (late[1] != 0 && e->late_policy == IGS_LATE_REJECT) {
+            igs_set_error(e, "the batch holds %u late event(s): an event older than one of the same account that is "
+                          "already resident or earlier in the batch (policy IGS_LATE_REJECT; see igs_set_late_policy)",
+                          late[1]);
+            return IGS_ERR_INVALID;
+        }
         const int rc = resolve_big_groups(e, sc, n_unres != 0, d_head, d_amt, n, d_dflag, d_scan_scratch_n, st);
         if (rc != IGS_OK) return rc;
     }
@@ -1052,7 +1091,7 @@ int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
         if ((err = cudaMalloc(&scr, scan_u32_scratch_elems(n) * 4)) != cudaSuccess) { bail(err, "cudaMalloc"); break; }
         last_keep = keep + n;
         cudaMemsetAsync(keep_from, 0, ((size_t)n_accounts + 1) * 4, st);
-        k_ev_breaks<<<nb, kThreads, 0, st>>>(x.seg, x.ts, n, n_accounts, keep_from);
+        k_ev_breaks<<<nb, kThreads, 0, st>>>(x.seg, x.ts, n, n_accounts, now, keep_from);
         k_ev_dead<<<(n_accounts + kThreads - 1) / kThreads, kThreads, 0, st>>>(x.seg, x.ts, n_accounts, now, keep_from);
         k_ev_keep<<<nb, kThreads, 0, st>>>(x.seg, x.seq, n, n_accounts, keep_from, keep);
         k_save_last_u32<<<1, 32, 0, st>>>(keep, n, last_keep);

@@ -253,11 +253,9 @@ static int radix_sort_pairs(igs_engine* e, uint64_t* keys[2], uint32_t* vals[2],
     const uint32_t bins = 1u << digit_bits;
     const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
     const uint32_t hist_elems = bins * nb_sort;
-    static bool smem_opt_in = false;       // per process; the attribute is per function and device-independent here
-    if (!smem_opt_in) {
-        IGS_CUDA(e, cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
-        smem_opt_in = true;
-    }
+    // the attribute belongs to the (function, device) pair and the engine's device is current: set it per sort
+    // (a few hundred ns) instead of remembering it per process
+    IGS_CUDA(e, cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
     int cur = 0;
     for (int p = 0; p < passes; ++p) {
         const int shift = p * digit_bits;

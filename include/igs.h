@@ -17,9 +17,13 @@
  * caller (the synchronous host-buffer calls all use slot 0).  The calls that replace device state —
  * igs_load_*, igs_append_events*, igs_evict_events, igs_blacklist_load / _add, igs_links_* — are
  * like ONNXModel.Close under its write lock (ml/onnx_model.go:349): they must not run while a
- * scoring or query call on the same engine is in flight.  igs_partition_tx_device keeps its counters in
- * one per-engine scratch buffer: issue one partition at a time per engine (or order them on one
- * stream).  igs_last_error returns the engine's single message buffer; read it on the thread
+ * scoring or query call on the same engine is in flight.  Three *_device calls work through per-engine
+ * scratch, not per-stream scratch: igs_partition_tx_device (its counters; grown with cudaFree +
+ * cudaMalloc when a batch needs more than any before), igs_ltv_batch_device and igs_ltv_hidden_device
+ * (two 512 MB activation buffers shared by every call).  On one engine, order such calls with respect to
+ * each other — one stream, or events between streams; two of them overlapping on the GPU overwrite each
+ * other's intermediate data and return wrong results silently.  The scoring *_device calls have no such
+ * scratch (the account-ordered visit of large fused batches allocates stream-ordered) and may overlap.  igs_last_error returns the engine's single message buffer; read it on the thread
  * that saw the failing status.  Configuration (weights / thresholds) is passed by value with
  * every call, so there is no shared mutable config (the reference has a latent race there:
  * scoring/engine.go:304-306 vs :498-504).
@@ -313,6 +317,15 @@ typedef struct igs_ltv_result {
     uint8_t pad[6];
 } igs_ltv_result;
 
+/* ml.LTVFeatures (ml/onnx_model.go:375-393): the 17 float32 inputs of ml.LTVModel, declaration
+ * order.  68 bytes.                                                                             */
+typedef struct igs_ltv_features {
+    float days_since_registration, days_since_last_deposit, days_since_last_bet, total_active_days;
+    float sessions_per_week, total_deposits, total_withdrawals, net_revenue, avg_deposit_amount;
+    float deposit_frequency, total_bets, bet_count, win_rate, avg_bet_size, games_played;
+    float bonuses_claimed, bonus_conversion_rate;
+} igs_ltv_features;
+
 /* ------------------------------------------------------------------------------------------ */
 /* engine life cycle                                                                          */
 /* ------------------------------------------------------------------------------------------ */
@@ -352,12 +365,39 @@ int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_
  * account is rejected as a whole and the history is left as it was.                                  */
 int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n);
 
+/* LATE EVENTS.  Redis applies every event when it arrives, with the event's own timestamp as "now"
+ * (features/redis_store.go:121: ZADD score, :132 trim bound, :155 SET last_tx), so an event that arrives
+ * after a newer event of the same account overwrites last_tx with an OLDER time, trims less, and renews
+ * TTLs from the past.  The index has no arrival-order state: it files an event where its timestamp says,
+ * i.e. it answers as if the events had been applied in (timestamp, arrival) order.  The two agree exactly
+ * when, per account, timestamps never decrease in arrival order; they differ for a late event — one whose
+ * timestamp is smaller than that of an event of the same account that arrived before it.
+ *   igs_load_events* (a replayed log) accepts late events and orders them by timestamp.
+ *   igs_append_events* (live ingest) by default REJECTS a batch that holds a late event (relative to the
+ *   resident history or to earlier events of the batch) with IGS_ERR_INVALID and leaves the history as it
+ *   was, so that the caller decides; with IGS_LATE_REORDER the batch is accepted and ordered by timestamp.
+ * igs_history_info reports how many late pairs the resident history holds.                            */
+#define IGS_LATE_REJECT  0
+#define IGS_LATE_REORDER 1
+int igs_set_late_policy(igs_engine* e, int policy);
+typedef struct igs_history_info {
+    uint64_t n_events;       /* resident events                                                       */
+    uint64_t late_events;    /* neighbouring events of one account whose arrival order is the reverse
+                                of their time order                                                   */
+    uint32_t n_accounts;
+    uint32_t has_identifiers;
+    uint64_t reserved[4];
+} igs_history_info;
+int igs_get_history_info(igs_engine* e, igs_history_info* out);
+
 /* Replaces the key expiry Redis does on its own (the TTLs of features/redis_store.go:133,138,144,151,
  * 155,160): drops from the resident history every event that cannot influence any query at
  * t >= now, and refreshes the index.  What is dropped, per account: everything before the trailing
  * chain of events with consecutive gaps <= 86400 s (the longest-lived chain key; the windows reach
  * back 24 h too), and the whole account once now - (its last event) > 7 d (last_tx, the longest TTL).
- * Queries at t >= now return exactly what they returned before; queries in the past may not.  An
+ * Queries at t >= now return exactly what they returned before; queries in the past may not.  Events
+ * dated after `now` (future-dated input, a caller whose clock is behind the ingest clock) are kept, and
+ * so is everything a query between `now` and their timestamp can still see.  An
  * account that never pauses for a day keeps its whole history — as its tx_sum / unique-identifier keys
  * never expire in Redis either.  The survivors keep their arrival order but are renumbered: pass
  * seq_limit = UINT32_MAX in queries afterwards.  *n_evicted (optional) receives the number of events
@@ -591,6 +631,25 @@ int igs_ltv_batch_device(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* 
  * ml/onnx_model.go:399).                                                                          */
 int igs_ltv_hidden_device(igs_engine* e, const uint16_t* d_x, uint64_t n, int layer, uint16_t* d_hidden,
                           void* stream);
+
+/* The reference's own LTV arithmetic, without any loaded model — what the LTV slot runs today.
+ *
+ * igs_ltv_predict_batch replaces LTVPredictor.BatchPredict (prediction/ltv.go:385-398) exactly as the
+ * reference executes it: calculateLTV (:155-178) where igs_ltv_batch puts the MLP, then the same
+ * churn / adjust / segment / survival / action / confidence steps (:124-139).  fp64 throughout,
+ * bit-identical to the CPU restatement.  ltv_raw (optional) receives calculateLTV's value.
+ *
+ * igs_ltv_mock_predict replaces ml.LTVModel.Predict (ml/onnx_model.go:405-432, with
+ * calculateEngagement :434-467 and calculateChurnRisk :469-490) for n feature rows: the model the
+ * ml package returns while `session: nil // Use mock for now` (:399) — the LTV counterpart of
+ * IGS_MODEL_MOCK.  ltv_out[i] = its float64 result.  Neither call needs igs_load_mlp.            */
+int igs_ltv_predict_batch(igs_engine* e, const igs_ltv_row* rows, uint64_t n, igs_ltv_result* out,
+                          double* ltv_raw);
+int igs_ltv_predict_batch_device(igs_engine* e, const igs_ltv_row* d_rows, uint64_t n,
+                                 igs_ltv_result* d_out, double* d_ltv_raw, void* stream);
+int igs_ltv_mock_predict(igs_engine* e, const igs_ltv_features* f, uint64_t n, double* ltv_out);
+int igs_ltv_mock_predict_device(igs_engine* e, const igs_ltv_features* d_f, uint64_t n, double* d_ltv_out,
+                                void* stream);
 
 /* ------------------------------------------------------------------------------------------ */
 /* host-side helpers (pure C, no GPU)                                                          */

@@ -920,6 +920,52 @@ void orc_ltv_epilogue(const igs_ltv_row* f, double ltv, igs_ltv_result* out) {
     out->next_best_action = (uint8_t)act;
 }
 
+/* ------------------------------------------------------------------------------------------ */
+/* ml.LTVModel (ml/onnx_model.go:366-490): the "model" the ml package returns for the LTV slot   */
+/* while `session: nil // Use mock for now` (:399).  Its two helpers are NOT the predictor's      */
+/* (prediction/ltv.go:181-262): no "< 14" / ">= 1" tiers, GamesPlayed >= 10 and                   */
+/* BonusConversionRate > 0.5 instead of the notification flags, fewer churn terms.  The fields    */
+/* are float32 and compare against untyped constants, i.e. in float32.                            */
+/* ------------------------------------------------------------------------------------------ */
+/* calculateEngagement, :434-467 */
+double orc_ltv_model_engagement(const igs_ltv_features* f) {
+    double score = 0;
+    if (f->days_since_last_bet < 3) score += 0.3;                      /* :437-441 */
+    else if (f->days_since_last_bet < 7) score += 0.2;
+    if (f->sessions_per_week >= 5) score += 0.2;                       /* :443-447 */
+    else if (f->sessions_per_week >= 3) score += 0.15;
+    if (f->deposit_frequency >= 4) score += 0.2;                       /* :449-453 */
+    else if (f->deposit_frequency >= 2) score += 0.15;
+    if (f->games_played >= 10) score += 0.15;                          /* :455-457 */
+    if (f->bonus_conversion_rate > 0.5f) score += 0.15;                /* :459-461 */
+    if (score > 1) score = 1;                                          /* :463-465 */
+    return score;
+}
+/* calculateChurnRisk, :469-490 */
+double orc_ltv_model_churn(const igs_ltv_features* f) {
+    double risk = 0;
+    if (f->days_since_last_bet > 30) risk += 0.5;                      /* :472-476 */
+    else if (f->days_since_last_bet > 14) risk += 0.3;
+    if (f->days_since_last_deposit > 30) risk += 0.2;                  /* :478-480 */
+    if (f->sessions_per_week < 1 && f->days_since_registration > 30) risk += 0.2;   /* :482-484 */
+    if (risk > 1) risk = 1;                                            /* :486-488 */
+    return risk;
+}
+/* Predict, :405-432 */
+double orc_ltv_model_predict(const igs_ltv_features* f) {
+    double current = (double)f->net_revenue;                           /* :412 */
+    double days = (double)f->days_since_registration;                  /* :415-418 */
+    if (days < 1) days = 1;
+    volatile double q = current / days;
+    volatile double monthly = q * 30;                                  /* :419 */
+    volatile double remaining = 12.0 * orc_ltv_model_engagement(f);    /* :422-423 */
+    volatile double half = orc_ltv_model_churn(f) * 0.5;
+    volatile double adjust = 1.0 - half;                               /* :426-427 */
+    volatile double future = monthly * remaining;
+    volatile double total = current + future;
+    return total * adjust;                                             /* :429 */
+}
+
 /* ========================================================================================== */
 /* MLP spec (parity unpinned: stands in for ltv_model.onnx)                                    */
 /* ========================================================================================== */

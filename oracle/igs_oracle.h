@@ -177,6 +177,10 @@ double orc_ltv_heuristic(const igs_ltv_row* f);                          /* calc
 double orc_ltv_churn(const igs_ltv_row* f);                              /* :228-262           */
 /* Everything after the model output, :124-139 (+ :265-382).                                    */
 void   orc_ltv_epilogue(const igs_ltv_row* f, double ltv, igs_ltv_result* out);
+/* ml.LTVModel (ml/onnx_model.go:405-490): Predict and its two helpers on ml.LTVFeatures.         */
+double orc_ltv_model_engagement(const igs_ltv_features* f);              /* :434-467           */
+double orc_ltv_model_churn(const igs_ltv_features* f);                   /* :469-490           */
+double orc_ltv_model_predict(const igs_ltv_features* f);                 /* :405-432           */
 float  orc_bf16_to_f32(uint16_t b);
 uint16_t orc_f32_to_bf16(float f);                                       /* round-nearest-even */
 /* MLP spec: bf16 operands, products exact, sums in fp64 then rounded once to fp32 per neuron,

@@ -139,6 +139,9 @@ def lib() -> C.CDLL:
         getattr(L, f).restype = C.c_double
     L.orc_ltv_epilogue.argtypes = [vp, C.c_double, vp]
     L.orc_ltv_epilogue.restype = None
+    for f in ("orc_ltv_model_engagement", "orc_ltv_model_churn", "orc_ltv_model_predict"):
+        getattr(L, f).argtypes = [vp]
+        getattr(L, f).restype = C.c_double
     L.orc_bf16_to_f32.argtypes = [C.c_uint16]
     L.orc_bf16_to_f32.restype = C.c_float
     L.orc_f32_to_bf16.argtypes = [C.c_float]
@@ -296,6 +299,23 @@ def ltv_epilogue(rows: np.ndarray, ltv: np.ndarray) -> np.ndarray:
     for i in range(rows.shape[0]):
         L.orc_ltv_epilogue(rows[i:i + 1].ctypes.data, float(ltv[i]), out[i:i + 1].ctypes.data)
     return out
+
+
+def ltv_predict_batch(rows: np.ndarray):
+    """LTVPredictor.BatchPredict as the reference runs it (prediction/ltv.go:385-398): calculateLTV, then the
+    post-model steps.  Returns (results, calculateLTV values)."""
+    rows = np.ascontiguousarray(rows, dtype=abi.ltv_row_dtype)
+    L = lib()
+    raw = np.array([L.orc_ltv_heuristic(rows[i:i + 1].ctypes.data) for i in range(rows.shape[0])], dtype=np.float64)
+    return ltv_epilogue(rows, raw), raw
+
+
+def ltv_model_predict(feats: np.ndarray) -> np.ndarray:
+    """ml.LTVModel.Predict (ml/onnx_model.go:405-432) per row of ml.LTVFeatures."""
+    feats = np.ascontiguousarray(feats, dtype=abi.ltv_features_dtype)
+    L = lib()
+    return np.array([L.orc_ltv_model_predict(feats[i:i + 1].ctypes.data) for i in range(feats.shape[0])],
+                    dtype=np.float64)
 
 
 def mlp_forward(model, x_bf16: np.ndarray, want_hidden=False):

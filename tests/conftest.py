@@ -49,3 +49,11 @@ def engine(pkg, built_lib):
         pytest.skip("no CUDA device")
     with pkg.Engine(device=0) as e:
         yield e
+
+
+@pytest.fixture
+def late_reorder(engine, pkg):
+    """igs_append_events accepts late events (ordered by timestamp) for the duration of one test."""
+    engine.set_late_policy(pkg.abi.LATE_REORDER)
+    yield engine
+    engine.set_late_policy(pkg.abi.LATE_REJECT)

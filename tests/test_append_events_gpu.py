@@ -13,7 +13,8 @@ def cut(ev, lo, hi, pkg):
     return pkg.Events(ev.account[lo:hi], ev.ts[lo:hi], ev.amount[lo:hi], ev.tx_type[lo:hi])
 
 
-def test_append_equals_bulk_load(engine, orc, pkg):
+def test_append_equals_bulk_load(engine, orc, pkg, late_reorder):
+    """Pieces of a history in random time order: with IGS_LATE_REORDER an append is a bulk load of the whole."""
     abi = pkg.abi
     n_acc, n = 700, 30000
     ev = synth.make_events(n, n_acc, seed=41, span=5 * 3600, collision_rate=0.04)
@@ -63,6 +64,62 @@ def test_score_then_append_stream_matches_oracle(engine, orc, pkg):
     assert fired > 0
 
 
+def test_late_events_policy(engine, orc, pkg):
+    """A late event — older than an event of its account that arrived before it — is where the index (events
+    filed by timestamp) and Redis (events applied on arrival, features/redis_store.go:121-160) part ways.
+    Smallest case, one account: arrivals (T0+100, 500) then (T0+10, 200); query at T0+120.  Applied on arrival,
+    the second event overwrites last_tx with the OLDER time (:155): time_since_last_tx = 110.  Filed by timestamp:
+    20.  igs_append_events refuses such a batch unless IGS_LATE_REORDER is set; igs_load_events (a replayed log)
+    orders by timestamp and reports the late pair."""
+    abi = pkg.abi
+    T0 = synth.T0
+    # the deviation itself, on the command-level emulation (wall clock == event timestamp, as everywhere)
+    acc = orc.lib().orc_redis_new()
+    rt = orc.Realtime()
+    import ctypes as C
+    for ts, amt in ((T0 + 100, 500), (T0 + 10, 200)):
+        orc.lib().orc_redis_update(acc, ts, amt)
+    orc.lib().orc_redis_get(acc, T0 + 120, C.byref(rt))
+    orc.lib().orc_redis_free(acc)
+    assert T0 + 120 - rt.last_tx_timestamp == 110 and rt.tx_count_5m == 2 and rt.tx_sum_1h == 700
+
+    def one(ts, amt):
+        return pkg.Events(np.array([0], np.uint32), np.array([ts], np.uint32), np.array([amt], np.int64), np.zeros(1, np.uint8))
+    q = np.zeros(1, dtype=abi.query_dtype)
+    q["ts"], q["seq_limit"] = T0 + 120, abi.SEQ_ALL
+    engine.load_events(one(T0 + 100, 500), 1)
+    with pytest.raises(pkg.IgsError) as ei:
+        engine.append_events(one(T0 + 10, 200))
+    assert ei.value.status == abi.ERR_INVALID and "late" in str(ei.value)
+    v = engine.get_velocity(q)[0]
+    assert (int(v["n_prior"]), int(v["time_since_last_tx"])) == (1, 20)          # the rejected event left no trace
+    assert engine.history_info()["late_events"] == 0
+    # late inside one batch: (T0+130) then (T0+125) of the same account
+    two = pkg.Events(np.zeros(2, np.uint32), np.array([T0 + 130, T0 + 125], np.uint32), np.array([1, 2], np.int64), np.zeros(2, np.uint8))
+    with pytest.raises(pkg.IgsError):
+        engine.append_events(two)
+    # equal timestamps are not late; neither is an old event of ANOTHER account
+    engine.load_events(one(T0 + 100, 500), 2)
+    engine.append_events(one(T0 + 100, 300))
+    engine.append_events(pkg.Events(np.array([1], np.uint32), np.array([T0 + 5], np.uint32), np.array([9], np.int64), np.zeros(1, np.uint8)))
+    assert engine.history_info() == {"n_events": 3, "late_events": 0, "n_accounts": 2, "has_identifiers": False}
+    # opt in: accepted and filed by timestamp == bulk load == the closed form on the time-ordered history
+    engine.set_late_policy(abi.LATE_REORDER)
+    try:
+        engine.load_events(one(T0 + 100, 500), 1)
+        engine.append_events(one(T0 + 10, 200))
+        got = engine.get_velocity(q)
+        assert engine.history_info()["late_events"] == 1
+    finally:
+        engine.set_late_policy(abi.LATE_REJECT)
+    both = pkg.Events(np.zeros(2, np.uint32), np.array([T0 + 100, T0 + 10], np.uint32), np.array([500, 200], np.int64), np.zeros(2, np.uint8))
+    assert got.tobytes() == orc.velocity_batch(both, 1, q).tobytes()
+    assert int(got[0]["time_since_last_tx"]) == 20 and int(got[0]["tx_count_5m"]) == 2
+    engine.load_events(both, 1)                                # bulk load: accepted under either policy, counted
+    assert engine.history_info()["late_events"] == 1
+    assert engine.get_velocity(q).tobytes() == got.tobytes()
+
+
 def test_append_errors(engine, pkg):
     abi = pkg.abi
     with pkg.Engine(device=0) as fresh:
@@ -109,6 +166,10 @@ def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg):
         else:              # last seen 2-6 days ago: chain keys dead, last_tx alive
             ts = now - rng.integers(2 * day, 6 * day) - rng.integers(0, 7200, rng.integers(1, 10))
         rows.append((np.full(ts.size, a), ts))
+    # a future-dated event more than a day after the account's last one (clock skew between the ingest clock and
+    # the `now` handed to evict): the break it forms lies beyond `now` and must not drop what precedes it
+    rows.append((np.full(3, n_acc), np.array([now - 4000, now - 100, now + 2 * day])))
+    n_acc += 1
     acct = np.concatenate([r[0] for r in rows]).astype(np.uint32)
     ts = np.concatenate([r[1] for r in rows]).astype(np.uint32)
     perm = rng.permutation(acct.size)
@@ -121,6 +182,7 @@ def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg):
     q["account"] = rng.integers(0, n_acc, q.shape[0])
     q["ts"] = now + rng.choice([0, 1, 60, 3600, day, 3 * day, 7 * day, 8 * day], q.shape[0]) + rng.integers(0, 100, q.shape[0])
     q["ts"][:50] = now
+    q["account"][:4], q["ts"][:4] = n_acc - 1, [now, now + 50, now + day, now + 3 * day]
     q["seq_limit"] = abi.SEQ_ALL
     v0, u0 = engine.get_velocity(q), engine.get_uniques(q)
     assert v0.tobytes() == orc.velocity_batch(ev, n_acc, q).tobytes()
@@ -132,6 +194,7 @@ def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg):
     assert v1.tobytes() == same.tobytes()
     assert (v1["n_prior"] <= v0["n_prior"]).all() and (v1["n_prior"] < v0["n_prior"]).any()
     assert u1.tobytes() == u0.tobytes()
+    assert v1["n_prior"][:2].tolist() == [2, 2] and int(v1["time_since_last_tx"][0]) == 100
     assert engine.evict_events(now) == 0                 # idempotent
     # appends after the eviction: as if nothing had been dropped
     m = 3000

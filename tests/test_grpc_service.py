@@ -284,3 +284,81 @@ def test_grpc_blacklist_and_ltv_on_the_gpu(engine, orc, pkg):
             engine.blacklist_load(kind, np.zeros(0, np.uint64))
         engine.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64),
                                       np.zeros(0, np.uint8)), 1)
+
+
+@pytest.mark.gpu
+def test_grpc_concurrent_rpcs_do_not_share_staging(engine, orc, pkg):
+    """The server runs a pool of worker threads and every synchronous engine call stages through slot 0
+    (include/igs.h, Threading).  Eight client threads fire ScoreBatch requests of different sizes while another
+    keeps adding to the device blacklist (its growth path re-allocates the set a scoring kernel probes): every
+    response must be the one for ITS request — compared with the oracle per request."""
+    import threading
+    sc, gs, abi = pkg.scoring, pkg.grpc_service, pkg.abi
+    n_players = 64
+    players = synth.make_players(n_players, seed=81, now=synth.T0 + 3600)
+    engine.load_players(players)
+    engine.load_events(pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int64), np.zeros(0, np.uint8)),
+                       n_players)
+    for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
+        engine.blacklist_load(kind, np.zeros(0, np.uint64))
+    d = sc.PlayerDirectory()
+    ids = [uuid.UUID(int=9000 + i) for i in range(n_players)]
+    for u in ids:
+        d.add(u)
+    cfg = pkg.default_config(model_kind=abi.MODEL_MOCK)
+    eng = sc.ScoringEngine(engine, d, config=cfg)
+    server = gs.serve(gs.RiskServicer(eng, players=players), "127.0.0.1:0", max_workers=8)
+    errors = []
+
+    def scorer(k):
+        client = gs.RiskClient(f"127.0.0.1:{server.bound_port}")
+        rng = np.random.default_rng(100 + k)
+        try:
+            for rep in range(12):
+                m = int(rng.integers(1, 400))
+                acct = rng.integers(0, n_players, m)
+                amount = rng.integers(1, 400000, m)
+                typ = rng.integers(0, 3, m)
+                msgs = [gs.ScoreTransactionRequest(account_id=str(ids[int(a)]), amount=int(v),
+                                                   transaction_type=["bet", "deposit", "withdraw"][int(t)])
+                        for a, v, t in zip(acct, amount, typ)]
+                resp = client.ScoreBatch(gs.ScoreBatchRequest(transactions=msgs))
+                # no history, no identifiers: the result depends on (player row, amount, type) only, except the
+                # account age, which moves with the wall clock by whole days — recompute with the handler's day
+                tx = np.zeros(m, dtype=abi.tx_dtype)
+                tx["account"], tx["amount"] = acct, amount
+                tx["tx_type"] = np.array([abi.TX_BET, abi.TX_DEPOSIT, abi.TX_WITHDRAW], np.uint8)[typ]
+                tx["ts"], tx["seq_limit"], tx["bits"] = int(__import__("time").time()), abi.SEQ_ALL, abi.BIT_VALID
+                want = orc.score_batch(cfg, None, players, pkg.Events(np.zeros(0, np.uint32), np.zeros(0, np.uint32),
+                                                                      np.zeros(0, np.int64), np.zeros(0, np.uint8)), tx)
+                got = [(r.score, r.action, r.rule_score) for r in resp.results]
+                exp = [(int(w["score"]), int(w["action"]), 0) for w in want]
+                if len(got) != m or any(g[:2] != e[:2] for g, e in zip(got, exp)):
+                    errors.append((k, rep, m))
+        except Exception as ex:            # noqa: BLE001
+            errors.append((k, repr(ex)))
+        finally:
+            client.close()
+
+    def blacklister():
+        client = gs.RiskClient(f"127.0.0.1:{server.bound_port}")
+        try:
+            for i in range(300):
+                assert client.AddToBlacklist(gs.AddToBlacklistRequest(type="device", value=f"bad-{i}")).success
+        except Exception as ex:            # noqa: BLE001
+            errors.append(("blacklist", repr(ex)))
+        finally:
+            client.close()
+
+    threads = [threading.Thread(target=scorer, args=(k,)) for k in range(8)] + [threading.Thread(target=blacklister)]
+    try:
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=120)
+        assert not errors, errors[:5]
+        hit = engine.blacklist_check(np.array([(pkg.hash_id("bad-299"), 0, 0)], dtype=abi.tx_ids_dtype))
+        assert hit.tolist() == [1]
+    finally:
+        server.stop(0)
+        engine.blacklist_load(abi.BL_DEVICE, np.zeros(0, np.uint64))

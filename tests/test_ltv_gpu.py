@@ -145,3 +145,63 @@ def test_ltv_needs_a_model(pkg):
         with pytest.raises(pkg.IgsError) as ei:
             fresh.ltv_batch(x, rows)
         assert ei.value.status == pkg.abi.ERR_STATE
+
+
+def make_ltv_features(n, seed, abi):
+    """ml.LTVFeatures rows that exercise every branch of ml.LTVModel (incl. the tier edges)."""
+    rng = np.random.default_rng(seed)
+    f = np.zeros(n, dtype=abi.ltv_features_dtype)
+    f["days_since_registration"] = rng.choice([0, 0.5, 1, 29, 30, 31, 400], n)
+    f["days_since_last_deposit"] = rng.choice([0, 30, 31, 90], n)
+    f["days_since_last_bet"] = rng.choice([0, 2, 3, 6, 7, 14, 15, 30, 31], n)
+    f["sessions_per_week"] = rng.choice([0, 0.99, 1, 2.99, 3, 5, 9], n)
+    f["deposit_frequency"] = rng.choice([0, 1.99, 2, 4, 7], n)
+    f["games_played"] = rng.choice([0, 9, 10, 50], n)
+    f["bonus_conversion_rate"] = rng.choice([0, 0.5, 0.5000001, 0.9], n)
+    f["net_revenue"] = rng.normal(0, 5000, n).astype(np.float32)
+    for k in ("total_active_days", "total_deposits", "total_withdrawals", "avg_deposit_amount", "total_bets",
+              "bet_count", "win_rate", "avg_bet_size", "bonuses_claimed"):
+        f[k] = rng.random(n).astype(np.float32) * 100      # read by nobody (:405-490): must not matter
+    return f
+
+
+def test_ltv_mock_model_kat_and_random(engine, orc, pkg):
+    """ml.LTVModel.Predict on the device (igs_ltv_mock_predict): KAT set C2 and 20 000 random rows, float64
+    results bit-identical to the restatement."""
+    abi = pkg.abi
+    cases = load("kat_ltv_model.json")["cases"]
+    rows = np.zeros(len(cases), dtype=abi.ltv_features_dtype)
+    for i, c in enumerate(cases):
+        for k, v in c["f"].items():
+            rows[i][k] = v
+    got = engine.ltv_mock_predict(rows)
+    assert got.tolist() == [c["ltv"] for c in cases]
+    f = make_ltv_features(20_000, 5, abi)
+    got, want = engine.ltv_mock_predict(f), orc.ltv_model_predict(f)
+    assert got.view(np.uint64).tolist() == want.view(np.uint64).tolist()
+    assert engine.ltv_mock_predict(f[:0]).shape == (0,)
+
+
+def test_ltv_predictor_without_model(engine, orc, pkg):
+    """LTVPredictor.BatchPredict as the reference runs it (calculateLTV in the model slot): KAT set C on the
+    device end to end, and random rows bit-identical to the restatement.  Needs no igs_load_mlp."""
+    abi = pkg.abi
+    cases = load("kat_ltv.json")["cases"]
+    rows = np.zeros(len(cases), dtype=abi.ltv_row_dtype)
+    for i, c in enumerate(cases):
+        for k, v in c["f"].items():
+            rows[i][k] = v
+    with pkg.Engine(device=0) as fresh:                     # no MLP loaded on this engine
+        out, raw = fresh.ltv_predict_batch(rows, want_raw=True)
+    for i, c in enumerate(cases):
+        assert raw[i] == pytest.approx(c["ltv"], rel=1e-12)
+        assert out[i]["predicted_ltv"] == pytest.approx(c["adjusted"], rel=1e-12)
+        assert SEGS[int(out[i]["segment"])] == c["segment"]
+        assert int(out[i]["days_survival"]) == c["survival"]
+        assert LTV_ACTIONS[int(out[i]["next_best_action"])] == c["action"]
+    _, r = synth.make_ltv_inputs(30_000, seed=9)
+    r["days_since_registration"][:2000] = np.arange(2000) % 40          # both branches of calculateLTV, incl. day 0
+    got, got_raw = engine.ltv_predict_batch(r, want_raw=True)
+    want, want_raw = orc.ltv_predict_batch(r)
+    assert got_raw.view(np.uint64).tolist() == want_raw.view(np.uint64).tolist()
+    assert got.tobytes() == want.tobytes()

@@ -221,6 +221,20 @@ def test_kat_ltv(orc, pkg, case):
     assert LTV_ACTIONS[int(out["next_best_action"])] == case["action"]
 
 
+@pytest.mark.parametrize("case", load("kat_ltv_model.json")["cases"], ids=lambda c: c["id"])
+def test_kat_ltv_model(orc, pkg, case):
+    """ml.LTVModel.Predict (ml/onnx_model.go:405-490) — exact: the vectors were derived by evaluating the cited
+    lines left to right in float64."""
+    row = np.zeros(1, dtype=pkg.abi.ltv_features_dtype)
+    for k, v in case["f"].items():
+        row[k] = v
+    L = orc.lib()
+    assert L.orc_ltv_model_engagement(row.ctypes.data) == case["engagement"]
+    assert L.orc_ltv_model_churn(row.ctypes.data) == case["churn"]
+    assert L.orc_ltv_model_predict(row.ctypes.data) == case["ltv"]
+    assert orc.ltv_model_predict(row)[0] == case["ltv"]
+
+
 def test_sigmoid_spec_is_accurate(orc):
     """The deterministic fp32 logistic stays within 2e-7 of the fp64 logistic on [-30, 30]."""
     xs = np.linspace(-30, 30, 20001).astype(np.float32)

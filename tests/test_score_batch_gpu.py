@@ -112,3 +112,24 @@ def test_fused_equals_two_step_path(engine, pkg):
     rows["bits"] = tx["bits"] | (bonus_only * abi.BIT_BONUS_ONLY).astype(np.uint8)
     again = engine.score_features(cfg, feats, rows)
     assert got.tobytes() == again.tobytes()
+
+
+def test_c1_reference_config_mock_model(engine, orc, pkg):
+    """BASELINE.json configs[0] — what the reference's own CPU run would score: 100 000 bet / deposit / withdraw
+    transactions over 10 000 Zipf(1.1) accounts, rules + the only model the reference can run (mockPredict,
+    ml/onnx_model.go:258-308), DefaultConfig.  Through igs_score_batch against the per-request restatement:
+    velocity blocks, assembled features, flags, ml, score, action bit-exact on all 100 000 rows."""
+    abi = pkg.abi
+    n, n_acc, n_ev = 100_000, 10_000, 200_000
+    now = synth.T0 + 48 * 3600
+    players = synth.make_players(n_acc, seed=synth.MASTER_SEED + 1, now=now)
+    ev = synth.make_events(n_ev, n_acc, seed=synth.MASTER_SEED + 2, zipf_s=1.1, collision_rate=0.01)
+    tx = synth.make_tx(n, n_acc, seed=synth.MASTER_SEED + 3, zipf_s=1.1, t_lo=synth.T0 + 24 * 3600, t_hi=now)
+    engine.load_players(players)
+    engine.load_events(ev, n_acc)
+    cfg = pkg.default_config()                       # DefaultConfig(): model_kind = IGS_MODEL_MOCK
+    assert cfg.model_kind == abi.MODEL_MOCK
+    want = check(engine, orc, pkg, cfg, None, players, ev, tx)
+    types = np.bincount(tx["tx_type"], minlength=3) / n
+    assert abs(types[abi.TX_BET] - 0.7) < 0.01 and abs(types[abi.TX_DEPOSIT] - 0.2) < 0.01
+    assert len(np.unique(want["action"])) >= 2 and (want["flags"] & abi.R_HIGH_VELOCITY).any()

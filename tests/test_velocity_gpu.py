@@ -101,7 +101,7 @@ def test_dedupe_and_ties_stress(engine, orc, pkg):
     assert int(want["tx_count_1m"].max()) <= 10      # at most 5 amounts x 2 seconds
 
 
-def test_same_second_bursts_of_any_size(engine, orc, pkg):
+def test_same_second_bursts_of_any_size(engine, orc, pkg, late_reorder):
     """Groups of events sharing (account, second) that are longer than the kernel's bounded backward walk
     (33 events) go through the per-group hash tables: sizes right at the boundary, thousands of events with
     few / many distinct amounts, the amount INT64_MIN (the tables' empty-slot marker), appended in pieces."""
