@@ -1,23 +1,33 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark of the B200 fraud-scoring engine.
+"""bench.py — benchmark of the B200 fraud-scoring engine: one JSON line per run (rank 0).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload (BASELINE.json configs[1]): 1M transactions x 64 fp32 features, 500-tree depth-8
-ensemble + the 8 rule checks + blend/action, per GPU.  A "step" = one pass of the fused score
-kernel over one 1M-tx batch.  N>1 (torchrun): every rank owns one GPU and one shard of the same
-size (transactions shard by player hash, no collective on the data path) -> weak scaling.
+Headline (top level of the line) = the FUSED PRODUCTION PATH on BASELINE.json's configs[1] model and batch with
+configs[2]'s history resident: per GPU, 1M compact transaction records (32 B) against 1M player rows and a
+10M-event index -> velocity lookup + feature assembly (64 f32) + 8 rules + 500-tree depth-8 ensemble + blend
++ action.  A "step" = one pass over one 1M-tx batch.  `value` = device-resident tx/s (CUDA events on the
+launching stream, max over ranks), `e2e` = the same through igs_score_batch with pinned HOST buffers (H2D of the
+tx records + kernels + D2H of the results inside the timed region).  N>1 (torchrun): every rank owns one GPU and
+one shard of the same size — transactions shard by player hash, no collective on the data path — weak scaling.
 
-Prints ONE JSON line (rank 0).  `value` = device-resident throughput, `e2e` = the same metric
-through the host-buffer C-ABI call (H2D + kernel + D2H inside the timed region), `roofline` and
-`cpu_baseline` as the task contract describes.  `--impl reference` times the CPU oracle (the
-restatement of the reference's per-request path; the Go + ONNX Runtime original cannot run here)
-on all host cores on a bounded sample of the same workload.
+Blocks in the same line (each with its own roofline / cpu_baseline / e2e where they apply):
+  path_a  configs[1] as worded: pre-assembled 1M x 64 f32 rows + rule sideband (igs_score_features)
+  c3      configs[2]: index build over 10M events / 1M accounts + 1M velocity queries
+  ltv     configs[3]: 256 -> 3 x 1024 -> 1 bf16 MLP over 4M players + the error distribution against the oracle
+  c5      configs[4] (N > 1): 100M tx split over the N GPUs: shard partition + fused scoring + one LTV evaluation
+          per player of the shard
+  live_loop  score a 65 536-tx micro-batch, then append it to the history (the reference's score-then-update order)
+
+`--impl reference` times the CPU restatement of the reference's per-request loop (oracle/; Go + ONNX Runtime +
+Redis cannot be built or run in this image) on all host threads, on the SAME workload: the full 1M-tx batch per
+step against the same players / history / model.
 """
 from __future__ import annotations
 
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -32,12 +42,24 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as ge  # noqa: E402
 
 N_TX = 1_000_000
+N_PLAYERS = 1_000_000
+N_EVENTS = 10_000_000
 N_TREES = 500
 LAT_BATCH = 65_536
-ALGO_BYTES_PER_TX = 256 + 48 + 8            # features + rule sideband in, result out
-MODEL_BYTES = N_TREES * (255 * 5 + 256 * 4)  # 1 149 500 B in the ABI layout (feat u8 + thr f32 + leaves)
+N_LTV = 4_000_000
+C5_TX = 100_000_000
+C5_PLAYERS = 4_000_000
+# SURVEY §8d algorithmic bytes
+FUSED_BYTES_PER_TX = 32 + 96 + 8            # tx record in + player row gather + result out
+PATH_A_BYTES_PER_TX = 256 + 48 + 8          # features + rule sideband in, result out
+MODEL_BYTES = N_TREES * (255 * 5 + 256 * 4)  # 1 149 500 B in the ABI layout, read once per launch
+K2_BYTES_PER_EVENT = 34                     # one read + one write of each 17 B record
+MLP_FLOP_PER_PLAYER = 2.0 * (256 * 1024 + 2 * 1024 * 1024 + 1024)
 METRIC = "transactions scored/sec"
 UNIT = "tx/s"
+WORKLOAD = ("fused production path: 1M compact tx (32 B) per GPU against 1M player rows + a resident 10M-event "
+            "index (C3 history) -> velocity lookup + 64-feature assembly + 8 rules + 500-tree depth-8 GBDT + "
+            "blend/action (C2 model and batch)")
 
 
 def env_int(k, d):
@@ -52,10 +74,36 @@ def load_peaks():
     if os.path.exists(p):
         try:
             j = json.load(open(p))
-            return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+            return {"hbm": float(j["hbm_gbs"]), "bf16": float(j.get("bf16_tflops_sustained", 1400.0)),
+                    "src": "measured (MEASURED_PEAKS.json)"}
         except Exception:
             pass
-    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+    return {"hbm": 6650.0, "bf16": 1400.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+def sha16(*paths):
+    h = hashlib.sha256()
+    for p in paths:
+        with open(os.path.join(ROOT, p), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_constants(kernel_key):
+    """Counters that only a profiler sees, from the committed capture summary (tools/ncu_constants.py writes
+    profiles/r2_ncu_constants.json from the .ncu-rep); `stale` = the kernel sources changed since the capture."""
+    p = os.path.join(ROOT, "profiles", "r2_ncu_constants.json")
+    if not os.path.exists(p):
+        return None
+    try:
+        rec = json.load(open(p)).get(kernel_key)
+        if not rec:
+            return None
+        rec = dict(rec)
+        rec["stale"] = rec.get("source_sha16") != sha16(*rec.get("sources", []))
+        return rec
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -108,140 +156,408 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def shard_skew(world, synth, pkg):
-    """max / mean shard size when a C5-style batch (Zipf(1.1) accounts) is partitioned by
-    splitmix64(account) % n_shards — the only scaling risk of a path without a collective."""
-    if world == 1:
-        return {"n_shards": 1, "max_over_mean": 1.0}
-    tx = synth.make_tx(2_000_000, 4_000_000, seed=synth.MASTER_SEED)
-    sizes = np.bincount(pkg.sharding.shard_of(tx["account"], world), minlength=world)
-    return {"n_shards": world, "max_over_mean": float(sizes.max() / sizes.mean()), "sample_tx": int(tx.shape[0])}
-
-
 def pinned_array(lib, shape, dtype):
     dtype = np.dtype(dtype)
     nbytes = int(np.prod(shape)) * dtype.itemsize
-    p = lib.igs_alloc_pinned(nbytes)
+    p = lib.igs_alloc_pinned(max(nbytes, 1))
     if not p:
         raise RuntimeError("igs_alloc_pinned failed")
     buf = (C.c_uint8 * nbytes).from_address(p)
     return np.frombuffer(buf, dtype=dtype).reshape(shape), p
 
 
-def cpu_baseline(orc, cfg, model, feats, rows, threads, target_s=3.0):
-    """Oracle (kind "port") timed on `threads` host threads on a bounded sample of the workload."""
-    n_cal = 4096
-    t0 = time.perf_counter()
-    orc.score_features(cfg, model, feats[:n_cal], rows[:n_cal], threads=threads)
-    dt = max(time.perf_counter() - t0, 1e-4)
-    n = int(min(feats.shape[0], max(n_cal, target_s * n_cal / dt)))
-    t0 = time.perf_counter()
-    orc.score_features(cfg, model, feats[:n], rows[:n], threads=threads)
-    dt = time.perf_counter() - t0
-    return n / dt, n, dt
+def workload_inputs(synth, rank, n_tx=N_TX):
+    """The headline workload's inputs, seeded per rank (both arms build exactly these)."""
+    seed = synth.MASTER_SEED + 7919 * rank
+    return {
+        "model": synth.make_gbdt(n_trees=N_TREES),
+        "players": synth.make_players(N_PLAYERS, seed=seed),
+        "events": synth.make_events(N_EVENTS, N_PLAYERS, seed=seed),
+        "tx": synth.make_tx(n_tx, N_PLAYERS, seed=seed),
+    }
 
 
+# ------------------------------------------------------------------------------------------------
+# reference arm
+# ------------------------------------------------------------------------------------------------
 def run_reference(args, rank, world):
-    """--impl reference: the CPU restatement of the reference's per-request scoring loop
-    (ml/onnx_model.go:311-326 PredictBatch + scoring/engine.go:262-323), all host threads."""
+    """--impl reference: the CPU restatement of the reference's per-request scoring loop (ml/onnx_model.go:311-326
+    PredictBatch, scoring/engine.go:262-323 Score, features/redis_store.go:60-116 lookups answered in O(log n) like
+    Redis's ZCOUNT), all host threads, the full 1M-tx batch per step."""
     if rank != 0:
         return
     from oracle import oracle as orc
     from tests import synth
     pkg = ge.load_package()
     threads = os.cpu_count() or 1
-    model = synth.make_gbdt(n_trees=N_TREES)
-    n_pool = 262_144
-    feats, rows = synth.make_feature_batch(n_pool)
+    w = workload_inputs(synth, 0, args.n_tx)
     cfg = orc.default_config(model_kind=pkg.abi.MODEL_GBDT)
-    # size the per-step sample so warmup+steps end within a few minutes
-    rate, _, _ = cpu_baseline(orc, cfg, model, feats, rows, threads, target_s=1.0)
-    n_step = int(min(n_pool, max(4096, rate * 2.0)))
+    t0 = time.perf_counter()
+    index = orc.FastIndex(w["events"], N_PLAYERS)
+    build_s = time.perf_counter() - t0
+    n = w["tx"].shape[0]
     for _ in range(args.warmup):
-        orc.score_features(cfg, model, feats[:n_step], rows[:n_step], threads=threads)
+        index.score_batch(cfg, w["model"], w["players"], w["tx"], threads=threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        orc.score_features(cfg, model, feats[:n_step], rows[:n_step], threads=threads)
+        index.score_batch(cfg, w["model"], w["players"], w["tx"], threads=threads)
     dt = time.perf_counter() - t0
-    value = n_step * args.steps / dt
-    sample = f"{n_step} tx per step from the same seeded C2 batch, {N_TREES} trees depth 8"
+    value = n * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": "C2: 1M tx x 64 f32 features, 500-tree depth-8 GBDT + 8 rules + blend "
-                               "(bounded sample per step)", "n_trees": N_TREES, "n_features": 64},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "tx_per_gpu": n, "n_trees": N_TREES, "n_features": 64, "depth": 8,
+                   "players": N_PLAYERS, "events": N_EVENTS},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"the full {n}-tx batch per step, {threads} host threads over static chunks; history "
+                                   f"indexed once before the timed region ({build_s:.1f} s, single thread)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference Go + ONNX Runtime + Redis cannot be built or run in this image; this is "
-                "the C restatement of its per-request loop (oracle/), all host threads",
+        "note": "reference Go + ONNX Runtime + Redis cannot be built or run in this image; this is the C restatement "
+                "of its per-request loop (oracle/): per tx, window lookups by binary search (Redis answers ZCOUNT in "
+                "O(log n)), extractFeatures, Normalize, a naive per-row walk of the 500 trees, applyRules, blend",
     }
     print(json.dumps(line), flush=True)
 
 
-def run_ltv(args, rank, world, local, pkg, lib, torch, dist, synth):
-    """Config C4: 256 -> 3 x 1024 -> 1 bf16 MLP over n players per GPU (device-resident inputs)."""
-    abi = pkg.abi
-    n = args.n_players
-    dev = torch.device("cuda", local)
-    eng = pkg.Engine(device=local)
-    eng.load_mlp(synth.make_mlp())
-    base_x, base_rows = synth.make_ltv_inputs(65536, seed=synth.MASTER_SEED + rank)
-    reps = -(-n // 65536)
-    d_x = torch.from_numpy(base_x.view(np.int16)).to(dev).repeat(reps, 1)[:n].contiguous()
-    d_rows = torch.from_numpy(base_rows.view(np.uint8).reshape(65536, -1)).to(dev).repeat(reps, 1)[:n].contiguous()
-    d_out = torch.zeros((n, 32), dtype=torch.uint8, device=dev)
-    d_raw = torch.zeros(n, dtype=torch.float32, device=dev)
-    stream = torch.cuda.current_stream().cuda_stream
+# ------------------------------------------------------------------------------------------------
+# my arm
+# ------------------------------------------------------------------------------------------------
+class Ctx:
+    pass
+
+
+def timed_events(ctx, fn, steps, warmup):
+    """Per-step ms (max over ranks) of `fn` queued `steps` times on the current stream, after `warmup` runs."""
+    torch = ctx.torch
+    for _ in range(warmup):
+        fn()
+    ctx.barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record()
+    for i in range(steps):
+        fn()
+        evs[i + 1].record()
+    ctx.barrier()
+    total = ctx.max_over_ranks(evs[0].elapsed_time(evs[-1]))
+    return total / steps, [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+
+
+def timed_wall(ctx, fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    ctx.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    ctx.torch.cuda.synchronize()
+    return ctx.max_over_ranks((time.perf_counter() - t0) * 1e3) / steps
+
+
+def latency(fn_of_offset, n, batches=1020, skip=20):
+    lats = []
+    for i in range(batches):
+        off = (i * LAT_BATCH) % (n - LAT_BATCH)
+        t0 = time.perf_counter()
+        fn_of_offset(off)
+        lats.append(time.perf_counter() - t0)
+    lats = np.array(lats[skip:]) * 1e3
+    return {"batch": LAT_BATCH, "batches": int(lats.size), "p50_ms": float(np.percentile(lats, 50)),
+            "p99_ms": float(np.percentile(lats, 99)), "max_ms": float(lats.max())}
+
+
+def check(st, lib, eng):
+    if st != 0:
+        raise RuntimeError(lib.igs_last_error(eng.handle).decode())
+
+
+def block_path_a(ctx, w):
+    """configs[1] as worded: pre-assembled normalised rows + the rule sideband, igs_score_features."""
+    lib, eng, torch, abi = ctx.lib, ctx.eng, ctx.torch, ctx.abi
+    n = ctx.args.n_tx
+    feats, rows = ctx.synth.make_feature_batch(n, seed=ctx.synth.MASTER_SEED + 7919 * ctx.rank)
+    d_feats = torch.from_numpy(feats).to(ctx.dev)
+    d_rows = torch.from_numpy(rows.view(np.uint8).reshape(n, -1)).to(ctx.dev)
+    d_out = torch.zeros((n, 8), dtype=torch.uint8, device=ctx.dev)
+    ms, per = timed_events(ctx, lambda: eng.score_features_device(ctx.cfg, d_feats.data_ptr(), d_rows.data_ptr(), n,
+                                                                  d_out.data_ptr(), 0, ctx.stream),
+                           ctx.args.steps, ctx.args.warmup)
+    got = np.frombuffer(d_out[:2048].cpu().numpy().tobytes(), dtype=abi.result_dtype)
+    h_feats, p1 = pinned_array(lib, (n, 64), np.float32)
+    h_rows, p2 = pinned_array(lib, (n,), abi.rule_row_dtype)
+    h_out, p3 = pinned_array(lib, (n,), abi.result_dtype)
+    h_feats[:] = feats
+    h_rows[:] = rows
+    e2e_ms = timed_wall(ctx, lambda: check(lib.igs_score_features(eng.handle, C.byref(ctx.cfg), h_feats.ctypes.data,
+                                                                  h_rows.ctypes.data, n, h_out.ctypes.data, None), lib, eng),
+                        ctx.e2e_steps, 2)
+    assert h_out[:2048].tobytes() == got.tobytes(), "host-buffer and device-buffer paths disagree"
+    k_ms = float(np.mean(per))
+    ach = (n * PATH_A_BYTES_PER_TX + MODEL_BYTES) / (k_ms * 1e-3) / 1e9
+    visits = n * N_TREES * 8 / (k_ms * 1e-3)
+    out = {"workload": "C2 as worded: 1M x 64 f32 pre-assembled rows + 48 B rule sideband per GPU, 500-tree depth-8 GBDT "
+                       "+ 8 rules + blend (igs_score_features)",
+           "value": n * ctx.world / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+           "e2e": {"value": n * ctx.world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(n * (256 + 48)),
+                   "d2h_bytes_per_step": int(n * 8), "api": "igs_score_features (pinned host buffers)",
+                   "note": "PCIe-bound: 312 B/tx over the host link"},
+           "roofline": {"bound": "hbm", "kernel": "k_score<features, Shape<12,20>>", "achieved": ach, "peak": ctx.peaks["hbm"],
+                        "unit": "GB/s", "frac": ach / ctx.peaks["hbm"], "launch_ms": k_ms,
+                        "note": "312 B/tx + model once; not the bounding resource (see on_chip)"},
+           "on_chip": {"node_visits_per_s": visits, "ncu": ncu_constants("k_score_features")}}
+    if ctx.rank == 0 and ctx.world == 1 and not ctx.args.skip_cpu:
+        from oracle import oracle as orc
+        ocfg = orc.default_config(model_kind=abi.MODEL_GBDT)
+        want = orc.score_features(ocfg, w["model"], feats[:2048], rows[:2048])
+        assert want.tobytes() == got.tobytes(), "path A disagrees with the oracle"
+    for p in (p1, p2, p3):
+        lib.igs_free_pinned(p)
+    del d_feats, d_rows, d_out
+    return out
+
+
+def block_c3(ctx, w):
+    """configs[2]: index build over the 10M-event history (device-resident columns and host columns) + 1M velocity
+    queries.  Roofline numerators are SURVEY §8d's: K2 34 B/event; K3 (H + Q) * 17 + Q * 100 B."""
+    lib, eng, torch, abi, synth = ctx.lib, ctx.eng, ctx.torch, ctx.abi, ctx.synth
+    ev = w["events"]
+    H, A, Q = len(ev), N_PLAYERS, ctx.args.n_tx
+    d_cols = [torch.from_numpy(a).to(ctx.dev) for a in (ev.account, ev.ts, ev.amount, ev.tx_type)]
+    cols = abi.EventCols(*(t.data_ptr() for t in d_cols))
+    launches0 = lib.igs_kernel_launches()
+
+    def build_dev():
+        check(lib.igs_load_events_device(eng.handle, C.byref(cols), None, H, A), lib, eng)
+
+    reps = max(3, min(ctx.args.steps, 5))
+    build_ms = timed_wall(ctx, build_dev, reps, 2)
+    build_launches = (lib.igs_kernel_launches() - launches0) // (reps + 2)
+    del d_cols
+    # end to end: pinned host columns -> resident index (17 B/event over PCIe + the same kernels)
+    h_cols, ptrs = [], []
+    for a in (ev.account, ev.ts, ev.amount, ev.tx_type):
+        h, p = pinned_array(lib, a.shape, a.dtype)
+        h[:] = a
+        h_cols.append(h)
+        ptrs.append(p)
+    hc = abi.EventCols(*(h.ctypes.data for h in h_cols))
+    e2e_ms = timed_wall(ctx, lambda: check(lib.igs_load_events(eng.handle, C.byref(hc), H, A), lib, eng), 3, 1)
+    for p in ptrs:
+        lib.igs_free_pinned(p)
+    q = synth.queries_of(w["tx"])
+    d_q = torch.from_numpy(q.view(np.uint8).reshape(Q, -1)).to(ctx.dev)
+    d_v = torch.zeros((Q, 128), dtype=torch.uint8, device=ctx.dev)
+    q_ms, _ = timed_events(ctx, lambda: check(lib.igs_get_velocity_device(eng.handle, d_q.data_ptr(), Q, d_v.data_ptr(),
+                                                                          ctx.stream), lib, eng), ctx.args.steps, ctx.args.warmup)
+    algo = H * K2_BYTES_PER_EVENT + (H + Q) * 17 + Q * 100
+    ach = algo / ((build_ms + q_ms) * 1e-3) / 1e9
+    out = {"workload": f"C3: index build over {H} events / {A} accounts (48 h, Zipf 1.05, bursts, 1 % forced (ts, amount) "
+                       f"collisions) + {Q} velocity queries, per GPU",
+           "index_build": {"ms": build_ms, "events_per_s": H * ctx.world / (build_ms * 1e-3),
+                           "api": "igs_load_events_device (columns resident in HBM; wall clock of the synchronous call, "
+                                  "which includes its three host read-backs)", "kernel_launches": int(build_launches)},
+           "velocity_queries": {"ms": q_ms, "queries_per_s": Q * ctx.world / (q_ms * 1e-3)},
+           "value": H * ctx.world / ((build_ms + q_ms) * 1e-3), "unit": "events/s",
+           "e2e": {"value": H * ctx.world / (e2e_ms * 1e-3), "unit": "events/s", "ms": e2e_ms,
+                   "h2d_bytes_per_step": int(H * 17), "d2h_bytes_per_step": 16,
+                   "api": "igs_load_events (pinned host columns)"},
+           "roofline": {"bound": "hbm", "kernel": "index build (K2 sort + K3 scans) + k_velocity", "achieved": ach,
+                        "peak": ctx.peaks["hbm"], "unit": "GB/s", "frac": ach / ctx.peaks["hbm"],
+                        "algorithmic_bytes": int(algo),
+                        "note": "SURVEY §8d numerator: 34 B/event for the sort + (H + Q) * 17 + Q * 100 B for scan and "
+                                "queries; the index itself is 72 B/event written, which the numerator does not count",
+                        "per_kernel": ncu_constants("c3_build")}}
+    if ctx.rank == 0 and ctx.world == 1 and not ctx.args.skip_cpu:
+        from oracle import oracle as orc
+        hs, qs = 1_000_000, 100_000                 # bounded sample: a tenth of the history, same generator
+        evs = synth.make_events(hs, N_PLAYERS // 10, seed=synth.MASTER_SEED)
+        qq = synth.queries_of(synth.make_tx(qs, N_PLAYERS // 10, seed=synth.MASTER_SEED))
+        t0 = time.perf_counter()
+        ix = orc.FastIndex(evs, N_PLAYERS // 10)
+        vb = ix.velocity(qq)
+        dt = time.perf_counter() - t0
+        ix.close()
+        out["cpu_baseline"] = {"value": hs / dt, "unit": "events/s", "cores": 1, "kind": "port",
+                               "sample": f"{hs} events / {N_PLAYERS // 10} accounts indexed + {qs} queries ({dt:.1f} s, "
+                                         "qsort + prefix columns + binary searches, one thread)"}
+        # the sample's queries on the GPU: same answers
+        eng.load_events(evs, N_PLAYERS // 10)
+        assert eng.get_velocity(qq).tobytes() == vb.tobytes(), "C3 sample: velocity blocks differ from the CPU port"
+    eng.load_events(ev, A)                           # restore the headline history
+    return out
+
+
+def block_ltv(ctx):
+    """configs[3]: 256 -> 3 x 1024 -> 1 bf16 MLP over 4M players per GPU + the end-to-end error against the oracle."""
+    lib, eng, torch, abi, synth = ctx.lib, ctx.eng, ctx.torch, ctx.abi, ctx.synth
+    n = ctx.args.n_players
+    mlp = synth.make_mlp()
+    eng.load_mlp(mlp)
+    base = 65536
+    base_x, base_rows = synth.make_ltv_inputs(base, seed=synth.MASTER_SEED + ctx.rank)
+    reps = -(-n // base)
+    d_x = torch.from_numpy(base_x.view(np.int16)).to(ctx.dev).repeat(reps, 1)[:n].contiguous()
+    d_rows = torch.from_numpy(base_rows.view(np.uint8).reshape(base, -1)).to(ctx.dev).repeat(reps, 1)[:n].contiguous()
+    d_out = torch.zeros((n, 32), dtype=torch.uint8, device=ctx.dev)
+    d_raw = torch.zeros(n, dtype=torch.float32, device=ctx.dev)
+    l0 = lib.igs_kernel_launches()
+    steps = max(3, min(ctx.args.steps, 8))
+    ms, _ = timed_events(ctx, lambda: check(lib.igs_ltv_batch_device(eng.handle, d_x.data_ptr(), d_rows.data_ptr(), n,
+                                                                     d_out.data_ptr(), d_raw.data_ptr(), ctx.stream), lib, eng),
+                         steps, 3)
+    launches = (lib.igs_kernel_launches() - l0) // (steps + 3)
+    ach = MLP_FLOP_PER_PLAYER * n / (ms * 1e-3) / 1e12
+    out = {"workload": f"C4: LTV MLP 256 -> 3 x 1024 -> 1 over {n} players per GPU, bf16 operands, fp32 accumulate, "
+                       "layer 4 + fp64 epilogue fused into layer 3",
+           "value": n * ctx.world / (ms * 1e-3), "unit": "players/s", "ms_per_step": ms, "kernel_launches_per_step": int(launches),
+           "roofline": {"bound": "tensor", "kernel": "k_mlp_gemm (3 launches per 262 144-row chunk)", "achieved": ach,
+                        "peak": ctx.peaks["bf16"], "unit": "TFLOP/s", "frac": ach / ctx.peaks["bf16"],
+                        "peak_source": "sustained bf16, " + ctx.peaks["src"], "ncu": ncu_constants("k_mlp_gemm")}}
+    # end to end through the host-buffer call on a bounded slice (512 B/player over PCIe dominates)
+    m = min(n, 524_288)
+    h_x, p1 = pinned_array(lib, (m, 256), np.uint16)
+    h_r, p2 = pinned_array(lib, (m,), abi.ltv_row_dtype)
+    h_o, p3 = pinned_array(lib, (m,), abi.ltv_result_dtype)
+    h_x[:] = np.tile(base_x, (-(-m // base), 1))[:m]
+    h_r[:] = np.tile(base_rows, -(-m // base))[:m]
+    e2e_ms = timed_wall(ctx, lambda: check(lib.igs_ltv_batch(eng.handle, h_x.ctypes.data, h_r.ctypes.data, m,
+                                                             h_o.ctypes.data, None), lib, eng), 3, 1)
+    out["e2e"] = {"value": m * ctx.world / (e2e_ms * 1e-3), "unit": "players/s", "h2d_bytes_per_step": int(m * (512 + 80)),
+                  "d2h_bytes_per_step": int(m * 32), "api": f"igs_ltv_batch, {m} players per call (pinned host buffers)"}
+    for p in (p1, p2, p3):
+        lib.igs_free_pinned(p)
+    if ctx.rank == 0 and ctx.world == 1 and not ctx.args.skip_cpu:
+        # error distribution of the fp32 model output over 4096 sampled players (bf16 flips next to the ReLU zero
+        # are the only source: both sides round operands and activations to bf16 at the same points)
+        from concurrent.futures import ThreadPoolExecutor
+        from oracle import oracle as orc
+        rng = np.random.default_rng(synth.MASTER_SEED)
+        pick = np.sort(rng.choice(min(n, base), size=4096, replace=False))
+        got = d_raw[torch.from_numpy(pick).to(ctx.dev)].cpu().numpy().astype(np.float64)
+        threads = os.cpu_count() or 1
+        chunks = np.array_split(pick, threads * 4)
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(threads) as ex:
+            want = np.concatenate(list(ex.map(lambda c: orc.mlp_forward(mlp, base_x[c]), chunks))).astype(np.float64)
+        dt = time.perf_counter() - t0
+        rel = np.abs(got - want) / np.maximum(1.0, np.abs(want))
+        out["error_vs_oracle"] = {"rows": int(pick.size), "metric": "|y - y_oracle| / max(1, |y_oracle|), fp32 model output",
+                                  "max": float(rel.max()), "p99": float(np.percentile(rel, 99)),
+                                  "p50": float(np.percentile(rel, 50)), "bit_identical_frac": float(np.mean(got == want)),
+                                  "rms_y": float(np.sqrt(np.mean(want ** 2)))}
+        out["cpu_baseline"] = {"value": pick.size / dt, "unit": "players/s", "cores": threads, "kind": "port",
+                               "sample": f"{pick.size} players through orc_mlp_forward on {threads} threads ({dt:.1f} s)"}
+    del d_x, d_rows, d_out, d_raw
+    return out
+
+
+def block_live_loop(ctx, w):
+    """Score a 65 536-tx micro-batch, then append it to the resident history — the reference's order
+    (Score, later UpdateFeatures; services/risk/cmd/main.go:219-224).  Events arrive in time order."""
+    lib, eng, abi, pkg = ctx.lib, ctx.eng, ctx.abi, ctx.pkg
+    ev = w["events"]
+    n_b = 48
+    t_start = int(ev.ts.max()) + 1
+    tx = ctx.synth.make_tx(LAT_BATCH * n_b, N_PLAYERS, seed=ctx.synth.MASTER_SEED + 99 + ctx.rank, t_lo=t_start,
+                           t_hi=t_start + 600)
+    tx = tx[np.argsort(tx["ts"], kind="stable")]
+    h_tx, p1 = pinned_array(lib, tx.shape, abi.tx_dtype)
+    h_out, p2 = pinned_array(lib, tx.shape, abi.result_dtype)
+    h_tx[:] = tx
+    lat, app = [], []
+    t_all = time.perf_counter()
+    for b in range(n_b):
+        sl = slice(b * LAT_BATCH, (b + 1) * LAT_BATCH)
+        t0 = time.perf_counter()
+        check(lib.igs_score_batch(eng.handle, C.byref(ctx.cfg), h_tx[sl].ctypes.data, LAT_BATCH, h_out[sl].ctypes.data,
+                                  None, None), lib, eng)
+        t1 = time.perf_counter()
+        part = pkg.Events(np.ascontiguousarray(tx["account"][sl]), np.ascontiguousarray(tx["ts"][sl]),
+                          np.ascontiguousarray(tx["amount"][sl]), np.ascontiguousarray(tx["tx_type"][sl]))
+        c = part.cols()
+        check(lib.igs_append_events(eng.handle, C.byref(c), LAT_BATCH), lib, eng)
+        t2 = time.perf_counter()
+        lat.append((t1 - t0) * 1e3)
+        app.append((t2 - t1) * 1e3)
+    total = ctx.max_over_ranks(time.perf_counter() - t_all)
+    warm = 8
+    steady = float(np.sum(lat[warm:]) + np.sum(app[warm:])) * 1e-3
+    out = {"workload": f"{n_b} micro-batches of {LAT_BATCH} tx in time order: igs_score_batch (host buffers), then "
+                       f"igs_append_events of the same transactions onto the {len(ev)}-event history",
+           "tx_per_s_steady": LAT_BATCH * (n_b - warm) / steady, "score_ms_p50": float(np.percentile(lat[warm:], 50)),
+           "score_ms_p99": float(np.percentile(lat[warm:], 99)), "append_ms_p50": float(np.percentile(app[warm:], 50)),
+           "append_ms_p99": float(np.percentile(app[warm:], 99)), "append_ms_max": float(np.max(app[warm:])),
+           "wall_s_all": total}
+    lib.igs_free_pinned(p1)
+    lib.igs_free_pinned(p2)
+    eng.load_events(ev, N_PLAYERS)
+    return out
+
+
+def block_c5(ctx, w):
+    """configs[4]: a 100M-tx batch over 4M players, split over the N GPUs by player hash.  Per GPU and step:
+    shard partition of a 100M/N-tx slice of the incoming stream (what the ingest tier does before routing), fused
+    scoring of the shard's own 100M/N tx, one LTV evaluation per player of the shard."""
+    lib, eng, torch, abi, synth = ctx.lib, ctx.eng, ctx.torch, ctx.abi, ctx.synth
+    world = ctx.world
+    n = C5_TX // world
+    n_pl = C5_PLAYERS // world
+    base_n = 2_000_000
+    seed = synth.MASTER_SEED + 31 * ctx.rank
+    # own shard: dense local player indices, C1 marginals, Zipf(1.1) accounts
+    base = synth.make_tx(base_n, min(n_pl, N_PLAYERS), seed=seed)
+    reps = -(-n // base_n)
+    d_tx = torch.from_numpy(base.view(np.uint8).reshape(base_n, -1)).to(ctx.dev).repeat(reps, 1)[:n].contiguous()
+    d_res = torch.zeros((n, 8), dtype=torch.uint8, device=ctx.dev)
+    # incoming slice with global account ids, to be partitioned into `world` shards
+    inc = synth.make_tx(base_n, C5_PLAYERS, seed=seed + 1)
+    d_inc = torch.from_numpy(inc.view(np.uint8).reshape(base_n, -1)).to(ctx.dev).repeat(reps, 1)[:n].contiguous()
+    d_part = torch.empty_like(d_inc)
+    d_perm = torch.zeros(n, dtype=torch.int32, device=ctx.dev)
+    d_off = torch.zeros(world + 1, dtype=torch.int32, device=ctx.dev)
+    # LTV inputs for the shard's players
+    bx, br = synth.make_ltv_inputs(65536, seed=seed)
+    r2 = -(-n_pl // 65536)
+    d_x = torch.from_numpy(bx.view(np.int16)).to(ctx.dev).repeat(r2, 1)[:n_pl].contiguous()
+    d_rows = torch.from_numpy(br.view(np.uint8).reshape(65536, -1)).to(ctx.dev).repeat(r2, 1)[:n_pl].contiguous()
+    d_lo = torch.zeros((n_pl, 32), dtype=torch.uint8, device=ctx.dev)
+
+    def part():
+        check(lib.igs_partition_tx_device(eng.handle, d_inc.data_ptr(), n, world, d_part.data_ptr(), d_perm.data_ptr(),
+                                          d_off.data_ptr(), ctx.stream), lib, eng)
+
+    def score():
+        check(lib.igs_score_batch_device(eng.handle, C.byref(ctx.cfg), d_tx.data_ptr(), n, d_res.data_ptr(), None, None,
+                                         ctx.stream), lib, eng)
+
+    def ltv():
+        check(lib.igs_ltv_batch_device(eng.handle, d_x.data_ptr(), d_rows.data_ptr(), n_pl, d_lo.data_ptr(), None,
+                                       ctx.stream), lib, eng)
 
     def step():
-        st = lib.igs_ltv_batch_device(eng.handle, d_x.data_ptr(), d_rows.data_ptr(), n, d_out.data_ptr(),
-                                      d_raw.data_ptr(), stream)
-        assert st == 0, lib.igs_last_error(eng.handle).decode()
+        part()
+        score()
+        ltv()
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item()) / args.steps
-    clocks = sampler.stop() if rank == 0 else None
-    if rank == 0:
-        flop = 2.0 * (256 * 1024 + 2 * 1024 * 1024 + 1024) * n
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
-            os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-        peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        ach = flop / (ms * 1e-3) / 1e12
-        print(json.dumps({
-            "metric": "players scored/sec (LTV MLP)", "value": n * world / (ms * 1e-3), "unit": "players/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"C4: LTV MLP 256 -> 3 x 1024 -> 1 over {n} players per GPU, bf16 operands, "
-                                   "fp32 accumulate, activations round-trip HBM between layers"},
-            "clocks": clocks, "gpu_launches": args.steps * 4 * (-(-n // 262144)),
-            "roofline": {"bound": "tensor", "kernel": "k_mlp_gemm (3 launches per 262144-row chunk)",
-                         "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
-                         "peak_source": "measured sustained bf16 (MEASURED_PEAKS.json)" if peaks else "fallback"},
-        }), flush=True)
-    eng.close()
-    if world > 1:
-        dist.destroy_process_group()
+    steps = 3
+    ms, _ = timed_events(ctx, step, steps, 1)
+    p_ms, _ = timed_events(ctx, part, steps, 1)
+    s_ms, _ = timed_events(ctx, score, steps, 1)
+    l_ms, _ = timed_events(ctx, ltv, steps, 1)
+    sizes = np.bincount(ctx.pkg.sharding.shard_of(inc["account"], world), minlength=world)
+    part_bytes = n * (32 + 32 + 4)
+    out = {"workload": f"C5: {C5_TX} tx over {C5_PLAYERS} players split over {world} GPUs by player hash; per GPU and step: "
+                       f"partition of a {n}-tx slice into {world} shards + fused scoring of {n} tx (1M-player table, "
+                       f"10M-event index) + LTV MLP over {n_pl} players",
+           "value": n * world / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+           "parts_ms": {"partition": p_ms, "fused_score": s_ms, "ltv": l_ms},
+           "partition_roofline": {"bound": "hbm", "achieved": part_bytes / (p_ms * 1e-3) / 1e9, "peak": ctx.peaks["hbm"],
+                                  "unit": "GB/s", "frac": part_bytes / (p_ms * 1e-3) / 1e9 / ctx.peaks["hbm"],
+                                  "algorithmic_bytes": int(part_bytes)},
+           "shard_skew": {"n_shards": world, "max_over_mean": float(sizes.max() / sizes.mean())},
+           "data": "2M-tx seeded base batches tiled to size on the device"}
+    del d_tx, d_res, d_inc, d_part, d_perm, d_x, d_rows, d_lo
+    return out
 
 
 def main():
@@ -251,14 +567,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n-tx", type=int, default=N_TX)
+    ap.add_argument("--n-players", type=int, default=N_LTV, help="players of the LTV block (C4)")
     ap.add_argument("--skip-latency", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
-    ap.add_argument("--skip-fused", action="store_true")
-    ap.add_argument("--workload", default="score", choices=["score", "ltv"],
-                    help="score = the headline C2 line (default); ltv = config C4, the LTV MLP head")
-    ap.add_argument("--n-players", type=int, default=4_000_000)
+    ap.add_argument("--skip", default="", help="comma list of blocks to skip: path_a,c3,ltv,c5,live_loop")
+    ap.add_argument("--c5", action="store_true", help="run the C5 block at N = 1 too (100M tx on one GPU)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    skip = set(filter(None, args.skip.split(",")))
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
@@ -281,273 +597,166 @@ def main():
     lib = abi.load_library()
     from tests import synth
 
-    if args.workload == "ltv":
-        run_ltv(args, rank, world, local, pkg, lib, torch, dist, synth)
-        return
-
-    n = args.n_tx
-    model = synth.make_gbdt(n_trees=N_TREES)
-    feats, rows = synth.make_feature_batch(n, seed=synth.MASTER_SEED + 7919 * rank)
-    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
-    eng = pkg.Engine(device=local)
-    eng.load_gbdt(model)
-
-    dev = torch.device("cuda", local)
-    d_feats = torch.from_numpy(feats).to(dev)
-    d_rows = torch.from_numpy(rows.view(np.uint8).reshape(n, -1)).to(dev)
-    d_out = torch.zeros((n, 8), dtype=torch.uint8, device=dev)
-    stream = torch.cuda.current_stream().cuda_stream
-
-    def step():
-        eng.score_features_device(cfg, d_feats.data_ptr(), d_rows.data_ptr(), n, d_out.data_ptr(), 0, stream)
+    ctx = Ctx()
+    ctx.args, ctx.rank, ctx.world, ctx.local = args, rank, world, local
+    ctx.torch, ctx.dist, ctx.pkg, ctx.abi, ctx.lib, ctx.synth = torch, dist, pkg, abi, lib, synth
+    ctx.dev = torch.device("cuda", local)
+    ctx.stream = torch.cuda.current_stream().cuda_stream
+    ctx.peaks = load_peaks()
+    ctx.e2e_steps = max(3, min(args.steps, 10))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput (`value`) and per-launch time of the score kernel ----------
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=ctx.dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ctx.barrier, ctx.max_over_ranks = barrier, max_over_ranks
+
+    n = args.n_tx
+    w = workload_inputs(synth, rank, n)
+    ctx.cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    eng = pkg.Engine(device=local)
+    ctx.eng = eng
+    eng.load_gbdt(w["model"])
+    eng.load_players(w["players"])
+    t0 = time.perf_counter()
+    eng.load_events(w["events"], N_PLAYERS)
+    first_load_s = time.perf_counter() - t0
+
+    # ---- headline: the fused production path ---------------------------------------------------------
+    d_tx = torch.from_numpy(w["tx"].view(np.uint8).reshape(n, -1)).to(ctx.dev)
+    d_out = torch.zeros((n, 8), dtype=torch.uint8, device=ctx.dev)
+
+    def step():
+        check(lib.igs_score_batch_device(eng.handle, C.byref(ctx.cfg), d_tx.data_ptr(), n, d_out.data_ptr(), None, None,
+                                         ctx.stream), lib, eng)
+
     for _ in range(args.warmup):
         step()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    barrier()
-    evs[0].record()
-    for i in range(args.steps):
-        step()
-        evs[i + 1].record()
-    barrier()
-    total_ms = evs[0].elapsed_time(evs[-1])
-    per_launch_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms_max = float(t.item())
-    value = n * world * args.steps / (total_ms_max * 1e-3)
-
-    # sanity: the bench batch really is what the oracle says (small prefix, rank 0)
+    l0 = lib.igs_kernel_launches()
+    ms, per_step = timed_events(ctx, step, args.steps, 0)
+    gpu_launches = int(lib.igs_kernel_launches() - l0)
+    value = n * world / (ms * 1e-3)
     got = np.frombuffer(d_out[:2048].cpu().numpy().tobytes(), dtype=abi.result_dtype)
 
-    # ---- end to end through the host-buffer C ABI (pinned host memory) --------------------------
-    h_feats, p1 = pinned_array(lib, (n, 64), np.float32)
-    h_rows, p2 = pinned_array(lib, (n,), abi.rule_row_dtype)
-    h_out, p3 = pinned_array(lib, (n,), abi.result_dtype)
-    h_feats[:] = feats
-    h_rows[:] = rows
+    h_tx, p1 = pinned_array(lib, (n,), abi.tx_dtype)
+    h_out, p2 = pinned_array(lib, (n,), abi.result_dtype)
+    h_tx[:] = w["tx"]
 
     def e2e_step():
-        st = lib.igs_score_features(eng.handle, C.byref(cfg), h_feats.ctypes.data, h_rows.ctypes.data,
-                                    n, h_out.ctypes.data, None)
-        if st != 0:
-            raise RuntimeError(lib.igs_last_error(eng.handle).decode())
+        check(lib.igs_score_batch(eng.handle, C.byref(ctx.cfg), h_tx.ctypes.data, n, h_out.ctypes.data, None, None), lib, eng)
 
-    e2e_steps = max(3, min(args.steps, 10))
-    for _ in range(2):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = n * world * e2e_steps / float(t.item())
+    e2e_ms = timed_wall(ctx, e2e_step, ctx.e2e_steps, 2)
     assert h_out[:2048].tobytes() == got.tobytes(), "host-buffer and device-buffer paths disagree"
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- p99 batch latency: 65 536-tx batches, host call -> results visible ---------------------
     lat = None
     if not args.skip_latency and rank == 0:
-        nb = LAT_BATCH
-        lats = []
-        for i in range(1020):
-            off = (i * nb) % (n - nb)
-            t0 = time.perf_counter()
-            st = lib.igs_score_features(eng.handle, C.byref(cfg), h_feats[off:].ctypes.data,
-                                        h_rows[off:].ctypes.data, nb, h_out[off:].ctypes.data, None)
-            lats.append(time.perf_counter() - t0)
-            assert st == 0
-        lats = np.array(lats[20:]) * 1e3
-        lat = {"batch": nb, "batches": int(lats.size), "p50_ms": float(np.percentile(lats, 50)),
-               "p99_ms": float(np.percentile(lats, 99)), "max_ms": float(lats.max())}
+        lat = latency(lambda off: check(lib.igs_score_batch(eng.handle, C.byref(ctx.cfg), h_tx[off:].ctypes.data, LAT_BATCH,
+                                                            h_out[off:].ctypes.data, None, None), lib, eng), n)
 
-    # ---- the fused production path (compact tx in, device-side velocity + assembly) -------------
-    fused = None
-    if not args.skip_fused:
-        n_pl, n_ev = 500_000, 5_000_000
-        players = synth.make_players(n_pl, seed=synth.MASTER_SEED + rank)
-        events = synth.make_events(n_ev, n_pl, seed=synth.MASTER_SEED + rank)
-        txb = synth.make_tx(n, n_pl, seed=synth.MASTER_SEED + rank)
-        t0 = time.perf_counter()
-        eng.load_players(players)
-        eng.load_events(events, n_pl)
-        load_s = time.perf_counter() - t0
-        d_tx = torch.from_numpy(txb.view(np.uint8).reshape(n, -1)).to(dev)
-        h_tx, p4 = pinned_array(lib, (n,), abi.tx_dtype)
-        h_tx[:] = txb
-
-        def fstep():
-            st = lib.igs_score_batch_device(eng.handle, C.byref(cfg), d_tx.data_ptr(), n, d_out.data_ptr(),
-                                            None, None, stream)
-            assert st == 0, lib.igs_last_error(eng.handle).decode()
-
-        def fe2e():
-            st = lib.igs_score_batch(eng.handle, C.byref(cfg), h_tx.ctypes.data, n, h_out.ctypes.data, None, None)
-            assert st == 0, lib.igs_last_error(eng.handle).decode()
-
-        for _ in range(args.warmup):
-            fstep()
-        barrier()
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record()
-        for _ in range(args.steps):
-            fstep()
-        f1.record()
-        barrier()
-        t = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        f_ms = float(t.item()) / args.steps
-        for _ in range(2):
-            fe2e()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            fe2e()
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        flat = None
-        if not args.skip_latency and rank == 0:
-            nb = LAT_BATCH
-            fl = []
-            for i in range(1020):
-                off = (i * nb) % (n - nb)
-                t0 = time.perf_counter()
-                st = lib.igs_score_batch(eng.handle, C.byref(cfg), h_tx[off:].ctypes.data, nb, h_out[off:].ctypes.data,
-                                         None, None)
-                fl.append(time.perf_counter() - t0)
-                assert st == 0
-            fl = np.array(fl[20:]) * 1e3
-            flat = {"batch": nb, "batches": int(fl.size), "p50_ms": float(np.percentile(fl, 50)),
-                    "p99_ms": float(np.percentile(fl, 99)), "max_ms": float(fl.max())}
-        fused = {"workload": f"per GPU: {n} compact tx (32 B) against {n_pl} players + {n_ev}-event index, "
-                             "velocity + assembly + rules + 500-tree GBDT + blend in one kernel",
-                 "value": n * world / (f_ms * 1e-3), "unit": UNIT, "ms_per_step": f_ms,
-                 "e2e": {"value": n * world * e2e_steps / float(t.item()), "unit": UNIT,
-                         "h2d_bytes_per_step": int(n * 32), "d2h_bytes_per_step": int(n * 8),
-                         "api": "igs_score_batch (pinned host buffers)"},
-                 "p99_batch_latency": flat, "index_build_s": load_s, "algorithmic_bytes_per_tx": 136}
-        lib.igs_free_pinned(p4)
-
-        # the same path with the identifier inputs on the device: unique devices / IPs from
-        # the event index, rule 8 from three 100k-member blacklist sets, 24 B/tx of identifiers in
-        ev_ids = synth.make_event_ids(events, seed=synth.MASTER_SEED + rank)
-        t0 = time.perf_counter()
-        eng.load_events(ev_ids, n_pl)
-        load_ids_s = time.perf_counter() - t0
-        rng = np.random.default_rng(synth.MASTER_SEED + rank)
-        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
-            eng.blacklist_load(kind, rng.integers(1, 1 << 63, 100_000, dtype=np.uint64))
-        ids = np.zeros(n, dtype=abi.tx_ids_dtype)
-        ids["device"] = ev_ids.device[rng.integers(0, n_ev, n)]
-        ids["fingerprint"] = rng.integers(1, 1 << 63, n, dtype=np.uint64)
-        ids["ip"] = ev_ids.ip[rng.integers(0, n_ev, n)]
-        d_ids = torch.from_numpy(ids.view(np.uint8).reshape(n, -1)).to(dev)
-
-        def istep():
-            st = lib.igs_score_batch_ids_device(eng.handle, C.byref(cfg), d_tx.data_ptr(), d_ids.data_ptr(), n,
-                                                d_out.data_ptr(), None, None, stream)
-            assert st == 0, lib.igs_last_error(eng.handle).decode()
-
-        for _ in range(args.warmup):
-            istep()
-        barrier()
-        i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        i0.record()
-        for _ in range(args.steps):
-            istep()
-        i1.record()
-        barrier()
-        t = torch.tensor([i0.elapsed_time(i1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        i_ms = float(t.item()) / args.steps
-        fused["with_identifiers"] = {
-            "workload": "same, history with device / IP columns (exact uniques from the index) + 3 x 100k-member "
-                        "blacklist sets probed per tx (igs_score_batch_ids_device)",
-            "value": n * world / (i_ms * 1e-3), "unit": UNIT, "ms_per_step": i_ms, "index_build_s": load_ids_s,
-            "algorithmic_bytes_per_tx": 160}
-        for kind in (abi.BL_DEVICE, abi.BL_FINGERPRINT, abi.BL_IP):
-            eng.blacklist_load(kind, np.zeros(0, np.uint64))
-
-    # ---- CPU baseline (oracle port) on rank 0, N=1 only ----------------------------------------
+    # ---- CPU baseline of the headline (oracle port), rank 0 at N = 1 only ------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         from oracle import oracle as orc
         threads = os.cpu_count() or 1
         ocfg = orc.default_config(model_kind=abi.MODEL_GBDT)
-        want = orc.score_features(ocfg, model, feats[:2048], rows[:2048])
+        t0 = time.perf_counter()
+        index = orc.FastIndex(w["events"], N_PLAYERS)
+        build_s = time.perf_counter() - t0
+        want = index.score_batch(ocfg, w["model"], w["players"], w["tx"][:2048], threads=threads)
         assert want.tobytes() == got.tobytes(), "bench batch disagrees with the oracle"
-        r_all, n_all, s_all = cpu_baseline(orc, ocfg, model, feats, rows, threads, target_s=4.0)
-        r_one, n_one, s_one = cpu_baseline(orc, ocfg, model, feats, rows, 1, target_s=3.0)
-        cpu = {"value": r_all, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"first {n_all} tx of the same batch ({s_all:.1f} s wall on {threads} threads)",
-               "single_thread": {"value": r_one, "sample": f"first {n_one} tx ({s_one:.1f} s)"}}
+        n_cal = 8192
+        t0 = time.perf_counter()
+        index.score_batch(ocfg, w["model"], w["players"], w["tx"][:n_cal], threads=threads)
+        rate = n_cal / max(time.perf_counter() - t0, 1e-4)
+        n_s = int(min(n, max(n_cal, rate * 6.0)))
+        t0 = time.perf_counter()
+        index.score_batch(ocfg, w["model"], w["players"], w["tx"][:n_s], threads=threads)
+        s_all = time.perf_counter() - t0
+        n_1 = int(min(n, max(2048, rate / threads * 4.0)))
+        t0 = time.perf_counter()
+        index.score_batch(ocfg, w["model"], w["players"], w["tx"][:n_1], threads=1)
+        s_one = time.perf_counter() - t0
+        index.close()
+        cpu = {"value": n_s / s_all, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"first {n_s} tx of the same batch ({s_all:.1f} s wall on {threads} threads); history indexed "
+                         f"once outside the timed region ({build_s:.1f} s)",
+               "single_thread": {"value": n_1 / s_one, "sample": f"first {n_1} tx ({s_one:.1f} s)"}}
+
+    # ---- blocks ------------------------------------------------------------------------------------------
+    blocks = {}
+    if "path_a" not in skip:
+        blocks["path_a"] = block_path_a(ctx, w)
+    if "c3" not in skip:
+        blocks["c3"] = block_c3(ctx, w)
+    if "live_loop" not in skip and not args.skip_latency:
+        blocks["live_loop"] = block_live_loop(ctx, w)
+    if "ltv" not in skip:
+        blocks["ltv"] = block_ltv(ctx)
+    if "c5" not in skip and (world > 1 or args.c5):
+        if not eng_has_mlp(blocks):
+            eng.load_mlp(synth.make_mlp())
+        blocks["c5"] = block_c5(ctx, w)
 
     if rank == 0:
-        peak, peak_src = load_peaks()
-        k_ms = float(np.mean(per_launch_ms))
-        algo_bytes = n * ALGO_BYTES_PER_TX + MODEL_BYTES
+        k_ms = float(np.mean(per_step))
+        algo_bytes = n * FUSED_BYTES_PER_TX + MODEL_BYTES
         achieved = algo_bytes / (k_ms * 1e-3) / 1e9
         visits = n * N_TREES * 8 / (k_ms * 1e-3)
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        ncu = ncu_constants("k_score_fused")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": "C2: 1M tx x 64 f32 features, 500-tree depth-8 GBDT + 8 rules + blend, per GPU",
-                       "tx_per_gpu": n, "n_trees": N_TREES, "n_features": 64, "depth": 8,
-                       "sharding": f"player-hash shards x{world}, no collective",
-                       "shard_skew": shard_skew(world, synth, pkg),
-                       "l2": "inputs 312 MB per step > 126 MB L2, no flush needed"},
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "tx_per_gpu": n, "n_trees": N_TREES, "n_features": 64, "depth": 8,
+                       "players": N_PLAYERS, "events": N_EVENTS,
+                       "sharding": f"player-hash shards x{world}, no collective on the data path",
+                       "l2": "per step 32 MB of tx records + random gathers over a 96 MB player table and a 720 MB "
+                             "index: the working set exceeds the 126 MB L2, no flush between steps",
+                       "first_index_load_s": first_load_s},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT,
-                    "h2d_bytes_per_step": int(n * (256 + 48)), "d2h_bytes_per_step": int(n * 8),
-                    "steps": e2e_steps, "api": "igs_score_features (pinned host buffers)"},
-            "gpu_launches": args.steps,
-            "roofline": {"bound": "hbm", "kernel": "k_score<features, Shape<12,20>>", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, from the
-                         # ncu --set full capture in profiles/r1e_score_ncu_full.csv (not measured live)
-                         "traffic": 314.7e6 if n == N_TX else None, "peak_source": peak_src,
-                         "launch_ms": k_ms,
-                         "note": "algorithmic bytes = 312 B/tx + model once; this kernel is bound by "
-                                 "shared-memory gathers / issue slots (4000 dependent node visits per "
-                                 "tx), not HBM — see on_chip"},
-            "on_chip": {"node_visits_per_s": visits,
-                        "node_visits_per_sm_cycle": visits / (148 * sm_mhz * 1e6),
-                        "sm_mhz_used": sm_mhz,
-                        "smem_pipe_frac_ncu": 0.823, "alu_pipe_frac_ncu": 0.534,
-                        "ncu_source": "profiles/r1e_score_ncu_full.csv (l1tex__data_pipe_lsu_wavefronts_mem_shared "
-                                      "pct_of_peak_sustained_elapsed; the resource that bounds this kernel)"},
+            "e2e": {"value": n * world / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(n * 32),
+                    "d2h_bytes_per_step": int(n * 8), "steps": ctx.e2e_steps, "ms_per_step": e2e_ms,
+                    "api": "igs_score_batch (pinned host buffers)"},
+            "gpu_launches": gpu_launches,
+            "roofline": {"bound": "hbm", "kernel": "k_score<tx, Shape<8,10,5,2>> (+ the account-order visit sort)",
+                         "achieved": achieved, "peak": ctx.peaks["hbm"], "unit": "GB/s", "frac": achieved / ctx.peaks["hbm"],
+                         "traffic": (ncu or {}).get("dram_bytes"), "traffic_source": (ncu or {}).get("source"),
+                         "traffic_stale": (ncu or {}).get("stale"), "peak_source": ctx.peaks["src"], "launch_ms": k_ms,
+                         "algorithmic_bytes": int(algo_bytes),
+                         "note": "algorithmic bytes = 136 B/tx (32 tx + 96 player row + 8 result) + model once; this kernel "
+                                 "is bound by shared-memory gathers / issue slots (4000 dependent node visits per tx), "
+                                 "not HBM — see on_chip; the HBM-bound kernels of the path are in blocks c3 and c5"},
+            "on_chip": {"node_visits_per_s": visits, "node_visits_per_sm_cycle": visits / (148 * sm_mhz * 1e6),
+                        "sm_mhz_used": sm_mhz, "ncu": ncu},
             "cpu_baseline": cpu,
             "p99_batch_latency": lat,
-            "fused_path": fused,
         }
+        line.update(blocks)
         print(json.dumps(line), flush=True)
 
-    for p in (p1, p2, p3):
-        lib.igs_free_pinned(p)
+    lib.igs_free_pinned(p1)
+    lib.igs_free_pinned(p2)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def eng_has_mlp(blocks):
+    return "ltv" in blocks
 
 
 if __name__ == "__main__":

@@ -175,7 +175,7 @@ EXPORTS = [
     "igs_abuse_signals", "igs_links_window_create", "igs_links_window_open", "igs_links_window_attach",
     "igs_links_window_reset", "igs_links_pairs_peer", "igs_links_group_peer", "igs_links_finish_peer",
     "igs_evict_events",
-    "igs_set_late_policy", "igs_get_history_info",
+    "igs_kernel_launches", "igs_load_events_device", "igs_set_late_policy", "igs_get_history_info",
     "igs_ltv_predict_batch", "igs_ltv_predict_batch_device", "igs_ltv_mock_predict", "igs_ltv_mock_predict_device",
 ]
 
@@ -269,11 +269,14 @@ def load_library() -> C.CDLL:
     lib.igs_ltv_predict_batch_device.argtypes = [vp, vp, u64, vp, vp, vp]
     lib.igs_ltv_mock_predict.argtypes = [vp, vp, u64, vp]
     lib.igs_ltv_mock_predict_device.argtypes = [vp, vp, u64, vp, vp]
+    lib.igs_load_events_device.argtypes = [vp, C.POINTER(EventCols), C.POINTER(EventIds), u64, C.c_uint32]
     lib.igs_set_late_policy.argtypes = [vp, i32]
     lib.igs_get_history_info.argtypes = [vp, C.POINTER(HistoryInfo)]
     lib.igs_evict_events.argtypes = [vp, C.c_uint32, C.POINTER(u64)]
     lib.igs_hash_id.argtypes = [C.c_char_p, C.c_size_t]
     lib.igs_hash_id.restype = u64
+    lib.igs_kernel_launches.argtypes = []
+    lib.igs_kernel_launches.restype = C.c_ulonglong
     lib.igs_version.argtypes = []
     lib.igs_version.restype = C.c_char_p
     _lib = lib

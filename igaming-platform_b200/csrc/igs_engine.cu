@@ -13,6 +13,7 @@
 #include "igs_internal.cuh"
 
 static thread_local char g_create_error[512] = "";
+unsigned long long g_igs_launches = 0;
 
 void igs_set_error(igs_engine* e, const char* fmt, ...) {
     va_list ap;
@@ -273,6 +274,16 @@ int igs_load_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event
     IGS_REQUIRE(e, n < 0xFFFFFFFFull, "at most 2^32-2 events per shard");
     std::lock_guard<std::mutex> lk(e->mu);
     return igs_build_event_index(e, ev, ids, n, n_accounts);
+}
+
+int igs_load_events_device(igs_engine* e, const igs_event_cols* d_ev, const igs_event_ids* d_ids, uint64_t n,
+                           uint32_t n_accounts) {
+    IGS_ENGINE(e);
+    IGS_REQUIRE(e, d_ev != nullptr, "event columns are null");
+    IGS_REQUIRE(e, n == 0 || (d_ev->account && d_ev->ts && d_ev->amount && d_ev->tx_type), "an event column is null");
+    IGS_REQUIRE(e, n < 0xFFFFFFFFull, "at most 2^32-2 events per shard");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_build_event_index(e, d_ev, d_ids, n, n_accounts);
 }
 
 int igs_append_events_ids(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
@@ -742,6 +753,8 @@ static uint64_t splitmix64(uint64_t x) {
 uint32_t igs_shard_of(uint64_t lo, uint64_t hi, uint32_t n_shards) {
     return n_shards ? (uint32_t)(splitmix64(lo ^ hi) % n_shards) : 0;
 }
+
+unsigned long long igs_kernel_launches(void) { return __atomic_load_n(&g_igs_launches, __ATOMIC_RELAXED); }
 
 const char* igs_version(void) { return "igs 0.1 sm_100a"; }
 

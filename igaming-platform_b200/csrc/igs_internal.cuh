@@ -145,6 +145,15 @@ void igs_set_error(igs_engine* e, const char* fmt, ...);
         }                                                                                  \
     } while (0)
 
+// After every kernel launch: counts it (igs_kernel_launches: what bench.py reports as gpu_launches) and
+// checks the launch status.
+extern unsigned long long g_igs_launches;
+#define IGS_LAUNCHED(e)                                                   \
+    do {                                                                  \
+        __atomic_fetch_add(&g_igs_launches, 1ull, __ATOMIC_RELAXED);      \
+        IGS_CUDA((e), cudaGetLastError());                                \
+    } while (0)
+
 #define IGS_REQUIRE(e, cond, msg)                                  \
     do {                                                           \
         if (!(cond)) {                                             \

@@ -117,7 +117,7 @@ int igs_launch_blacklist_check(igs_engine* e, const igs_tx_ids* d_ids, uint64_t 
     if (n == 0) return IGS_OK;
     k_blacklist_check<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, stream>>>(
         view_of(e->bl[IGS_BL_DEVICE]), view_of(e->bl[IGS_BL_FINGERPRINT]), view_of(e->bl[IGS_BL_IP]), d_ids, n, d_out);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 

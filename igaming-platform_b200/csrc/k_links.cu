@@ -349,7 +349,7 @@ int sort_records(igs_engine* e, Scratch& sc, const Rec* d_rec, uint32_t n, int b
     *cur = 0;
     if (n == 0) return IGS_OK;
     k_rec_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(d_rec, n, by_first_only, keys[0], vals[0]);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return radix_sort_pairs(e, keys, vals, n, kKeyPasses, kKeyBits / kKeyPasses, d_hist, d_scr, st, cur);
 }
 
@@ -369,12 +369,12 @@ int distinct_records(igs_engine* e, Scratch& sc, const Rec* d_rec, uint32_t n, R
     if (n == 0) return IGS_OK;
     const uint32_t nb = (n + kThreads - 1) / kThreads;
     k_rec_first<<<nb, kThreads, 0, st>>>(keys[cur], vals[cur], d_rec, n, first);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_save_last<<<1, 32, 0, st>>>(first, n, last_flag);
     rc = scan_u32(e, first, n, scr, st);
     if (rc != IGS_OK) return rc;
     k_compact_flagged<<<nb, kThreads, 0, st>>>(vals[cur], d_rec, first, last_flag, n, *d_out);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     uint32_t ex = 0, lf = 0;
     IGS_CUDA(e, cudaMemcpyAsync(&ex, first + (n - 1), 4, cudaMemcpyDeviceToHost, st));
     IGS_CUDA(e, cudaMemcpyAsync(&lf, last_flag, 4, cudaMemcpyDeviceToHost, st));
@@ -425,13 +425,13 @@ int igs_links_pairs(igs_engine* e, uint32_t shard, uint32_t n_shards, const igs_
     if (n) {
         const uint32_t nb = (n + kThreads - 1) / kThreads;
         k_lp_count<<<std::min<uint32_t>(nb, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(e->raw_device, n, n_shards, d_counts);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         IGS_CUDA(e, cudaMemcpyAsync(h_counts, d_counts, n_shards * 8, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
         offsets_of(h_counts, n_shards, h_starts);
         IGS_CUDA(e, cudaMemcpyAsync(d_counts, h_starts, n_shards * 8, cudaMemcpyHostToDevice, st));
         k_lp_scatter<<<nb, kThreads, 0, st>>>(e->raw_device, e->raw_account, n, shard, n_shards, d_counts, d_out);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         IGS_CUDA(e, cudaStreamSynchronize(st));
     }
     for (uint32_t s = 0; s < n_shards; ++s) counts[s] = h_counts[s];
@@ -469,13 +469,13 @@ static int links_group_impl(igs_engine* e, const igs_link_pair* d_pairs, uint64_
     const uint32_t mb = (m + kThreads - 1) / kThreads;
     if (m) {
         k_gather_rec<<<mb, kThreads, 0, st>>>(vals[cur], d_distinct, m, d_sorted);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         k_lg_count<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_counts);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         if (d_wins) {
             k_lg_emit_peer<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_wins,
                                                     (unsigned long long)e->links_cap_links);
-            IGS_CUDA(e, cudaGetLastError());
+            IGS_LAUNCHED(e);
         }
         IGS_CUDA(e, cudaMemcpyAsync(h_counts, d_counts, n_shards * 8, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
@@ -493,7 +493,7 @@ static int links_group_impl(igs_engine* e, const igs_link_pair* d_pairs, uint64_
     if (total) {
         IGS_CUDA(e, cudaMemcpyAsync(d_counts, h_starts, n_shards * 8, cudaMemcpyHostToDevice, st));
         k_lg_emit<<<mb, kThreads, 0, st>>>(keys[cur], d_sorted, m, n_shards, d_links_of, d_counts, d_out);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         IGS_CUDA(e, cudaStreamSynchronize(st));
     }
     *d_links = d_out;
@@ -524,7 +524,7 @@ static int links_finish_impl(igs_engine* e, const igs_link* d_links, uint64_t n6
     e->d_links_rows = nullptr; e->n_links_rows = 0;
     IGS_CUDA(e, cudaMalloc(&e->d_links_rows, std::max<size_t>(n_rows, 1) * sizeof(igs_links_row)));
     if (n_rows) k_lf_init<<<(n_rows + kThreads - 1) / kThreads, kThreads, 0, st>>>(e->d_links_rows, n_rows);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     // The links buffer may be stage 2's output (one shard), which lives in the pool: take scratch behind it.
     Scratch sc(e->links_pool);
     if (e->links_pool.size() < kStage3First) e->links_pool.resize(kStage3First);
@@ -536,11 +536,11 @@ static int links_finish_impl(igs_engine* e, const igs_link* d_links, uint64_t n6
         const uint32_t mb = (m + kThreads - 1) / kThreads;
         for (int round = 0; round < 3; ++round) {
             k_lf_round<<<mb, kThreads, 0, st>>>(d_distinct, m, shard, n_rows, round, e->d_links_rows);
-            IGS_CUDA(e, cudaGetLastError());
+            IGS_LAUNCHED(e);
         }
     }
     if (n_rows) k_lf_close<<<(n_rows + kThreads - 1) / kThreads, kThreads, 0, st>>>(e->d_links_rows, n_rows);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     IGS_CUDA(e, cudaStreamSynchronize(st));
     e->n_links_rows = n_rows;
     return IGS_OK;     // the stage scratch stays in the pool for the next run of this periodic job
@@ -661,7 +661,7 @@ int igs_links_pairs_peer(igs_engine* e, uint32_t shard, uint32_t n_shards) {
     if (n) {
         k_lp_scatter_peer<<<(n + kThreads * kPeerItems - 1) / (kThreads * kPeerItems), kThreads, 0, st>>>(
             e->raw_device, e->raw_account, n, shard, n_shards, d_wins, (unsigned long long)e->links_cap_pairs);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
     }
     IGS_CUDA(e, cudaStreamSynchronize(st));
     return IGS_OK;
@@ -722,7 +722,7 @@ int igs_get_links(igs_engine* e, const uint32_t* accounts, uint64_t n, igs_links
     IGS_CUDA(e, cudaMemcpyAsync(sl.in0.p, accounts, n * 4, cudaMemcpyHostToDevice, sl.stream));
     k_links_get<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, sl.stream>>>(
         e->d_links_rows, e->n_links_rows, (const uint32_t*)sl.in0.p, n, (igs_links_row*)sl.out0.p);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_links_row), cudaMemcpyDeviceToHost, sl.stream));
     IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
     return IGS_OK;
@@ -742,7 +742,7 @@ int igs_check_bonus_abuse(igs_engine* e, const uint32_t* accounts, uint64_t n, i
     k_bonus_abuse<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, sl.stream>>>(
         e->d_links_rows, e->n_links_rows, e->d_players, e->d_players ? e->n_players : 0, (const uint32_t*)sl.in0.p, n,
         (igs_abuse*)sl.out0.p);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     IGS_CUDA(e, cudaMemcpyAsync(out, sl.out0.p, n * sizeof(igs_abuse), cudaMemcpyDeviceToHost, sl.stream));
     IGS_CUDA(e, cudaStreamSynchronize(sl.stream));
     return IGS_OK;

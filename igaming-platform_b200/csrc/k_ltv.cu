@@ -414,7 +414,7 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
     const uint32_t items = head ? (M + BM - 1) / BM : ((M + BM - 1) / BM) * (N / BN);
     const uint32_t grid = items < (uint32_t)e->sm_count ? items : (uint32_t)e->sm_count;
     kern<<<grid, threads, kGemmSmem, st>>>(p);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -443,7 +443,7 @@ int launch_fused(igs_engine* e, MlpDevice* m, const uint16_t* d_x, const igs_ltv
     p.w4 = m->w4; p.b4 = m->b4; p.M = n; p.single = single ? 1u : 0u; p.rows = d_rows; p.res = d_out; p.raw = d_raw;
     IGS_CUDA(e, cudaFuncSetAttribute(k_mlp_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
     k_mlp_fused<<<grid, kFusedThreads, kFusedSmem, st>>>(p);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 

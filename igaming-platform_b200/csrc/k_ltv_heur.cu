@@ -46,7 +46,7 @@ int launch_predictor(igs_engine* e, const igs_ltv_row* d_rows, uint64_t n, igs_l
     const uint64_t nb = (n + kHeurThreads - 1) / kHeurThreads;
     IGS_REQUIRE(e, nb <= 0x7FFFFFFFull, "too many rows for one launch");
     k_ltv_predictor<<<(unsigned)nb, kHeurThreads, 0, st>>>(d_rows, n, d_out, d_raw);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -55,7 +55,7 @@ int launch_mock(igs_engine* e, const igs_ltv_features* d_f, uint64_t n, double* 
     const uint64_t nb = (n + kHeurThreads - 1) / kHeurThreads;
     IGS_REQUIRE(e, nb <= 0x7FFFFFFFull, "too many rows for one launch");
     k_ltv_mock<<<(unsigned)nb, kHeurThreads, 0, st>>>(d_f, n, d_out);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 

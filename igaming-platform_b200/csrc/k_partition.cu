@@ -145,11 +145,11 @@ int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t 
         return IGS_OK;
     }
     k_part_hist<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_part_scan<<<1, kThreads, 0, stream>>>(counts, n_shards * nblocks, n_shards, nblocks, n, d_offsets);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_part_scatter<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 

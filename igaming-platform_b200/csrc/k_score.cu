@@ -487,7 +487,7 @@ static int launch_shape(igs_engine* e, int src, const ScoreParams& p, bool leave
     const unsigned long long max_ctas = (unsigned long long)e->sm_count * S::kCtasPerSm;
     const unsigned grid = (unsigned)(n_tiles < max_ctas ? n_tiles : max_ctas);
     kern<<<grid, S::kThreads, S::kSmemBytes, stream>>>(p);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -584,7 +584,7 @@ static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, int passes
     while (acct_bits < 32 && (e->ev.n_accounts >> acct_bits)) ++acct_bits;
     const int drop = std::max(0, acct_bits - passes * kSortMaxBits);
     k_visit_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, stream>>>(d_tx, n, drop, keys[0], vals[0]);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     int cur = 0;
     const int rc = radix_sort_pairs(e, keys, vals, n, passes, kSortMaxBits, hist, scr, stream, &cur);
     if (rc != IGS_OK) return rc;

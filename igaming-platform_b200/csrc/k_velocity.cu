@@ -666,6 +666,7 @@ void igs_free_event_index(igs_engine* e) {
 }
 
 // Appends n host events to the device-resident raw columns (capacity grows by 1.5x).
+// (the source columns may be host or device memory: cudaMemcpyDefault lets the runtime tell)
 static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
                       cudaStream_t st) {
     const uint64_t need = e->n_raw + n;
@@ -710,17 +711,17 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
         e->cap_raw = cap; e->n_raw = keep;
     }
     if (n) {
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyHostToDevice, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyHostToDevice, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyHostToDevice, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyHostToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyDefault, st));
         if (e->has_event_ids) {       // a missing column = events without that identifier
             if (ids && ids->device)
-                IGS_CUDA(e, cudaMemcpyAsync(e->raw_device + e->n_raw, ids->device, n * 8, cudaMemcpyHostToDevice, st));
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_device + e->n_raw, ids->device, n * 8, cudaMemcpyDefault, st));
             else
                 IGS_CUDA(e, cudaMemsetAsync(e->raw_device + e->n_raw, 0, n * 8, st));
             if (ids && ids->ip)
-                IGS_CUDA(e, cudaMemcpyAsync(e->raw_ip + e->n_raw, ids->ip, n * 8, cudaMemcpyHostToDevice, st));
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_ip + e->n_raw, ids->ip, n * 8, cudaMemcpyDefault, st));
             else
                 IGS_CUDA(e, cudaMemsetAsync(e->raw_ip + e->n_raw, 0, n * 8, st));
         }
@@ -788,7 +789,7 @@ static int resolve_big_groups(igs_engine* e, Scratch& sc, bool needed, const uin
     uint32_t n_groups = 0;
     if (needed) {
         k_dg_heads_u32<<<nb, kThreads, 0, st>>>(d_head, n, gid);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         const int rc = scan_u32(e, gid, n, d_scan_scratch, st);
         if (rc != IGS_OK) return rc;
         uint32_t last_ex = 0; uint8_t last_head = 0;
@@ -806,9 +807,9 @@ static int resolve_big_groups(igs_engine* e, Scratch& sc, bool needed, const uin
         IGS_CUDA(e, cudaMemsetAsync(special, 0xFF, (size_t)n_groups * 4, st));
         IGS_CUDA(e, cudaMemsetAsync(cap + n_groups, 0, 4, st));
         k_dg_starts<<<nb, kThreads, 0, st>>>(d_head, gid, n, gstart, n_groups);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         k_dg_caps<<<(n_groups + kThreads - 1) / kThreads, kThreads, 0, st>>>(gstart, n_groups, cap);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         // exclusive scan over n_groups + 1 entries: cap[n_groups] becomes the total table size
         const int rc = scan_u32(e, cap, n_groups + 1, scr, st);
         if (rc != IGS_OK) return rc;
@@ -821,9 +822,9 @@ static int resolve_big_groups(igs_engine* e, Scratch& sc, bool needed, const uin
         IGS_CUDA(e, cudaMemsetAsync(keys, 0, (size_t)total * 8, st));
         IGS_CUDA(e, cudaMemsetAsync(minpos, 0xFF, (size_t)total * 4, st));
         k_dg_insert<<<nb, kThreads, 0, st>>>(gid, gstart, cap, d_amt, n, keys, minpos, special);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         k_dg_resolve<<<nb, kThreads, 0, st>>>(gid, cap, d_amt, n, keys, minpos, special, d_dflag);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
     }
     return IGS_OK;
 }
@@ -843,7 +844,7 @@ static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, con
     igs_event_index& x = e->ev;
     const uint32_t nb = (n + kThreads - 1) / kThreads;
     k_id_gather<<<nb, kThreads, 0, st>>>(raw, x.seq, n, s.id_s, s.fex);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     int rc = scan_u32(e, s.fex, n, s.scan_scratch, st);
     if (rc != IGS_OK) return rc;
     uint32_t last_ex = 0; uint64_t last_id = 0;
@@ -854,23 +855,23 @@ static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, con
     if (m == 0) return IGS_OK;                         // the tail records already say "no key"
     const uint32_t mb = (m + kThreads - 1) / kThreads;
     k_id_compact<<<nb, kThreads, 0, st>>>(s.id_s, s.fex, n, s.cpos, s.cid);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_id_heads<<<mb, kThreads, 0, st>>>(s.cpos, d_acct, x.ts, m, s.head, s.chain);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     rc = scan_u32(e, s.chain, m, s.scan_scratch, st);
     if (rc != IGS_OK) return rc;
     k_id_chain<<<mb, kThreads, 0, st>>>(s.head, s.chain, s.cid, m, s.chain_head, s.keys[0], s.vals[0]);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     int cur = 0;
     rc = radix_sort_pairs(e, s.keys, s.vals, m, kIdKeyBits / kSortMaxBits, kSortMaxBits, s.hist, s.scan_scratch, st, &cur);
     if (rc != IGS_OK) return rc;
     k_id_new<<<mb, kThreads, 0, st>>>(s.keys[cur], s.vals[cur], s.chain, s.cid, m, s.isnew8, s.nex);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     rc = scan_u32(e, s.nex, m, s.scan_scratch, st);
     if (rc != IGS_OK) return rc;
     k_id_expand<kCol><<<nb, kThreads, 0, st>>>(s.id_s, s.fex, s.cpos, s.chain, s.chain_head, s.nex, s.isnew8, d_acct,
                                                x.ts, n, x.tail);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -917,7 +918,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, cudaMemcpyAsync(d_mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, st));
     const uint32_t nb_el = (n + kThreads - 1) / kThreads;
     k_minmax<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct_in, d_ts_in, n, d_mm);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     uint32_t mm[4];
     IGS_CUDA(e, cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, st));
     IGS_CUDA(e, cudaStreamSynchronize(st));
@@ -947,7 +948,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, sc.alloc(&d_hist, hist_elems));
     IGS_CUDA(e, sc.alloc(&d_scan_scratch, scan_u32_scratch_elems(hist_elems)));
     k_make_keys<<<nb_el, kThreads, 0, st>>>(d_acct_in, d_ts_in, n, ts_min, ts_bits, d_keys[0], d_vals[0]);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     int cur = 0;
     {
         const int rc = radix_sort_pairs(e, d_keys, d_vals, n, passes, digit_bits, d_hist, d_scan_scratch, st, &cur);
@@ -963,18 +964,18 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, cudaMemcpyAsync(x.seq, d_vals[cur], (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
                                                 d_acct, x.ts, d_amt, d_type);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, x.seq, n, n_accounts, (uint32_t)n_before, x.seg, d_mm + 4);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     uint8_t* d_head;
     IGS_CUDA(e, sc.alloc(&d_head, n));
     uint32_t* d_scan_scratch_n;                                        // scratch of an n-element u32 scan
     IGS_CUDA(e, sc.alloc(&d_scan_scratch_n, scan_u32_scratch_elems(n + 1)));
     k_group_heads<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, n, d_head);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     IGS_CUDA(e, cudaMemsetAsync(d_mm, 0, 4, st));                     // d_mm[0] is free again: unresolved counter
     k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_mm);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     {
         uint32_t n_unres = 0, late[2] = {0, 0};
         IGS_CUDA(e, cudaMemcpyAsync(&n_unres, d_mm, 4, cudaMemcpyDeviceToHost, st));
@@ -1001,15 +1002,15 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     const uint32_t warps_per_block = kThreads / 32;
     const uint32_t g1 = (n1 + warps_per_block - 1) / warps_per_block, g2 = (n2 + warps_per_block - 1) / warps_per_block;
     k_vs_reduce<ElemSrc><<<g1, kThreads, 0, st>>>(ElemSrc{cols}, d_agg1);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_vs_reduce<AggSrc><<<g2, kThreads, 0, st>>>(AggSrc{d_agg1, n1}, d_agg2);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_vs_scan_small<<<1, 32, 0, st>>>(d_agg2, n2);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_vs_apply_aggs<<<g2, kThreads, 0, st>>>(d_agg1, n1, d_agg2);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     k_vs_apply_elems<<<g1, kThreads, 0, st>>>(cols, d_agg1, x.pre, x.tail);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
 
     // ---- identifier columns ---------------------------------------------------------------------
     if (e->has_event_ids) {
@@ -1044,7 +1045,7 @@ int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniq
     if (n == 0) return IGS_OK;
     const unsigned long long nb = (n + kThreads - 1) / kThreads;
     k_uniques<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -1057,7 +1058,7 @@ int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_vel
     if (n == 0) return IGS_OK;
     const unsigned long long nb = (n + kThreads - 1) / kThreads;
     k_velocity<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 

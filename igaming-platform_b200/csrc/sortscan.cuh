@@ -205,12 +205,12 @@ int scan_u32(igs_engine* e, uint32_t* data, uint32_t n, uint32_t* scratch, cudaS
     if (n == 0) return IGS_OK;
     const uint32_t nb = (n + kScanTile - 1) / kScanTile;
     k_scan_u32_tile<<<nb, kThreads, 0, st>>>(data, n, scratch);
-    IGS_CUDA(e, cudaGetLastError());
+    IGS_LAUNCHED(e);
     if (nb > 1) {
         int rc = scan_u32(e, scratch, nb, scratch + nb, st);
         if (rc != IGS_OK) return rc;
         k_scan_u32_add<<<nb, kThreads, 0, st>>>(data, n, scratch);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
     }
     return IGS_OK;
 }
@@ -260,12 +260,12 @@ static int radix_sort_pairs(igs_engine* e, uint64_t* keys[2], uint32_t* vals[2],
     for (int p = 0; p < passes; ++p) {
         const int shift = p * digit_bits;
         k_radix_hist<<<nb_sort, kThreads, 0, st>>>(keys[cur], n, shift, bins, d_hist, nb_sort);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         int rc = scan_u32(e, d_hist, hist_elems, d_scan_scratch, st);
         if (rc != IGS_OK) return rc;
         k_radix_scatter<<<nb_sort, kThreads, sizeof(SortSmem), st>>>(
             keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, bins, d_hist, nb_sort);
-        IGS_CUDA(e, cudaGetLastError());
+        IGS_LAUNCHED(e);
         cur ^= 1;
     }
     *cur_out = cur;

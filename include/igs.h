@@ -355,6 +355,13 @@ int igs_load_players(igs_engine* e, const igs_player_row* rows, uint64_t n);
  * n_accounts = size of the dense account index space.                                          */
 int igs_load_events(igs_engine* e, const igs_event_cols* ev, uint64_t n, uint32_t n_accounts);
 
+/* igs_load_events / igs_load_events_ids with the columns already in device memory (a history restored
+ * from a device-side snapshot, or produced by an upstream GPU stage): the structs hold device pointers
+ * (d_ids may be NULL = no identifier columns).  The columns are copied; the caller keeps its buffers.
+ * Synchronous like the host-buffer loads.  No counterpart in the reference.                         */
+int igs_load_events_device(igs_engine* e, const igs_event_cols* d_ev, const igs_event_ids* d_ids, uint64_t n,
+                           uint32_t n_accounts);
+
 /* Replaces FeatureStore.UpdateRealTimeFeatures (scoring/engine.go:111; features/redis_store.go:119-168)
  * for a batch of completed transactions — what ScoringEngine.UpdateFeatures (scoring/engine.go:486-488)
  * does per "transaction.completed" event (services/risk/cmd/main.go:219-224): appends n events, in
@@ -671,6 +678,9 @@ uint32_t igs_shard_of(uint64_t uuid_lo, uint64_t uuid_hi, uint32_t n_shards);
  * by the splitmix64 finaliser; len 0 -> 0, a non-empty string never maps to 0.  No reference
  * counterpart (Redis keys the strings themselves).                                              */
 uint64_t igs_hash_id(const char* s, size_t len);
+/* Number of CUDA kernels this library has launched in this process since it was loaded (all engines, all
+ * devices) — instrumentation for benchmarks and tests; no reference counterpart.                  */
+unsigned long long igs_kernel_launches(void);
 /* Library / build identification, e.g. "igs 0.1 sm_100a".                                       */
 const char* igs_version(void);
 

@@ -716,6 +716,165 @@ void orc_score_batch(const igs_config* c, const igs_gbdt_desc* m, const igs_play
     ev_index_free(&ix);
 }
 
+/* ------------------------------------------------------------------------------------------ */
+/* Indexed form of the same lookups — the timed CPU baseline of the fused workload.               */
+/* ev_index_query above walks an account's events linearly (the obvious restatement; fine for     */
+/* checking, hopeless on an account with 10^5 events).  Redis answers ZCOUNT in O(log n) from a   */
+/* skiplist (features/redis_store.go:72-74), so a CPU baseline worth comparing against needs the   */
+/* same complexity: per sorted event the running distinct count, per-type counts / sums, the      */
+/* tx_sum chain and the session start are precomputed once, and a query is a few binary searches  */
+/* and differences.  tests/ prove it equal to the linear closed form.                              */
+/* ------------------------------------------------------------------------------------------ */
+struct orc_fast_index {
+    ev_index ix;
+    uint32_t* dcnt;          /* [n+1] distinct (account, ts, amount) first occurrences before i      */
+    uint32_t* cnt[2];        /* [n+1] bets / deposits before i                                        */
+    int64_t*  sum[2];        /* [n+1]                                                                  */
+    int64_t*  chain;         /* [n] tx_sum chain (gaps <= 3600) ending at i                            */
+    uint32_t* sess;          /* [n] first ts of the gap <= 1800 chain ending at i                      */
+};
+
+typedef struct { int64_t amt; uint64_t pos; } amt_pos;
+static int amt_pos_cmp(const void* a, const void* b) {
+    const amt_pos* x = (const amt_pos*)a; const amt_pos* y = (const amt_pos*)b;
+    if (x->amt != y->amt) return x->amt < y->amt ? -1 : 1;
+    return x->pos < y->pos ? -1 : x->pos > y->pos;
+}
+
+orc_fast_index* orc_fast_index_build(const igs_event_cols* ev, uint64_t n, uint32_t n_accounts) {
+    orc_fast_index* f = (orc_fast_index*)calloc(1, sizeof(*f));
+    ev_index_build(&f->ix, ev, n, n_accounts);
+    const ev_index* ix = &f->ix;
+    f->dcnt = (uint32_t*)calloc(n + 1, 4);
+    for (int t = 0; t < 2; ++t) {
+        f->cnt[t] = (uint32_t*)calloc(n + 1, 4);
+        f->sum[t] = (int64_t*)calloc(n + 1, 8);
+    }
+    f->chain = (int64_t*)calloc(n ? n : 1, 8);
+    f->sess = (uint32_t*)calloc(n ? n : 1, 4);
+    uint8_t* distinct = (uint8_t*)malloc(n ? n : 1);
+    amt_pos* tmp = NULL; size_t tmp_cap = 0;
+    for (uint64_t g0 = 0; g0 < n;) {                  /* (account, ts) groups: ZSET member dedupe */
+        uint64_t g1 = g0 + 1;
+        while (g1 < n && ix->keys[g1].account == ix->keys[g0].account && ix->ts[g1] == ix->ts[g0]) ++g1;
+        const uint64_t len = g1 - g0;
+        if (len <= 16) {
+            for (uint64_t j = g0; j < g1; ++j) {
+                distinct[j] = 1;
+                for (uint64_t k = g0; k < j; ++k)
+                    if (ix->amt[k] == ix->amt[j]) { distinct[j] = 0; break; }
+            }
+        } else {
+            if (len > tmp_cap) { tmp_cap = len * 2; tmp = (amt_pos*)realloc(tmp, tmp_cap * sizeof(amt_pos)); }
+            for (uint64_t j = 0; j < len; ++j) tmp[j] = (amt_pos){ix->amt[g0 + j], g0 + j};
+            qsort(tmp, len, sizeof(amt_pos), amt_pos_cmp);
+            for (uint64_t j = 0; j < len; ++j) distinct[tmp[j].pos] = j == 0 || tmp[j].amt != tmp[j - 1].amt;
+        }
+        g0 = g1;
+    }
+    free(tmp);
+    for (uint64_t i = 0; i < n; ++i) {
+        const int head = i == 0 || ix->keys[i].account != ix->keys[i - 1].account;
+        const int64_t gap = head ? 0 : (int64_t)ix->ts[i] - (int64_t)ix->ts[i - 1];
+        f->dcnt[i + 1] = f->dcnt[i] + distinct[i];
+        for (int t = 0; t < 2; ++t) {
+            f->cnt[t][i + 1] = f->cnt[t][i] + (ix->ty[i] == t);
+            f->sum[t][i + 1] = f->sum[t][i] + (ix->ty[i] == t ? ix->amt[i] : 0);
+        }
+        f->chain[i] = (head || gap > 3600) ? ix->amt[i] : f->chain[i - 1] + ix->amt[i];
+        f->sess[i] = (head || gap > 1800) ? ix->ts[i] : f->sess[i - 1];
+    }
+    free(distinct);
+    return f;
+}
+void orc_fast_index_free(orc_fast_index* f) {
+    if (!f) return;
+    ev_index_free(&f->ix);
+    free(f->dcnt); free(f->cnt[0]); free(f->cnt[1]); free(f->sum[0]); free(f->sum[1]); free(f->chain); free(f->sess);
+    free(f);
+}
+static uint64_t fast_lower_ts(const uint32_t* ts, uint64_t lo, uint64_t hi, int64_t key) {   /* first ts >= key */
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if ((int64_t)ts[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+void orc_fast_velocity(const orc_fast_index* f, uint32_t account, uint32_t ts_u, uint32_t seq_limit,
+                       igs_velocity* v) {
+    memset(v, 0, sizeof(*v));
+    const ev_index* ix = &f->ix;
+    if (account >= ix->n_accounts) return;
+    const uint64_t s = ix->seg[account], e = ix->seg[account + 1];
+    uint64_t lo = s, hi = e;                            /* prior events: (ts, seq) < (now, seq_limit) */
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if (ix->ts[mid] < ts_u || (ix->ts[mid] == ts_u && ix->seq[mid] < seq_limit)) lo = mid + 1; else hi = mid;
+    }
+    const uint64_t u = lo;
+    v->n_prior = (uint32_t)(u - s);
+    if (u == s) return;
+    const int64_t now = ts_u, L = ix->ts[u - 1];
+    const uint64_t alive = fast_lower_ts(ix->ts, s, u, L - 3599);        /* ZSET after the last trim: ts > L-3600 */
+    const uint64_t b60 = fast_lower_ts(ix->ts, s, u, now - 60), b300 = fast_lower_ts(ix->ts, s, u, now - 300);
+    const uint64_t b3600 = fast_lower_ts(ix->ts, s, u, now - 3600), b86400 = fast_lower_ts(ix->ts, s, u, now - 86400);
+    #define ORC_MAX(a, b) ((a) > (b) ? (a) : (b))
+    v->tx_count_1m = f->dcnt[u] - f->dcnt[ORC_MAX(b60, alive)];           /* ZCOUNT :72-74 */
+    v->tx_count_5m = f->dcnt[u] - f->dcnt[ORC_MAX(b300, alive)];
+    v->tx_count_1h = f->dcnt[u] - f->dcnt[ORC_MAX(b3600, alive)];
+    #undef ORC_MAX
+    const uint64_t wb[3] = {b60, b3600, b86400};
+    for (int t = 0; t < 2; ++t)
+        for (int w = 0; w < 3; ++w) {
+            v->win[t][w].count = f->cnt[t][u] - f->cnt[t][wb[w]];
+            v->win[t][w].sum = f->sum[t][u] - f->sum[t][wb[w]];
+        }
+    if (now - L <= 3600) v->tx_sum_1h = f->chain[u - 1];                  /* :77, :136-138 */
+    if (now - L <= 7 * 24 * 3600) v->time_since_last_tx = (uint32_t)(now - L);
+    if (now - L <= 1800) v->session_duration = (uint32_t)(now - (int64_t)f->sess[u - 1]);
+}
+void orc_fast_velocity_batch(const orc_fast_index* f, const igs_query* q, uint64_t n_q, igs_velocity* out) {
+    for (uint64_t i = 0; i < n_q; ++i) orc_fast_velocity(f, q[i].account, q[i].ts, q[i].seq_limit, out + i);
+}
+
+typedef struct {
+    const igs_config* c; const igs_gbdt_desc* m; const igs_player_row* players; uint64_t n_players;
+    const orc_fast_index* f; const igs_tx* tx; uint64_t lo, hi; igs_result* out;
+} sb_job;
+static void* sb_worker(void* p) {
+    sb_job* j = (sb_job*)p;
+    for (uint64_t i = j->lo; i < j->hi; ++i) {           /* one request at a time: PredictBatch's loop, :314-326 */
+        igs_velocity v;
+        orc_fast_velocity(j->f, j->tx[i].account, j->tx[i].ts, j->tx[i].seq_limit, &v);
+        orc_features fv; float x[64]; igs_rule_row row; orc_score s;
+        const igs_player_row* pl = j->tx[i].account < j->n_players ? j->players + j->tx[i].account : NULL;
+        orc_assemble(&j->tx[i], &v, pl, &fv, x, &row);
+        orc_score_features_row(j->c, j->m, x, &row, &s, NULL);
+        to_result(&s, j->out + i);
+    }
+    return NULL;
+}
+/* orc_score_batch against a prebuilt index, `threads` host threads over static chunks. */
+void orc_score_batch_indexed(const igs_config* c, const igs_gbdt_desc* m, const igs_player_row* players,
+                             uint64_t n_players, const orc_fast_index* f, const igs_tx* tx, uint64_t n,
+                             igs_result* out, int threads) {
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t th[256];
+    sb_job jobs[256];
+    const uint64_t chunk = (n + threads - 1) / threads;
+    for (int t = 0; t < threads; ++t) {
+        uint64_t lo = (uint64_t)t * chunk, hi = lo + chunk;
+        if (lo > n) lo = n;
+        if (hi > n) hi = n;
+        jobs[t] = (sb_job){c, m, players, n_players, f, tx, lo, hi, out};
+        if (threads == 1) sb_worker(&jobs[t]);
+        else pthread_create(&th[t], NULL, sb_worker, &jobs[t]);
+    }
+    if (threads > 1)
+        for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+}
+
 /* Path B with the identifier inputs computed here instead of arriving with the tx: uniques from
  * the history's identifier columns (when ev_ids != NULL), R8 from the blacklist sets (when
  * tx_ids != NULL; OR-ed with the tx's own IGS_BIT_BLACKLISTED). */

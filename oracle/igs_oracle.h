@@ -157,6 +157,18 @@ void orc_score_batch(const igs_config* cfg, const igs_gbdt_desc* m, const igs_pl
                      const igs_tx* tx, uint64_t n, igs_result* out, float* features_out,
                      igs_velocity* velocity_out);
 
+/* The same lookups from precomputed prefix columns and binary searches (O(log n) per query, like
+ * Redis's ZCOUNT) — the timed CPU baseline of the fused workload; proven equal to the linear form.   */
+typedef struct orc_fast_index orc_fast_index;
+orc_fast_index* orc_fast_index_build(const igs_event_cols* ev, uint64_t n_events, uint32_t n_accounts);
+void orc_fast_index_free(orc_fast_index* f);
+void orc_fast_velocity(const orc_fast_index* f, uint32_t account, uint32_t ts, uint32_t seq_limit,
+                       igs_velocity* out);
+void orc_fast_velocity_batch(const orc_fast_index* f, const igs_query* q, uint64_t n_q, igs_velocity* out);
+void orc_score_batch_indexed(const igs_config* cfg, const igs_gbdt_desc* m, const igs_player_row* players,
+                             uint64_t n_players, const orc_fast_index* f, const igs_tx* tx, uint64_t n,
+                             igs_result* out, int threads);
+
 void orc_score_batch_ids(const igs_config* cfg, const igs_gbdt_desc* m, const igs_player_row* players,
                          uint64_t n_players, const igs_event_cols* ev, const igs_event_ids* ev_ids,
                          uint64_t n_events, const orc_blacklist* bl, const igs_tx* tx,

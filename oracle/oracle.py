@@ -130,6 +130,15 @@ def lib() -> C.CDLL:
                                       C.POINTER(abi.EventCols), C.POINTER(abi.EventIds), u64,
                                       C.POINTER(Blacklist), vp, vp, u64, vp, vp]
     L.orc_score_batch_ids.restype = None
+    L.orc_fast_index_build.argtypes = [C.POINTER(abi.EventCols), u64, C.c_uint32]
+    L.orc_fast_index_build.restype = vp
+    L.orc_fast_index_free.argtypes = [vp]
+    L.orc_fast_index_free.restype = None
+    L.orc_fast_velocity_batch.argtypes = [vp, vp, u64, vp]
+    L.orc_fast_velocity_batch.restype = None
+    L.orc_score_batch_indexed.argtypes = [C.POINTER(abi.Config), C.POINTER(abi.GbdtDesc), vp, u64, vp, vp, u64, vp,
+                                          C.c_int]
+    L.orc_score_batch_indexed.restype = None
     L.orc_links.argtypes = [vp, vp, u64, vp, u64, vp]
     L.orc_links.restype = None
     L.orc_check_bonus_abuse.argtypes = [vp, vp, vp]
@@ -221,6 +230,39 @@ def score_batch(cfg, model, players, ev, tx, want_features=False, want_velocity=
     if want_features or want_velocity:
         return out, feats, vel
     return out
+
+
+class FastIndex:
+    """Prefix-column index over a history (orc_fast_index): O(log n) lookups, the timed CPU baseline of the fused
+    workload.  Build once, query / score many times."""
+
+    def __init__(self, ev, n_accounts: int):
+        c = ev.cols()
+        self._keep = (ev, c)
+        self.n_events, self.n_accounts = len(ev), n_accounts
+        self._h = lib().orc_fast_index_build(C.byref(c), len(ev), n_accounts)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orc_fast_index_free(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def velocity(self, queries: np.ndarray) -> np.ndarray:
+        queries = np.ascontiguousarray(queries, dtype=abi.query_dtype)
+        out = np.zeros(queries.shape[0], dtype=abi.velocity_dtype)
+        lib().orc_fast_velocity_batch(self._h, abi.ptr(queries), queries.shape[0], abi.ptr(out))
+        return out
+
+    def score_batch(self, cfg, model, players, tx, threads: int = 1) -> np.ndarray:
+        players = np.ascontiguousarray(players, dtype=abi.player_row_dtype)
+        tx = np.ascontiguousarray(tx, dtype=abi.tx_dtype)
+        out = np.zeros(tx.shape[0], dtype=abi.result_dtype)
+        d = model.desc() if model is not None else None
+        lib().orc_score_batch_indexed(C.byref(cfg), C.byref(d) if d is not None else None, abi.ptr(players),
+                                      players.shape[0], self._h, abi.ptr(tx), tx.shape[0], abi.ptr(out), threads)
+        return out
 
 
 def uniques_batch(ev, n_accounts: int, queries: np.ndarray) -> np.ndarray:

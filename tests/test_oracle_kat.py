@@ -268,3 +268,35 @@ def test_account_age_matches_integer_days(orc, pkg):
         p["account_created_at"] = now - d
         orc.lib().orc_extract_features(None, p.ctypes.data, now, 0, C.byref(f))
         assert f.account_age == d // 86400
+
+
+def test_indexed_cpu_port_equals_the_linear_closed_form(orc, pkg):
+    """orc_fast_index (prefix columns + binary searches; the timed CPU baseline of the fused workload) against the
+    linear restatement, on histories with forced (ts, amount) collisions, same-second bursts, every TTL boundary
+    and stream-mode queries (seq_limit); then whole results through the multi-threaded scorer."""
+    from tests import synth
+    abi = pkg.abi
+    rng = np.random.default_rng(12)
+    n_acc, n = 300, 30000
+    ev = synth.make_events(n, n_acc, seed=31, span=30 * 3600, collision_rate=0.05)
+    ev.ts[:400] = ev.ts[0]                                   # one big same-second group (sort path of the dedupe)
+    ev.account[:400] = 7
+    ev.amount[:400] = rng.integers(1, 40, 400) * 100
+    q = np.zeros(20000, dtype=abi.query_dtype)
+    pick = rng.integers(0, n, q.shape[0])
+    q["account"] = ev.account[pick]
+    q["ts"] = ev.ts[pick] + rng.choice([0, 1, 59, 60, 61, 300, 1800, 1801, 3599, 3600, 3601, 86400, 86401, 700000],
+                                       q.shape[0]).astype(np.uint32)
+    q["seq_limit"] = abi.SEQ_ALL
+    q["seq_limit"][::3] = rng.integers(0, n, q[::3].shape[0])
+    q["account"][::501] = n_acc + 5                          # unknown account
+    fast = orc.FastIndex(ev, n_acc)
+    assert fast.velocity(q).tobytes() == orc.velocity_batch(ev, n_acc, q).tobytes()
+    players = synth.make_players(n_acc, seed=32, now=synth.T0 + 30 * 3600)
+    tx = synth.make_tx(5000, n_acc, seed=33, t_lo=synth.T0 + 3600, t_hi=synth.T0 + 30 * 3600, invalid_rate=0.02)
+    model = synth.make_gbdt(n_trees=20, seed=34)
+    cfg = orc.default_config(model_kind=abi.MODEL_GBDT)
+    want = orc.score_batch(cfg, model, players, ev, tx)
+    assert fast.score_batch(cfg, model, players, tx, threads=1).tobytes() == want.tobytes()
+    assert fast.score_batch(cfg, model, players, tx, threads=5).tobytes() == want.tobytes()
+    fast.close()
