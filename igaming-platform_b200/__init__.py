@@ -198,11 +198,16 @@ class Engine:
         them and orders by timestamp (see include/igs.h, LATE EVENTS)."""
         self._check(self._lib.igs_set_late_policy(self._h, policy))
 
+    def set_compaction_threshold(self, min_delta_events: int) -> None:
+        """Appended events live in a delta index folded into the base beyond max(min_delta_events, base / 8)."""
+        self._check(self._lib.igs_set_compaction_threshold(self._h, min_delta_events))
+
     def history_info(self) -> dict:
         info = abi.HistoryInfo()
         self._check(self._lib.igs_get_history_info(self._h, C.byref(info)))
         return {"n_events": int(info.n_events), "late_events": int(info.late_events),
-                "n_accounts": int(info.n_accounts), "has_identifiers": bool(info.has_identifiers)}
+                "n_accounts": int(info.n_accounts), "has_identifiers": bool(info.has_identifiers),
+                "delta_events": int(info.delta_events)}
 
     def evict_events(self, now: int) -> int:
         """igs_evict_events: drop what can no longer influence a query at t >= now; -> events dropped."""
@@ -398,7 +403,7 @@ def _serialised(fn):
 
 # every method that uses slot 0's staging or replaces device state; the *_device methods are ordered by the
 # caller's streams and stay lock-free
-for _name in ("load_gbdt", "load_mlp", "load_players", "load_events", "append_events", "set_late_policy",
+for _name in ("load_gbdt", "load_mlp", "load_players", "load_events", "append_events", "set_late_policy", "set_compaction_threshold",
               "history_info", "evict_events", "get_uniques", "blacklist_load", "blacklist_add", "blacklist_check",
               "links_pairs", "links_group", "links_finish", "get_links", "check_bonus_abuse", "score_features",
               "get_velocity", "score_batch", "ltv_batch", "ltv_predict_batch", "ltv_mock_predict"):

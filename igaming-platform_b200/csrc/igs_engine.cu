@@ -111,6 +111,11 @@ int igs_engine_create(int device, igs_engine** out) {
     }
     e->device = device;
     e->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&e->ingest_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        igs_set_error(nullptr, "stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        igs_engine_destroy(e);
+        return IGS_ERR_CUDA;
+    }
     for (int s = 0; s < IGS_NUM_SLOTS; ++s) {
         igs_slot& sl = e->slot[s];
         bool ok = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking) == cudaSuccess &&
@@ -144,9 +149,11 @@ void igs_engine_destroy(igs_engine* e) {
         if (sl.stream) cudaStreamDestroy(sl.stream);
     }
     free_buf(&e->part_scratch);
+    if (e->ingest_stream) cudaStreamDestroy(e->ingest_stream);
     if (e->d_model) cudaFree(e->d_model);
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
+    igs_free_history_events(e);
     for (int k = 0; k < 3; ++k) igs_idset_free(&e->bl[k]);
     igs_links_free(e);
     igs_mlp_free(e);
@@ -308,6 +315,13 @@ int igs_set_late_policy(igs_engine* e, int policy) {
     return IGS_OK;
 }
 
+int igs_set_compaction_threshold(igs_engine* e, uint64_t min_delta_events) {
+    IGS_ENGINE(e);
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->delta_min = min_delta_events;
+    return IGS_OK;
+}
+
 int igs_get_history_info(igs_engine* e, igs_history_info* out) {
     IGS_ENGINE(e);
     IGS_REQUIRE(e, out != nullptr, "out is null");
@@ -317,6 +331,7 @@ int igs_get_history_info(igs_engine* e, igs_history_info* out) {
     out->n_events = e->n_raw;
     out->late_events = e->late_events;
     out->n_accounts = e->ev.n_accounts;
+    out->delta_events = e->n_raw - e->base_n;
     out->has_identifiers = e->has_event_ids ? 1u : 0u;
     return IGS_OK;
 }

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "igs.h"
+#include "velocity.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // device-resident model layout
@@ -76,6 +77,10 @@ struct igs_event_index {
     uint32_t* seq = nullptr;          // [n] arrival index of the sorted event
     igs_prefix_rec* pre = nullptr;    // [n + 1] exclusive prefix columns
     igs_tail_rec* tail = nullptr;     // [n] inclusive chain columns
+    // kernels launched while this set of arrays was the published one: one event each, recorded on the
+    // launching stream right after the launch.  The ingest stream waits for them before it overwrites the
+    // arrays (igs_history_reader in k_velocity.cu).
+    std::vector<cudaEvent_t> readers;
 };
 
 struct igs_engine {
@@ -106,7 +111,17 @@ struct igs_engine {
     uint64_t* raw_ip = nullptr;
     bool      has_event_ids = false;
     uint64_t  n_raw = 0, cap_raw = 0;
-    igs_event_index ev;
+    // The history as scoring sees it: a base index over raw[0, base_n) and a delta index over
+    // raw[base_n, n_raw) (empty after a bulk load / compaction).  Each has a spare set of arrays: a build
+    // writes the spare, then the two are swapped under view_mu — kernels already launched keep reading the
+    // arrays they were launched with.
+    igs_event_index ev, ev_spare;     // base
+    igs_event_index dv, dv_spare;     // delta
+    uint64_t base_n = 0;
+    uint64_t delta_min = 65536;       // igs_set_compaction_threshold
+    std::mutex view_mu;               // guards ev / dv (pointers, sizes) and the readers lists
+    std::vector<cudaEvent_t> free_events;
+    cudaStream_t ingest_stream = nullptr;   // every index build runs here
     bool has_events = false;
     std::vector<igs_buf> build_pool;  // scratch of the index build, kept between igs_append_events calls
     int      late_policy = IGS_LATE_REJECT;   // igs_set_late_policy
@@ -187,6 +202,21 @@ void igs_idset_free(igs_idset* s);
 int igs_launch_blacklist_check(igs_engine* e, const igs_tx_ids* d_ids, uint64_t n, uint8_t* d_out,
                                cudaStream_t stream);
 void igs_free_event_index(igs_engine* e);
+void igs_free_history_events(igs_engine* e);
+// Snapshot of the published history for the kernel(s) of one call.  Holds the engine's view lock from construction
+// until done(): take it, launch what reads `view`, call done(stream) — it records, per index level, an event on the
+// launching stream that the next build overwriting those arrays will wait for.
+struct igs_history_reader {
+    igs_engine* e;
+    igs_history_view view;
+    explicit igs_history_reader(igs_engine* e);
+    void done(cudaStream_t st);
+    ~igs_history_reader();
+    igs_history_reader(const igs_history_reader&) = delete;
+    igs_history_reader& operator=(const igs_history_reader&) = delete;
+   private:
+    bool locked;
+};
 int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted);
 int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);

@@ -69,7 +69,7 @@ struct ScoreParams {
     const igs_tx* tx;
     const igs_player_row* players;
     unsigned long long n_players;
-    igs_index_view ix;
+    igs_history_view ix;
     float* features_out;
     igs_velocity* velocity_out;
     const uint32_t* perm;          // optional: slot -> row, the batch visited in account order (see launch)
@@ -566,8 +566,8 @@ __global__ void k_visit_keys(const igs_tx* __restrict__ tx, uint32_t n, int drop
     keys[i] = (uint64_t)(__ldg(&tx[i].account) >> drop_bits);
     vals[i] = i;
 }
-static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, int passes, cudaStream_t stream, void** scratch,
-                       const uint32_t** perm) {
+static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, uint32_t n_accounts, int passes, cudaStream_t stream,
+                       void** scratch, const uint32_t** perm) {
     const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
     const size_t hist_elems = (size_t)kSortBins * nb_sort;
     const size_t b_keys = ((size_t)n * 8 + 255) & ~(size_t)255, b_vals = ((size_t)n * 4 + 255) & ~(size_t)255;
@@ -581,7 +581,7 @@ static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, int passes
     uint32_t* hist = (uint32_t*)(base + 2 * b_keys + 2 * b_vals);
     uint32_t* scr = (uint32_t*)(base + 2 * b_keys + 2 * b_vals + b_hist);
     int acct_bits = 1;
-    while (acct_bits < 32 && (e->ev.n_accounts >> acct_bits)) ++acct_bits;
+    while (acct_bits < 32 && (n_accounts >> acct_bits)) ++acct_bits;
     const int drop = std::max(0, acct_bits - passes * kSortMaxBits);
     k_visit_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, stream>>>(d_tx, n, drop, keys[0], vals[0]);
     IGS_LAUNCHED(e);
@@ -603,7 +603,8 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     p.tx = d_tx;
     p.players = e->d_players;
     p.n_players = e->d_players ? e->n_players : 0;
-    p.ix = igs_index_view_of(e);       // n_accounts = 0 when no history is loaded: empty velocity
+    igs_history_reader rd(e);          // the published base + delta; n_accounts = 0 when no history is loaded
+    p.ix = rd.view;
     p.features_out = d_features_out;
     p.velocity_out = d_velocity_out;
     p.tx_ids = d_ids;
@@ -614,10 +615,11 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     static const int visit_passes = getenv("IGS_VISIT_SORT_PASSES") ? atoi(getenv("IGS_VISIT_SORT_PASSES")) : 3;   // tuning knob (0 = off)
     void* scratch = nullptr;
     if (visit_passes > 0 && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
-        rc = visit_order(e, d_tx, (uint32_t)n, std::min(visit_passes, 4), stream, &scratch, &p.perm);
+        rc = visit_order(e, d_tx, (uint32_t)n, rd.view.base.n_accounts, std::min(visit_passes, 4), stream, &scratch, &p.perm);
         if (rc != IGS_OK) { if (scratch) cudaFreeAsync(scratch, stream); return rc; }
     }
     rc = launch(e, kSrcTx, p, false, stream);
+    if (rc == IGS_OK) rd.done(stream);
     if (scratch) cudaFreeAsync(scratch, stream);
     return rc;
 }

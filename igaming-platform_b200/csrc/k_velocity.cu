@@ -70,17 +70,20 @@ __global__ void k_make_keys(const uint32_t* __restrict__ account, const uint32_t
 // ------------------------------------------------------------------------------------------------
 // post-sort columns
 // ------------------------------------------------------------------------------------------------
-__global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ seq,
+// `local` = position of the sorted event inside the raw range being indexed (the *_in columns start at the range);
+// seq_out receives its global arrival index (local + seq_base): base and delta share one numbering.
+__global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ local,
                                 const uint32_t* __restrict__ ts_in,
                                 const int64_t* __restrict__ amount_in, const uint8_t* __restrict__ type_in,
-                                uint32_t n, uint32_t ts_min, int ts_bits, uint32_t* __restrict__ acct,
-                                uint32_t* __restrict__ ts, int64_t* __restrict__ amount,
-                                uint8_t* __restrict__ type) {
+                                uint32_t n, uint32_t ts_min, int ts_bits, uint32_t seq_base,
+                                uint32_t* __restrict__ acct, uint32_t* __restrict__ ts, uint32_t* __restrict__ seq_out,
+                                int64_t* __restrict__ amount, uint8_t* __restrict__ type) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint64_t k = __ldg(keys + i);
     acct[i] = (uint32_t)(k >> ts_bits);
-    const uint32_t s = __ldg(seq + i);
+    const uint32_t s = __ldg(local + i);
+    seq_out[i] = s + seq_base;
     ts[i] = ts_bits ? ts_min + (uint32_t)(k & ((1ull << ts_bits) - 1ull)) : __ldg(ts_in + s);
     amount[i] = __ldg(amount_in + s);
     type[i] = __ldg(type_in + s);
@@ -91,13 +94,17 @@ __global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_
 // timestamp as "now" (features/redis_store.go:121,132,155); the index files it where its timestamp says.
 // late[0] = such pairs in the whole history, late[1] = those whose late event has arrival index >= n_before
 // (the batch being appended).
-__global__ void k_segments(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ seq, uint32_t n,
-                           uint32_t n_accounts, uint32_t n_before, uint32_t* __restrict__ seg,
+// When a delta is being built over a base (base.n != 0), the first delta event of an account is also late if it
+// is older than the account's last base event.
+__global__ void k_segments(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
+                           const uint32_t* __restrict__ seq, uint32_t n,
+                           uint32_t n_accounts, uint32_t n_before, igs_index_view base, uint32_t* __restrict__ seg,
                            uint32_t* __restrict__ late) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     bool is_late = false, is_new = false;
     if (i < n) {
         const uint32_t a = __ldg(acct + i);
+        bool first_of_account = i == 0;
         if (i == 0) {
             for (uint32_t x = 0; x <= a; ++x) seg[x] = 0;
         } else {
@@ -106,6 +113,14 @@ __global__ void k_segments(const uint32_t* __restrict__ acct, const uint32_t* __
             const uint32_t sp = __ldg(seq + i - 1);
             is_late = p == a && sp > __ldg(seq + i);
             is_new = is_late && sp >= n_before;
+            first_of_account = p != a;
+        }
+        if (first_of_account && base.n != 0 && a < base.n_accounts) {
+            const uint32_t sb = __ldg(base.seg + a), eb = __ldg(base.seg + a + 1);
+            if (eb > sb && __ldg(ts + i) < __ldg(base.ts + eb - 1)) {
+                is_late = true;
+                is_new = __ldg(seq + i) >= n_before;
+            }
         }
         if (i == n - 1)
             for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
@@ -234,6 +249,28 @@ __global__ void k_dg_resolve(const uint32_t* __restrict__ gid, const uint32_t* _
     dflag[i] = minpos[base + h] == i;
 }
 
+// ---- delta over a base: the ZSET member dedupe across the boundary --------------------------------------
+// A delta event in the first (account, ts) group of its account whose ts equals the ts of the account's last
+// base event shares that second with base events: it is not a first occurrence if a base event of that second
+// carries the same amount.  (Later delta groups have a larger ts than every base event.)  Linear walk over the
+// base's trailing group — a same-second burst that straddles an append.
+__global__ void k_delta_boundary_dedupe(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
+                                        const int64_t* __restrict__ amount, const uint32_t* __restrict__ seg,
+                                        uint32_t n, igs_index_view base, const int64_t* __restrict__ raw_amount,
+                                        uint8_t* __restrict__ dflag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !dflag[i]) return;
+    const uint32_t a = __ldg(acct + i);
+    if (a >= base.n_accounts) return;
+    const uint32_t sb = __ldg(base.seg + a), eb = __ldg(base.seg + a + 1);
+    if (eb == sb) return;
+    const uint32_t t = __ldg(ts + i);
+    if (__ldg(base.ts + eb - 1) != t || __ldg(ts + __ldg(seg + a)) != t) return;
+    const int64_t m = __ldg(amount + i);
+    for (uint32_t k = eb; k-- > sb && __ldg(base.ts + k) == t;)
+        if (__ldg(raw_amount + __ldg(base.seq + k)) == m) { dflag[i] = 0; return; }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused scan of the velocity columns
 // ------------------------------------------------------------------------------------------------
@@ -257,6 +294,7 @@ __device__ __forceinline__ VScan vs_combine(const VScan& a, const VScan& b) {   
 struct VCols {
     const uint32_t* acct; const uint32_t* ts; const int64_t* amount; const uint8_t* type;
     const uint8_t* dflag; uint32_t n;
+    igs_index_view base;       // base.n != 0: a delta is being built and the chains continue the base's
 };
 __device__ __forceinline__ VScan vs_element(const VCols& c, uint32_t i) {
     VScan r = vs_identity();
@@ -276,6 +314,19 @@ __device__ __forceinline__ VScan vs_element(const VCols& c, uint32_t i) {
     r.cf = (new_acct || gap > 3600) ? 1u : 0u;        // tx_sum:1h key expired (redis_store.go:138)
     r.sf = (new_acct || gap > 1800) ? 1u : 0u;        // session key expired (:159-160)
     r.st = r.sf ? t : 0u;
+    if (new_acct && c.base.n != 0) {
+        // first delta event of the account: the keys it finds are the ones the account's last base event left
+        const uint32_t a = __ldg(c.acct + i);
+        if (a < c.base.n_accounts) {
+            const uint32_t sb = __ldg(c.base.seg + a), eb = __ldg(c.base.seg + a + 1);
+            if (eb > sb) {
+                const long long gb = (long long)t - (long long)__ldg(c.base.ts + eb - 1);
+                const igs_tail_rec tb = c.base.tail[eb - 1];
+                if (gb <= 3600) r.chain = m + tb.chain_sum;      // still a segment head for the scan: the value is complete
+                if (gb <= 1800) r.st = tb.sess_start;
+            }
+        }
+    }
     return r;
 }
 
@@ -424,7 +475,7 @@ k_vs_apply_elems(VCols c, const VScan* __restrict__ tile_excl, igs_prefix_rec* _
 // query kernel
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
-k_velocity(igs_index_view ix, const igs_query* __restrict__ q, unsigned long long n,
+k_velocity(igs_history_view ix, const igs_query* __restrict__ q, unsigned long long n,
            igs_velocity* __restrict__ out) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -437,7 +488,7 @@ k_velocity(igs_index_view ix, const igs_query* __restrict__ q, unsigned long lon
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_uniques(igs_index_view ix, const igs_query* __restrict__ q, unsigned long long n,
+k_uniques(igs_history_view ix, const igs_query* __restrict__ q, unsigned long long n,
           igs_uniques* __restrict__ out) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -619,19 +670,87 @@ int bits_for(uint64_t v) {   // number of bits needed to represent v
     return b;
 }
 
-static void free_build_pool(igs_engine* e) {
+void free_build_pool(igs_engine* e) {
     for (igs_buf& b : e->build_pool)
         if (b.p) cudaFree(b.p);
     e->build_pool.clear();
 }
 
+igs_index_view view_of(const igs_event_index& x, bool valid) {
+    igs_index_view v;
+    v.seg = x.seg; v.ts = x.ts; v.seq = x.seq; v.pre = x.pre; v.tail = x.tail;
+    v.n_accounts = valid ? x.n_accounts : 0;
+    v.n = valid ? (uint32_t)x.n : 0;
+    return v;
+}
+igs_index_view no_view() {
+    igs_index_view v;
+    v.seg = nullptr; v.ts = nullptr; v.seq = nullptr; v.pre = nullptr; v.tail = nullptr;
+    v.n_accounts = 0; v.n = 0;
+    return v;
+}
+
+void release_index_arrays(igs_engine* e, igs_event_index& x) {
+    if (x.seg) cudaFree(x.seg);
+    if (x.ts) cudaFree(x.ts);
+    if (x.seq) cudaFree(x.seq);
+    if (x.pre) cudaFree(x.pre);
+    if (x.tail) cudaFree(x.tail);
+    for (cudaEvent_t ev : x.readers) e->free_events.push_back(ev);   // cudaFree has waited for the device
+    x = igs_event_index();
+}
+
+// Makes `st` wait for every kernel that was launched while x's arrays were the published ones.  Caller holds view_mu.
+void wait_for_readers(igs_engine* e, igs_event_index& x, cudaStream_t st) {
+    for (cudaEvent_t ev : x.readers) {
+        cudaStreamWaitEvent(st, ev, 0);
+        e->free_events.push_back(ev);
+    }
+    x.readers.clear();
+}
+
 }  // namespace
 
-igs_index_view igs_index_view_of(const igs_engine* e) {
-    igs_index_view v;
-    v.seg = e->ev.seg; v.ts = e->ev.ts; v.seq = e->ev.seq; v.pre = e->ev.pre; v.tail = e->ev.tail;
-    v.n_accounts = e->has_events ? e->ev.n_accounts : 0;
-    v.n = (uint32_t)e->ev.n;
+// ------------------------------------------------------------------------------------------------
+// published view + reader bookkeeping
+// ------------------------------------------------------------------------------------------------
+igs_history_reader::igs_history_reader(igs_engine* eng) : e(eng), locked(true) {
+    e->view_mu.lock();
+    view.base = view_of(e->ev, e->has_events);
+    view.delta = e->has_events && e->dv.n != 0 ? view_of(e->dv, true) : no_view();
+}
+void igs_history_reader::done(cudaStream_t st) {
+    if (!locked) return;
+    igs_event_index* levels[2] = {&e->ev, &e->dv};
+    for (igs_event_index* x : levels) {
+        if (x->n == 0 || !e->has_events) continue;
+        if (x->readers.size() >= 64) {               // drop the ones that have completed
+            size_t k = 0;
+            for (cudaEvent_t ev : x->readers) {
+                if (cudaEventQuery(ev) == cudaSuccess) e->free_events.push_back(ev);
+                else x->readers[k++] = ev;
+            }
+            x->readers.resize(k);
+            cudaGetLastError();                      // cudaErrorNotReady is not an error
+        }
+        cudaEvent_t ev = nullptr;
+        if (!e->free_events.empty()) { ev = e->free_events.back(); e->free_events.pop_back(); }
+        else if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (cudaEventRecord(ev, st) == cudaSuccess) x->readers.push_back(ev);
+        else { cudaGetLastError(); e->free_events.push_back(ev); }
+    }
+    locked = false;
+    e->view_mu.unlock();
+}
+igs_history_reader::~igs_history_reader() {
+    if (locked) e->view_mu.unlock();
+}
+
+igs_history_view igs_history_view_of(igs_engine* e) {
+    std::lock_guard<std::mutex> lk(e->view_mu);
+    igs_history_view v;
+    v.base = view_of(e->ev, e->has_events);
+    v.delta = e->has_events && e->dv.n != 0 ? view_of(e->dv, true) : no_view();
     return v;
 }
 
@@ -645,27 +764,25 @@ static void free_raw_events(igs_engine* e) {
     e->raw_account = e->raw_ts = nullptr; e->raw_amount = nullptr; e->raw_type = nullptr;
     e->raw_device = e->raw_ip = nullptr;
     e->has_event_ids = false;
-    e->n_raw = e->cap_raw = 0;
-}
-
-static void release_index_arrays(igs_engine* e) {
-    igs_event_index& x = e->ev;
-    if (x.seg) cudaFree(x.seg);
-    if (x.ts) cudaFree(x.ts);
-    if (x.seq) cudaFree(x.seq);
-    if (x.pre) cudaFree(x.pre);
-    if (x.tail) cudaFree(x.tail);
-    x = igs_event_index();
-    e->has_events = false;
+    e->n_raw = e->cap_raw = e->base_n = 0;
 }
 
 void igs_free_event_index(igs_engine* e) {
-    release_index_arrays(e);
+    {
+        std::lock_guard<std::mutex> lk(e->view_mu);
+        e->has_events = false;
+        for (igs_event_index* x : {&e->ev, &e->ev_spare, &e->dv, &e->dv_spare}) release_index_arrays(e, *x);
+    }
     free_raw_events(e);
     free_build_pool(e);
 }
 
-// Appends n host events to the device-resident raw columns (capacity grows by 1.5x).
+void igs_free_history_events(igs_engine* e) {       // engine teardown: the pooled events
+    for (cudaEvent_t ev : e->free_events) cudaEventDestroy(ev);
+    e->free_events.clear();
+}
+
+// Appends n events to the device-resident raw columns (capacity grows by 1.5x).
 // (the source columns may be host or device memory: cudaMemcpyDefault lets the runtime tell)
 static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
                       cudaStream_t st) {
@@ -689,26 +806,22 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
                 return err == cudaErrorMemoryAllocation ? IGS_ERR_NOMEM : IGS_ERR_CUDA;
             }
         }
-        if (e->has_event_ids) {
-            if (e->n_raw) {
-                IGS_CUDA(e, cudaMemcpyAsync(d, e->raw_device, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
-                IGS_CUDA(e, cudaMemcpyAsync(p, e->raw_ip, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
-                IGS_CUDA(e, cudaStreamSynchronize(st));
-            }
-            if (e->raw_device) { cudaFree(e->raw_device); cudaFree(e->raw_ip); }
-            e->raw_device = d; e->raw_ip = p;
-        }
         if (e->n_raw) {
             IGS_CUDA(e, cudaMemcpyAsync(a, e->raw_account, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
             IGS_CUDA(e, cudaMemcpyAsync(t, e->raw_ts, e->n_raw * 4, cudaMemcpyDeviceToDevice, st));
             IGS_CUDA(e, cudaMemcpyAsync(m, e->raw_amount, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
             IGS_CUDA(e, cudaMemcpyAsync(y, e->raw_type, e->n_raw, cudaMemcpyDeviceToDevice, st));
+            if (e->has_event_ids) {
+                IGS_CUDA(e, cudaMemcpyAsync(d, e->raw_device, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
+                IGS_CUDA(e, cudaMemcpyAsync(p, e->raw_ip, e->n_raw * 8, cudaMemcpyDeviceToDevice, st));
+            }
             IGS_CUDA(e, cudaStreamSynchronize(st));
         }
-        const uint64_t keep = e->n_raw;
         if (e->raw_account) { cudaFree(e->raw_account); cudaFree(e->raw_ts); cudaFree(e->raw_amount); cudaFree(e->raw_type); }
+        if (e->raw_device) { cudaFree(e->raw_device); cudaFree(e->raw_ip); }
         e->raw_account = a; e->raw_ts = t; e->raw_amount = m; e->raw_type = y;
-        e->cap_raw = cap; e->n_raw = keep;
+        e->raw_device = d; e->raw_ip = p;
+        e->cap_raw = cap;
     }
     if (n) {
         IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyDefault, st));
@@ -728,52 +841,6 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
     }
     e->n_raw = need;
     return IGS_OK;
-}
-
-// n_before: arrival indices >= n_before are the batch being appended (late events among them are subject to the
-// late policy); a bulk load or an eviction passes "none"
-static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_before = 0xFFFFFFFFull);
-
-int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
-    if (!e->has_events) {
-        igs_set_error(e, "igs_append_events needs a loaded history (igs_load_events, possibly with n = 0)");
-        return IGS_ERR_STATE;
-    }
-    if (ids && !e->has_event_ids) {
-        igs_set_error(e, "the loaded history carries no identifiers (load it with igs_load_events_ids)");
-        return IGS_ERR_STATE;
-    }
-    if (e->n_raw + n >= 0xFFFFFFFFull) {
-        igs_set_error(e, "at most 2^32-2 events per shard");
-        return IGS_ERR_INVALID;
-    }
-    IGS_CUDA(e, cudaDeviceSynchronize());
-    const uint64_t before = e->n_raw;
-    const uint32_t n_accounts = e->ev.n_accounts;   // the rebuild resets e->ev
-    int rc = append_raw(e, ev, ids, n, e->slot[0].stream);
-    if (rc != IGS_OK) return rc;
-    rc = build_index_from_raw(e, n_accounts, before);
-    if (rc != IGS_OK) {                      // an account index out of range, late events: drop the rejected batch
-        char msg[sizeof(e->err)];
-        memcpy(msg, e->err, sizeof(msg));
-        e->n_raw = before;
-        build_index_from_raw(e, n_accounts);
-        memcpy(e->err, msg, sizeof(msg));    // report the rejection, not the recovery
-    }
-    return rc;
-}
-
-int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,
-                          uint32_t n_accounts) {
-    IGS_CUDA(e, cudaDeviceSynchronize());
-    igs_free_event_index(e);
-    e->has_event_ids = ids != nullptr;
-    int rc = append_raw(e, ev, ids, n64, e->slot[0].stream);
-    if (rc != IGS_OK) return rc;
-    rc = build_index_from_raw(e, n_accounts);
-    if (rc != IGS_OK) igs_free_event_index(e);
-    else free_build_pool(e);           // a bulk load does not keep ~70 B/event of scratch around
-    return rc;
 }
 
 // Settles the distinct flags of the (account, ts) groups that are too long for k_distinct's bounded walk.
@@ -836,12 +903,11 @@ struct IdScratch {
     uint8_t *head, *isnew8;
 };
 
-// Step 5 for one identifier column: fills tail[p].{dev,ip}_{ts,cnt}.  d_acct / e->ev.ts / e->ev.seq are the
-// sorted columns of the build in progress.
+// Step 5 for one identifier column: fills tail[p].{dev,ip}_{ts,cnt}.  d_acct / x.ts / x.seq are the sorted
+// columns of the build in progress; `raw` is the whole raw column (x.seq holds global arrival indices).
 template <int kCol>
-static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, const uint32_t* d_acct, uint32_t n,
-                           cudaStream_t st) {
-    igs_event_index& x = e->ev;
+static int build_id_column(igs_engine* e, igs_event_index& x, IdScratch& s, const uint64_t* raw, const uint32_t* d_acct,
+                           uint32_t n, cudaStream_t st) {
     const uint32_t nb = (n + kThreads - 1) / kThreads;
     k_id_gather<<<nb, kThreads, 0, st>>>(raw, x.seq, n, s.id_s, s.fex);
     IGS_LAUNCHED(e);
@@ -875,18 +941,35 @@ static int build_id_column(igs_engine* e, IdScratch& s, const uint64_t* raw, con
     return IGS_OK;
 }
 
-// (Re)builds the index from the raw columns e->raw_* [0, n_raw).
-static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_before) {
-    const uint32_t n = (uint32_t)e->n_raw;
-    cudaStream_t st = e->slot[0].stream;
-    igs_event_index& x = e->ev;
+// One index build: raw events [lo, hi) -> the arrays of *dst (not published; the caller swaps them in).
+//   base      carry-in for a delta build (base.n != 0): chain columns continue the base's, the distinct flags know
+//             the base's last (account, ts) group, a delta event older than its account's last base event is late
+//   n_before  arrival indices >= n_before are the batch being appended: late[1] counts the late pairs among them
+//             (late[0]: all late pairs of the range)
+// Runs on the ingest stream and returns after its kernels have completed.
+struct BuildSpec {
+    uint64_t lo = 0, hi = 0;
+    uint32_t n_accounts = 0;
+    igs_event_index* dst = nullptr;
+    igs_index_view base;
+    uint64_t n_before = 0xFFFFFFFFull;
+};
+
+static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
+    const uint32_t n = (uint32_t)(spec.hi - spec.lo);
+    const uint32_t n_accounts = spec.n_accounts;
+    cudaStream_t st = e->ingest_stream;
+    igs_event_index& x = *spec.dst;
     Scratch sc(e->build_pool);
-    e->has_events = false;
+    late[0] = late[1] = 0;
     if ((uint64_t)n + 1 > x.cap_events || (uint64_t)n_accounts + 1 > x.cap_accounts) {
         // (re)allocate the index arrays with headroom so that appends rarely come back here
         const uint64_t ce = std::max<uint64_t>((uint64_t)n + 1, x.cap_events + x.cap_events / 2);
         const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
-        release_index_arrays(e);
+        {
+            std::lock_guard<std::mutex> lk(e->view_mu);
+            release_index_arrays(e, x);
+        }
         IGS_CUDA(e, cudaMalloc(&x.seg, ca * sizeof(uint32_t)));
         IGS_CUDA(e, cudaMalloc(&x.ts, ce * sizeof(uint32_t)));
         IGS_CUDA(e, cudaMalloc(&x.seq, ce * sizeof(uint32_t)));
@@ -901,15 +984,14 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, cudaMemsetAsync(x.pre, 0, sizeof(igs_prefix_rec), st));
     if (n == 0) {
         IGS_CUDA(e, cudaStreamSynchronize(st));
-        e->has_events = true;
         return IGS_OK;
     }
 
     // ---- the raw columns are already on the device -----------------------------------------------
-    const uint32_t* d_acct_in = e->raw_account;
-    const uint32_t* d_ts_in = e->raw_ts;
-    const int64_t* d_amt_in = e->raw_amount;
-    const uint8_t* d_type_in = e->raw_type;
+    const uint32_t* d_acct_in = e->raw_account + spec.lo;
+    const uint32_t* d_ts_in = e->raw_ts + spec.lo;
+    const int64_t* d_amt_in = e->raw_amount + spec.lo;
+    const uint8_t* d_type_in = e->raw_type + spec.lo;
     uint32_t* d_mm;
     IGS_CUDA(e, sc.alloc(&d_mm, 8));            // [0..3] key range, [4..5] late-event counters
 
@@ -924,7 +1006,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, cudaStreamSynchronize(st));
     if (mm[2] >= n_accounts) {
         igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
-        return IGS_ERR_INVALID;          // has_events stays false until a build succeeds
+        return IGS_ERR_INVALID;
     }
     const uint32_t ts_min = mm[0];
     // Events that arrive in time order (a log, a queue, appended micro-batches) only need a stable sort by
@@ -961,11 +1043,11 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     IGS_CUDA(e, sc.alloc(&d_amt, n));
     IGS_CUDA(e, sc.alloc(&d_type, n));
     IGS_CUDA(e, sc.alloc(&d_dflag, n));
-    IGS_CUDA(e, cudaMemcpyAsync(x.seq, d_vals[cur], (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], x.seq, d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
-                                                d_acct, x.ts, d_amt, d_type);
+    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], d_vals[cur], d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
+                                                (uint32_t)spec.lo, d_acct, x.ts, x.seq, d_amt, d_type);
     IGS_LAUNCHED(e);
-    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, x.seq, n, n_accounts, (uint32_t)n_before, x.seg, d_mm + 4);
+    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, x.seq, n, n_accounts, (uint32_t)spec.n_before, spec.base, x.seg,
+                                           d_mm + 4);
     IGS_LAUNCHED(e);
     uint8_t* d_head;
     IGS_CUDA(e, sc.alloc(&d_head, n));
@@ -977,19 +1059,17 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_mm);
     IGS_LAUNCHED(e);
     {
-        uint32_t n_unres = 0, late[2] = {0, 0};
+        uint32_t n_unres = 0;
         IGS_CUDA(e, cudaMemcpyAsync(&n_unres, d_mm, 4, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaMemcpyAsync(late, d_mm + 4, 8, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
-        e->late_events = late[0];
-        if (late[1] != 0 && e->late_policy == IGS_LATE_REJECT) {
-            igs_set_error(e, "the batch holds %u late event(s): an event older than one of the same account that is "
-                          "already resident or earlier in the batch (policy IGS_LATE_REJECT; see igs_set_late_policy)",
-                          late[1]);
-            return IGS_ERR_INVALID;
-        }
+        if (late[1] != 0 && e->late_policy == IGS_LATE_REJECT) return IGS_OK;   // the caller drops the batch: stop here
         const int rc = resolve_big_groups(e, sc, n_unres != 0, d_head, d_amt, n, d_dflag, d_scan_scratch_n, st);
         if (rc != IGS_OK) return rc;
+    }
+    if (spec.base.n != 0) {
+        k_delta_boundary_dedupe<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, d_amt, x.seg, n, spec.base, e->raw_amount, d_dflag);
+        IGS_LAUNCHED(e);
     }
 
     // ---- fused scan: reduce up two levels, scan the top, apply down ---------------------------------
@@ -998,7 +1078,7 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
     VScan *d_agg1, *d_agg2;
     IGS_CUDA(e, sc.alloc(&d_agg1, n1));
     IGS_CUDA(e, sc.alloc(&d_agg2, n2));
-    VCols cols{d_acct, x.ts, d_amt, d_type, d_dflag, n};
+    VCols cols{d_acct, x.ts, d_amt, d_type, d_dflag, n, spec.base};
     const uint32_t warps_per_block = kThreads / 32;
     const uint32_t g1 = (n1 + warps_per_block - 1) / warps_per_block, g2 = (n2 + warps_per_block - 1) / warps_per_block;
     k_vs_reduce<ElemSrc><<<g1, kThreads, 0, st>>>(ElemSrc{cols}, d_agg1);
@@ -1027,14 +1107,120 @@ static int build_index_from_raw(igs_engine* e, uint32_t n_accounts, uint64_t n_b
         IGS_CUDA(e, sc.alloc(&is.nex, n));
         IGS_CUDA(e, sc.alloc(&is.hist, (size_t)kSortBins * nb_sort));
         IGS_CUDA(e, sc.alloc(&is.scan_scratch, scan_u32_scratch_elems(std::max<uint32_t>((uint32_t)kSortBins * nb_sort, n))));
-        int rc = build_id_column<0>(e, is, e->raw_device, d_acct, n, st);
+        int rc = build_id_column<0>(e, x, is, e->raw_device, d_acct, n, st);
         if (rc != IGS_OK) return rc;
-        rc = build_id_column<1>(e, is, e->raw_ip, d_acct, n, st);
+        rc = build_id_column<1>(e, x, is, e->raw_ip, d_acct, n, st);
         if (rc != IGS_OK) return rc;
     }
     IGS_CUDA(e, cudaStreamSynchronize(st));
+    return IGS_OK;
+}
+
+static int reject_late(igs_engine* e, uint32_t n_late) {
+    igs_set_error(e, "the batch holds %u late event(s): an event older than one of the same account that is already "
+                  "resident or earlier in the batch (policy IGS_LATE_REJECT; see igs_set_late_policy)", n_late);
+    return IGS_ERR_INVALID;
+}
+
+// (Re)builds the base over every resident raw event and publishes it; the delta becomes empty.  A bulk load, an
+// eviction, a compaction, an append that cannot go through the delta.  On any failure — a bad account index, a
+// rejected late batch — nothing is published and the caller restores n_raw.
+static int rebuild_base(igs_engine* e, uint32_t n_accounts, uint64_t n_before) {
+    {
+        std::lock_guard<std::mutex> lk(e->view_mu);
+        wait_for_readers(e, e->ev_spare, e->ingest_stream);
+    }
+    BuildSpec spec;
+    spec.lo = 0; spec.hi = e->n_raw; spec.n_accounts = n_accounts; spec.dst = &e->ev_spare;
+    spec.base = no_view(); spec.n_before = n_before;
+    uint32_t late[2];
+    const int rc = build_index(e, spec, late);
+    if (rc != IGS_OK) return rc;
+    if (late[1] != 0 && e->late_policy == IGS_LATE_REJECT) return reject_late(e, late[1]);
+    std::lock_guard<std::mutex> lk(e->view_mu);
+    std::swap(e->ev, e->ev_spare);
+    e->dv.n = 0;                         // its arrays stay until the next delta build has waited for their readers
+    e->base_n = e->n_raw;
+    e->late_events = late[0];
     e->has_events = true;
     return IGS_OK;
+}
+
+// Appended events sit in a delta index until it outgrows max(delta_min, base / 8); then base and delta are rebuilt
+// into one base (amortised: a delta rebuild costs what the delta holds, a compaction what everything holds).
+
+int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n) {
+    if (!e->has_events) {
+        igs_set_error(e, "igs_append_events needs a loaded history (igs_load_events, possibly with n = 0)");
+        return IGS_ERR_STATE;
+    }
+    if (ids && !e->has_event_ids) {
+        igs_set_error(e, "the loaded history carries no identifiers (load it with igs_load_events_ids)");
+        return IGS_ERR_STATE;
+    }
+    if (e->n_raw + n >= 0xFFFFFFFFull) {
+        igs_set_error(e, "at most 2^32-2 events per shard");
+        return IGS_ERR_INVALID;
+    }
+    if (n == 0) return IGS_OK;
+    const uint64_t before = e->n_raw;
+    const uint32_t n_accounts = e->ev.n_accounts;
+    int rc = append_raw(e, ev, ids, n, e->ingest_stream);
+    if (rc != IGS_OK) { e->n_raw = before; return rc; }
+    // Histories with identifier columns still rebuild everything: a delta would have to know which identifiers
+    // the base's trailing 24h chains hold.
+    bool through_delta = !e->has_event_ids;
+    if (through_delta) {
+        {
+            std::lock_guard<std::mutex> lk(e->view_mu);
+            wait_for_readers(e, e->dv_spare, e->ingest_stream);
+        }
+        BuildSpec spec;
+        spec.lo = e->base_n; spec.hi = e->n_raw; spec.n_accounts = n_accounts; spec.dst = &e->dv_spare;
+        spec.base = view_of(e->ev, true); spec.n_before = before;
+        uint32_t late[2];
+        rc = build_index(e, spec, late);
+        if (rc != IGS_OK) { e->n_raw = before; return rc; }
+        if (late[1] != 0) {
+            if (e->late_policy == IGS_LATE_REJECT) { e->n_raw = before; return reject_late(e, late[1]); }
+            through_delta = false;       // IGS_LATE_REORDER: file everything by timestamp in a new base
+        } else {
+            {
+                std::lock_guard<std::mutex> lk(e->view_mu);
+                std::swap(e->dv, e->dv_spare);
+            }
+            const uint64_t delta_n = e->n_raw - e->base_n;
+            if (delta_n <= std::max<uint64_t>(e->delta_min, e->base_n / 8)) return IGS_OK;
+            rc = rebuild_base(e, n_accounts, 0xFFFFFFFFull);          // compaction: nothing in it is new
+            if (rc != IGS_OK) igs_set_error(e, "compaction of the event index failed; the appended events stay in the delta");
+            return IGS_OK;               // the batch is in either way: base + delta still answer correctly
+        }
+    }
+    rc = rebuild_base(e, n_accounts, before);
+    if (rc != IGS_OK) e->n_raw = before;
+    return rc;
+}
+
+int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,
+                          uint32_t n_accounts) {
+    IGS_CUDA(e, cudaDeviceSynchronize());
+    // The previous history's allocations (raw columns, index arrays, build scratch) are kept and reused when they
+    // are large enough: allocating and freeing a dozen buffers of hundreds of MB costs tens of milliseconds, ten
+    // times the kernels of the build.  They are released when the load fails and when the engine is destroyed.
+    {
+        std::lock_guard<std::mutex> lk(e->view_mu);
+        e->has_events = false;
+        e->ev.n = e->dv.n = 0;
+    }
+    const bool with_ids = ids != nullptr;
+    if (with_ids != e->has_event_ids || (with_ids && !e->raw_device)) free_raw_events(e);   // different column set
+    e->has_event_ids = with_ids;
+    e->n_raw = e->base_n = 0;
+    e->late_events = 0;
+    int rc = append_raw(e, ev, ids, n64, e->ingest_stream);
+    if (rc == IGS_OK) rc = rebuild_base(e, n_accounts, 0xFFFFFFFFull);
+    if (rc != IGS_OK) igs_free_event_index(e);
+    return rc;
 }
 
 int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out, cudaStream_t stream) {
@@ -1044,8 +1230,10 @@ int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniq
     }
     if (n == 0) return IGS_OK;
     const unsigned long long nb = (n + kThreads - 1) / kThreads;
-    k_uniques<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
+    igs_history_reader rd(e);
+    k_uniques<<<(unsigned)nb, kThreads, 0, stream>>>(rd.view, d_q, n, d_out);
     IGS_LAUNCHED(e);
+    rd.done(stream);
     return IGS_OK;
 }
 
@@ -1057,8 +1245,10 @@ int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_vel
     }
     if (n == 0) return IGS_OK;
     const unsigned long long nb = (n + kThreads - 1) / kThreads;
-    k_velocity<<<(unsigned)nb, kThreads, 0, stream>>>(igs_index_view_of(e), d_q, n, d_out);
+    igs_history_reader rd(e);
+    k_velocity<<<(unsigned)nb, kThreads, 0, stream>>>(rd.view, d_q, n, d_out);
     IGS_LAUNCHED(e);
+    rd.done(stream);
     return IGS_OK;
 }
 
@@ -1074,12 +1264,16 @@ int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
     const uint32_t n_accounts = e->ev.n_accounts;
     if (n == 0) return IGS_OK;
     IGS_CUDA(e, cudaDeviceSynchronize());
-    cudaStream_t st = e->slot[0].stream;
+    int rc = IGS_OK;
+    if (e->base_n != e->n_raw) {                      // fold the delta in: the passes below walk one index
+        rc = rebuild_base(e, n_accounts, 0xFFFFFFFFull);
+        if (rc != IGS_OK) return rc;
+    }
+    cudaStream_t st = e->ingest_stream;
     const igs_event_index& x = e->ev;
     const uint32_t nb = (n + kThreads - 1) / kThreads;
     uint32_t *keep_from = nullptr, *keep = nullptr, *scr = nullptr, *last_keep = nullptr;
     void* fresh[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    int rc = IGS_OK;
     auto bail = [&](cudaError_t err, const char* what) {
         igs_set_error(e, "%s failed: %s", what, cudaGetErrorString(err));
         rc = err == cudaErrorMemoryAllocation ? IGS_ERR_NOMEM : IGS_ERR_CUDA;
@@ -1131,7 +1325,7 @@ int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted) {
         for (void*& f : fresh) f = nullptr;
         e->n_raw = kept;
         e->cap_raw = cap;
-        rc = build_index_from_raw(e, n_accounts);
+        rc = rebuild_base(e, n_accounts, 0xFFFFFFFFull);
     } while (false);
     for (void* f : fresh) if (f) cudaFree(f);
     cudaFree(keep_from); cudaFree(keep); cudaFree(scr);

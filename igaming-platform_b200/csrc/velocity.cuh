@@ -2,7 +2,7 @@
 //
 // The index (built by k_velocity.cu) holds the shard's events sorted by (account, ts, arrival)
 // plus scan columns, so that "what would GetRealTimeFeatures return for this account at time t"
-// (features/redis_store.go:60-116) is a handful of binary searches and prefix differences —
+// (features/redis_store.go:60-116) is a handful of searches and prefix differences —
 // O(log events-of-the-account) per query, independent of the history size.
 //
 // Closed form (proven equal to a command-level Redis emulation by the CPU tests):
@@ -15,6 +15,18 @@
 //   extension     = per-type (bet, deposit) count / sum over [t-W, t], W = 1m, 1h, 24h, multiset
 //   uniques       = distinct identifiers of the trailing chain (gaps <= 86400) of the prior events that
 //                   carried one, iff t - (ts of the last of them) <= 86400   (PFADD/EXPIRE :141-152)
+//
+// Two levels.  The history is a BASE index plus a (possibly empty) DELTA index over the events appended
+// since the base was built (igs_append_events): per account every delta event is ordered after every base
+// event (appends with late events are refused or trigger a rebuild), the delta's chain columns continue the
+// base's (carried in when the delta is built) and its distinct flags know the base's last (account, ts) group.
+// A query whose prior events end in the base is answered from the base alone; one whose prior events reach
+// into the delta adds the two levels' prefix differences and takes the chain columns from the delta.
+//
+// Searching.  All five window bounds lie at the END of the prior events (the last 24 h), and most queries are
+// "now" queries whose prior events are the whole segment, so every search starts at the end and gallops
+// backwards (1, 2, 4 ... events) before bisecting: an account with a long history costs as many dependent
+// loads as its last day is long, and the probes of a short gallop share one 32-byte sector of ts[].
 #pragma once
 
 #include <cuda_runtime.h>
@@ -52,82 +64,120 @@ union __align__(16) igs_velocity_a16 {
     __device__ igs_velocity_a16() {}
 };
 
+// one level of the index
 struct igs_index_view {
     const uint32_t* seg;             // [n_accounts+1]
     const uint32_t* ts;              // [n]
-    const uint32_t* seq;             // [n]
+    const uint32_t* seq;             // [n] arrival index (global: base and delta share one numbering)
     const igs_prefix_rec* pre;       // [n+1]
     const igs_tail_rec* tail;        // [n]
     uint32_t n_accounts;
     uint32_t n;
 };
+// base + delta (delta.n == 0: no delta)
+struct igs_history_view {
+    igs_index_view base, delta;
+};
 
-// first i in [lo, hi) with ts[i] >= key  (key may be negative: then lo)
-__device__ __forceinline__ uint32_t igs_lower_ts(const uint32_t* __restrict__ ts, uint32_t lo,
-                                                 uint32_t hi, long long key) {
-    if (key <= 0) return lo;
+// first i in [s, hi) with ts[i] >= key, searched backwards from hi (key may be negative: then s)
+__device__ __forceinline__ uint32_t igs_lower_ts_back(const uint32_t* __restrict__ ts, uint32_t s, uint32_t hi,
+                                                      long long key) {
+    if (key <= 0) return s;
     if (key > 0xFFFFFFFFll) return hi;
     const uint32_t k = (uint32_t)key;
-    while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        if (__ldg(ts + mid) < k) lo = mid + 1; else hi = mid;
+    uint32_t left = s, right = hi, step = 1;
+    while (right > left) {                       // gallop: ts[right ..] >= k is known
+        const uint32_t probe = right - left > step ? right - step : left;
+        if (__ldg(ts + probe) < k) { left = probe + 1; break; }
+        right = probe;
+        step <<= 1;
     }
-    return lo;
+    while (left < right) {                       // bisect (left - 1 is < k, right is >= k)
+        const uint32_t mid = left + ((right - left) >> 1);
+        if (__ldg(ts + mid) < k) left = mid + 1; else right = mid;
+    }
+    return left;
 }
 
-__device__ __forceinline__ void igs_velocity_lookup(const igs_index_view& ix, uint32_t account,
-                                                    uint32_t t, uint32_t seq_limit, igs_velocity* v,
-                                                    igs_uniques* uq = nullptr) {
-    if (uq) uq->devices_24h = uq->ips_24h = 0;
-    v->tx_sum_1h = 0;
-    v->tx_count_1m = v->tx_count_5m = v->tx_count_1h = 0;
-    v->time_since_last_tx = v->session_duration = v->n_prior = 0;
-#pragma unroll
-    for (int ty = 0; ty < 2; ++ty)
-#pragma unroll
-        for (int w = 0; w < 3; ++w) { v->win[ty][w].sum = 0; v->win[ty][w].count = 0; v->win[ty][w].pad = 0; }
-    if (account >= ix.n_accounts) return;
-    const uint32_t s = __ldg(ix.seg + account), e = __ldg(ix.seg + account + 1);
-    // u = number of prior events: first position whose (ts, seq) is not < (t, seq_limit)
-    uint32_t lo = s, hi = e;
+// number of events in [s, e) ordered before (t, seq_limit), as a position: first one that is not
+__device__ __forceinline__ uint32_t igs_prior_end(const igs_index_view& ix, uint32_t s, uint32_t e, uint32_t t,
+                                                  uint32_t seq_limit) {
+    if (s == e) return s;
+    {   // the common query is newer than everything the account has done
+        const uint32_t tl = __ldg(ix.ts + e - 1);
+        if (tl < t || (tl == t && __ldg(ix.seq + e - 1) < seq_limit)) return e;
+    }
+    uint32_t lo = s, hi = e - 1;
     while (lo < hi) {
         const uint32_t mid = lo + ((hi - lo) >> 1);
         const uint32_t tm = __ldg(ix.ts + mid);
         const bool before = tm < t || (tm == t && __ldg(ix.seq + mid) < seq_limit);
         if (before) lo = mid + 1; else hi = mid;
     }
-    const uint32_t u = lo;
-    if (u == s) return;
-    v->n_prior = u - s;
-    const long long now = t;
-    const long long L = __ldg(ix.ts + u - 1);
-    const uint32_t lo60 = igs_lower_ts(ix.ts, s, u, now - 60);
-    const uint32_t lo300 = igs_lower_ts(ix.ts, s, lo60, now - 300);
-    const uint32_t lo3600 = igs_lower_ts(ix.ts, s, lo300, now - 3600);
-    const uint32_t lo86400 = igs_lower_ts(ix.ts, s, lo3600, now - 86400);
-    const uint32_t alive = igs_lower_ts(ix.ts, s, u, L - 3599);   // ts > L-3600
-    const igs_prefix_rec pu = ix.pre[u];
-    const igs_prefix_rec p60 = ix.pre[lo60];
-    const igs_prefix_rec p3600 = ix.pre[lo3600];
-    const igs_prefix_rec p86400 = ix.pre[lo86400];
-    const uint32_t a300 = lo300 > alive ? lo300 : alive;
-    const uint32_t a3600 = lo3600 > alive ? lo3600 : alive;
-    v->tx_count_1m = pu.dcnt - (lo60 >= alive ? p60.dcnt : ix.pre[alive].dcnt);
-    v->tx_count_5m = pu.dcnt - ix.pre[a300].dcnt;
-    v->tx_count_1h = pu.dcnt - (a3600 == lo3600 ? p3600.dcnt : ix.pre[a3600].dcnt);
+    return lo;
+}
+
+// window bounds of the prior events [s, u) of one level
+struct igs_bounds {
+    uint32_t lo60, lo300, lo3600, lo86400;
+    uint32_t alive;   // first position that survived the last 1h trim (ts > L-3600); s when it cannot bind
+};
+// `last_is_now`: the newest prior event (of the whole history, both levels) has ts == now.  Only then can the
+// trim bound L-3599 exceed the 1h window bound now-3600 (quirk Q4); otherwise alive <= lo3600 and never binds.
+__device__ __forceinline__ igs_bounds igs_window_bounds(const uint32_t* __restrict__ ts, uint32_t s, uint32_t u,
+                                                        long long now, bool last_is_now) {
+    igs_bounds b;
+    b.lo60 = igs_lower_ts_back(ts, s, u, now - 60);
+    b.lo300 = igs_lower_ts_back(ts, s, b.lo60, now - 300);
+    b.lo3600 = igs_lower_ts_back(ts, s, b.lo300, now - 3600);
+    b.lo86400 = igs_lower_ts_back(ts, s, b.lo3600, now - 86400);
+    b.alive = s;
+    if (last_is_now) {                            // now-3599 lies between the 1h and the 5m bound
+        uint32_t lo = b.lo3600, hi = b.lo300;
+        const uint32_t k = now - 3599 > 0 ? (uint32_t)(now - 3599) : 0u;
+        while (lo < hi) {
+            const uint32_t mid = lo + ((hi - lo) >> 1);
+            if (__ldg(ts + mid) < k) lo = mid + 1; else hi = mid;
+        }
+        b.alive = lo;
+    }
+    return b;
+}
+
+// adds one level's contribution: prefix differences between position u and the bounds
+__device__ __forceinline__ void igs_velocity_accumulate(const igs_prefix_rec* __restrict__ pre, uint32_t u,
+                                                        const igs_bounds& b, igs_velocity* v) {
+    const igs_prefix_rec pu = pre[u];
+    const igs_prefix_rec p60 = pre[b.lo60];
+    const igs_prefix_rec p3600 = pre[b.lo3600];
+    const igs_prefix_rec p86400 = pre[b.lo86400];
+    const uint32_t a60 = b.lo60 > b.alive ? b.lo60 : b.alive;
+    const uint32_t a300 = b.lo300 > b.alive ? b.lo300 : b.alive;
+    const uint32_t a3600 = b.lo3600 > b.alive ? b.lo3600 : b.alive;
+    const uint32_t d60 = a60 == b.lo60 ? p60.dcnt : pre[a60].dcnt;
+    const uint32_t d300 = a300 == b.lo60 ? p60.dcnt : (a300 == b.lo3600 ? p3600.dcnt : pre[a300].dcnt);
+    const uint32_t d3600 = a3600 == b.lo3600 ? p3600.dcnt : pre[a3600].dcnt;
+    v->tx_count_1m += pu.dcnt - d60;
+    v->tx_count_5m += pu.dcnt - d300;
+    v->tx_count_1h += pu.dcnt - d3600;
 #pragma unroll
     for (int ty = 0; ty < 2; ++ty) {
-        v->win[ty][0].count = pu.cnt[ty] - p60.cnt[ty];
-        v->win[ty][0].sum = pu.sum[ty] - p60.sum[ty];
-        v->win[ty][1].count = pu.cnt[ty] - p3600.cnt[ty];
-        v->win[ty][1].sum = pu.sum[ty] - p3600.sum[ty];
-        v->win[ty][2].count = pu.cnt[ty] - p86400.cnt[ty];
-        v->win[ty][2].sum = pu.sum[ty] - p86400.sum[ty];
+        v->win[ty][0].count += pu.cnt[ty] - p60.cnt[ty];
+        v->win[ty][0].sum += pu.sum[ty] - p60.sum[ty];
+        v->win[ty][1].count += pu.cnt[ty] - p3600.cnt[ty];
+        v->win[ty][1].sum += pu.sum[ty] - p3600.sum[ty];
+        v->win[ty][2].count += pu.cnt[ty] - p86400.cnt[ty];
+        v->win[ty][2].sum += pu.sum[ty] - p86400.sum[ty];
     }
+}
+
+// the chain columns of the newest prior event (position `last` of level ix)
+__device__ __forceinline__ void igs_velocity_tail(const igs_index_view& ix, uint32_t last, long long now, long long L,
+                                                  igs_velocity* v, igs_uniques* uq) {
     const long long gap = now - L;
     union __align__(16) { igs_tail_rec r; uint4 q[2]; } tlu;
     {
-        const uint4* src = reinterpret_cast<const uint4*>(ix.tail + (u - 1));
+        const uint4* src = reinterpret_cast<const uint4*>(ix.tail + last);
         tlu.q[0] = __ldg(src);
         if (uq) tlu.q[1] = __ldg(src + 1);
     }
@@ -141,5 +191,49 @@ __device__ __forceinline__ void igs_velocity_lookup(const igs_index_view& ix, ui
     if (gap <= 1800) v->session_duration = (uint32_t)(now - (long long)tl.sess_start);
 }
 
-// view of the engine's loaded index (n_accounts = 0 when no history is loaded)
-struct igs_index_view igs_index_view_of(const igs_engine* e);
+__device__ __forceinline__ void igs_velocity_lookup(const igs_history_view& hv, uint32_t account, uint32_t t,
+                                                    uint32_t seq_limit, igs_velocity* v, igs_uniques* uq = nullptr) {
+    if (uq) uq->devices_24h = uq->ips_24h = 0;
+    v->tx_sum_1h = 0;
+    v->tx_count_1m = v->tx_count_5m = v->tx_count_1h = 0;
+    v->time_since_last_tx = v->session_duration = v->n_prior = 0;
+#pragma unroll
+    for (int ty = 0; ty < 2; ++ty)
+#pragma unroll
+        for (int w = 0; w < 3; ++w) { v->win[ty][w].sum = 0; v->win[ty][w].count = 0; v->win[ty][w].pad = 0; }
+    const igs_index_view& bx = hv.base;
+    const igs_index_view& dx = hv.delta;
+    uint32_t sb = 0, eb = 0, sd = 0, ed = 0;
+    if (account < bx.n_accounts) { sb = __ldg(bx.seg + account); eb = __ldg(bx.seg + account + 1); }
+    if (dx.n != 0 && account < dx.n_accounts) { sd = __ldg(dx.seg + account); ed = __ldg(dx.seg + account + 1); }
+    const long long now = t;
+    const uint32_t ud = igs_prior_end(dx, sd, ed, t, seq_limit);
+    if (ud == sd) {                                     // the prior events end in the base
+        const uint32_t ub = igs_prior_end(bx, sb, eb, t, seq_limit);
+        if (ub == sb) return;
+        v->n_prior = ub - sb;
+        const long long L = __ldg(bx.ts + ub - 1);
+        const igs_bounds b = igs_window_bounds(bx.ts, sb, ub, now, L == now);
+        igs_velocity_accumulate(bx.pre, ub, b, v);
+        igs_velocity_tail(bx, ub - 1, now, L, v, uq);
+        return;
+    }
+    // the prior events reach into the delta: every base event of the account is prior too
+    v->n_prior = (eb - sb) + (ud - sd);
+    const long long L = __ldg(dx.ts + ud - 1);
+    const igs_bounds d = igs_window_bounds(dx.ts, sd, ud, now, L == now);
+    igs_velocity_accumulate(dx.pre, ud, d, v);
+    if (eb > sb && d.lo86400 == sd) {                   // some window reaches back into the base
+        igs_bounds b = igs_window_bounds(bx.ts, sb, eb, now, L == now);
+        // a bound that fell inside the delta excludes the base altogether for that window
+        if (d.lo60 != sd) b.lo60 = eb;
+        if (d.lo300 != sd) b.lo300 = eb;
+        if (d.lo3600 != sd) b.lo3600 = eb;
+        if (d.alive != sd) b.alive = eb;
+        igs_velocity_accumulate(bx.pre, eb, b, v);
+    }
+    igs_velocity_tail(dx, ud - 1, now, L, v, uq);       // chain columns were carried over from the base at build time
+}
+
+// views of the engine's loaded history (n_accounts = 0 when nothing is loaded), taken under the engine's view lock
+struct igs_history_view igs_history_view_of(igs_engine* e);

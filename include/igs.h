@@ -17,7 +17,8 @@
  * caller (the synchronous host-buffer calls all use slot 0).  The calls that replace device state —
  * igs_load_*, igs_append_events*, igs_evict_events, igs_blacklist_load / _add, igs_links_* — are
  * like ONNXModel.Close under its write lock (ml/onnx_model.go:349): they must not run while a
- * scoring or query call on the same engine is in flight.  Three *_device calls work through per-engine
+ * scoring or query call on the same engine is in flight — with one exception: igs_append_events
+ * (history without identifiers) may run concurrently with scoring and query calls, see there.  Three *_device calls work through per-engine
  * scratch, not per-stream scratch: igs_partition_tx_device (its counters; grown with cudaFree +
  * cudaMalloc when a batch needs more than any before), igs_ltv_batch_device and igs_ltv_hidden_device
  * (two 512 MB activation buffers shared by every call).  On one engine, order such calls with respect to
@@ -365,12 +366,25 @@ int igs_load_events_device(igs_engine* e, const igs_event_cols* d_ev, const igs_
 /* Replaces FeatureStore.UpdateRealTimeFeatures (scoring/engine.go:111; features/redis_store.go:119-168)
  * for a batch of completed transactions — what ScoringEngine.UpdateFeatures (scoring/engine.go:486-488)
  * does per "transaction.completed" event (services/risk/cmd/main.go:219-224): appends n events, in
- * arrival order after everything loaded or appended so far, and refreshes the index.  The result is
- * identical to igs_load_events of the concatenated history (the raw columns stay on the device; only the
- * new events cross PCIe; the index is rebuilt — about 0.2 ms per million resident events on a B200).
+ * arrival order after everything loaded or appended so far.  Every query afterwards answers exactly as
+ * after igs_load_events of the concatenated history.
+ * How: the raw columns stay on the device and only the new events cross PCIe.  The index built by the last
+ * load stays as it is (the BASE); the events appended since form a second, small index (the DELTA) that is
+ * rebuilt on every append — its chain sums, session starts and duplicate flags continue the base's — and the
+ * lookup consults both.  When the delta outgrows max(threshold, base / 8) events the two are rebuilt into
+ * one base (igs_set_compaction_threshold; default threshold 65 536).  Cost of an append = the delta's size,
+ * not the history's; a compaction costs one full build.  Histories that carry identifiers
+ * (igs_load_events_ids) still rebuild the whole index on every append.
+ * Concurrency: an append builds into arrays no kernel is reading and then swaps them in, so scoring and
+ * query calls on other slots / streams of the same engine may run WHILE an append is in progress: they see
+ * the history either before or after the batch, never a mixture.  Appends themselves (and the loads,
+ * igs_evict_events) are serialised by the engine.
  * Needs a prior igs_load_events (n = 0 is fine) that fixed n_accounts.  A batch with an out-of-range
  * account is rejected as a whole and the history is left as it was.                                  */
 int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n);
+/* The delta index is folded into the base when it holds more than max(min_delta_events, base / 8) events.
+ * No counterpart in the reference (Redis updates in place).                                          */
+int igs_set_compaction_threshold(igs_engine* e, uint64_t min_delta_events);
 
 /* LATE EVENTS.  Redis applies every event when it arrives, with the event's own timestamp as "now"
  * (features/redis_store.go:121: ZADD score, :132 trim bound, :155 SET last_tx), so an event that arrives
@@ -393,7 +407,8 @@ typedef struct igs_history_info {
                                 of their time order                                                   */
     uint32_t n_accounts;
     uint32_t has_identifiers;
-    uint64_t reserved[4];
+    uint64_t delta_events;   /* of n_events: appended since the base index was last built (see igs_append_events) */
+    uint64_t reserved[3];
 } igs_history_info;
 int igs_get_history_info(igs_engine* e, igs_history_info* out);
 

@@ -102,7 +102,8 @@ def test_late_events_policy(engine, orc, pkg):
     engine.load_events(one(T0 + 100, 500), 2)
     engine.append_events(one(T0 + 100, 300))
     engine.append_events(pkg.Events(np.array([1], np.uint32), np.array([T0 + 5], np.uint32), np.array([9], np.int64), np.zeros(1, np.uint8)))
-    assert engine.history_info() == {"n_events": 3, "late_events": 0, "n_accounts": 2, "has_identifiers": False}
+    assert engine.history_info() == {"n_events": 3, "late_events": 0, "n_accounts": 2, "has_identifiers": False,
+                                     "delta_events": 2}
     # opt in: accepted and filed by timestamp == bulk load == the closed form on the time-ordered history
     engine.set_late_policy(abi.LATE_REORDER)
     try:
@@ -118,6 +119,138 @@ def test_late_events_policy(engine, orc, pkg):
     engine.load_events(both, 1)                                # bulk load: accepted under either policy, counted
     assert engine.history_info()["late_events"] == 1
     assert engine.get_velocity(q).tobytes() == got.tobytes()
+
+
+def test_base_delta_boundary_kats(engine, orc, pkg):
+    """Appended events live in a delta index next to the base (igs_append_events): hand-built cases where a
+    quantity straddles the boundary, each checked against the oracle on the concatenated history and against a
+    bulk load of it.  One account per case; base = what igs_load_events gets, delta = what is appended."""
+    abi = pkg.abi
+    T = synth.T0 + 10_000
+    cases = {
+        # Q1: the ZSET member "ts:amount" exists in the base; its duplicates in the delta must not count again
+        "q1_duplicate_split": ([(T, 100), (T, 200)], [(T, 100), (T, 300), (T, 200), (T, 100)]),
+        # chain sum (tx_sum:1h, gaps <= 3600) and session (gaps <= 1800) continue across the boundary ...
+        "chains_continue": ([(T - 5000, 7), (T - 1800, 11)], [(T, 13), (T + 1800, 17)]),
+        # ... and break exactly one second later
+        "chains_break": ([(T - 5000, 7), (T - 3601, 11)], [(T, 13), (T + 1801, 17)]),
+        "chain_at_3600": ([(T - 3600, 11)], [(T, 13)]),
+        # an event exactly at t - 3600 / t - 60 / t - 300 with the window bound falling on the boundary
+        "window_edges": ([(T - 3600, 1), (T - 300, 2), (T - 60, 3)], [(T - 60, 4), (T, 5)]),
+        # Q4: the newest prior event has ts == now, so the 1h trim bound (now - 3599) beats the window bound
+        "q4_trim": ([(T - 3600, 1), (T - 3599, 2)], [(T, 3)]),
+        # everything in the delta, nothing in the base, and the reverse
+        "delta_only": ([], [(T - 100, 1), (T - 50, 2), (T, 3)]),
+        "base_only": ([(T - 100, 1), (T - 50, 2), (T, 3)], []),
+        # windows that end inside the base while the prior events reach the delta
+        "long_tail": ([(T - 90000, 1), (T - 86400, 2), (T - 86399, 3), (T - 4000, 4)], [(T - 10, 5)]),
+    }
+    names = list(cases)
+    base_rows = [(a, ts, amt) for a, k in enumerate(names) for ts, amt in cases[k][0]]
+    delta_rows = [(a, ts, amt) for a, k in enumerate(names) for ts, amt in cases[k][1]]
+    delta_rows.sort(key=lambda r: r[1])                      # arrival in time order
+
+    def events(rows):
+        a = np.array([r[0] for r in rows], np.uint32)
+        return pkg.Events(a, np.array([r[1] for r in rows], np.uint32), np.array([r[2] for r in rows], np.int64),
+                          (np.arange(len(rows)) % 3).astype(np.uint8))
+    base, delta = events(base_rows), events(delta_rows)
+    n_acc = len(names)
+    q_ts = [T - 1, T, T + 1, T + 59, T + 60, T + 61, T + 300, T + 1800, T + 1801, T + 3599, T + 3600, T + 3601,
+            T + 86399, T + 86400, T + 86401, T + 8 * 86400]
+    q = np.zeros(n_acc * len(q_ts) * 2, dtype=abi.query_dtype)
+    q["account"] = np.repeat(np.arange(n_acc), len(q_ts) * 2)
+    q["ts"] = np.tile(np.repeat(q_ts, 2), n_acc)
+    q["seq_limit"] = abi.SEQ_ALL
+    q["seq_limit"][1::2] = np.tile(np.arange(len(q_ts)) % (len(base) + len(delta) + 1), n_acc)   # stream-mode cuts
+    full = pkg.Events(np.concatenate([base.account, delta.account]), np.concatenate([base.ts, delta.ts]),
+                      np.concatenate([base.amount, delta.amount]), np.concatenate([base.tx_type, delta.tx_type]))
+    want = orc.velocity_batch(full, n_acc, q)
+    engine.load_events(base, n_acc)
+    half = len(delta) // 2
+    engine.append_events(pkg.Events(delta.account[:half], delta.ts[:half], delta.amount[:half], delta.tx_type[:half]))
+    engine.append_events(pkg.Events(delta.account[half:], delta.ts[half:], delta.amount[half:], delta.tx_type[half:]))
+    assert engine.history_info()["delta_events"] == len(delta)           # nothing was folded into the base
+    got = engine.get_velocity(q)
+    bad = np.nonzero(got.view(np.uint8).reshape(len(q), -1) != want.view(np.uint8).reshape(len(q), -1))[0]
+    assert bad.size == 0, [(names[int(q["account"][i])], int(q["ts"][i]) - T, int(q["seq_limit"][i])) for i in np.unique(bad)[:6]]
+    engine.load_events(full, n_acc)
+    assert engine.get_velocity(q).tobytes() == want.tobytes()
+
+
+def test_delta_random_streams_and_compaction(engine, orc, pkg):
+    """Time-ordered appends of uneven sizes onto a base, with forced (ts, amount) collisions and bursts: after every
+    append the velocity blocks (incl. stream-mode queries cutting inside base and delta) equal the oracle on the
+    concatenation.  With a small compaction threshold the delta is folded into the base on the way — same answers."""
+    abi = pkg.abi
+    n_acc, n = 120, 24000
+    ev = synth.make_events(n, n_acc, seed=77, span=7 * 3600, collision_rate=0.08, zipf_s=0.9)
+    order = np.argsort(ev.ts, kind="stable")
+    ev = pkg.Events(ev.account[order], ev.ts[order], ev.amount[order], ev.tx_type[order])
+    rng = np.random.default_rng(8)
+    for threshold in (1 << 30, 3000):
+        engine.set_compaction_threshold(threshold)
+        try:
+            cuts = [0, 9000, 9001, 9800, 13000, 13001, 20000, n]
+            engine.load_events(cut(ev, 0, cuts[1], pkg), n_acc)
+            folded = False
+            for lo, hi in zip(cuts[1:-1], cuts[2:]):
+                engine.append_events(cut(ev, lo, hi, pkg))
+                info = engine.history_info()
+                assert info["n_events"] == hi
+                folded |= info["delta_events"] < hi - cuts[1]
+                q = np.zeros(4000, dtype=abi.query_dtype)
+                pick = rng.integers(0, hi, q.shape[0])
+                q["account"] = ev.account[pick]
+                q["ts"] = ev.ts[pick] + rng.choice([0, 0, 1, 60, 61, 300, 1800, 1801, 3600, 3601, 90000], q.shape[0]).astype(np.uint32)
+                q["seq_limit"] = abi.SEQ_ALL
+                q["seq_limit"][::2] = rng.integers(0, hi + 1, q[::2].shape[0])
+                got, want = engine.get_velocity(q), orc.velocity_batch(cut(ev, 0, hi, pkg), n_acc, q)
+                assert got.tobytes() == want.tobytes(), f"threshold {threshold}, after appending [{lo}, {hi})"
+            assert folded == (threshold == 3000)
+        finally:
+            engine.set_compaction_threshold(65536)
+
+
+def test_append_overlaps_scoring_on_another_stream(engine, orc, pkg):
+    """An append builds into arrays no kernel reads and swaps them in: scoring calls queued on another stream before,
+    during and after appends return the history either without or with each batch — here every scoring launch
+    is ordered against the appends by the host, so each must equal the oracle on exactly the prefix appended so far,
+    while its kernels are still running when the next append starts."""
+    import torch
+    abi = pkg.abi
+    lib = abi.load_library()
+    import ctypes as C
+    n_acc, n0, step, rounds = 3000, 200_000, 20_000, 6
+    n = n0 + step * rounds
+    ev = synth.make_events(n, n_acc, seed=91, span=6 * 3600, zipf_s=0.9)
+    order = np.argsort(ev.ts, kind="stable")
+    ev = pkg.Events(ev.account[order], ev.ts[order], ev.amount[order], ev.tx_type[order])
+    players = synth.make_players(n_acc, seed=92, now=synth.T0 + 6 * 3600)
+    model = synth.make_gbdt(n_trees=200, seed=93)
+    engine.load_players(players)
+    engine.load_gbdt(model)
+    engine.load_events(cut(ev, 0, n0, pkg), n_acc)
+    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    m = 300_000                                               # large enough to still be running when the append starts
+    tx = synth.make_tx(m, n_acc, seed=94, t_lo=int(ev.ts[n0 - 1]), t_hi=int(ev.ts[-1]) + 100)
+    dev = torch.device("cuda", 0)
+    d_tx = torch.from_numpy(tx.view(np.uint8).reshape(m, -1)).to(dev)
+    side = torch.cuda.Stream()
+    outs = []
+    for r in range(rounds):
+        d_out = torch.zeros((m, 8), dtype=torch.uint8, device=dev)
+        st = lib.igs_score_batch_device(engine.handle, C.byref(cfg), d_tx.data_ptr(), m, d_out.data_ptr(), None, None,
+                                        side.cuda_stream)
+        assert st == 0
+        outs.append(d_out)
+        engine.append_events(cut(ev, n0 + r * step, n0 + (r + 1) * step, pkg))     # while that kernel runs
+    torch.cuda.synchronize()
+    pick = np.random.default_rng(3).choice(m, 3000, replace=False)
+    for r, d_out in enumerate(outs):
+        got = np.frombuffer(d_out.cpu().numpy().tobytes(), dtype=abi.result_dtype)[pick]
+        want = orc.score_batch(cfg, model, players, cut(ev, 0, n0 + r * step, pkg), np.ascontiguousarray(tx[pick]))
+        assert got.tobytes() == want.tobytes(), f"scoring launch {r} saw a different history"
 
 
 def test_append_errors(engine, pkg):
@@ -141,7 +274,7 @@ def test_append_errors(engine, pkg):
         assert fresh.get_velocity(q)["n_prior"].tolist() == [1, 1, 0]
 
 
-def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg):
+def test_eviction_is_invisible_to_present_and_future_queries(engine, orc, pkg, late_reorder):
     """igs_evict_events(now) = the TTLs of the Redis keys: what it drops cannot influence any query at
     t >= now.  History with dormant accounts (dead for more than 7 days), accounts that paused for more than a
     day and came back, and accounts that never pause; with identifier columns.  Velocity blocks and unique

@@ -8,6 +8,9 @@ points on both sides and accumulation is fp32 (tensor core) vs fp64-then-fp32 (o
   * the fp32 model output from identical layer-3 activations: |dy| <= 1e-5 * max(1, |y|);
   * end to end (a 1-ulp bf16 flip of one activation, 2^-8 relative, propagates through up to 3
     layers): |dy| <= 1e-2 * max(1, |y|, rms(y) of the batch) for every row, <= 1e-3 for 90 % of them;
+    MEASURED on config C4 (bench.py, block `ltv`, 4096 sampled players of the 4M, |dy| / max(1, |y|)):
+    median 1.2e-7 (one fp32 ulp), 99th percentile 2.2e-3, maximum 1.2e-2 — test_error_distribution pins
+    the distribution at 2x those figures;
   * everything after the model output (churn, adjusted LTV, segment, survival, action, confidence):
     exact, given the same model output.
 """
@@ -98,6 +101,25 @@ def test_end_to_end_vs_oracle(engine, orc, pkg, n):
     want_out = orc.ltv_epilogue(rows, raw.astype(np.float64))
     assert out.tobytes() == want_out.tobytes()
     assert len(set(out["segment"].tolist())) >= (3 if n >= 1000 else 1)
+
+
+def test_error_distribution(engine, orc, pkg):
+    """The end-to-end error of the fp32 model output against the oracle is a distribution, not one number: most
+    rows agree to an fp32 ulp, the rows where a bf16 rounding of an activation flipped are off by 1e-4 .. 1e-2.
+    Bounds = 2x what bench.py measured on C4 (see the header)."""
+    from concurrent.futures import ThreadPoolExecutor
+    model = synth.make_mlp()
+    engine.load_mlp(model)
+    n = 2048
+    x, rows = synth.make_ltv_inputs(n, seed=synth.MASTER_SEED)
+    _, raw = engine.ltv_batch(x, rows, want_raw=True)
+    with ThreadPoolExecutor(os.cpu_count() or 1) as ex:
+        want = np.concatenate(list(ex.map(lambda c: orc.mlp_forward(model, x[c]), np.array_split(np.arange(n), 64))))
+    rel = np.abs(raw.astype(np.float64) - want) / np.maximum(1.0, np.abs(want))
+    assert np.percentile(rel, 50) <= 2.5e-7, np.percentile(rel, 50)
+    assert np.percentile(rel, 90) <= 1e-3, np.percentile(rel, 90)
+    assert np.percentile(rel, 99) <= 5e-3, np.percentile(rel, 99)
+    assert rel.max() <= 2.5e-2, rel.max()
 
 
 def test_chunked_batch_is_consistent(engine, pkg):
