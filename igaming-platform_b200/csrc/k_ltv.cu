@@ -331,8 +331,6 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
     }
 }
 
-#include "k_ltv_fused.cuh"
-
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -341,7 +339,6 @@ struct MlpDevice {
     float *b1 = nullptr, *b2 = nullptr, *b3 = nullptr;
     float b4 = 0.f;
     igs_buf act[2];   // ping-pong activations of one row chunk
-    igs_buf scratch;  // k_mlp_fused: three 128 x 1024 bf16 tiles per CTA
 };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -420,33 +417,6 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
 
 constexpr uint64_t kLtvChunkRows = 256 * 1024;   // 512 MB of bf16 activations per ping-pong buffer
 
-// All three layers + head in one persistent launch (k_ltv_fused.cuh).
-int launch_fused(igs_engine* e, MlpDevice* m, const uint16_t* d_x, const igs_ltv_row* d_rows, uint32_t n,
-                 igs_ltv_result* d_out, float* d_raw, cudaStream_t st) {
-    const uint32_t H = IGS_MLP_HIDDEN;
-    static const bool single = getenv("IGS_MLP_FUSED") && atoi(getenv("IGS_MLP_FUSED")) == 2;
-    const uint32_t m_blks = (n + BM - 1) / BM, n_pairs = single ? m_blks : (m_blks + 1) / 2;
-    const uint32_t grid = n_pairs < (uint32_t)e->sm_count ? n_pairs : (uint32_t)e->sm_count;
-    const uint64_t scratch_rows = (uint64_t)e->sm_count * 3 * BM;
-    int rc = igs_reserve(e, &m->scratch, scratch_rows * H * 2);
-    if (rc != IGS_OK) return rc;
-    FusedParams p;
-    memset(&p, 0, sizeof(p));
-    if ((rc = make_tmap(e, &p.tm_x, d_x, n, IGS_MLP_IN, BM)) != IGS_OK) return rc;
-    if ((rc = make_tmap(e, &p.tm_w[0], m->w1, H, IGS_MLP_IN, BN)) != IGS_OK) return rc;
-    if ((rc = make_tmap(e, &p.tm_w[1], m->w2, H, H, BN)) != IGS_OK) return rc;
-    if ((rc = make_tmap(e, &p.tm_w[2], m->w3, H, H, BN)) != IGS_OK) return rc;
-    if ((rc = make_tmap(e, &p.tm_s_ld, m->scratch.p, scratch_rows, H, BM)) != IGS_OK) return rc;
-    if ((rc = make_tmap(e, &p.tm_s_st, m->scratch.p, scratch_rows, H, kOutBoxRows, kOutBoxCols,
-                        CU_TENSOR_MAP_SWIZZLE_128B)) != IGS_OK) return rc;
-    p.bias[0] = m->b1; p.bias[1] = m->b2; p.bias[2] = m->b3;
-    p.w4 = m->w4; p.b4 = m->b4; p.M = n; p.single = single ? 1u : 0u; p.rows = d_rows; p.res = d_out; p.raw = d_raw;
-    IGS_CUDA(e, cudaFuncSetAttribute(k_mlp_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmem));
-    k_mlp_fused<<<grid, kFusedThreads, kFusedSmem, st>>>(p);
-    IGS_LAUNCHED(e);
-    return IGS_OK;
-}
-
 }  // namespace
 
 void igs_mlp_free(igs_engine* e) {
@@ -456,7 +426,6 @@ void igs_mlp_free(igs_engine* e) {
         if (p) cudaFree(p);
     for (igs_buf& b : m->act)
         if (b.p) cudaFree(b.p);
-    if (m->scratch.p) cudaFree(m->scratch.p);
     delete m;
     e->d_mlp = nullptr;
     e->has_mlp = false;
@@ -520,17 +489,6 @@ int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows
     }
     MlpDevice* m = (MlpDevice*)e->d_mlp;
     const uint32_t H = IGS_MLP_HIDDEN;
-    static const bool fused = getenv("IGS_MLP_FUSED") && atoi(getenv("IGS_MLP_FUSED")) != 0;   // opt-in, see profiles/README.md
-    if (fused) {
-        constexpr uint64_t kFusedMaxRows = 1ull << 30;            // tensor-map row coordinates are 32-bit ints
-        for (uint64_t off = 0; off < n; off += kFusedMaxRows) {
-            const uint32_t cnt = (uint32_t)(n - off < kFusedMaxRows ? n - off : kFusedMaxRows);
-            const int rc = launch_fused(e, m, d_x + off * IGS_MLP_IN, d_rows + off, cnt, d_out + off,
-                                        d_ltv_raw ? d_ltv_raw + off : nullptr, st);
-            if (rc != IGS_OK) return rc;
-        }
-        return IGS_OK;
-    }
     for (igs_buf& b : m->act) {
         int rc = igs_reserve(e, &b, (size_t)kLtvChunkRows * H * 2);
         if (rc != IGS_OK) return rc;

@@ -29,6 +29,7 @@
 #include "idset.cuh"
 #include "igs_internal.cuh"
 #include "igs_math.cuh"
+#include "onesweep.cuh"
 #include "sortscan.cuh"
 #include "velocity.cuh"
 
@@ -72,7 +73,7 @@ struct ScoreParams {
     igs_history_view ix;
     float* features_out;
     igs_velocity* velocity_out;
-    const uint32_t* perm;          // optional: slot -> row, the batch visited in account order (see launch)
+    const uint64_t* perm;          // optional: low 32 bits = slot -> row, the batch visited in account order (see launch)
     const igs_tx_ids* tx_ids;      // optional: rule 8 evaluated against the blacklist sets
     igs_idset_view bl[3];
     int uniques_from_index;        // the history carries identifiers: ignore the tx's unique counts
@@ -387,7 +388,7 @@ k_score(const __grid_constant__ ScoreParams p) {
         const bool in_range = slot < p.n;
         // path B may visit the batch in account order: neighbouring lanes then gather neighbouring (often the
         // same) index records.  Every read and write of the row goes through the permutation.
-        const unsigned long long row = (kSrc == kSrcTx && p.perm != nullptr && in_range) ? __ldg(p.perm + slot) : slot;
+        const unsigned long long row = (kSrc == kSrcTx && p.perm != nullptr && in_range) ? (uint32_t)__ldg(p.perm + slot) : slot;
 
         RuleIn ri;
         if (kSrc == kSrcFeatures) {
@@ -559,36 +560,47 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
 // ms including the sort; one pass — locality without adjacency — gains nothing).  The scratch is stream-ordered
 // (cudaMallocAsync), so concurrent calls on different streams do not share it.
 constexpr unsigned long long kVisitSortMin = 262144;
-__global__ void k_visit_keys(const igs_tx* __restrict__ tx, uint32_t n, int drop_bits, uint64_t* __restrict__ keys,
-                             uint32_t* __restrict__ vals) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    keys[i] = (uint64_t)(__ldg(&tx[i].account) >> drop_bits);
-    vals[i] = i;
+// key = [account (top bits) | row]: sorted on the account bits by the one-sweep radix sort (onesweep.cuh); the row
+// rides in the low word and is what the score kernel reads back.  The key pass also fills the digit histograms.
+__global__ void __launch_bounds__(kOsThreads)
+k_visit_keys(const igs_tx* __restrict__ tx, uint32_t n, OsPlan plan, OsScratch sc, uint64_t* __restrict__ keys) {
+    extern __shared__ uint32_t vk_sh_hist[];
+    __shared__ OsPlan sh_plan;
+    if (threadIdx.x == 0) sh_plan = plan;
+    os_hist_clear(vk_sh_hist, plan.passes);
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * kOsThreads + threadIdx.x; i < n; i += gridDim.x * kOsThreads) {
+        const uint64_t k = ((uint64_t)__ldg(&tx[i].account) << 32) | i;
+        keys[i] = k;
+        os_hist_accumulate(vk_sh_hist, sh_plan, k);
+    }
+    __syncthreads();
+    os_hist_flush(vk_sh_hist, sh_plan, sc);
 }
 static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, uint32_t n_accounts, int passes, cudaStream_t stream,
-                       void** scratch, const uint32_t** perm) {
-    const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
-    const size_t hist_elems = (size_t)kSortBins * nb_sort;
-    const size_t b_keys = ((size_t)n * 8 + 255) & ~(size_t)255, b_vals = ((size_t)n * 4 + 255) & ~(size_t)255;
-    const size_t b_hist = (hist_elems * 4 + 255) & ~(size_t)255;
-    const size_t b_scr = (scan_u32_scratch_elems((uint32_t)hist_elems) * 4 + 255) & ~(size_t)255;
-    char* base = nullptr;
-    IGS_CUDA(e, cudaMallocAsync((void**)&base, 2 * b_keys + 2 * b_vals + b_hist + b_scr, stream));
-    *scratch = base;
-    uint64_t* keys[2] = {(uint64_t*)base, (uint64_t*)(base + b_keys)};
-    uint32_t* vals[2] = {(uint32_t*)(base + 2 * b_keys), (uint32_t*)(base + 2 * b_keys + b_vals)};
-    uint32_t* hist = (uint32_t*)(base + 2 * b_keys + 2 * b_vals);
-    uint32_t* scr = (uint32_t*)(base + 2 * b_keys + 2 * b_vals + b_hist);
+                       void** scratch, const uint64_t** perm) {
     int acct_bits = 1;
     while (acct_bits < 32 && (n_accounts >> acct_bits)) ++acct_bits;
-    const int drop = std::max(0, acct_bits - passes * kSortMaxBits);
-    k_visit_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, stream>>>(d_tx, n, drop, keys[0], vals[0]);
+    // the top `passes` digits of the account: locality needs the accounts grouped, not fully ordered
+    const int begin = 32 + std::max(0, acct_bits - passes * 8), end = 32 + acct_bits;
+    const OsPlan plan = os_plan(begin, end);
+    const size_t b_keys = ((size_t)n * 8 + 255) & ~(size_t)255;
+    const size_t b_os = (OsScratch::words(n, plan.passes) * 4 + 255) & ~(size_t)255;
+    char* base = nullptr;
+    IGS_CUDA(e, cudaMallocAsync((void**)&base, 2 * b_keys + b_os, stream));
+    *scratch = base;
+    uint64_t* keys[2] = {(uint64_t*)base, (uint64_t*)(base + b_keys)};
+    OsScratch sc;
+    int rc = os_prepare(e, &sc, (uint32_t*)(base + 2 * b_keys), n, plan, stream);
+    if (rc != IGS_OK) return rc;
+    IGS_CUDA(e, cudaFuncSetAttribute(k_visit_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)os_hist_smem_bytes(plan.passes)));
+    k_visit_keys<<<std::min<uint32_t>((n + kOsThreads - 1) / kOsThreads, (uint32_t)e->sm_count * 8), kOsThreads,
+                   os_hist_smem_bytes(plan.passes), stream>>>(d_tx, n, plan, sc, keys[0]);
     IGS_LAUNCHED(e);
     int cur = 0;
-    const int rc = radix_sort_pairs(e, keys, vals, n, passes, kSortMaxBits, hist, scr, stream, &cur);
+    rc = os_sort_passes(e, keys, n, plan, sc, stream, &cur);
     if (rc != IGS_OK) return rc;
-    *perm = vals[cur];
+    *perm = keys[cur];
     return IGS_OK;
 }
 

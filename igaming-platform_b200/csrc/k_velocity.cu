@@ -27,6 +27,7 @@
 
 #include "idset.cuh"
 #include "igs_internal.cuh"
+#include "onesweep.cuh"
 #include "sortscan.cuh"
 #include "velocity.cuh"
 
@@ -67,6 +68,72 @@ __global__ void k_make_keys(const uint32_t* __restrict__ account, const uint32_t
     vals[i] = i;
 }
 
+// ---- packed keys: everything the sort has to carry in one 64-bit word --------------------------------------
+//   [ account | ts - ts_min | type (2 bits) | arrival index inside the range ]      (high ... low)
+// sorted on the account (and ts) bits only; the low fields ride along, so that after the sort the account, the
+// timestamp, the type and the arrival index come out of the key and only the amount has to be gathered.
+// ts_bits == 0: the events are already in time order per account (a log, micro-batches of a live feed): a stable
+// sort by account keeps that order and the timestamp is gathered like the amount.
+struct KeyLayout {
+    int seq_bits, ts_bits, acct_shift;     // acct_shift = seq_bits + 2 + ts_bits
+    uint32_t ts_min;
+};
+// Builds the keys and, in the same pass over the raw columns, the global digit histograms of every sort pass.
+// bad[0] = largest account index seen that is >= n_accounts (0 = none).
+__global__ void __launch_bounds__(kOsThreads)
+k_make_keys_hist(const uint32_t* __restrict__ account, const uint32_t* __restrict__ ts,
+                 const uint8_t* __restrict__ type, uint32_t n, uint32_t n_accounts, KeyLayout lay, OsPlan plan,
+                 OsScratch sc, uint64_t* __restrict__ keys, uint32_t* __restrict__ bad) {
+    extern __shared__ uint32_t mk_sh_hist[];
+    __shared__ OsPlan sh_plan;                     // indexed per pass: shared memory, not a local copy of the parameter
+    if (threadIdx.x == 0) sh_plan = plan;
+    os_hist_clear(mk_sh_hist, plan.passes);
+    __syncthreads();
+    uint32_t worst = 0;
+    constexpr int kU = 4;                          // four events per thread and round: their loads are in flight together
+    const uint32_t stride = gridDim.x * kOsThreads;
+    for (uint32_t i0 = blockIdx.x * kOsThreads + threadIdx.x; i0 < n; i0 += stride * kU) {
+        uint32_t a[kU], t[kU], ty[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const uint32_t i = i0 + u * stride;
+            const bool ok = i < n;
+            a[u] = ok ? __ldg(account + i) : 0u;
+            t[u] = ok && lay.ts_bits ? __ldg(ts + i) : lay.ts_min;
+            ty[u] = ok ? min((uint32_t)__ldg(type + i), 3u) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const uint32_t i = i0 + u * stride;
+            if (i >= n) break;
+            if (a[u] >= n_accounts) worst = max(worst, a[u]);
+            const uint64_t k = ((uint64_t)a[u] << lay.acct_shift) | ((uint64_t)(t[u] - lay.ts_min) << (lay.seq_bits + 2)) |
+                               ((uint64_t)ty[u] << lay.seq_bits) | (uint64_t)i;
+            keys[i] = k;
+            os_hist_accumulate(mk_sh_hist, sh_plan, k);
+        }
+    }
+    if (worst) atomicMax(bad, worst);
+    __syncthreads();
+    os_hist_flush(mk_sh_hist, sh_plan, sc);
+}
+
+__global__ void k_unpack_gather_packed(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ ts_in,
+                                       const int64_t* __restrict__ amount_in, uint32_t n, KeyLayout lay, uint32_t seq_base,
+                                       uint32_t* __restrict__ acct, uint32_t* __restrict__ ts, uint32_t* __restrict__ seq_out,
+                                       int64_t* __restrict__ amount, uint8_t* __restrict__ type) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t k = __ldg(keys + i);
+    const uint32_t local = (uint32_t)(k & ((1ull << lay.seq_bits) - 1ull));
+    acct[i] = (uint32_t)(k >> lay.acct_shift);
+    type[i] = (uint8_t)((k >> lay.seq_bits) & 3u);
+    ts[i] = lay.ts_bits ? lay.ts_min + (uint32_t)((k >> (lay.seq_bits + 2)) & ((1ull << lay.ts_bits) - 1ull))
+                        : __ldg(ts_in + local);
+    seq_out[i] = local + seq_base;
+    amount[i] = __ldg(amount_in + local);
+}
+
 // ------------------------------------------------------------------------------------------------
 // post-sort columns
 // ------------------------------------------------------------------------------------------------
@@ -89,164 +156,166 @@ __global__ void k_unpack_gather(const uint64_t* __restrict__ keys, const uint32_
     type[i] = __ldg(type_in + s);
 }
 
-// Also counts LATE events: sorted neighbours of one account whose arrival order is the reverse of their time
-// order — the earlier-timestamped one arrived later.  Redis would have applied it on arrival, with its old
-// timestamp as "now" (features/redis_store.go:121,132,155); the index files it where its timestamp says.
-// late[0] = such pairs in the whole history, late[1] = those whose late event has arrival index >= n_before
-// (the batch being appended).
-// When a delta is being built over a base (base.n != 0), the first delta event of an account is also late if it
-// is older than the account's last base event.
-__global__ void k_segments(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
-                           const uint32_t* __restrict__ seq, uint32_t n,
-                           uint32_t n_accounts, uint32_t n_before, igs_index_view base, uint32_t* __restrict__ seg,
-                           uint32_t* __restrict__ late) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool is_late = false, is_new = false;
-    if (i < n) {
-        const uint32_t a = __ldg(acct + i);
-        bool first_of_account = i == 0;
+// CSR segments + (account, ts) group heads + LATE events, one pass over the sorted columns.
+// Late: sorted neighbours of one account whose arrival order contradicts their time order — either the earlier-
+// timestamped one arrived later (sort by (account, ts): arrival indices invert), or, under a sort by account alone,
+// the later arrival carries the smaller timestamp.  Redis would have applied a late event on arrival, with its old
+// timestamp as "now" (features/redis_store.go:121,132,155); the index files events where their timestamps say, and
+// under an account-only sort a late pair means the order is not the timestamp order at all (the caller rejects or
+// re-sorts).  late[0] = late pairs in the range, late[1] = those whose late event has arrival index >= n_before
+// (the batch being appended).  When a delta is built over a base (base.n != 0), the first delta event of an
+// account is also late if it is older than the account's last base event.
+__global__ void __launch_bounds__(kThreads)
+k_segments_heads(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts,
+                 const uint32_t* __restrict__ seq, uint32_t n, uint32_t n_accounts, uint32_t n_before,
+                 igs_index_view base, uint32_t* __restrict__ seg, uint8_t* __restrict__ head,
+                 uint32_t* __restrict__ late) {
+    __shared__ uint32_t sh_late[2];
+    if (threadIdx.x < 2) sh_late[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t n_late = 0, n_new = 0;                // a history in random time order is full of late pairs: count locally
+    for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) {
+        // (an out-of-range account is reported by the key pass; clamped here so that seg[] is never overrun)
+        const uint32_t a = min(__ldg(acct + i), n_accounts), t = __ldg(ts + i);
+        bool first_of_account = i == 0, group_head = i == 0;
+        bool is_late = false, is_new = false;
         if (i == 0) {
             for (uint32_t x = 0; x <= a; ++x) seg[x] = 0;
         } else {
-            const uint32_t p = __ldg(acct + i - 1);
+            const uint32_t p = min(__ldg(acct + i - 1), n_accounts), tp = __ldg(ts + i - 1);
             for (uint32_t x = p + 1; x <= a; ++x) seg[x] = i;
-            const uint32_t sp = __ldg(seq + i - 1);
-            is_late = p == a && sp > __ldg(seq + i);
-            is_new = is_late && sp >= n_before;
             first_of_account = p != a;
+            group_head = first_of_account || tp != t;
+            if (!first_of_account) {
+                const uint32_t sp = __ldg(seq + i - 1), si = __ldg(seq + i);
+                if (sp > si) { is_late = true; is_new = sp >= n_before; }          // i-1 arrived later, is not newer
+                else if (tp > t) { is_late = true; is_new = si >= n_before; }       // i arrived later, is older
+            }
         }
+        head[i] = group_head;
         if (first_of_account && base.n != 0 && a < base.n_accounts) {
             const uint32_t sb = __ldg(base.seg + a), eb = __ldg(base.seg + a + 1);
-            if (eb > sb && __ldg(ts + i) < __ldg(base.ts + eb - 1)) {
+            if (eb > sb && t < __ldg(base.ts + eb - 1)) {
                 is_late = true;
                 is_new = __ldg(seq + i) >= n_before;
             }
         }
         if (i == n - 1)
             for (uint32_t x = a + 1; x <= n_accounts; ++x) seg[x] = n;
+        n_late += is_late;
+        n_new += is_new;
     }
-    const unsigned m0 = __ballot_sync(0xffffffffu, is_late), m1 = __ballot_sync(0xffffffffu, is_new);
-    if ((threadIdx.x & 31) == 0) {
-        if (m0) atomicAdd(late + 0, (uint32_t)__popc(m0));
-        if (m1) atomicAdd(late + 1, (uint32_t)__popc(m1));
-    }
-}
-
-// head[i] = 1 iff event i is the first of its (account, ts) group in sorted order
-__global__ void k_group_heads(const uint32_t* __restrict__ acct, const uint32_t* __restrict__ ts, uint32_t n,
-                              uint8_t* __restrict__ head) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    head[i] = i == 0 || __ldg(acct + i) != __ldg(acct + i - 1) || __ldg(ts + i) != __ldg(ts + i - 1);
+    n_late = __reduce_add_sync(0xffffffffu, n_late);
+    n_new = __reduce_add_sync(0xffffffffu, n_new);
+    if ((threadIdx.x & 31) == 0 && n_late) { atomicAdd(&sh_late[0], n_late); atomicAdd(&sh_late[1], n_new); }
+    __syncthreads();
+    if (threadIdx.x == 0 && sh_late[0]) { atomicAdd(late + 0, sh_late[0]); atomicAdd(late + 1, sh_late[1]); }
 }
 
 // distinct flag: no earlier event of the same (account, ts) group has the same amount (the ZSET member
 // "ts:amount" dedupe).  Walks back through the group four events at a time (the loads of a step do not
 // depend on each other), at most kDistinctWalk events: groups of up to kDistinctWalk + 1 events — all of
-// them in ordinary traffic — are settled here.  An event that is deeper in its group and found no equal
-// amount on the way is marked kUnresolved and counted; the hash pass below settles those groups, so a
-// same-second burst of any size (a bot, a replayed queue) costs linear, not quadratic, work.
+// them in ordinary traffic — are settled here.  The members of LONGER groups (a bot, a replayed queue: a
+// same-second burst of any size) are collected in a work list instead and settled by the hash pass below, so
+// that such a burst costs linear, not quadratic, work — and only its own members pay for it.
 constexpr uint32_t kDistinctWalk = 32;
-constexpr uint8_t kUnresolved = 2;
 
 __global__ void k_distinct(const uint8_t* __restrict__ head, const int64_t* __restrict__ amount, uint32_t n,
-                           uint8_t* __restrict__ dflag, uint32_t* __restrict__ n_unresolved) {
+                           uint8_t* __restrict__ dflag, uint32_t* __restrict__ work, uint32_t* __restrict__ n_work) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint8_t d = 1;
-    if (i < n && !__ldg(head + i)) {
-        const int64_t m = __ldg(amount + i);
-        uint32_t j = i;                       // candidates are j-1, j-2, ... down to the group head
-        bool done = false;
-        for (uint32_t step = 0; step < kDistinctWalk / 4 && !done; ++step) {
-            int64_t a[4];
-            uint8_t h[4];
+    bool big = false;
+    if (i < n) {
+        uint32_t start = i;                       // group head, once known
+        bool found_head = __ldg(head + i) != 0;
+        if (!found_head) {
+            const int64_t m = __ldg(amount + i);
+            uint32_t j = i;                       // candidates are j-1, j-2, ... down to the group head
+            bool dup = false;
+            for (uint32_t step = 0; step < kDistinctWalk / 4 && !found_head; ++step) {
+                int64_t a[4];
+                uint8_t h[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t jj = j >= (uint32_t)(k + 1) ? j - (k + 1) : 0;
-                a[k] = __ldg(amount + jj);
-                h[k] = j >= (uint32_t)(k + 1) ? __ldg(head + jj) : 1;
-            }
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t jj = j >= (uint32_t)(k + 1) ? j - (k + 1) : 0;
+                    a[k] = __ldg(amount + jj);
+                    h[k] = j >= (uint32_t)(k + 1) ? __ldg(head + jj) : 1;
+                }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (done) break;
-                if (a[k] == m) { d = 0; done = true; }
-                else if (h[k]) done = true;   // reached the first event of the group
+                for (int k = 0; k < 4; ++k) {
+                    if (found_head) break;
+                    if (a[k] == m) dup = true;
+                    if (h[k]) { found_head = true; start = j - (k + 1); }   // reached the first event of the group
+                }
+                j = j >= 4 ? j - 4 : 0;
             }
-            j = j >= 4 ? j - 4 : 0;
+            d = dup ? 0 : 1;                      // (a duplicate seen before the head was reached is a duplicate either way)
         }
-        if (!done) d = kUnresolved;
+        if (!found_head) {
+            big = true;                           // deeper than the walk: the group has more than kDistinctWalk + 1 members
+        } else {
+            // a member near the head of a long group must be in the hash table too: does the group reach past
+            // start + kDistinctWalk + 1 ?
+            big = true;
+            for (uint32_t j = i + 1; j <= start + kDistinctWalk + 1; ++j)
+                if (j >= n || __ldg(head + j)) { big = false; break; }
+        }
+        dflag[i] = d;
     }
-    const unsigned unres = __ballot_sync(0xffffffffu, d == kUnresolved);
-    if (unres && (threadIdx.x & 31) == 0) atomicAdd(n_unresolved, (uint32_t)__popc(unres));
-    if (i < n) dflag[i] = d;
+    const unsigned m = __ballot_sync(0xffffffffu, big);
+    if (m) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(n_work, (uint32_t)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (big) work[base + __popc(m & ((1u << lane) - 1u))] = i;
+    }
 }
 
-// ---- hash pass for the groups k_distinct could not settle (rare) ---------------------------------
-// Every (account, ts) group with more than kDistinctWalk + 1 events gets its own open-addressing table
-// (capacity = power of two >= 2 x group size): key = amount, value = smallest sorted position that carries
-// it.  An event is distinct iff it is that smallest position.  The amount INT64_MIN would collide with the
-// empty-slot marker and is tracked in a per-group word instead.
-__global__ void k_dg_heads_u32(const uint8_t* __restrict__ head, uint32_t n, uint32_t* __restrict__ out) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = __ldg(head + i);
+// ---- hash pass for the long groups (rare) ------------------------------------------------------------
+// One open-addressing table for all of them.  A slot is claimed by the first member that gets there and holds that
+// member's sorted position (its "representative"); later members compare their (account, ts, amount) with the
+// representative's — exact, whatever the hash does — and the smallest position per (account, ts, amount) wins.
+__device__ __forceinline__ uint32_t dg_hash(uint32_t a, uint32_t t, int64_t m, uint32_t mask) {
+    return (uint32_t)(igs_idset_mix(((uint64_t)a << 32 | t) ^ igs_idset_mix((uint64_t)m)) & mask);
 }
-// gid = exclusive scan of the head flags on entry; group of event i = gid[i] + head[i] - 1
-__global__ void k_dg_starts(const uint8_t* __restrict__ head, uint32_t* __restrict__ gid, uint32_t n,
-                            uint32_t* __restrict__ gstart, uint32_t n_groups) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t h = __ldg(head + i);
-    const uint32_t g = gid[i] + h - 1;
-    gid[i] = g;
-    if (h) gstart[g] = i;
-    if (i == n - 1) gstart[n_groups] = n;
-}
-__global__ void k_dg_caps(const uint32_t* __restrict__ gstart, uint32_t n_groups, uint32_t* __restrict__ cap) {
-    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= n_groups) return;
-    const uint32_t size = __ldg(gstart + g + 1) - __ldg(gstart + g);
-    uint32_t c = 0;
-    if (size > kDistinctWalk + 1) {
-        c = 64;
-        while (c < 2 * size) c <<= 1;
-    }
-    cap[g] = c;
-}
-__device__ __forceinline__ uint32_t dg_slot(uint64_t key, uint32_t mask) {
-    return (uint32_t)(igs_idset_mix(key) & mask);
-}
-__global__ void k_dg_insert(const uint32_t* __restrict__ gid, const uint32_t* __restrict__ gstart,
-                            const uint32_t* __restrict__ toff /* exclusive scan of cap, [n_groups + 1] */,
-                            const int64_t* __restrict__ amount, uint32_t n, unsigned long long* __restrict__ keys,
-                            uint32_t* __restrict__ minpos, uint32_t* __restrict__ special) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t g = __ldg(gid + i);
-    const uint32_t base = __ldg(toff + g), cap = __ldg(toff + g + 1) - base;
-    if (cap == 0) return;                                   // small group: settled by k_distinct
-    const uint64_t key = (uint64_t)__ldg(amount + i) ^ 0x8000000000000000ull;
-    if (key == 0) { atomicMin(special + g, i); return; }
-    uint32_t h = dg_slot(key, cap - 1);
+__global__ void k_dg_insert(const uint32_t* __restrict__ work, uint32_t n_work, const uint32_t* __restrict__ acct,
+                            const uint32_t* __restrict__ ts, const int64_t* __restrict__ amount, uint32_t mask,
+                            uint32_t* __restrict__ rep, uint32_t* __restrict__ minpos) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_work) return;
+    const uint32_t i = __ldg(work + k);
+    const uint32_t a = __ldg(acct + i), t = __ldg(ts + i);
+    const int64_t m = __ldg(amount + i);
+    uint32_t h = dg_hash(a, t, m, mask);
     for (;;) {
-        const unsigned long long prev = atomicCAS(keys + base + h, 0ull, (unsigned long long)key);
-        if (prev == 0ull || prev == key) { atomicMin(minpos + base + h, i); return; }
-        h = (h + 1) & (cap - 1);
+        uint32_t r = atomicCAS(rep + h, 0xFFFFFFFFu, i);
+        if (r == 0xFFFFFFFFu) r = i;
+        if (r == i || (__ldg(acct + r) == a && __ldg(ts + r) == t && __ldg(amount + r) == m)) {
+            atomicMin(minpos + h, i);
+            return;
+        }
+        h = (h + 1) & mask;
     }
 }
-__global__ void k_dg_resolve(const uint32_t* __restrict__ gid, const uint32_t* __restrict__ toff,
-                             const int64_t* __restrict__ amount, uint32_t n,
-                             const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ minpos,
-                             const uint32_t* __restrict__ special, uint8_t* __restrict__ dflag) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t g = __ldg(gid + i);
-    const uint32_t base = __ldg(toff + g), cap = __ldg(toff + g + 1) - base;
-    if (cap == 0) return;
-    const uint64_t key = (uint64_t)__ldg(amount + i) ^ 0x8000000000000000ull;
-    if (key == 0) { dflag[i] = __ldg(special + g) == i; return; }
-    uint32_t h = dg_slot(key, cap - 1);
-    while (keys[base + h] != key) h = (h + 1) & (cap - 1);  // present: inserted by k_dg_insert
-    dflag[i] = minpos[base + h] == i;
+__global__ void k_dg_resolve(const uint32_t* __restrict__ work, uint32_t n_work, const uint32_t* __restrict__ acct,
+                             const uint32_t* __restrict__ ts, const int64_t* __restrict__ amount, uint32_t mask,
+                             const uint32_t* __restrict__ rep, const uint32_t* __restrict__ minpos,
+                             uint8_t* __restrict__ dflag) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_work) return;
+    const uint32_t i = __ldg(work + k);
+    const uint32_t a = __ldg(acct + i), t = __ldg(ts + i);
+    const int64_t m = __ldg(amount + i);
+    uint32_t h = dg_hash(a, t, m, mask);
+    for (;;) {
+        const uint32_t r = rep[h];                // present: k_dg_insert put this member's key there
+        if (r == i || (__ldg(acct + r) == a && __ldg(ts + r) == t && __ldg(amount + r) == m)) {
+            dflag[i] = minpos[h] == i;
+            return;
+        }
+        h = (h + 1) & mask;
+    }
 }
 
 // ---- delta over a base: the ZSET member dedupe across the boundary --------------------------------------
@@ -370,16 +439,100 @@ __device__ __forceinline__ VScan vs_warp_scan(VScan v, int lane) {
     return v;
 }
 
-struct ElemSrc {
-    VCols c;
-    __device__ __forceinline__ VScan operator()(uint32_t i) const { return vs_element(c, i); }
-    __device__ __forceinline__ uint32_t size() const { return c.n; }
-};
 struct AggSrc {
     const VScan* a; uint32_t n;
     __device__ __forceinline__ VScan operator()(uint32_t i) const { return a[i]; }
     __device__ __forceinline__ uint32_t size() const { return n; }
 };
+
+// Level 0 works lane-serially: a lane owns 8 consecutive events (vector loads: 32 B of accounts, 32 B of
+// timestamps, 64 B of amounts, 8 B of types, 8 B of flags), combines them in order in registers, and the warp
+// scans the 32 lane aggregates once — one round of shuffles per 256 events instead of eight.
+constexpr int kVLane = kVTile / 32;      // 8
+static_assert(kVLane == 8, "vector loads below assume 8 events per lane");
+
+struct VLaneItems {
+    uint32_t a[kVLane], t[kVLane];
+    int64_t  m[kVLane];
+    uint8_t  ty[kVLane], d[kVLane];
+    uint32_t prev_a, prev_t;             // event first - 1 (undefined when first == 0)
+};
+__device__ __forceinline__ void vs_load_lane(const VCols& c, uint32_t first, VLaneItems& it) {
+    if (first + kVLane <= c.n) {
+        const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(c.acct + first)), a1 = __ldg(reinterpret_cast<const uint4*>(c.acct + first) + 1);
+        const uint4 t0 = __ldg(reinterpret_cast<const uint4*>(c.ts + first)), t1 = __ldg(reinterpret_cast<const uint4*>(c.ts + first) + 1);
+        it.a[0] = a0.x; it.a[1] = a0.y; it.a[2] = a0.z; it.a[3] = a0.w; it.a[4] = a1.x; it.a[5] = a1.y; it.a[6] = a1.z; it.a[7] = a1.w;
+        it.t[0] = t0.x; it.t[1] = t0.y; it.t[2] = t0.z; it.t[3] = t0.w; it.t[4] = t1.x; it.t[5] = t1.y; it.t[6] = t1.z; it.t[7] = t1.w;
+        const longlong2* mp = reinterpret_cast<const longlong2*>(c.amount + first);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const longlong2 v = __ldg(mp + k); it.m[2 * k] = v.x; it.m[2 * k + 1] = v.y; }
+        const uint2 ty = __ldg(reinterpret_cast<const uint2*>(c.type + first));
+        const uint2 df = __ldg(reinterpret_cast<const uint2*>(c.dflag + first));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            it.ty[k] = (uint8_t)(ty.x >> (8 * k)); it.ty[4 + k] = (uint8_t)(ty.y >> (8 * k));
+            it.d[k] = (uint8_t)(df.x >> (8 * k)); it.d[4 + k] = (uint8_t)(df.y >> (8 * k));
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kVLane; ++k) {
+            const uint32_t i = first + k;
+            const bool ok = i < c.n;
+            it.a[k] = ok ? __ldg(c.acct + i) : 0; it.t[k] = ok ? __ldg(c.ts + i) : 0; it.m[k] = ok ? __ldg(c.amount + i) : 0;
+            it.ty[k] = ok ? __ldg(c.type + i) : 0; it.d[k] = ok ? __ldg(c.dflag + i) : 0;
+        }
+    }
+    it.prev_a = first > 0 && first <= c.n ? __ldg(c.acct + first - 1) : 0;
+    it.prev_t = first > 0 && first <= c.n ? __ldg(c.ts + first - 1) : 0;
+}
+// element k of the lane (same arithmetic as vs_element, from registers)
+__device__ __forceinline__ VScan vs_lane_element(const VCols& c, const VLaneItems& it, uint32_t first, int k) {
+    VScan r = vs_identity();
+    const uint32_t i = first + k;
+    const uint32_t t = it.t[k];
+    const int64_t m = it.m[k];
+    const bool new_acct = i == 0 || it.a[k] != (k ? it.a[k - 1] : it.prev_a);
+    const long long gap = i == 0 ? 0 : (long long)t - (long long)(k ? it.t[k - 1] : it.prev_t);
+    r.d = it.d[k];
+    if (it.ty[k] == IGS_TX_BET) { r.c0 = 1; r.s0 = m; }
+    if (it.ty[k] == IGS_TX_DEPOSIT) { r.c1 = 1; r.s1 = m; }
+    r.chain = m;
+    r.cf = (new_acct || gap > 3600) ? 1u : 0u;        // tx_sum:1h key expired (redis_store.go:138)
+    r.sf = (new_acct || gap > 1800) ? 1u : 0u;        // session key expired (:159-160)
+    r.st = r.sf ? t : 0u;
+    if (new_acct && c.base.n != 0) {
+        // first delta event of the account: the keys it finds are the ones the account's last base event left
+        const uint32_t a = it.a[k];
+        if (a < c.base.n_accounts) {
+            const uint32_t sb = __ldg(c.base.seg + a), eb = __ldg(c.base.seg + a + 1);
+            if (eb > sb) {
+                const long long gb = (long long)t - (long long)__ldg(c.base.ts + eb - 1);
+                const igs_tail_rec tb = c.base.tail[eb - 1];
+                if (gb <= 3600) r.chain = m + tb.chain_sum;      // still a segment head for the scan: the value is complete
+                if (gb <= 1800) r.st = tb.sess_start;
+            }
+        }
+    }
+    return r;
+}
+
+// one aggregate per 256 events
+__global__ void __launch_bounds__(kThreads)
+k_vs_reduce_elems(VCols c, VScan* __restrict__ agg) {
+    const uint32_t gw = (blockIdx.x * kThreads + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t base = gw * kVTile;
+    if (base >= c.n) return;
+    const uint32_t first = base + lane * kVLane;
+    VLaneItems it;
+    vs_load_lane(c, first, it);
+    VScan v = vs_identity();
+#pragma unroll
+    for (int k = 0; k < kVLane; ++k)
+        if (first + k < c.n) v = vs_combine(v, vs_lane_element(c, it, first, k));
+    const VScan inc = vs_warp_scan(v, lane);
+    if (lane == 31) agg[gw] = inc;
+}
 
 template <typename Src>
 __global__ void __launch_bounds__(kThreads)
@@ -434,6 +587,9 @@ k_vs_apply_aggs(VScan* __restrict__ a, uint32_t n, const VScan* __restrict__ til
     }
 }
 
+// The element pass keeps the round-based traversal (lane = consecutive event): its 64 B of output per event leave
+// the warp as whole contiguous lines.  (A lane-serial version — as in k_vs_reduce_elems — halves the shuffles but
+// writes 32 separate sectors per store instruction: 279 us against 166 us per 10M events.)
 __global__ void __launch_bounds__(kThreads)
 k_vs_apply_elems(VCols c, const VScan* __restrict__ tile_excl, igs_prefix_rec* __restrict__ pre,
                  igs_tail_rec* __restrict__ tail) {
@@ -843,56 +999,27 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
     return IGS_OK;
 }
 
-// Settles the distinct flags of the (account, ts) groups that are too long for k_distinct's bounded walk.
-// Its buffers come from the build pool like everything else; they are requested on every build, in the same
-// order (one element each when there is nothing to settle), so that the pool's request sequence stays fixed
-// and rebuilds after igs_append_events reuse them.
-static int resolve_big_groups(igs_engine* e, Scratch& sc, bool needed, const uint8_t* d_head, const int64_t* d_amt,
-                              uint32_t n, uint8_t* d_dflag, uint32_t* d_scan_scratch, cudaStream_t st) {
-    const uint32_t nb = (n + kThreads - 1) / kThreads;
-    uint32_t *gid, *gstart, *cap, *minpos, *special, *scr;
-    unsigned long long* keys;
-    IGS_CUDA(e, sc.alloc(&gid, needed ? n : 1));
-    uint32_t n_groups = 0;
-    if (needed) {
-        k_dg_heads_u32<<<nb, kThreads, 0, st>>>(d_head, n, gid);
-        IGS_LAUNCHED(e);
-        const int rc = scan_u32(e, gid, n, d_scan_scratch, st);
-        if (rc != IGS_OK) return rc;
-        uint32_t last_ex = 0; uint8_t last_head = 0;
-        IGS_CUDA(e, cudaMemcpyAsync(&last_ex, gid + (n - 1), 4, cudaMemcpyDeviceToHost, st));
-        IGS_CUDA(e, cudaMemcpyAsync(&last_head, d_head + (n - 1), 1, cudaMemcpyDeviceToHost, st));
-        IGS_CUDA(e, cudaStreamSynchronize(st));
-        n_groups = last_ex + last_head;
+// Settles the distinct flags of the members of long (account, ts) groups (k_distinct's work list).  The table comes
+// from the build pool like everything else and is requested on every build (one element when there is nothing to
+// settle), so that the pool's request sequence stays fixed and rebuilds reuse the buffers.
+static int resolve_big_groups(igs_engine* e, Scratch& sc, uint32_t n_work, const uint32_t* d_work, const uint32_t* d_acct,
+                              const uint32_t* d_ts, const int64_t* d_amt, uint8_t* d_dflag, cudaStream_t st) {
+    uint32_t cap = 1;
+    if (n_work) {
+        cap = 64;
+        while (cap < 2 * (uint64_t)n_work && cap < 0x80000000u) cap <<= 1;
     }
-    IGS_CUDA(e, sc.alloc(&gstart, (size_t)n_groups + 1));
-    IGS_CUDA(e, sc.alloc(&cap, (size_t)n_groups + 1));
-    IGS_CUDA(e, sc.alloc(&special, n_groups));
-    IGS_CUDA(e, sc.alloc(&scr, scan_u32_scratch_elems(n_groups + 1)));
-    uint32_t total = 0;
-    if (needed) {
-        IGS_CUDA(e, cudaMemsetAsync(special, 0xFF, (size_t)n_groups * 4, st));
-        IGS_CUDA(e, cudaMemsetAsync(cap + n_groups, 0, 4, st));
-        k_dg_starts<<<nb, kThreads, 0, st>>>(d_head, gid, n, gstart, n_groups);
-        IGS_LAUNCHED(e);
-        k_dg_caps<<<(n_groups + kThreads - 1) / kThreads, kThreads, 0, st>>>(gstart, n_groups, cap);
-        IGS_LAUNCHED(e);
-        // exclusive scan over n_groups + 1 entries: cap[n_groups] becomes the total table size
-        const int rc = scan_u32(e, cap, n_groups + 1, scr, st);
-        if (rc != IGS_OK) return rc;
-        IGS_CUDA(e, cudaMemcpyAsync(&total, cap + n_groups, 4, cudaMemcpyDeviceToHost, st));
-        IGS_CUDA(e, cudaStreamSynchronize(st));
-    }
-    IGS_CUDA(e, sc.alloc(&keys, total));
-    IGS_CUDA(e, sc.alloc(&minpos, total));
-    if (needed) {
-        IGS_CUDA(e, cudaMemsetAsync(keys, 0, (size_t)total * 8, st));
-        IGS_CUDA(e, cudaMemsetAsync(minpos, 0xFF, (size_t)total * 4, st));
-        k_dg_insert<<<nb, kThreads, 0, st>>>(gid, gstart, cap, d_amt, n, keys, minpos, special);
-        IGS_LAUNCHED(e);
-        k_dg_resolve<<<nb, kThreads, 0, st>>>(gid, cap, d_amt, n, keys, minpos, special, d_dflag);
-        IGS_LAUNCHED(e);
-    }
+    uint32_t *rep, *minpos;
+    IGS_CUDA(e, sc.alloc(&rep, cap));
+    IGS_CUDA(e, sc.alloc(&minpos, cap));
+    if (!n_work) return IGS_OK;
+    IGS_CUDA(e, cudaMemsetAsync(rep, 0xFF, (size_t)cap * 4, st));
+    IGS_CUDA(e, cudaMemsetAsync(minpos, 0xFF, (size_t)cap * 4, st));
+    const uint32_t nb = (n_work + kThreads - 1) / kThreads;
+    k_dg_insert<<<nb, kThreads, 0, st>>>(d_work, n_work, d_acct, d_ts, d_amt, cap - 1, rep, minpos);
+    IGS_LAUNCHED(e);
+    k_dg_resolve<<<nb, kThreads, 0, st>>>(d_work, n_work, d_acct, d_ts, d_amt, cap - 1, rep, minpos, d_dflag);
+    IGS_LAUNCHED(e);
     return IGS_OK;
 }
 
@@ -953,6 +1080,8 @@ struct BuildSpec {
     igs_event_index* dst = nullptr;
     igs_index_view base;
     uint64_t n_before = 0xFFFFFFFFull;
+    bool assume_time_ordered = false;   // delta builds: sort by account only, no key-range pass (see build_index)
+    uint64_t reserve = 0;               // size allocations for at least this many events
 };
 
 static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
@@ -962,9 +1091,12 @@ static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
     igs_event_index& x = *spec.dst;
     Scratch sc(e->build_pool);
     late[0] = late[1] = 0;
+    // sizes of allocations: at least what the caller expects the range to grow to (a delta is sized for its
+    // compaction threshold once, instead of being re-allocated every few appends)
+    const uint32_t nr = (uint32_t)std::max<uint64_t>(n, std::min<uint64_t>(spec.reserve, 0xFFFFFFF0ull));
     if ((uint64_t)n + 1 > x.cap_events || (uint64_t)n_accounts + 1 > x.cap_accounts) {
         // (re)allocate the index arrays with headroom so that appends rarely come back here
-        const uint64_t ce = std::max<uint64_t>((uint64_t)n + 1, x.cap_events + x.cap_events / 2);
+        const uint64_t ce = std::max<uint64_t>((uint64_t)nr + 1, x.cap_events + x.cap_events / 2);
         const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
         {
             std::lock_guard<std::mutex> lk(e->view_mu);
@@ -993,78 +1125,127 @@ static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
     const int64_t* d_amt_in = e->raw_amount + spec.lo;
     const uint8_t* d_type_in = e->raw_type + spec.lo;
     uint32_t* d_mm;
-    IGS_CUDA(e, sc.alloc(&d_mm, 8));            // [0..3] key range, [4..5] late-event counters
-
-    // ---- key range ------------------------------------------------------------------------------
+    IGS_CUDA(e, sc.alloc(&d_mm, 8));            // [0..3] key range, [4..5] late-event counters, [6] bad account
     const uint32_t mm_init[8] = {0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     IGS_CUDA(e, cudaMemcpyAsync(d_mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, st));
     const uint32_t nb_el = (n + kThreads - 1) / kThreads;
-    k_minmax<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct_in, d_ts_in, n, d_mm);
-    IGS_LAUNCHED(e);
-    uint32_t mm[4];
-    IGS_CUDA(e, cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, st));
-    IGS_CUDA(e, cudaStreamSynchronize(st));
-    if (mm[2] >= n_accounts) {
-        igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
-        return IGS_ERR_INVALID;
-    }
-    const uint32_t ts_min = mm[0];
-    // Events that arrive in time order (a log, a queue, appended micro-batches) only need a stable sort by
-    // account: the radix passes over the timestamp bits are skipped.
-    const bool time_ordered = mm[3] == 0;
-    const int ts_bits = time_ordered ? 0 : (bits_for(mm[1] - mm[0]) > 0 ? bits_for(mm[1] - mm[0]) : 1);
-    const int key_bits = ts_bits + (bits_for(mm[2]) > 0 ? bits_for(mm[2]) : 1);
-    const int passes = (key_bits + kSortMaxBits - 1) / kSortMaxBits;
-    const int digit_bits = (key_bits + passes - 1) / passes;      // <= 8
-    const uint32_t bins = 1u << digit_bits;
 
-    // ---- radix sort -----------------------------------------------------------------------------
+    // ---- key range ------------------------------------------------------------------------------
+    // A delta build skips this pass and its read-back: its events must be in time order per account anyway (a late
+    // event gets the batch refused, or everything re-sorted into a new base), so a stable sort by account alone is
+    // the right order, and the account range is that of the table.
+    uint32_t ts_min = 0, acct_max = n_accounts ? n_accounts - 1 : 0;
+    bool time_ordered = true;
+    uint32_t ts_span = 0;
+    if (!spec.assume_time_ordered) {
+        k_minmax<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct_in, d_ts_in, n, d_mm);
+        IGS_LAUNCHED(e);
+        uint32_t mm[4];
+        IGS_CUDA(e, cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+        if (mm[2] >= n_accounts) {
+            igs_set_error(e, "event account index %u >= n_accounts %u", mm[2], n_accounts);
+            return IGS_ERR_INVALID;
+        }
+        ts_min = mm[0];
+        ts_span = mm[1] - mm[0];
+        acct_max = mm[2];
+        // Events that arrive in time order (a log, a queue) only need a stable sort by account.
+        time_ordered = mm[3] == 0;
+    }
+    const int ts_bits = time_ordered ? 0 : (bits_for(ts_span) > 0 ? bits_for(ts_span) : 1);
+    const int acct_bits = bits_for(acct_max) > 0 ? bits_for(acct_max) : 1;
+    const int seq_bits = bits_for(n - 1) > 0 ? bits_for(n - 1) : 1;
+    static const bool force_pairs = getenv("IGS_SORT_PAIRS") && atoi(getenv("IGS_SORT_PAIRS")) != 0;   // test knob: old path
+    const bool packed = !force_pairs && n < (1u << 30) && seq_bits + 2 + ts_bits + acct_bits <= 64;
+
+    uint32_t* d_acct; int64_t* d_amt; uint8_t *d_type, *d_dflag;
     uint64_t* d_keys[2]; uint32_t* d_vals[2];
-    IGS_CUDA(e, sc.alloc(&d_keys[0], n));
-    IGS_CUDA(e, sc.alloc(&d_keys[1], n));
-    IGS_CUDA(e, sc.alloc(&d_vals[0], n));
-    IGS_CUDA(e, sc.alloc(&d_vals[1], n));
+    IGS_CUDA(e, sc.alloc(&d_keys[0], nr));
+    IGS_CUDA(e, sc.alloc(&d_keys[1], nr));
+    const bool need_vals = !packed || e->has_event_ids;               // the identifier columns sort (hash, position) pairs
+    IGS_CUDA(e, sc.alloc(&d_vals[0], need_vals ? nr : 1));
+    IGS_CUDA(e, sc.alloc(&d_vals[1], need_vals ? nr : 1));
+    IGS_CUDA(e, sc.alloc(&d_acct, nr));
+    IGS_CUDA(e, sc.alloc(&d_amt, nr));
+    IGS_CUDA(e, sc.alloc(&d_type, nr));
+    IGS_CUDA(e, sc.alloc(&d_dflag, nr));
     const uint32_t nb_sort = (n + kSortTile - 1) / kSortTile;
-    const uint32_t hist_elems = bins * nb_sort;
-    uint32_t *d_hist, *d_scan_scratch;
-    IGS_CUDA(e, sc.alloc(&d_hist, hist_elems));
-    IGS_CUDA(e, sc.alloc(&d_scan_scratch, scan_u32_scratch_elems(hist_elems)));
-    k_make_keys<<<nb_el, kThreads, 0, st>>>(d_acct_in, d_ts_in, n, ts_min, ts_bits, d_keys[0], d_vals[0]);
-    IGS_LAUNCHED(e);
-    int cur = 0;
-    {
+    if (packed) {
+        // ---- one-sweep radix sort of packed keys (onesweep.cuh) ---------------------------------------
+        KeyLayout lay;
+        lay.seq_bits = seq_bits; lay.ts_bits = ts_bits; lay.acct_shift = seq_bits + 2 + ts_bits; lay.ts_min = ts_min;
+        const OsPlan plan = os_plan(seq_bits + 2, seq_bits + 2 + ts_bits + acct_bits);
+        uint32_t* d_os;
+        IGS_CUDA(e, sc.alloc(&d_os, OsScratch::words(nr, kOsMaxPasses)));
+        OsScratch osc;
+        int rc = os_prepare(e, &osc, d_os, n, plan, st);
+        if (rc != IGS_OK) return rc;
+        IGS_CUDA(e, cudaFuncSetAttribute(k_make_keys_hist, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)os_hist_smem_bytes(plan.passes)));
+        k_make_keys_hist<<<min((n + kOsThreads - 1) / kOsThreads, (uint32_t)e->sm_count * 8), kOsThreads,
+                           os_hist_smem_bytes(plan.passes), st>>>(d_acct_in, d_ts_in, d_type_in, n, n_accounts, lay, plan, osc,
+                                                                  d_keys[0], d_mm + 6);
+        IGS_LAUNCHED(e);
+        int cur = 0;
+        rc = os_sort_passes(e, d_keys, n, plan, osc, st, &cur);
+        if (rc != IGS_OK) return rc;
+        IGS_CUDA(e, cudaMemcpyAsync(d_mm + 7, osc.error(), 4, cudaMemcpyDeviceToDevice, st));
+        k_unpack_gather_packed<<<nb_el, kThreads, 0, st>>>(d_keys[cur], d_ts_in, d_amt_in, n, lay, (uint32_t)spec.lo, d_acct,
+                                                           x.ts, x.seq, d_amt, d_type);
+        IGS_LAUNCHED(e);
+    } else {
+        // ---- (key, value) pairs: histories whose account / time / arrival bits do not fit one word --------
+        if (spec.assume_time_ordered) {
+            igs_set_error(e, "internal: a delta build needs packed sort keys");
+            return IGS_ERR_INVALID;
+        }
+        const int key_bits = ts_bits + acct_bits;
+        const int passes = (key_bits + kSortMaxBits - 1) / kSortMaxBits;
+        const int digit_bits = (key_bits + passes - 1) / passes;      // <= 8
+        const uint32_t bins = 1u << digit_bits;
+        const uint32_t hist_elems = bins * nb_sort;
+        uint32_t *d_hist, *d_scan_scratch;
+        IGS_CUDA(e, sc.alloc(&d_hist, hist_elems));
+        IGS_CUDA(e, sc.alloc(&d_scan_scratch, scan_u32_scratch_elems(hist_elems)));
+        k_make_keys<<<nb_el, kThreads, 0, st>>>(d_acct_in, d_ts_in, n, ts_min, ts_bits, d_keys[0], d_vals[0]);
+        IGS_LAUNCHED(e);
+        int cur = 0;
         const int rc = radix_sort_pairs(e, d_keys, d_vals, n, passes, digit_bits, d_hist, d_scan_scratch, st, &cur);
         if (rc != IGS_OK) return rc;
+        k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], d_vals[cur], d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
+                                                    (uint32_t)spec.lo, d_acct, x.ts, x.seq, d_amt, d_type);
+        IGS_LAUNCHED(e);
     }
 
-    // ---- sorted columns, segments, distinct flags -----------------------------------------------
-    uint32_t* d_acct; int64_t* d_amt; uint8_t *d_type, *d_dflag;
-    IGS_CUDA(e, sc.alloc(&d_acct, n));
-    IGS_CUDA(e, sc.alloc(&d_amt, n));
-    IGS_CUDA(e, sc.alloc(&d_type, n));
-    IGS_CUDA(e, sc.alloc(&d_dflag, n));
-    k_unpack_gather<<<nb_el, kThreads, 0, st>>>(d_keys[cur], d_vals[cur], d_ts_in, d_amt_in, d_type_in, n, ts_min, ts_bits,
-                                                (uint32_t)spec.lo, d_acct, x.ts, x.seq, d_amt, d_type);
-    IGS_LAUNCHED(e);
-    k_segments<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, x.seq, n, n_accounts, (uint32_t)spec.n_before, spec.base, x.seg,
-                                           d_mm + 4);
-    IGS_LAUNCHED(e);
+    // ---- segments, group heads, late events, distinct flags -----------------------------------------
     uint8_t* d_head;
-    IGS_CUDA(e, sc.alloc(&d_head, n));
-    uint32_t* d_scan_scratch_n;                                        // scratch of an n-element u32 scan
-    IGS_CUDA(e, sc.alloc(&d_scan_scratch_n, scan_u32_scratch_elems(n + 1)));
-    k_group_heads<<<nb_el, kThreads, 0, st>>>(d_acct, x.ts, n, d_head);
+    IGS_CUDA(e, sc.alloc(&d_head, nr));
+    uint32_t* d_work;                                                  // members of long (account, ts) groups
+    IGS_CUDA(e, sc.alloc(&d_work, nr));
+    k_segments_heads<<<min(nb_el, (uint32_t)e->sm_count * 8), kThreads, 0, st>>>(d_acct, x.ts, x.seq, n, n_accounts, (uint32_t)spec.n_before, spec.base,
+                                                 x.seg, d_head, d_mm + 4);
     IGS_LAUNCHED(e);
     IGS_CUDA(e, cudaMemsetAsync(d_mm, 0, 4, st));                     // d_mm[0] is free again: unresolved counter
-    k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_mm);
+    k_distinct<<<nb_el, kThreads, 0, st>>>(d_head, d_amt, n, d_dflag, d_work, d_mm);
     IGS_LAUNCHED(e);
     {
-        uint32_t n_unres = 0;
+        uint32_t n_unres = 0, flags[4] = {0, 0, 0, 0};           // late[0], late[1], bad account, look-back gave up
         IGS_CUDA(e, cudaMemcpyAsync(&n_unres, d_mm, 4, cudaMemcpyDeviceToHost, st));
-        IGS_CUDA(e, cudaMemcpyAsync(late, d_mm + 4, 8, cudaMemcpyDeviceToHost, st));
+        IGS_CUDA(e, cudaMemcpyAsync(flags, d_mm + 4, 16, cudaMemcpyDeviceToHost, st));
         IGS_CUDA(e, cudaStreamSynchronize(st));
+        late[0] = flags[0]; late[1] = flags[1];
+        if (flags[2] != 0) {
+            igs_set_error(e, "event account index %u >= n_accounts %u", flags[2], n_accounts);
+            return IGS_ERR_INVALID;
+        }
+        if (flags[3] != 0) {
+            igs_set_error(e, "internal: the radix sort's look-back gave up waiting for an earlier tile");
+            return IGS_ERR_CUDA;
+        }
+        if (spec.assume_time_ordered && late[0] != 0) return IGS_OK;   // not in time order after all: the caller decides
         if (late[1] != 0 && e->late_policy == IGS_LATE_REJECT) return IGS_OK;   // the caller drops the batch: stop here
-        const int rc = resolve_big_groups(e, sc, n_unres != 0, d_head, d_amt, n, d_dflag, d_scan_scratch_n, st);
+        const int rc = resolve_big_groups(e, sc, n_unres, d_work, d_acct, x.ts, d_amt, d_dflag, st);
         if (rc != IGS_OK) return rc;
     }
     if (spec.base.n != 0) {
@@ -1076,12 +1257,12 @@ static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
     const uint32_t n1 = (n + kVTile - 1) / kVTile;            // level-0 aggregates (one per 256 events)
     const uint32_t n2 = (n1 + kVTile - 1) / kVTile;           // level-1 aggregates (one per 65 536 events)
     VScan *d_agg1, *d_agg2;
-    IGS_CUDA(e, sc.alloc(&d_agg1, n1));
-    IGS_CUDA(e, sc.alloc(&d_agg2, n2));
+    IGS_CUDA(e, sc.alloc(&d_agg1, (nr + kVTile - 1) / kVTile));
+    IGS_CUDA(e, sc.alloc(&d_agg2, ((nr + kVTile - 1) / kVTile + kVTile - 1) / kVTile));
     VCols cols{d_acct, x.ts, d_amt, d_type, d_dflag, n, spec.base};
     const uint32_t warps_per_block = kThreads / 32;
     const uint32_t g1 = (n1 + warps_per_block - 1) / warps_per_block, g2 = (n2 + warps_per_block - 1) / warps_per_block;
-    k_vs_reduce<ElemSrc><<<g1, kThreads, 0, st>>>(ElemSrc{cols}, d_agg1);
+    k_vs_reduce_elems<<<g1, kThreads, 0, st>>>(cols, d_agg1);
     IGS_LAUNCHED(e);
     k_vs_reduce<AggSrc><<<g2, kThreads, 0, st>>>(AggSrc{d_agg1, n1}, d_agg2);
     IGS_LAUNCHED(e);
@@ -1169,7 +1350,8 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_
     if (rc != IGS_OK) { e->n_raw = before; return rc; }
     // Histories with identifier columns still rebuild everything: a delta would have to know which identifiers
     // the base's trailing 24h chains hold.
-    bool through_delta = !e->has_event_ids;
+    static const bool sort_pairs = getenv("IGS_SORT_PAIRS") && atoi(getenv("IGS_SORT_PAIRS")) != 0;   // test knob (build_index)
+    bool through_delta = !e->has_event_ids && !sort_pairs;
     if (through_delta) {
         {
             std::lock_guard<std::mutex> lk(e->view_mu);
@@ -1177,12 +1359,13 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_
         }
         BuildSpec spec;
         spec.lo = e->base_n; spec.hi = e->n_raw; spec.n_accounts = n_accounts; spec.dst = &e->dv_spare;
-        spec.base = view_of(e->ev, true); spec.n_before = before;
+        spec.base = view_of(e->ev, true); spec.n_before = before; spec.assume_time_ordered = true;
+        spec.reserve = std::max<uint64_t>(e->delta_min, e->base_n / 8) + n;      // the most the delta holds before it is folded in
         uint32_t late[2];
         rc = build_index(e, spec, late);
         if (rc != IGS_OK) { e->n_raw = before; return rc; }
-        if (late[1] != 0) {
-            if (e->late_policy == IGS_LATE_REJECT) { e->n_raw = before; return reject_late(e, late[1]); }
+        if (late[0] != 0) {
+            if (e->late_policy == IGS_LATE_REJECT) { e->n_raw = before; return reject_late(e, late[1] ? late[1] : late[0]); }
             through_delta = false;       // IGS_LATE_REORDER: file everything by timestamp in a new base
         } else {
             {

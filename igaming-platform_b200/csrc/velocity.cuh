@@ -24,9 +24,9 @@
 // into the delta adds the two levels' prefix differences and takes the chain columns from the delta.
 //
 // Searching.  All five window bounds lie at the END of the prior events (the last 24 h), and most queries are
-// "now" queries whose prior events are the whole segment, so every search starts at the end and gallops
-// backwards (1, 2, 4 ... events) before bisecting: an account with a long history costs as many dependent
-// loads as its last day is long, and the probes of a short gallop share one 32-byte sector of ts[].
+// "now" queries whose prior events are the whole segment, so every search first probes the last eight events
+// (four independent loads in one or two sectors of ts[]) and only bisects what is left: the typical account is
+// settled in one round trip per bound, a hot one pays the bisection it always paid.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -79,20 +79,27 @@ struct igs_history_view {
     igs_index_view base, delta;
 };
 
-// first i in [s, hi) with ts[i] >= key, searched backwards from hi (key may be negative: then s)
+// first i in [s, hi) with ts[i] >= key, searched backwards from hi (key may be negative: then s).
+// The four probes at hi-1, hi-2, hi-4, hi-8 are independent loads that share one or two 32-byte sectors: one
+// round trip settles every bound that lies within the last eight events; the rest is bisected.
 __device__ __forceinline__ uint32_t igs_lower_ts_back(const uint32_t* __restrict__ ts, uint32_t s, uint32_t hi,
                                                       long long key) {
     if (key <= 0) return s;
     if (key > 0xFFFFFFFFll) return hi;
     const uint32_t k = (uint32_t)key;
-    uint32_t left = s, right = hi, step = 1;
-    while (right > left) {                       // gallop: ts[right ..] >= k is known
-        const uint32_t probe = right - left > step ? right - step : left;
-        if (__ldg(ts + probe) < k) { left = probe + 1; break; }
-        right = probe;
-        step <<= 1;
+    uint32_t left = s, right = hi;
+    if (right > left) {
+        const uint32_t len = right - left;
+        const uint32_t p1 = right - 1, p2 = len > 2 ? right - 2 : left, p4 = len > 4 ? right - 4 : left,
+                       p8 = len > 8 ? right - 8 : left;
+        const uint32_t t1 = __ldg(ts + p1), t2 = __ldg(ts + p2), t4 = __ldg(ts + p4), t8 = __ldg(ts + p8);
+        if (t1 < k) return right;
+        if (t8 >= k) right = p8;                               // farther back (or p8 == left: done below)
+        else if (t4 >= k) { left = p8 + 1; right = p4; }
+        else if (t2 >= k) { left = p4 + 1; right = p2; }
+        else { left = p2 + 1; right = p1; }
     }
-    while (left < right) {                       // bisect (left - 1 is < k, right is >= k)
+    while (left < right) {                       // bisect (left - 1 is < k or left == s; right is >= k)
         const uint32_t mid = left + ((right - left) >> 1);
         if (__ldg(ts + mid) < k) left = mid + 1; else right = mid;
     }
@@ -175,7 +182,7 @@ __device__ __forceinline__ void igs_velocity_accumulate(const igs_prefix_rec* __
 __device__ __forceinline__ void igs_velocity_tail(const igs_index_view& ix, uint32_t last, long long now, long long L,
                                                   igs_velocity* v, igs_uniques* uq) {
     const long long gap = now - L;
-    union __align__(16) { igs_tail_rec r; uint4 q[2]; } tlu;
+    union __align__(32) { igs_tail_rec r; uint4 q[2]; } tlu;
     {
         const uint4* src = reinterpret_cast<const uint4*>(ix.tail + last);
         tlu.q[0] = __ldg(src);
