@@ -202,6 +202,10 @@ class Engine:
         """Appended events live in a delta index folded into the base beyond max(min_delta_events, base / 8)."""
         self._check(self._lib.igs_set_compaction_threshold(self._h, min_delta_events))
 
+    def prepare_ingest(self, max_batch_events: int) -> None:
+        """Pre-allocate what appends of up to max_batch_events events will need (igs_prepare_ingest)."""
+        self._check(self._lib.igs_prepare_ingest(self._h, max_batch_events))
+
     def history_info(self) -> dict:
         info = abi.HistoryInfo()
         self._check(self._lib.igs_get_history_info(self._h, C.byref(info)))
@@ -403,7 +407,7 @@ def _serialised(fn):
 
 # every method that uses slot 0's staging or replaces device state; the *_device methods are ordered by the
 # caller's streams and stay lock-free
-for _name in ("load_gbdt", "load_mlp", "load_players", "load_events", "append_events", "set_late_policy", "set_compaction_threshold",
+for _name in ("load_gbdt", "load_mlp", "load_players", "load_events", "append_events", "set_late_policy", "set_compaction_threshold", "prepare_ingest",
               "history_info", "evict_events", "get_uniques", "blacklist_load", "blacklist_add", "blacklist_check",
               "links_pairs", "links_group", "links_finish", "get_links", "check_bonus_abuse", "score_features",
               "get_velocity", "score_batch", "ltv_batch", "ltv_predict_batch", "ltv_mock_predict"):

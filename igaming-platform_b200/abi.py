@@ -175,7 +175,7 @@ EXPORTS = [
     "igs_abuse_signals", "igs_links_window_create", "igs_links_window_open", "igs_links_window_attach",
     "igs_links_window_reset", "igs_links_pairs_peer", "igs_links_group_peer", "igs_links_finish_peer",
     "igs_evict_events",
-    "igs_set_compaction_threshold", "igs_kernel_launches", "igs_load_events_device", "igs_set_late_policy", "igs_get_history_info",
+    "igs_set_compaction_threshold", "igs_prepare_ingest", "igs_kernel_launches", "igs_load_events_device", "igs_set_late_policy", "igs_get_history_info",
     "igs_ltv_predict_batch", "igs_ltv_predict_batch_device", "igs_ltv_mock_predict", "igs_ltv_mock_predict_device",
 ]
 
@@ -271,6 +271,7 @@ def load_library() -> C.CDLL:
     lib.igs_ltv_mock_predict_device.argtypes = [vp, vp, u64, vp, vp]
     lib.igs_load_events_device.argtypes = [vp, C.POINTER(EventCols), C.POINTER(EventIds), u64, C.c_uint32]
     lib.igs_set_compaction_threshold.argtypes = [vp, u64]
+    lib.igs_prepare_ingest.argtypes = [vp, u64]
     lib.igs_set_late_policy.argtypes = [vp, i32]
     lib.igs_get_history_info.argtypes = [vp, C.POINTER(HistoryInfo)]
     lib.igs_evict_events.argtypes = [vp, C.c_uint32, C.POINTER(u64)]

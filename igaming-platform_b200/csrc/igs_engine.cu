@@ -322,6 +322,12 @@ int igs_set_compaction_threshold(igs_engine* e, uint64_t min_delta_events) {
     return IGS_OK;
 }
 
+int igs_prepare_ingest(igs_engine* e, uint64_t max_batch_events) {
+    IGS_ENGINE(e);
+    std::lock_guard<std::mutex> lk(e->mu);
+    return igs_prepare_event_ingest(e, max_batch_events);
+}
+
 int igs_get_history_info(igs_engine* e, igs_history_info* out) {
     IGS_ENGINE(e);
     IGS_REQUIRE(e, out != nullptr, "out is null");

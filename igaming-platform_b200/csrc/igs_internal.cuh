@@ -218,6 +218,7 @@ struct igs_history_reader {
     bool locked;
 };
 int igs_evict_event_history(igs_engine* e, uint32_t now, uint64_t* n_evicted);
+int igs_prepare_event_ingest(igs_engine* e, uint64_t max_batch);
 int igs_mlp_upload(igs_engine* e, const igs_mlp_desc* d);
 void igs_mlp_free(igs_engine* e);
 int igs_launch_ltv(igs_engine* e, const uint16_t* d_x, const igs_ltv_row* d_rows, uint64_t n,

@@ -940,11 +940,39 @@ void igs_free_history_events(igs_engine* e) {       // engine teardown: the pool
 
 // Appends n events to the device-resident raw columns (capacity grows by 1.5x).
 // (the source columns may be host or device memory: cudaMemcpyDefault lets the runtime tell)
+static int reserve_raw(igs_engine* e, uint64_t need, cudaStream_t st);
 static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n,
                       cudaStream_t st) {
     const uint64_t need = e->n_raw + n;
-    if (need > e->cap_raw) {
-        const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
+    {
+        const int rc = reserve_raw(e, need, st);
+        if (rc != IGS_OK) return rc;
+    }
+    if (n) {
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyDefault, st));
+        IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyDefault, st));
+        if (e->has_event_ids) {       // a missing column = events without that identifier
+            if (ids && ids->device)
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_device + e->n_raw, ids->device, n * 8, cudaMemcpyDefault, st));
+            else
+                IGS_CUDA(e, cudaMemsetAsync(e->raw_device + e->n_raw, 0, n * 8, st));
+            if (ids && ids->ip)
+                IGS_CUDA(e, cudaMemcpyAsync(e->raw_ip + e->n_raw, ids->ip, n * 8, cudaMemcpyDefault, st));
+            else
+                IGS_CUDA(e, cudaMemsetAsync(e->raw_ip + e->n_raw, 0, n * 8, st));
+        }
+    }
+    e->n_raw = need;
+    return IGS_OK;
+}
+
+// Grows the raw columns to hold at least `need` events (capacity grows by 1.5x); the resident events are kept.
+static int reserve_raw(igs_engine* e, uint64_t need, cudaStream_t st) {
+    if (need <= e->cap_raw) return IGS_OK;
+    const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
+    {
         uint32_t *a = nullptr, *t = nullptr; int64_t* m = nullptr; uint8_t* y = nullptr;
         uint64_t *d = nullptr, *p = nullptr;
         {
@@ -979,23 +1007,6 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
         e->raw_device = d; e->raw_ip = p;
         e->cap_raw = cap;
     }
-    if (n) {
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_account + e->n_raw, ev->account, n * 4, cudaMemcpyDefault, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_ts + e->n_raw, ev->ts, n * 4, cudaMemcpyDefault, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_amount + e->n_raw, ev->amount, n * 8, cudaMemcpyDefault, st));
-        IGS_CUDA(e, cudaMemcpyAsync(e->raw_type + e->n_raw, ev->tx_type, n, cudaMemcpyDefault, st));
-        if (e->has_event_ids) {       // a missing column = events without that identifier
-            if (ids && ids->device)
-                IGS_CUDA(e, cudaMemcpyAsync(e->raw_device + e->n_raw, ids->device, n * 8, cudaMemcpyDefault, st));
-            else
-                IGS_CUDA(e, cudaMemsetAsync(e->raw_device + e->n_raw, 0, n * 8, st));
-            if (ids && ids->ip)
-                IGS_CUDA(e, cudaMemcpyAsync(e->raw_ip + e->n_raw, ids->ip, n * 8, cudaMemcpyDefault, st));
-            else
-                IGS_CUDA(e, cudaMemsetAsync(e->raw_ip + e->n_raw, 0, n * 8, st));
-        }
-    }
-    e->n_raw = need;
     return IGS_OK;
 }
 
@@ -1084,6 +1095,26 @@ struct BuildSpec {
     uint64_t reserve = 0;               // size allocations for at least this many events
 };
 
+// (Re)allocates the arrays of an unpublished index so that they hold `events` events of `n_accounts` accounts, with
+// headroom so that appends rarely come back here.
+static int ensure_index_capacity(igs_engine* e, igs_event_index& x, uint64_t events, uint32_t n_accounts) {
+    if (events + 1 <= x.cap_events && (uint64_t)n_accounts + 1 <= x.cap_accounts) return IGS_OK;
+    const uint64_t ce = std::max<uint64_t>(events + 1, x.cap_events + x.cap_events / 2);
+    const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
+    {
+        std::lock_guard<std::mutex> lk(e->view_mu);
+        release_index_arrays(e, x);
+    }
+    IGS_CUDA(e, cudaMalloc(&x.seg, ca * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.ts, ce * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.seq, ce * sizeof(uint32_t)));
+    IGS_CUDA(e, cudaMalloc(&x.pre, ce * sizeof(igs_prefix_rec)));
+    IGS_CUDA(e, cudaMalloc(&x.tail, ce * sizeof(igs_tail_rec)));
+    x.cap_events = ce;
+    x.cap_accounts = ca;
+    return IGS_OK;
+}
+
 static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
     const uint32_t n = (uint32_t)(spec.hi - spec.lo);
     const uint32_t n_accounts = spec.n_accounts;
@@ -1094,21 +1125,9 @@ static int build_index(igs_engine* e, const BuildSpec& spec, uint32_t late[2]) {
     // sizes of allocations: at least what the caller expects the range to grow to (a delta is sized for its
     // compaction threshold once, instead of being re-allocated every few appends)
     const uint32_t nr = (uint32_t)std::max<uint64_t>(n, std::min<uint64_t>(spec.reserve, 0xFFFFFFF0ull));
-    if ((uint64_t)n + 1 > x.cap_events || (uint64_t)n_accounts + 1 > x.cap_accounts) {
-        // (re)allocate the index arrays with headroom so that appends rarely come back here
-        const uint64_t ce = std::max<uint64_t>((uint64_t)nr + 1, x.cap_events + x.cap_events / 2);
-        const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
-        {
-            std::lock_guard<std::mutex> lk(e->view_mu);
-            release_index_arrays(e, x);
-        }
-        IGS_CUDA(e, cudaMalloc(&x.seg, ca * sizeof(uint32_t)));
-        IGS_CUDA(e, cudaMalloc(&x.ts, ce * sizeof(uint32_t)));
-        IGS_CUDA(e, cudaMalloc(&x.seq, ce * sizeof(uint32_t)));
-        IGS_CUDA(e, cudaMalloc(&x.pre, ce * sizeof(igs_prefix_rec)));
-        IGS_CUDA(e, cudaMalloc(&x.tail, ce * sizeof(igs_tail_rec)));
-        x.cap_events = ce;
-        x.cap_accounts = ca;
+    {
+        const int rc = ensure_index_capacity(e, x, nr, n_accounts);
+        if (rc != IGS_OK) return rc;
     }
     x.n = n;
     x.n_accounts = n_accounts;
@@ -1360,7 +1379,8 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_
         BuildSpec spec;
         spec.lo = e->base_n; spec.hi = e->n_raw; spec.n_accounts = n_accounts; spec.dst = &e->dv_spare;
         spec.base = view_of(e->ev, true); spec.n_before = before; spec.assume_time_ordered = true;
-        spec.reserve = std::max<uint64_t>(e->delta_min, e->base_n / 8) + n;      // the most the delta holds before it is folded in
+        // the most the delta holds before it is folded in (bounded: a huge threshold is not a reason to allocate for it)
+        spec.reserve = std::min<uint64_t>(std::max<uint64_t>(e->delta_min, e->base_n / 8), 8u << 20) + n;
         uint32_t late[2];
         rc = build_index(e, spec, late);
         if (rc != IGS_OK) { e->n_raw = before; return rc; }
@@ -1382,6 +1402,32 @@ int igs_append_event_columns(igs_engine* e, const igs_event_cols* ev, const igs_
     rc = rebuild_base(e, n_accounts, before);
     if (rc != IGS_OK) e->n_raw = before;
     return rc;
+}
+
+// Everything an append allocates on demand, allocated now: room in the raw columns for the events until the next
+// compaction, both sets of delta arrays, the spare set of base arrays for the compaction.
+int igs_prepare_event_ingest(igs_engine* e, uint64_t max_batch) {
+    if (!e->has_events) {
+        igs_set_error(e, "igs_prepare_ingest needs a loaded history (igs_load_events, possibly with n = 0)");
+        return IGS_ERR_STATE;
+    }
+    const uint32_t n_accounts = e->ev.n_accounts;
+    const uint64_t threshold = std::min<uint64_t>(std::max<uint64_t>(e->delta_min, e->n_raw / 8), 8u << 20);
+    const uint64_t delta_cap = threshold + max_batch;
+    if (e->n_raw + delta_cap >= 0xFFFFFFFFull) {
+        igs_set_error(e, "at most 2^32-2 events per shard");
+        return IGS_ERR_INVALID;
+    }
+    {
+        const int rc = reserve_raw(e, e->n_raw + delta_cap, e->ingest_stream);
+        if (rc != IGS_OK) return rc;
+    }
+    if (!e->has_event_ids) {
+        int rc = ensure_index_capacity(e, e->dv_spare, delta_cap, n_accounts);
+        if (rc == IGS_OK && e->dv.n == 0) rc = ensure_index_capacity(e, e->dv, delta_cap, n_accounts);
+        if (rc != IGS_OK) return rc;
+    }
+    return ensure_index_capacity(e, e->ev_spare, e->n_raw + delta_cap, n_accounts);
 }
 
 int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,

@@ -382,6 +382,12 @@ int igs_load_events_device(igs_engine* e, const igs_event_cols* d_ev, const igs_
  * Needs a prior igs_load_events (n = 0 is fine) that fixed n_accounts.  A batch with an out-of-range
  * account is rejected as a whole and the history is left as it was.                                  */
 int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n);
+/* Allocates now what igs_append_events would otherwise allocate when it first needs it — room in the resident
+ * columns for the events up to the next compaction, both sets of delta arrays, the spare base arrays a
+ * compaction builds into — for batches of up to max_batch_events.  Optional; a live service calls it once
+ * after igs_load_events so that no append pays for (and no scoring call stalls behind) a device allocation.
+ * Costs about another index worth of device memory.  No counterpart in the reference.                  */
+int igs_prepare_ingest(igs_engine* e, uint64_t max_batch_events);
 /* The delta index is folded into the base when it holds more than max(min_delta_events, base / 8) events.
  * No counterpart in the reference (Redis updates in place).                                          */
 int igs_set_compaction_threshold(igs_engine* e, uint64_t min_delta_events);
