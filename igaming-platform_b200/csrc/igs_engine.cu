@@ -111,6 +111,21 @@ int igs_engine_create(int device, igs_engine** out) {
     }
     e->device = device;
     e->sm_count = prop.multiProcessorCount;
+    {
+        cudaMemPoolProps props;
+        memset(&props, 0, sizeof(props));
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        unsigned long long keep = ~0ull;
+        if (cudaMemPoolCreate(&e->scratch_pool, &props) != cudaSuccess ||
+            cudaMemPoolSetAttribute(e->scratch_pool, cudaMemPoolAttrReleaseThreshold, &keep) != cudaSuccess) {
+            igs_set_error(nullptr, "memory pool creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+            igs_engine_destroy(e);
+            return IGS_ERR_CUDA;
+        }
+    }
     if (cudaStreamCreateWithFlags(&e->ingest_stream, cudaStreamNonBlocking) != cudaSuccess) {
         igs_set_error(nullptr, "stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
         igs_engine_destroy(e);
@@ -150,6 +165,7 @@ void igs_engine_destroy(igs_engine* e) {
     }
     free_buf(&e->part_scratch);
     if (e->ingest_stream) cudaStreamDestroy(e->ingest_stream);
+    if (e->scratch_pool) cudaMemPoolDestroy(e->scratch_pool);
     if (e->d_model) cudaFree(e->d_model);
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
@@ -376,10 +392,14 @@ int igs_append_events(igs_engine* e, const igs_event_cols* ev, uint64_t n) {
 // batch is cut into chunks that go round-robin over the slot's worker streams: the H2D copy of chunk
 // k+1, the kernel of chunk k and the D2H copy of chunk k-1 overlap.  The workers fork from and join
 // back into the slot's stream, so ordering against earlier calls on the slot and igs_wait() hold.
-constexpr uint64_t kPipeChunkRows = 128 * 1024;
+constexpr uint64_t kPipeChunkRowsA = 128 * 1024;   // path A: 312 B/tx -> 40 MB per chunk
+// Path B: 40 B/tx; chunks of kVisitSortMin rows (k_score.cu), the smallest batch that is visited in account order.
+// (Larger chunks leave the three pipeline streams too few pieces to overlap: 256K-row chunks cost 7 % end to end.)
+constexpr uint64_t kPipeChunkRowsB = 128 * 1024;
 
 template <typename Body>
-static int run_pipelined(igs_engine* e, igs_slot& sl, uint64_t n, Body&& body /* (stream, off, cnt) -> int */) {
+static int run_pipelined(igs_engine* e, igs_slot& sl, uint64_t n, uint64_t kPipeChunkRows,
+                         Body&& body /* (stream, off, cnt) -> int */) {
     if (n <= 2 * kPipeChunkRows) return body(sl.stream, (uint64_t)0, n);
     IGS_CUDA(e, cudaEventRecord(sl.ev_fork, sl.stream));
     for (int k = 0; k < IGS_PIPE_STREAMS; ++k) IGS_CUDA(e, cudaStreamWaitEvent(sl.pipe[k], sl.ev_fork, 0));
@@ -442,7 +462,7 @@ static int score_features_host(igs_engine* e, int s, const igs_config* cfg, cons
     igs_rule_row* d_rows = (igs_rule_row*)sl.in1.p;
     igs_result* d_out = (igs_result*)sl.out0.p;
     uint8_t* d_leaf = leaves ? (uint8_t*)sl.aux0.p : nullptr;
-    return run_pipelined(e, sl, n, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
+    return run_pipelined(e, sl, n, kPipeChunkRowsA, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
         if (need_feat)
             IGS_CUDA(e, cudaMemcpyAsync(d_feat + off * IGS_NUM_FEATURES, features + off * IGS_NUM_FEATURES,
                                         cnt * IGS_NUM_FEATURES * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -528,7 +548,7 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
     igs_result* d_out = (igs_result*)sl.out0.p;
     float* d_feat = features_out ? (float*)sl.aux0.p : nullptr;
     igs_velocity* d_vel = velocity_out ? (igs_velocity*)sl.aux1.p : nullptr;
-    return run_pipelined(e, sl, n, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
+    return run_pipelined(e, sl, n, kPipeChunkRowsB, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
         IGS_CUDA(e, cudaMemcpyAsync(d_tx + off, tx + off, cnt * sizeof(igs_tx), cudaMemcpyHostToDevice, st));
         if (ids)
             IGS_CUDA(e, cudaMemcpyAsync(d_ids + off, ids + off, cnt * sizeof(igs_tx_ids), cudaMemcpyHostToDevice, st));

@@ -90,6 +90,11 @@ struct igs_engine {
     std::mutex mu;                // guards loads vs. scoring calls
     igs_slot slot[IGS_NUM_SLOTS];
     igs_buf  part_scratch;        // shard-partition counters (k_partition.cu)
+    // Stream-ordered scratch of the scoring calls (the visit-order sort of large fused batches): an engine-private
+    // pool that keeps what it has allocated (release threshold = max), so that a call's cudaMallocFromPoolAsync /
+    // cudaFreeAsync pair costs microseconds instead of a round trip to the driver, and calls on different streams
+    // still get disjoint memory.
+    cudaMemPool_t scratch_pool = nullptr;
 
     // tree ensemble
     uint8_t* d_model = nullptr;   // n_trees * IGS_DEV_TREE_BYTES

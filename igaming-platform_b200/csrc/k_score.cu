@@ -557,9 +557,9 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
 // The index gathers of the fused path are bound by random 32-byte sector reads.  Visiting the batch in
 // account order makes neighbouring lanes read neighbouring records (the same ones for a hot account): one or
 // three radix passes over (account, row) cost less than they save once the batch is large (1M tx: 1.85 -> 1.76
-// ms including the sort; one pass — locality without adjacency — gains nothing).  The scratch is stream-ordered
-// (cudaMallocAsync), so concurrent calls on different streams do not share it.
-constexpr unsigned long long kVisitSortMin = 262144;
+// ms including the sort; one pass — locality without adjacency — gains nothing).  The scratch is stream-ordered, from
+// the engine's own pool (igs_engine::scratch_pool), so concurrent calls on different streams do not share it.
+constexpr unsigned long long kVisitSortMin = 131072;   // = the chunk size of host-buffer calls (igs_engine.cu)
 // key = [account (top bits) | row]: sorted on the account bits by the one-sweep radix sort (onesweep.cuh); the row
 // rides in the low word and is what the score kernel reads back.  The key pass also fills the digit histograms.
 __global__ void __launch_bounds__(kOsThreads)
@@ -587,7 +587,7 @@ static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, uint32_t n
     const size_t b_keys = ((size_t)n * 8 + 255) & ~(size_t)255;
     const size_t b_os = (OsScratch::words(n, plan.passes) * 4 + 255) & ~(size_t)255;
     char* base = nullptr;
-    IGS_CUDA(e, cudaMallocAsync((void**)&base, 2 * b_keys + b_os, stream));
+    IGS_CUDA(e, cudaMallocFromPoolAsync((void**)&base, 2 * b_keys + b_os, e->scratch_pool, stream));
     *scratch = base;
     uint64_t* keys[2] = {(uint64_t*)base, (uint64_t*)(base + b_keys)};
     OsScratch sc;

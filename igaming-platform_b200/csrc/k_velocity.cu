@@ -971,7 +971,7 @@ static int append_raw(igs_engine* e, const igs_event_cols* ev, const igs_event_i
 // Grows the raw columns to hold at least `need` events (capacity grows by 1.5x); the resident events are kept.
 static int reserve_raw(igs_engine* e, uint64_t need, cudaStream_t st) {
     if (need <= e->cap_raw) return IGS_OK;
-    const uint64_t cap = std::max<uint64_t>(need, e->cap_raw + e->cap_raw / 2 + 1024);
+    const uint64_t cap = e->cap_raw == 0 ? need : need + need / 2 + 1024;
     {
         uint32_t *a = nullptr, *t = nullptr; int64_t* m = nullptr; uint8_t* y = nullptr;
         uint64_t *d = nullptr, *p = nullptr;
@@ -1099,7 +1099,9 @@ struct BuildSpec {
 // headroom so that appends rarely come back here.
 static int ensure_index_capacity(igs_engine* e, igs_event_index& x, uint64_t events, uint32_t n_accounts) {
     if (events + 1 <= x.cap_events && (uint64_t)n_accounts + 1 <= x.cap_accounts) return IGS_OK;
-    const uint64_t ce = std::max<uint64_t>(events + 1, x.cap_events + x.cap_events / 2);
+    // first allocation: what is asked for; growth: half as much again, so that a history that grows by an eighth
+    // per compaction comes back here every few compactions, not every time
+    const uint64_t ce = x.cap_events == 0 ? events + 1 : events + 1 + events / 2;
     const uint64_t ca = std::max<uint64_t>((uint64_t)n_accounts + 1, x.cap_accounts);
     {
         std::lock_guard<std::mutex> lk(e->view_mu);
@@ -1412,14 +1414,17 @@ int igs_prepare_event_ingest(igs_engine* e, uint64_t max_batch) {
         return IGS_ERR_STATE;
     }
     const uint32_t n_accounts = e->ev.n_accounts;
-    const uint64_t threshold = std::min<uint64_t>(std::max<uint64_t>(e->delta_min, e->n_raw / 8), 8u << 20);
+    // sized for the history growing by half: the compaction threshold grows with the base (base / 8), so arrays that
+    // fit exactly today would be re-allocated right after the first compaction
+    const uint64_t horizon = e->n_raw + e->n_raw / 2;
+    const uint64_t threshold = std::min<uint64_t>(std::max<uint64_t>(e->delta_min, horizon / 8), 8u << 20);
     const uint64_t delta_cap = threshold + max_batch;
-    if (e->n_raw + delta_cap >= 0xFFFFFFFFull) {
+    if (horizon + delta_cap >= 0xFFFFFFFFull) {
         igs_set_error(e, "at most 2^32-2 events per shard");
         return IGS_ERR_INVALID;
     }
     {
-        const int rc = reserve_raw(e, e->n_raw + delta_cap, e->ingest_stream);
+        const int rc = reserve_raw(e, horizon + delta_cap, e->ingest_stream);
         if (rc != IGS_OK) return rc;
     }
     if (!e->has_event_ids) {
@@ -1427,7 +1432,7 @@ int igs_prepare_event_ingest(igs_engine* e, uint64_t max_batch) {
         if (rc == IGS_OK && e->dv.n == 0) rc = ensure_index_capacity(e, e->dv, delta_cap, n_accounts);
         if (rc != IGS_OK) return rc;
     }
-    return ensure_index_capacity(e, e->ev_spare, e->n_raw + delta_cap, n_accounts);
+    return ensure_index_capacity(e, e->ev_spare, horizon + delta_cap, n_accounts);
 }
 
 int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,

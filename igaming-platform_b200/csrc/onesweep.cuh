@@ -200,7 +200,9 @@ k_os_pass(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
         }
     }
     {   // look back: sum the counts of the preceding tiles until one of them knows its inclusive prefix.  Four
-        // predecessors are polled at a time (independent loads), then consumed in order.
+        // predecessors are polled at a time (independent loads), then consumed in order.  (Polling 8 .. 32 at a time
+        // shortens the chain of a wave of tiles that starts at once but costs more in traffic and registers than it
+        // saves: 95 -> 210 us per 10M-key pass.)
         uint32_t excl = 0;
         if (d < bins && tile != 0) {
             uint32_t polls = 0;
