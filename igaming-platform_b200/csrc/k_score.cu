@@ -559,7 +559,9 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
 // three radix passes over (account, row) cost less than they save once the batch is large (1M tx: 1.85 -> 1.76
 // ms including the sort; one pass — locality without adjacency — gains nothing).  The scratch is stream-ordered, from
 // the engine's own pool (igs_engine::scratch_pool), so concurrent calls on different streams do not share it.
-constexpr unsigned long long kVisitSortMin = 131072;   // = the chunk size of host-buffer calls (igs_engine.cu)
+// (Host-buffer calls arrive here in 131 072-row chunks, below this threshold: sorting them was measured and costs
+// more than it saves end to end — 2.03 -> 2.17 ms per 1M tx through igs_score_batch.)
+constexpr unsigned long long kVisitSortMin = 262144;
 // key = [account (top bits) | row]: sorted on the account bits by the one-sweep radix sort (onesweep.cuh); the row
 // rides in the low word and is what the score kernel reads back.  The key pass also fills the digit histograms.
 __global__ void __launch_bounds__(kOsThreads)

@@ -1432,7 +1432,35 @@ int igs_prepare_event_ingest(igs_engine* e, uint64_t max_batch) {
         if (rc == IGS_OK && e->dv.n == 0) rc = ensure_index_capacity(e, e->dv, delta_cap, n_accounts);
         if (rc != IGS_OK) return rc;
     }
-    return ensure_index_capacity(e, e->ev_spare, horizon + delta_cap, n_accounts);
+    {
+        const int rc = ensure_index_capacity(e, e->ev_spare, horizon + delta_cap, n_accounts);
+        if (rc != IGS_OK) return rc;
+    }
+    // The published base becomes the spare set at the first compaction and would be re-allocated at the second:
+    // move it into arrays of the same capacity now (a device-to-device copy; this is a set-up call).
+    if (e->ev.cap_events < horizon + delta_cap + 1 && e->ev.n != 0) {
+        igs_event_index big;
+        int rc = ensure_index_capacity(e, big, horizon + delta_cap, n_accounts);
+        if (rc != IGS_OK) { release_index_arrays(e, big); return rc; }
+        cudaStream_t st = e->ingest_stream;
+        const igs_event_index& x = e->ev;
+        IGS_CUDA(e, cudaMemcpyAsync(big.seg, x.seg, ((size_t)x.n_accounts + 1) * 4, cudaMemcpyDeviceToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(big.ts, x.ts, (size_t)x.n * 4, cudaMemcpyDeviceToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(big.seq, x.seq, (size_t)x.n * 4, cudaMemcpyDeviceToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(big.pre, x.pre, ((size_t)x.n + 1) * sizeof(igs_prefix_rec), cudaMemcpyDeviceToDevice, st));
+        IGS_CUDA(e, cudaMemcpyAsync(big.tail, x.tail, (size_t)x.n * sizeof(igs_tail_rec), cudaMemcpyDeviceToDevice, st));
+        IGS_CUDA(e, cudaStreamSynchronize(st));
+        big.n = x.n;
+        big.n_accounts = x.n_accounts;
+        {
+            std::lock_guard<std::mutex> lk(e->view_mu);
+            std::swap(e->ev, big);                   // `big` now holds the old arrays and their readers
+        }
+        IGS_CUDA(e, cudaDeviceSynchronize());        // kernels still reading the old arrays
+        std::lock_guard<std::mutex> lk(e->view_mu);
+        release_index_arrays(e, big);
+    }
+    return IGS_OK;
 }
 
 int igs_build_event_index(igs_engine* e, const igs_event_cols* ev, const igs_event_ids* ids, uint64_t n64,

@@ -23,10 +23,12 @@
 // A query whose prior events end in the base is answered from the base alone; one whose prior events reach
 // into the delta adds the two levels' prefix differences and takes the chain columns from the delta.
 //
-// Searching.  All five window bounds lie at the END of the prior events (the last 24 h), and most queries are
-// "now" queries whose prior events are the whole segment, so every search first probes the last eight events
-// (four independent loads in one or two sectors of ts[]) and only bisects what is left: the typical account is
-// settled in one round trip per bound, a hot one pays the bisection it always paid.
+// Searching.  A lookup is a chain of dependent loads, and on a hot account (10^5 .. 10^6 events) that chain is what
+// it costs: five bisections of 20 probes each.  So (1) the position of the query among the account's events is a
+// 4-ary search (three probes per round trip), with the "newer than everything" case — every live query — answered
+// by the first round; (2) the four window bounds are searched together: four probes over the last eight events
+// settle the typical account in ONE round trip, the rest is bisected in lock step — log2(length) round trips for
+// all four bounds, not four times that.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -79,47 +81,42 @@ struct igs_history_view {
     igs_index_view base, delta;
 };
 
-// first i in [s, hi) with ts[i] >= key, searched backwards from hi (key may be negative: then s).
-// The four probes at hi-1, hi-2, hi-4, hi-8 are independent loads that share one or two 32-byte sectors: one
-// round trip settles every bound that lies within the last eight events; the rest is bisected.
-__device__ __forceinline__ uint32_t igs_lower_ts_back(const uint32_t* __restrict__ ts, uint32_t s, uint32_t hi,
-                                                      long long key) {
-    if (key <= 0) return s;
-    if (key > 0xFFFFFFFFll) return hi;
-    const uint32_t k = (uint32_t)key;
-    uint32_t left = s, right = hi;
-    if (right > left) {
-        const uint32_t len = right - left;
-        const uint32_t p1 = right - 1, p2 = len > 2 ? right - 2 : left, p4 = len > 4 ? right - 4 : left,
-                       p8 = len > 8 ? right - 8 : left;
-        const uint32_t t1 = __ldg(ts + p1), t2 = __ldg(ts + p2), t4 = __ldg(ts + p4), t8 = __ldg(ts + p8);
-        if (t1 < k) return right;
-        if (t8 >= k) right = p8;                               // farther back (or p8 == left: done below)
-        else if (t4 >= k) { left = p8 + 1; right = p4; }
-        else if (t2 >= k) { left = p4 + 1; right = p2; }
-        else { left = p2 + 1; right = p1; }
-    }
-    while (left < right) {                       // bisect (left - 1 is < k or left == s; right is >= k)
-        const uint32_t mid = left + ((right - left) >> 1);
-        if (__ldg(ts + mid) < k) left = mid + 1; else right = mid;
-    }
-    return left;
-}
-
-// number of events in [s, e) ordered before (t, seq_limit), as a position: first one that is not
+// number of events in [s, e) ordered before (t, seq_limit), as a position: first one that is not.
+// 4-ary search: three probes per round trip (independent loads) — half the dependent depth of a bisection, which
+// is what a lookup in a long segment waits for.
 __device__ __forceinline__ uint32_t igs_prior_end(const igs_index_view& ix, uint32_t s, uint32_t e, uint32_t t,
                                                   uint32_t seq_limit) {
     if (s == e) return s;
-    {   // the common query is newer than everything the account has done
-        const uint32_t tl = __ldg(ix.ts + e - 1);
-        if (tl < t || (tl == t && __ldg(ix.seq + e - 1) < seq_limit)) return e;
+    auto before = [&](uint32_t tm, uint32_t sm) { return tm < t || (tm == t && sm < seq_limit); };
+    uint32_t lo = s, hi = e;                      // answer in [lo, hi]
+    {   // the common query is newer than everything the account has done: probe the last event together with the
+        // first round of the search
+        const uint32_t len = hi - lo;
+        const uint32_t m1 = lo + len / 4, m2 = lo + len / 2, m3 = lo + (len / 4) * 3, ml = e - 1;
+        const uint32_t t1 = __ldg(ix.ts + m1), t2 = __ldg(ix.ts + m2), t3 = __ldg(ix.ts + m3), tl = __ldg(ix.ts + ml);
+        const uint32_t q1 = __ldg(ix.seq + m1), q2 = __ldg(ix.seq + m2), q3 = __ldg(ix.seq + m3), ql = __ldg(ix.seq + ml);
+        if (before(tl, ql)) return e;
+        hi = ml;
+        if (!before(t1, q1)) hi = m1;
+        else if (!before(t2, q2)) { lo = m1 + 1; hi = m2; }
+        else if (!before(t3, q3)) { lo = m2 + 1; hi = m3; }
+        else lo = m3 + 1;
     }
-    uint32_t lo = s, hi = e - 1;
     while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        const uint32_t tm = __ldg(ix.ts + mid);
-        const bool before = tm < t || (tm == t && __ldg(ix.seq + mid) < seq_limit);
-        if (before) lo = mid + 1; else hi = mid;
+        const uint32_t len = hi - lo;
+        if (len <= 2) {
+            const uint32_t tm = __ldg(ix.ts + lo), sm = __ldg(ix.seq + lo);
+            if (!before(tm, sm)) return lo;
+            ++lo;
+            continue;
+        }
+        const uint32_t m1 = lo + len / 4, m2 = lo + len / 2, m3 = lo + (len / 4) * 3;
+        const uint32_t t1 = __ldg(ix.ts + m1), t2 = __ldg(ix.ts + m2), t3 = __ldg(ix.ts + m3);
+        const uint32_t q1 = __ldg(ix.seq + m1), q2 = __ldg(ix.seq + m2), q3 = __ldg(ix.seq + m3);
+        if (!before(t1, q1)) hi = m1;
+        else if (!before(t2, q2)) { lo = m1 + 1; hi = m2; }
+        else if (!before(t3, q3)) { lo = m2 + 1; hi = m3; }
+        else lo = m3 + 1;
     }
     return lo;
 }
@@ -129,16 +126,51 @@ struct igs_bounds {
     uint32_t lo60, lo300, lo3600, lo86400;
     uint32_t alive;   // first position that survived the last 1h trim (ts > L-3600); s when it cannot bind
 };
+// The four lower bounds (first position with ts >= now - W) are searched TOGETHER:
+//   1. four probes at u-1, u-2, u-4, u-8 — independent loads in one or two sectors of ts[] — bracket every bound
+//      that lies within the last eight events (the typical account: one round trip for all four bounds);
+//   2. what is left is bisected in lock step, one probe per bound and round trip, so a long segment costs
+//      log2(length) dependent loads for the four bounds together instead of four times that.
 // `last_is_now`: the newest prior event (of the whole history, both levels) has ts == now.  Only then can the
 // trim bound L-3599 exceed the 1h window bound now-3600 (quirk Q4); otherwise alive <= lo3600 and never binds.
 __device__ __forceinline__ igs_bounds igs_window_bounds(const uint32_t* __restrict__ ts, uint32_t s, uint32_t u,
                                                         long long now, bool last_is_now) {
     igs_bounds b;
-    b.lo60 = igs_lower_ts_back(ts, s, u, now - 60);
-    b.lo300 = igs_lower_ts_back(ts, s, b.lo60, now - 300);
-    b.lo3600 = igs_lower_ts_back(ts, s, b.lo300, now - 3600);
-    b.lo86400 = igs_lower_ts_back(ts, s, b.lo3600, now - 86400);
     b.alive = s;
+    if (u == s) { b.lo60 = b.lo300 = b.lo3600 = b.lo86400 = s; return b; }
+    const long long w[4] = {60, 300, 3600, 86400};
+    uint32_t key[4], left[4], right[4];
+    const uint32_t len = u - s;
+    const uint32_t p1 = u - 1, p2 = len > 2 ? u - 2 : s, p4 = len > 4 ? u - 4 : s, p8 = len > 8 ? u - 8 : s;
+    const uint32_t t1 = __ldg(ts + p1), t2 = __ldg(ts + p2), t4 = __ldg(ts + p4), t8 = __ldg(ts + p8);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const long long k = now - w[j];
+        key[j] = k > 0 ? (uint32_t)k : 0u;        // now < 2^32: the key fits; a key <= 0 selects everything
+        if (t1 < key[j]) { left[j] = right[j] = u; }
+        else if (t8 >= key[j]) { left[j] = s; right[j] = p8; }
+        else if (t4 >= key[j]) { left[j] = p8 + 1; right[j] = p4; }
+        else if (t2 >= key[j]) { left[j] = p4 + 1; right[j] = p2; }
+        else { left[j] = p2 + 1; right[j] = p1; }
+    }
+    // the bounds are nested (a longer window starts no later): a settled bound caps the ones after it
+#pragma unroll
+    for (int j = 1; j < 4; ++j)
+        if (right[j] > right[j - 1]) { right[j] = right[j - 1]; if (left[j] > right[j]) left[j] = right[j]; }
+    while ((left[0] < right[0]) | (left[1] < right[1]) | (left[2] < right[2]) | (left[3] < right[3])) {
+        uint32_t mid[4], tm[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            mid[j] = left[j] + ((right[j] - left[j]) >> 1);
+            tm[j] = left[j] < right[j] ? __ldg(ts + mid[j]) : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (left[j] < right[j]) {
+                if (tm[j] < key[j]) left[j] = mid[j] + 1; else right[j] = mid[j];
+            }
+    }
+    b.lo60 = left[0]; b.lo300 = left[1]; b.lo3600 = left[2]; b.lo86400 = left[3];
     if (last_is_now) {                            // now-3599 lies between the 1h and the 5m bound
         uint32_t lo = b.lo3600, hi = b.lo300;
         const uint32_t k = now - 3599 > 0 ? (uint32_t)(now - 3599) : 0u;
