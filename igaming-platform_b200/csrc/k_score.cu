@@ -499,6 +499,7 @@ static int launch(igs_engine* e, int src, const ScoreParams& p, bool leaves, cud
     case 2: return launch_shape<Shape<16, 10>>(e, src, p, leaves, stream);
     case 3: return launch_shape<Shape<8, 25>>(e, src, p, leaves, stream);
     case 4: return launch_shape<Shape<16, 14, 7>>(e, src, p, leaves, stream);
+    case 5: return launch_shape<Shape<6, 5, 5, 3>>(e, src, p, leaves, stream);     // three small CTAs per SM
     default:
         // latency-sized batches: if the 12-warp shape would need a second, nearly empty round of tiles while
         // the 16-warp shape covers the batch in one round, take the latter
