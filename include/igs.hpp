@@ -16,6 +16,7 @@
 #include <map>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <tuple>
 #include <utility>
 #include <vector>
@@ -265,6 +266,104 @@ private:
     Pinned<igs_tx_ids> ids_;
     Pinned<igs_result> out_;
     bool device_ids_ = false;
+};
+
+// ShardedEngine — the in-process shape of the risk service on a multi-GPU box (services/risk/cmd/main.go:72-164 is
+// ONE process): one igs_engine, one host thread and one set of pinned staging buffers per shard, shards placed
+// round-robin on the visible devices, records routed by igs_shard_of(account).  Every feature, rule and score
+// depends on one account only, so the shards never talk to each other; a batch is split, the shards
+// score their parts concurrently, the results land back in the caller's order.  Accounts are GLOBAL dense indices
+// here; the engine of a shard sees the local index (position among the shard's accounts in increasing global order).
+class ShardedEngine {
+public:
+    explicit ShardedEngine(int n_shards, int n_devices = 1) : shards_(n_shards) {
+        if (n_shards < 1 || n_devices < 1) throw Error(IGS_ERR_INVALID, "n_shards and n_devices must be >= 1");
+        for (int s = 0; s < n_shards; ++s)
+            if (int rc = igs_engine_create(s % n_devices, &shards_[s].e); rc != IGS_OK) {
+                const std::string msg = igs_last_error(nullptr);
+                for (int k = 0; k < s; ++k) igs_engine_destroy(shards_[k].e);
+                throw Error(rc, msg);
+            }
+    }
+    ~ShardedEngine() { for (Shard& sh : shards_) igs_engine_destroy(sh.e); }
+    ShardedEngine(const ShardedEngine&) = delete;
+    ShardedEngine& operator=(const ShardedEngine&) = delete;
+
+    int n_shards() const { return (int)shards_.size(); }
+    igs_engine* shard(int s) { return shards_[s].e; }
+    uint32_t ShardOf(uint32_t account) const { return igs_shard_of(account, 0, (uint32_t)shards_.size()); }
+
+    void LoadGbdt(const igs_gbdt_desc& d) { for (Shard& sh : shards_) check(sh, igs_load_gbdt(sh.e, &d)); }
+
+    // FeatureStore.GetBatchFeatures for every shard: rows[g] = BatchFeatures of global account g
+    void LoadPlayers(const igs_player_row* rows, uint32_t n) {
+        local_.assign(n, 0);
+        std::vector<std::vector<igs_player_row>> part(shards_.size());
+        for (uint32_t g = 0; g < n; ++g) {
+            auto& p = part[ShardOf(g)];
+            local_[g] = (uint32_t)p.size();
+            p.push_back(rows[g]);
+        }
+        for (size_t s = 0; s < shards_.size(); ++s) {
+            shards_[s].n_accounts = (uint32_t)part[s].size();
+            check(shards_[s], igs_load_players(shards_[s].e, part[s].data(), part[s].size()));
+        }
+    }
+    // the event history, split by account shard (arrival order is kept inside a shard); needs LoadPlayers first
+    void LoadEvents(const uint32_t* account, const uint32_t* ts, const int64_t* amount, const uint8_t* type, uint64_t n) {
+        struct Cols { std::vector<uint32_t> a, t; std::vector<int64_t> m; std::vector<uint8_t> y; };
+        std::vector<Cols> part(shards_.size());
+        for (uint64_t i = 0; i < n; ++i) {
+            if (account[i] >= local_.size()) throw Error(IGS_ERR_INVALID, "event of an account beyond the player table");
+            Cols& c = part[ShardOf(account[i])];
+            c.a.push_back(local_[account[i]]); c.t.push_back(ts[i]); c.m.push_back(amount[i]); c.y.push_back(type[i]);
+        }
+        for (size_t s = 0; s < shards_.size(); ++s) {
+            const igs_event_cols cols{part[s].a.data(), part[s].t.data(), part[s].m.data(), part[s].y.data()};
+            check(shards_[s], igs_load_events(shards_[s].e, &cols, part[s].a.size(), shards_[s].n_accounts));
+        }
+    }
+
+    // rpc ScoreBatch over all shards: tx[i].account is a GLOBAL index; out[i] belongs to tx[i]
+    void ScoreBatch(const igs_config& cfg, const igs_tx* tx, uint64_t n, igs_result* out) {
+        for (Shard& sh : shards_) sh.rows.clear();
+        for (uint64_t i = 0; i < n; ++i) shards_[ShardOf(tx[i].account)].rows.push_back(i);
+        std::vector<std::thread> workers;
+        for (Shard& sh : shards_)
+            workers.emplace_back([&, this, shp = &sh] {       // one host thread per shard (Go: LockOSThread per device)
+                Shard& s = *shp;
+                const size_t m = s.rows.size();
+                s.rc = IGS_OK;
+                if (m == 0) return;
+                igs_tx* in = s.tx.reserve(m);
+                igs_result* res = s.out.reserve(m);
+                for (size_t k = 0; k < m; ++k) {
+                    in[k] = tx[s.rows[k]];
+                    const uint32_t g = in[k].account;
+                    in[k].account = g < local_.size() ? local_[g] : 0xFFFFFFFEu;   // unknown account: zero features
+                }
+                s.rc = igs_score_batch(s.e, &cfg, in, m, res, nullptr, nullptr);
+                if (s.rc == IGS_OK)
+                    for (size_t k = 0; k < m; ++k) out[s.rows[k]] = res[k];
+            });
+        for (std::thread& w : workers) w.join();
+        for (Shard& sh : shards_) check(sh, sh.rc);
+    }
+
+private:
+    struct Shard {
+        igs_engine* e = nullptr;
+        uint32_t n_accounts = 0;
+        std::vector<uint64_t> rows;
+        Pinned<igs_tx> tx;
+        Pinned<igs_result> out;
+        int rc = IGS_OK;
+    };
+    static void check(const Shard& sh, int rc) {
+        if (rc != IGS_OK) throw Error(rc, igs_last_error(sh.e));
+    }
+    std::vector<Shard> shards_;
+    std::vector<uint32_t> local_;      // global account -> local index on its shard
 };
 
 }  // namespace igs

@@ -196,6 +196,53 @@ int main(int argc, char** argv) {
         }
         REQUIRE(want_rows[0].n_linked == 1 && want_rows[0].linked[0] == 7 && want_rows[2].n_linked == 0);
     }
+    {
+        // ShardedEngine: three shards (engines) in this process, one host thread each, against one engine holding
+        // everything — a result depends on its own account only, so the two must agree bit for bit
+        const uint32_t np = 500, ne = 20000, nt = 30000;
+        std::vector<igs_player_row> pl(np);
+        for (uint32_t i = 0; i < np; ++i) {
+            igs_player_row p{};
+            p.account_created_at = now - (int64_t)(rng() % 600) * 86400;
+            p.total_deposits = (int64_t)(rng() % 300000); p.total_withdrawals = (int64_t)(rng() % 300000);
+            p.deposit_count = (int32_t)(rng() % 9); p.bet_count = (int32_t)(rng() % 500); p.win_count = p.bet_count / 3;
+            p.bonus_claim_count = (int32_t)(rng() % 6);
+            pl[i] = p;
+        }
+        std::vector<uint32_t> a(ne), t(ne); std::vector<int64_t> m(ne); std::vector<uint8_t> y(ne);
+        for (uint32_t i = 0; i < ne; ++i) {
+            a[i] = (uint32_t)(rng() % np); t[i] = (uint32_t)(now - 7200 + (int64_t)(rng() % 7200));
+            m[i] = 100 * (int64_t)(1 + rng() % 50); y[i] = (uint8_t)(rng() % 3);
+        }
+        std::vector<igs_tx> tx(nt);
+        for (uint32_t i = 0; i < nt; ++i) {
+            igs_tx x{};
+            x.account = (uint32_t)(rng() % (np + 3));               // a few unknown accounts
+            x.ts = (uint32_t)(now - 600 + (int64_t)(rng() % 600)); x.seq_limit = 0xFFFFFFFFu;
+            x.amount = (int64_t)(rng() % 400000); x.tx_type = (uint8_t)(rng() % 3);
+            x.unique_devices_24h = (uint16_t)(rng() % 6); x.unique_ips_24h = (uint16_t)(rng() % 8);
+            x.bits = IGS_BIT_VALID | (uint8_t)(rng() % 100 < 3 ? IGS_BIT_VPN : 0);
+            tx[i] = x;
+        }
+        igs_config cfg = igs::DefaultConfig();                      // mock model: needs no loaded ensemble
+        igs::ShardedEngine sharded(3, 1);
+        sharded.LoadPlayers(pl.data(), np);
+        sharded.LoadEvents(a.data(), t.data(), m.data(), y.data(), ne);
+        std::vector<igs_result> got(nt), want(nt);
+        sharded.ScoreBatch(cfg, tx.data(), nt, got.data());
+        igs_engine* one = nullptr;
+        REQUIRE(igs_engine_create(0, &one) == IGS_OK);
+        REQUIRE(igs_load_players(one, pl.data(), np) == IGS_OK);
+        const igs_event_cols cols{a.data(), t.data(), m.data(), y.data()};
+        REQUIRE(igs_load_events(one, &cols, ne, np) == IGS_OK);
+        for (igs_tx& x : tx) if (x.account >= np) x.account = 0xFFFFFFFEu;
+        REQUIRE(igs_score_batch(one, &cfg, tx.data(), nt, want.data(), nullptr, nullptr) == IGS_OK);
+        igs_engine_destroy(one);
+        REQUIRE(std::memcmp(got.data(), want.data(), nt * sizeof(igs_result)) == 0);
+        uint32_t used = 0;
+        for (uint32_t g = 0; g < np; ++g) used |= 1u << sharded.ShardOf(g);
+        REQUIRE(used == 7u);
+    }
     std::printf("test_scoring_engine: %zu requests, flags seen 0x%x: ok\n", res.size(), seen);
     return 0;
 }

@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def build(tmp_path, built_lib, orc):
     exe = str(tmp_path / "test_scoring_engine")
     pkg_dir = os.path.dirname(built_lib)
-    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"),
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-pthread", "-I", os.path.join(ROOT, "include"),
            os.path.join(ROOT, "tests", "cpp", "test_scoring_engine.cc"), "-o", exe,
            "-L", pkg_dir, "-ligs", "-L", os.path.join(ROOT, "oracle"), "-loracle_igs",
            f"-Wl,-rpath,{pkg_dir}", f"-Wl,-rpath,{os.path.join(ROOT, 'oracle')}"]
