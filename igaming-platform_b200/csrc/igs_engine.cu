@@ -167,6 +167,7 @@ void igs_engine_destroy(igs_engine* e) {
     if (e->ingest_stream) cudaStreamDestroy(e->ingest_stream);
     if (e->scratch_pool) cudaMemPoolDestroy(e->scratch_pool);
     if (e->d_model) cudaFree(e->d_model);
+    if (e->d_model_ws) cudaFree(e->d_model_ws);
     if (e->d_players) cudaFree(e->d_players);
     igs_free_event_index(e);
     igs_free_history_events(e);
@@ -204,9 +205,11 @@ int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d) {
     std::lock_guard<std::mutex> lk(e->mu);
     // host-side repack into the device layout (see igs_internal.cuh)
     const size_t bytes = (size_t)d->n_trees * IGS_DEV_TREE_BYTES;
-    std::vector<uint8_t> img(bytes ? bytes : 16, 0);
+    std::vector<uint8_t> img(bytes ? bytes : 16, 0), img_ws(bytes ? bytes : 16, 0);
+    auto ws_feat = [](uint32_t f) { return (uint32_t)igs_ws_row((int)f); };
     for (uint32_t t = 0; t < d->n_trees; ++t) {
         uint8_t* tb = img.data() + (size_t)t * IGS_DEV_TREE_BYTES;
+        uint8_t* tw = img_ws.data() + (size_t)t * IGS_DEV_TREE_BYTES;
         const uint8_t* feat = d->feat + (size_t)t * IGS_TREE_NODES;
         const float* thr = d->thr + (size_t)t * IGS_TREE_NODES;
         for (int i = 0; i < IGS_TREE_NODES; ++i)
@@ -223,8 +226,11 @@ int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d) {
                     nd.feats = ((uint32_t)feat[i] << 7) | ((uint32_t)feat[2 * i + 1] << 13) | ((uint32_t)feat[2 * i + 2] << 19);
                     nd.thr = thr[i];
                     memcpy(tb + igs_dev_level_off(lvl) + j * 8, &nd, 8);
+                    nd.feats = (ws_feat(feat[i]) << 7) | (ws_feat(feat[2 * i + 1]) << 13) | (ws_feat(feat[2 * i + 2]) << 19);
+                    memcpy(tw + igs_dev_level_off(lvl) + j * 8, &nd, 8);
                 } else {
                     memcpy(tb + igs_dev_level_off(lvl) + j * 4, &thr[i], 4);
+                    memcpy(tw + igs_dev_level_off(lvl) + j * 4, &thr[i], 4);
                 }
             }
         }
@@ -237,15 +243,22 @@ int igs_load_gbdt(igs_engine* e, const igs_gbdt_desc* d) {
             }
             leaves[i] = lf;
         }
+        memcpy(tw + IGS_DEV_LEAF_OFF, tb + IGS_DEV_LEAF_OFF, IGS_TREE_LEAVES * sizeof(float));
     }
     IGS_CUDA(e, cudaDeviceSynchronize());
     if (e->d_model) {
         IGS_CUDA(e, cudaFree(e->d_model));
         e->d_model = nullptr;
     }
+    if (e->d_model_ws) {
+        IGS_CUDA(e, cudaFree(e->d_model_ws));
+        e->d_model_ws = nullptr;
+    }
     e->has_gbdt = false;
     IGS_CUDA(e, cudaMalloc(&e->d_model, img.size()));
     IGS_CUDA(e, cudaMemcpy(e->d_model, img.data(), img.size(), cudaMemcpyHostToDevice));
+    IGS_CUDA(e, cudaMalloc(&e->d_model_ws, img_ws.size()));
+    IGS_CUDA(e, cudaMemcpy(e->d_model_ws, img_ws.data(), img_ws.size(), cudaMemcpyHostToDevice));
     e->n_trees = d->n_trees;
     e->n_features = d->n_features;
     e->post_transform = d->post_transform;

@@ -37,6 +37,15 @@ __host__ __device__ constexpr int igs_dev_level_off(int d) {   // 0, 8, 16, 48, 
 }
 static_assert(igs_dev_level_off(7) == 848 && igs_dev_level_off(8) == 1360, "tree image layout");
 constexpr int IGS_DEV_LEAF_OFF = 1360;
+// On the fused path (assembly on the device) 39 of the 64 model inputs are live: 7 (IPCountryChanges), 8 (DeviceAge)
+// and 22 (DisposableEmail) are never set by the reference (scoring/engine.go:326-417) and 42..63 are spare.  The
+// warp-specialised kernel keeps one shared zero row for all of them: feature index -> tile row.
+constexpr int IGS_WS_ROWS = 40;
+__host__ __device__ constexpr int igs_ws_row(int f) {
+    return f < 7 ? f : (f >= 9 && f <= 21) ? f - 2 : (f >= 23 && f <= 41) ? f - 3 : IGS_WS_ROWS - 1;
+}
+static_assert(igs_ws_row(6) == 6 && igs_ws_row(9) == 7 && igs_ws_row(21) == 19 && igs_ws_row(23) == 20 &&
+              igs_ws_row(41) == 38 && igs_ws_row(7) == 39 && igs_ws_row(63) == 39, "row map");
 constexpr int IGS_DEV_TREE_BYTES = 1360 + 256 * 4;  // 2384
 
 // ---------------------------------------------------------------------------------------------
@@ -98,6 +107,7 @@ struct igs_engine {
 
     // tree ensemble
     uint8_t* d_model = nullptr;   // n_trees * IGS_DEV_TREE_BYTES
+    uint8_t* d_model_ws = nullptr;  // same, feature indices replaced by igs_ws_row (k_score_ws)
     uint32_t n_trees = 0, n_features = 0, post_transform = 0;
     float    base_score = 0.f;
     bool     has_gbdt = false;

@@ -82,6 +82,7 @@ struct ScoreParams {
     uint8_t* leaf_idx;
     unsigned long long n;
     const uint8_t* model;
+    const uint8_t* model_ws;       // the same ensemble with the feature indices >= 42 mapped onto row 42 (k_score_ws)
     unsigned n_trees;
     float base_score;
     unsigned post;
@@ -206,8 +207,9 @@ __device__ __forceinline__ void walk_chunk(uint32_t cb, int trees, uint32_t tile
 }
 
 // mockPredict, ml/onnx_model.go:258-308, on the already-normalised tile column of this lane.
+template <bool kCompact = false>
 __device__ __forceinline__ double mock_predict(const float* tile_lane) {
-    auto v = [&](int i) { return tile_lane[i * 32]; };
+    auto v = [&](int i) { return tile_lane[(kCompact ? igs_ws_row(i) : i) * 32]; };
     double s = 0.0;
     if (v(0) > 0.5f) s = __dadd_rn(s, 0.2);                        // :262
     if (v(2) > 0.5f) s = __dadd_rn(s, 0.15);                       // :265
@@ -227,6 +229,9 @@ __device__ __forceinline__ double mock_predict(const float* tile_lane) {
 // Path B staging for one lane: velocity lookup + player gather + extractFeatures
 // (scoring/engine.go:326-417) + scoring->ml mapping (ToSlice order, ml/onnx_model.go:133-166) +
 // Normalize (:169-184) + extension block.  Writes the lane's column of the [64][32] tile.
+// kCompact: the tile of the warp-specialised kernel — IGS_WS_ROWS rows, the features that are constant zero on this
+// path share the last one (igs_ws_row); the engine's second model image uses the same row numbers.
+template <bool kCompact = false>
 __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long long row, bool in_range,
                                             float* tile_lane /* my_tile + lane */, RuleIn* r) {
     igs_tx t;
@@ -281,7 +286,11 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
     if (v.tx_count_1h > 0)                                                     // :412-414
         avg1h = __double2float_rn(__ddiv_rn((double)v.tx_sum_1h, (double)v.tx_count_1h));
     const long long net = pl.r.total_deposits - pl.r.total_withdrawals;        // :370
-    auto put = [&](int i, float x) { tile_lane[i * 32] = x; };
+    auto put = [&](int i, float x) {
+        if (!kCompact) tile_lane[i * 32] = x;
+        else if (igs_ws_row(i) != IGS_WS_ROWS - 1) tile_lane[igs_ws_row(i) * 32] = x;     // constant zeros: written once below
+    };
+    if (kCompact) tile_lane[(IGS_WS_ROWS - 1) * 32] = 0.f;
     put(0, igs_min_max(__uint2float_rn(v.tx_count_1m), 20.f));
     put(1, igs_min_max(__uint2float_rn(v.tx_count_5m), 50.f));
     put(2, igs_min_max(__uint2float_rn(v.tx_count_1h), 200.f));
@@ -320,8 +329,10 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
             put(k++, __uint2float_rn(v.win[ty][w].count));
             put(k++, __ll2float_rn(v.win[ty][w].sum));
         }
+    if (!kCompact) {
 #pragma unroll
-    for (int i = 42; i < IGS_NUM_FEATURES; ++i) put(i, 0.f);
+        for (int i = 42; i < IGS_NUM_FEATURES; ++i) put(i, 0.f);
+    }
     r->amount = t.amount;
     r->total_deposits = pl.r.total_deposits;
     r->total_withdrawals = pl.r.total_withdrawals;
@@ -475,6 +486,166 @@ k_score(const __grid_constant__ ScoreParams p) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Warp-specialised fused kernel (path B, large batches).
+// In k_score every warp alternates between two phases with opposite needs: the lookup + assembly of its 32
+// transactions (chains of dependent global loads, nothing for the shared-memory pipe to do) and the walk of 500
+// trees (shared-memory pipe, no global traffic).  Here the phases run on different warps of ONE persistent CTA per
+// SM: kWalkers warps only walk, kProducers warps only look up and assemble — into the OTHER half of each walker's
+// double-buffered feature tile — so that the walkers never wait for DRAM and the lookups need no visit-order sort
+// to be cheap.  Hand-over per (walker, buffer) through two mbarriers (full / empty); the tree chunks stream through
+// shared memory exactly as in k_score, the chunk hand-over being a named barrier over the walker warps only.
+// Shared memory: 16 walkers x 2 x 40 rows x 128 B of feature tiles (the 25 features that are constant zero on this
+// path share one row: igs_ws_row; the engine keeps a second model image with the feature indices replaced by row
+// numbers) + two 10-tree chunk buffers + the rule sideband = 215 KB.
+// Registers: 640 threads leave ~100 registers per thread, which the five independent tree walks of a walker need;
+// more producer warps would feed the walkers better but push the walk into spills (see launch_fused).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int kWsRows = IGS_WS_ROWS;
+template <int W, int P, int C, int I>
+struct WsShape {
+    static constexpr int kWalkers = W, kProducers = P, kIlp = I, kChunkTrees = C;
+    static constexpr int kThreads = (W + P) * 32;
+    static constexpr int kTileTx = W * 32;
+    static constexpr int kTileBytes = kWsRows * 32 * 4;                 // 5 120
+    static constexpr int kChunkBytes = C * IGS_DEV_TREE_BYTES;
+    static constexpr int kSideBytes = W * 2 * 32 * 8;                   // {rule score, flags | valid << 31} per lane
+    static constexpr int kBarBytes = 16 + W * 2 * 2 * 8;                // 2 chunk barriers + full / empty per (walker, buffer)
+    static constexpr int kSmemBytes = W * 2 * kTileBytes + 2 * kChunkBytes + kSideBytes + kBarBytes + 64;
+    static_assert(C % I == 0, "chunk must be a whole number of ILP groups");
+    static_assert(kSmemBytes <= 227 * 1024, "smem budget");
+};
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// bounded wait: a hand-over that never comes is a bug, and a trap beats a hung GPU
+__device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity) {
+    uint32_t ok, spins = 0;
+    do {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            " selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (!ok && ++spins > (1u << 26)) __trap();
+    } while (!ok);
+}
+
+template <typename S>
+__global__ void __launch_bounds__(S::kThreads, 1)
+k_score_ws(const __grid_constant__ ScoreParams p) {
+    constexpr int W = S::kWalkers, P = S::kProducers, kTileTx = S::kTileTx, kChunkTrees = S::kChunkTrees,
+                  kChunkBytes = S::kChunkBytes, kTileBytes = S::kTileBytes;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* tiles = smem;                                              // [W][2][kWsRows][32] f32
+    uint8_t* chunk_buf = tiles + W * 2 * kTileBytes;
+    uint2* side = reinterpret_cast<uint2*>(chunk_buf + 2 * kChunkBytes);    // [W][2][32]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(side) + S::kSideBytes);
+    const uint32_t bar_chunk = smem_u32(bars);                          // [2]
+    const uint32_t bar_full = bar_chunk + 16;                           // [W][2]
+    const uint32_t bar_empty = bar_full + W * 2 * 8;                    // [W][2]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        mbar_init(bar_chunk, 1);
+        mbar_init(bar_chunk + 8, 1);
+        for (int i = 0; i < W * 2; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int model_kind = p.cfg.model_kind;
+    const unsigned n_chunks = (p.n_trees + kChunkTrees - 1) / kChunkTrees;
+    const bool use_gbdt = model_kind == IGS_MODEL_GBDT && n_chunks > 0;
+    const unsigned long long n_tiles = (p.n + kTileTx - 1) / kTileTx;
+    const unsigned long long my_tiles = n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp >= W) {
+        // ---------------- producers: lookup + assembly + rules for the walkers w = pw, pw + P, ... ----------------
+        const int pw = warp - W;
+        for (unsigned long long k = 0; k < my_tiles; ++k) {
+            const unsigned long long tile = blockIdx.x + k * gridDim.x;
+            const unsigned b = (unsigned)(k & 1);
+            for (int w = pw; w < W; w += P) {
+                const unsigned long long slot = tile * kTileTx + (unsigned)w * 32 + lane;
+                const bool in_range = slot < p.n;
+                const unsigned long long row = (p.perm != nullptr && in_range) ? (uint32_t)__ldg(p.perm + slot) : slot;
+                mbar_wait_bounded(bar_empty + 8 * (w * 2 + b), (uint32_t)(((k >> 1) & 1) ^ 1));   // the walker is done with it
+                float* tile_lane = reinterpret_cast<float*>(tiles + (size_t)(w * 2 + b) * kTileBytes) + lane;
+                RuleIn ri;
+                assemble_tx<true>(p, row, in_range, tile_lane, &ri);
+                unsigned flags;
+                const int rule = igs_apply_rules(p.cfg, ri.amount, ri.tx_type, ri.tx_count_1m, ri.account_age, ri.uniq_dev,
+                                                 ri.uniq_ip, ri.bits, ri.tslt, ri.deposit_count, ri.total_deposits,
+                                                 ri.total_withdrawals, &flags);
+                side[(w * 2 + b) * 32 + lane] = make_uint2((uint32_t)rule, flags | ((ri.bits & IGS_BIT_VALID) ? 0x80000000u : 0u));
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_full + 8 * (w * 2 + b));
+            }
+        }
+        return;
+    }
+
+    // ---------------- walkers -------------------------------------------------------------------------------------
+    const unsigned long long total_chunks = use_gbdt ? my_tiles * n_chunks : 0;
+    auto issue = [&](unsigned long long g) {   // g-th chunk of this CTA's sequence; thread 0 only
+        const unsigned c = (unsigned)(g % n_chunks);
+        const unsigned b = (unsigned)(g & 1);
+        const unsigned trees = min((unsigned)kChunkTrees, p.n_trees - c * kChunkTrees);
+        const uint32_t bytes = trees * IGS_DEV_TREE_BYTES;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(bar_chunk + 8 * b, bytes);
+        bulk_g2s(smem_u32(chunk_buf + b * kChunkBytes), p.model + (size_t)c * kChunkBytes, bytes, bar_chunk + 8 * b);
+    };
+    if (threadIdx.x == 0) {
+        if (total_chunks > 0) issue(0);
+        if (total_chunks > 1) issue(1);
+    }
+    const uint32_t chunk_addr = smem_u32(chunk_buf);
+    unsigned long long g = 0;
+    for (unsigned long long k = 0; k < my_tiles; ++k) {
+        const unsigned long long tile = blockIdx.x + k * gridDim.x;
+        const unsigned b = (unsigned)(k & 1);
+        const unsigned long long slot = tile * kTileTx + (unsigned)warp * 32 + lane;
+        const bool in_range = slot < p.n;
+        const unsigned long long row = (p.perm != nullptr && in_range) ? (uint32_t)__ldg(p.perm + slot) : slot;
+        mbar_wait_bounded(bar_full + 8 * (warp * 2 + b), (uint32_t)((k >> 1) & 1));       // the producer has filled it
+        const float* my_tile = reinterpret_cast<const float*>(tiles + (size_t)(warp * 2 + b) * kTileBytes);
+        const uint32_t tile_lane_addr = smem_u32(my_tile + lane);
+        const uint2 sd = side[(warp * 2 + b) * 32 + lane];
+        const int rule = (int)sd.x;
+        const unsigned flags = sd.y & 0x7FFFFFFFu;
+        const bool valid = (sd.y >> 31) != 0;
+        double ml = 0.0;
+        if (model_kind == IGS_MODEL_MOCK) {
+            ml = mock_predict<true>(my_tile + lane);
+        } else if (model_kind == IGS_MODEL_GBDT) {
+            float margin = p.base_score;
+            for (unsigned c = 0; c < n_chunks; ++c, ++g) {
+                const unsigned cb = (unsigned)(g & 1);
+                const int trees = (int)min((unsigned)kChunkTrees, p.n_trees - c * kChunkTrees);
+                mbar_wait(bar_chunk + 8 * cb, (uint32_t)((g >> 1) & 1));
+                walk_chunk<false, S::kIlp>(chunk_addr + cb * kChunkBytes, trees, tile_lane_addr, &margin, nullptr);
+                asm volatile("bar.sync 1, %0;" ::"n"(W * 32) : "memory");   // every walker is done with buffer cb
+                if (threadIdx.x == 0 && g + 2 < total_chunks) issue(g + 2);
+            }
+            float y = p.post == IGS_POST_LOGISTIC ? igs_sigmoid(margin) : margin;
+            if (y < 0.f) y = 0.f;                                   // ml/onnx_model.go:247-252
+            if (y > 1.f) y = 1.f;
+            ml = (double)y;                                         // float64(result) :254
+        }
+        if (model_kind != IGS_MODEL_NONE && !valid) ml = 0.5;      // scoring/engine.go:279-282
+        if (in_range) {
+            igs_result r;
+            igs_blend(p.cfg, rule, flags, ml, model_kind != IGS_MODEL_NONE, &r);
+            p.out[row] = r;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8 * (warp * 2 + b));     // the producer may refill this half
+    }
+}
+
 }  // namespace
 
 template <typename S>
@@ -530,6 +701,7 @@ static void fill_common(igs_engine* e, const igs_config* cfg, ScoreParams* p) {
     memset(p, 0, sizeof(*p));
     p->cfg = *cfg;
     p->model = e->d_model;
+    p->model_ws = e->d_model_ws;
     p->n_trees = e->has_gbdt ? e->n_trees : 0;
     p->base_score = e->base_score;
     p->post = e->post_transform;
@@ -607,6 +779,32 @@ static int visit_order(igs_engine* e, const igs_tx* d_tx, uint32_t n, uint32_t n
     return IGS_OK;
 }
 
+// Large fused batches that want nothing but the results go through the warp-specialised kernel; the rest (latency-
+// sized batches, calls that also return the assembled features or the velocity blocks) through k_score.
+template <typename S>
+static int launch_ws(igs_engine* e, const ScoreParams& p, cudaStream_t stream) {
+    auto kern = k_score_ws<S>;
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kSmemBytes));
+    const unsigned long long n_tiles = (p.n + S::kTileTx - 1) / S::kTileTx;
+    const unsigned grid = (unsigned)(n_tiles < (unsigned long long)e->sm_count ? n_tiles : (unsigned long long)e->sm_count);
+    kern<<<grid, S::kThreads, S::kSmemBytes, stream>>>(p);
+    IGS_LAUNCHED(e);
+    return IGS_OK;
+}
+static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
+    static const int ws = getenv("IGS_SCORE_WS") ? atoi(getenv("IGS_SCORE_WS")) : 1;      // tuning knob: 0 = never
+    const bool eligible = ws != 0 && p.features_out == nullptr && p.velocity_out == nullptr &&
+                          p.n > (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx &&
+                          (p.cfg.model_kind != IGS_MODEL_GBDT || e->d_model_ws != nullptr);
+    if (!eligible) return launch(e, kSrcTx, p, false, stream);
+    p.model = p.model_ws ? p.model_ws : p.model;
+    // 16 walkers + 4 producers (640 threads, ~100 registers each).  Measured alternatives, 1M tx against 500k players
+    // and a 5M-event index, ms per batch with / without the visit-order sort (k_score: 1.757 / 1.959):
+    //   16 + 4: 1.671 / 1.749     16 + 6: 1.725 / 1.797     16 + 8: 1.774 / 1.908 (80 registers: the walk spills)
+    //   12 + 8: 1.695 / 1.722     16 + 8 re-balanced with setmaxnreg (96 / 64): never finished — removed
+    return launch_ws<WsShape<16, 4, 10, 5>>(e, p, stream);
+}
+
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
                            cudaStream_t stream) {
@@ -633,7 +831,7 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
         rc = visit_order(e, d_tx, (uint32_t)n, rd.view.base.n_accounts, std::min(visit_passes, 4), stream, &scratch, &p.perm);
         if (rc != IGS_OK) { if (scratch) cudaFreeAsync(scratch, stream); return rc; }
     }
-    rc = launch(e, kSrcTx, p, false, stream);
+    rc = launch_fused(e, p, stream);
     if (rc == IGS_OK) rd.done(stream);
     if (scratch) cudaFreeAsync(scratch, stream);
     return rc;
