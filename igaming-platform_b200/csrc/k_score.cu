@@ -263,7 +263,8 @@ __device__ __forceinline__ void assemble_tx(const ScoreParams& p, unsigned long 
 #pragma unroll
         for (int k = 0; k < (int)(sizeof(igs_velocity) / 16); ++k) dst[k] = vb.q[k];
     }
-    // BatchFeatures row (GetBatchFeatures, scoring/engine.go:362); absent -> zero features (:363-366)
+    // BatchFeatures row (GetBatchFeatures, scoring/engine.go:362); absent -> zero features (:363-366).  (Requesting it
+    // before the lookup would hide one round trip but keeps 24 registers alive across it: measured slower.)
     const bool have_player = in_range && (unsigned long long)t.account < p.n_players;
     union __align__(16) { igs_player_row r; uint4 q[sizeof(igs_player_row) / 16]; } pl;
     {
@@ -502,9 +503,15 @@ k_score(const __grid_constant__ ScoreParams p) {
 // more producer warps would feed the walkers better but push the walk into spills (see launch_fused).
 // ------------------------------------------------------------------------------------------------------------
 constexpr int kWsRows = IGS_WS_ROWS;
-template <int W, int P, int C, int I>
+template <int W, int P, int C, int I, int RW = 0, int RP = 0>
 struct WsShape {
     static constexpr int kWalkers = W, kProducers = P, kIlp = I, kChunkTrees = C;
+    // setmaxnreg targets (0 = leave as compiled).  A CTA never holds more registers than it was launched with: the
+    // walkers can only take what the producers have given back (an inc beyond that waits forever).
+    static constexpr int kRegsWalker = RW, kRegsProducer = RP;
+    static constexpr int kRegsLaunch = (65536 / ((W + P) * 32)) / 8 * 8;
+    static_assert(RW == 0 || (W % 4 == 0 && P % 4 == 0), "setmaxnreg works on warpgroups of four warps");
+    static_assert(RW == 0 || W * (RW - kRegsLaunch) <= P * (kRegsLaunch - RP), "the walkers' increase must fit the producers' decrease");
     static constexpr int kThreads = (W + P) * 32;
     static constexpr int kTileTx = W * 32;
     static constexpr int kTileBytes = kWsRows * 32 * 4;                 // 5 120
@@ -563,6 +570,7 @@ k_score_ws(const __grid_constant__ ScoreParams p) {
 
     if (warp >= W) {
         // ---------------- producers: lookup + assembly + rules for the walkers w = pw, pw + P, ... ----------------
+        if (S::kRegsProducer) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(S::kRegsProducer ? S::kRegsProducer : 24));
         const int pw = warp - W;
         for (unsigned long long k = 0; k < my_tiles; ++k) {
             const unsigned long long tile = blockIdx.x + k * gridDim.x;
@@ -588,6 +596,7 @@ k_score_ws(const __grid_constant__ ScoreParams p) {
     }
 
     // ---------------- walkers -------------------------------------------------------------------------------------
+    if (S::kRegsWalker) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(S::kRegsWalker ? S::kRegsWalker : 24));
     const unsigned long long total_chunks = use_gbdt ? my_tiles * n_chunks : 0;
     auto issue = [&](unsigned long long g) {   // g-th chunk of this CTA's sequence; thread 0 only
         const unsigned c = (unsigned)(g % n_chunks);
@@ -801,7 +810,8 @@ static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
     // 16 walkers + 4 producers (640 threads, ~100 registers each).  Measured alternatives, 1M tx against 500k players
     // and a 5M-event index, ms per batch with / without the visit-order sort (k_score: 1.757 / 1.959):
     //   16 + 4: 1.671 / 1.749     16 + 6: 1.725 / 1.797     16 + 8: 1.774 / 1.908 (80 registers: the walk spills)
-    //   12 + 8: 1.695 / 1.722     16 + 8 re-balanced with setmaxnreg (96 / 64): never finished — removed
+    //   12 + 8: 1.695 / 1.722
+    //   16 + 8 re-balanced with setmaxnreg (walkers 96 / producers 48 registers): 1.731 / 1.874 — the producers spill
     return launch_ws<WsShape<16, 4, 10, 5>>(e, p, stream);
 }
 
