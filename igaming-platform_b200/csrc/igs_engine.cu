@@ -413,7 +413,7 @@ constexpr uint64_t kPipeChunkRowsB = 128 * 1024;
 template <typename Body>
 static int run_pipelined(igs_engine* e, igs_slot& sl, uint64_t n, uint64_t kPipeChunkRows,
                          Body&& body /* (stream, off, cnt) -> int */) {
-    if (n <= 2 * kPipeChunkRows) return body(sl.stream, (uint64_t)0, n);
+    if (n < 2 * kPipeChunkRows) return body(sl.stream, (uint64_t)0, n);
     IGS_CUDA(e, cudaEventRecord(sl.ev_fork, sl.stream));
     for (int k = 0; k < IGS_PIPE_STREAMS; ++k) IGS_CUDA(e, cudaStreamWaitEvent(sl.pipe[k], sl.ev_fork, 0));
     int k = 0, rc = IGS_OK;
@@ -545,12 +545,25 @@ int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs
 // ------------------------------------------------------------------------------------------------
 // path B
 // ------------------------------------------------------------------------------------------------
+// pinned host memory that the device can address through the same pointer (cudaHostAlloc / igs_alloc_pinned under UVA)
+static bool host_mapped(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost && a.devicePointer == p;
+}
+
 static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const igs_tx* tx, const igs_tx_ids* ids,
                             uint64_t n, igs_result* out, float* features_out, igs_velocity* velocity_out) {
     IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
     IGS_REQUIRE(e, n == 0 || (tx && out), "tx / out is null");
     if (n == 0) return IGS_OK;
     igs_slot& sl = e->slot[s];
+    // Large batches in pinned (mapped) host buffers are not staged: the warp-specialised kernel's producer warps read
+    // the 32-byte records over PCIe as they go and the walkers write the 8-byte results back the same way — 40 B/tx
+    // at ~0.6e9 tx/s is a third of the link, and no copy has to finish before the first tile starts.
+    if (!features_out && !velocity_out && igs_fused_direct_eligible(e, n) && host_mapped(tx) && host_mapped(out) &&
+        (!ids || host_mapped(ids)))
+        return igs_launch_score_batch(e, cfg, tx, ids, n, out, nullptr, nullptr, sl.stream, true);
     IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_tx)));
     if (ids) IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_tx_ids)));
     igs_tx_ids* d_ids = ids ? (igs_tx_ids*)sl.in1.p : nullptr;
@@ -561,7 +574,12 @@ static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const i
     igs_result* d_out = (igs_result*)sl.out0.p;
     float* d_feat = features_out ? (float*)sl.aux0.p : nullptr;
     igs_velocity* d_vel = velocity_out ? (igs_velocity*)sl.aux1.p : nullptr;
-    return run_pipelined(e, sl, n, kPipeChunkRowsB, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
+    // Chunks large enough for the warp-specialised kernel (>= 4 tiles of 512 tx per SM, k_score.cu) and equal in size:
+    // 1M tx on 148 SMs = three chunks of 333 334 rows.
+    const uint64_t ws_rows = 4ull * (uint64_t)e->sm_count * 512ull;
+    const uint64_t pieces = std::max<uint64_t>(1, n / (ws_rows + ws_rows / 16));
+    const uint64_t chunk_rows = std::max<uint64_t>(kPipeChunkRowsB, (n + pieces - 1) / pieces);
+    return run_pipelined(e, sl, n, chunk_rows, [&](cudaStream_t st, uint64_t off, uint64_t cnt) -> int {
         IGS_CUDA(e, cudaMemcpyAsync(d_tx + off, tx + off, cnt * sizeof(igs_tx), cudaMemcpyHostToDevice, st));
         if (ids)
             IGS_CUDA(e, cudaMemcpyAsync(d_ids + off, ids + off, cnt * sizeof(igs_tx_ids), cudaMemcpyHostToDevice, st));

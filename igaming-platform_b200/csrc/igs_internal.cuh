@@ -198,9 +198,11 @@ int igs_reserve(igs_engine* e, igs_buf* b, size_t bytes);
 int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float* d_features,
                               const igs_rule_row* d_rows, uint64_t n, igs_result* d_out,
                               uint8_t* d_leaf_idx, cudaStream_t stream);
+// tx_over_pcie: d_tx / d_ids / d_out are mapped host memory — read each record once (no visit-order sort)
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
-                           cudaStream_t stream);
+                           cudaStream_t stream, bool tx_over_pcie = false);
+bool igs_fused_direct_eligible(const igs_engine* e, uint64_t n);
 int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
                         cudaStream_t stream);
 int igs_launch_uniques(igs_engine* e, const igs_query* d_q, uint64_t n, igs_uniques* d_out, cudaStream_t stream);

@@ -802,8 +802,10 @@ static int launch_ws(igs_engine* e, const ScoreParams& p, cudaStream_t stream) {
 }
 static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
     static const int ws = getenv("IGS_SCORE_WS") ? atoi(getenv("IGS_SCORE_WS")) : 1;      // tuning knob: 0 = never
+    // at least four tiles per SM: with fewer the producers' head start on the first tile and the drain of the last
+    // are not amortised (the 131 072-row chunks of a host-buffer call were measured slower through this kernel)
     const bool eligible = ws != 0 && p.features_out == nullptr && p.velocity_out == nullptr &&
-                          p.n > (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx &&
+                          p.n >= 4ull * (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx &&
                           (p.cfg.model_kind != IGS_MODEL_GBDT || e->d_model_ws != nullptr);
     if (!eligible) return launch(e, kSrcTx, p, false, stream);
     p.model = p.model_ws ? p.model_ws : p.model;
@@ -815,9 +817,17 @@ static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
     return launch_ws<WsShape<16, 4, 10, 5>>(e, p, stream);
 }
 
+// batches the warp-specialised kernel takes (launch_fused) — the host-buffer call reads such batches straight from
+// pinned host memory instead of staging them
+bool igs_fused_direct_eligible(const igs_engine* e, uint64_t n) {
+    static const int ws = getenv("IGS_SCORE_WS") ? atoi(getenv("IGS_SCORE_WS")) : 1;
+    static const int direct = getenv("IGS_SCORE_DIRECT") ? atoi(getenv("IGS_SCORE_DIRECT")) : 1;   // tuning knob: 0 = always stage
+    return ws != 0 && direct != 0 && n >= 4ull * (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx;
+}
+
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, bool tx_over_pcie) {
     if (n == 0) return IGS_OK;
     int rc = check_model(e, cfg);
     if (rc != IGS_OK) return rc;
@@ -837,7 +847,7 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     p.n = n;
     static const int visit_passes = getenv("IGS_VISIT_SORT_PASSES") ? atoi(getenv("IGS_VISIT_SORT_PASSES")) : 3;   // tuning knob (0 = off)
     void* scratch = nullptr;
-    if (visit_passes > 0 && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
+    if (visit_passes > 0 && !tx_over_pcie && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
         rc = visit_order(e, d_tx, (uint32_t)n, rd.view.base.n_accounts, std::min(visit_passes, 4), stream, &scratch, &p.perm);
         if (rc != IGS_OK) { if (scratch) cudaFreeAsync(scratch, stream); return rc; }
     }

@@ -465,6 +465,10 @@ int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs
  * applyRules (:420-483), the model and the blend (:284-310) all run on the device against the
  * loaded players / events / model.  features_out (optional, may be NULL) receives the n x 64
  * assembled model input, velocity_out (optional) the n velocity blocks.                         */
+/* Host buffers.  Pageable memory is staged through the slot's device buffers in chunks (copy, kernel and copy
+ * back overlap).  Large batches (>= 4 x 512 tx per SM) whose tx / out (/ ids) buffers come from igs_alloc_pinned
+ * and that ask for the results only are not staged at all: the kernel reads the records from, and writes the
+ * results to, the pinned host memory directly over PCIe.                                              */
 int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n,
                     igs_result* out, float* features_out, igs_velocity* velocity_out);
 int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const igs_tx* tx,

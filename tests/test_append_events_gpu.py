@@ -237,7 +237,7 @@ def test_append_overlaps_scoring_on_another_stream(engine, orc, pkg):
     engine.load_gbdt(model)
     engine.load_events(cut(ev, 0, n0, pkg), n_acc)
     cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
-    m = 300_000                                               # large enough to still be running when the append starts
+    m = 320_000                                               # large enough to still be running when the append starts (and for k_score_ws)
     tx = synth.make_tx(m, n_acc, seed=94, t_lo=int(ev.ts[n0 - 1]), t_hi=int(ev.ts[-1]) + 100)
     dev = torch.device("cuda", 0)
     d_tx = torch.from_numpy(tx.view(np.uint8).reshape(m, -1)).to(dev)

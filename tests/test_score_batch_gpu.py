@@ -133,3 +133,35 @@ def test_c1_reference_config_mock_model(engine, orc, pkg):
     types = np.bincount(tx["tx_type"], minlength=3) / n
     assert abs(types[abi.TX_BET] - 0.7) < 0.01 and abs(types[abi.TX_DEPOSIT] - 0.2) < 0.01
     assert len(np.unique(want["action"])) >= 2 and (want["flags"] & abi.R_HIGH_VELOCITY).any()
+
+
+@pytest.mark.parametrize("kind", ["none", "mock", "gbdt"])
+def test_large_batches_take_the_warp_specialised_kernel(engine, orc, pkg, kind):
+    """Batches of at least 4 x 148 x 512 tx that want only the results run through k_score_ws (producer warps look up and
+    assemble, walker warps walk the trees; the model image with compacted feature rows).  Ragged size, rows from
+    unknown accounts, invalid rows, a model that splits on every feature index incl. the constant-zero ones, all three
+    model kinds — bit-identical to the per-request restatement, and to k_score (which serves the same call when the
+    assembled features are requested too)."""
+    abi = pkg.abi
+    n_players, n_events, n = 3000, 60000, 4 * 148 * 512 + 4321
+    now = synth.T0 + 6 * 3600
+    players = synth.make_players(n_players, seed=105, now=now)
+    ev = synth.make_events(n_events, n_players, seed=106, span=6 * 3600, collision_rate=0.03)
+    tx = synth.make_tx(n, n_players, seed=107, t_lo=synth.T0 + 3600, t_hi=now, invalid_rate=0.02)
+    tx["account"][::1013] = n_players + 5
+    engine.load_players(players)
+    engine.load_events(ev, n_players)
+    model = None
+    if kind == "gbdt":
+        model = synth.make_gbdt(n_trees=57, seed=108)          # 5 full chunks of 10 trees + a ragged one
+        model.feat[:, ::3] = np.array([7, 8, 22, 42, 63, 50, 41, 0, 6, 9, 21, 23], dtype=np.uint8)[
+            np.arange(model.feat[:, ::3].size).reshape(model.feat[:, ::3].shape) % 12]
+        engine.load_gbdt(model)
+    cfg = pkg.default_config(model_kind={"none": abi.MODEL_NONE, "mock": abi.MODEL_MOCK, "gbdt": abi.MODEL_GBDT}[kind])
+    got = engine.score_batch(cfg, tx)                                          # k_score_ws
+    via_k_score, _, _ = engine.score_batch(cfg, tx, want_features=True)        # k_score
+    assert got.tobytes() == via_k_score.tobytes()
+    pick = np.concatenate([np.arange(0, 3000), np.arange(n - 3000, n)])
+    want = orc.score_batch(cfg, model, players, ev, np.ascontiguousarray(tx[pick]))
+    assert got[pick].tobytes() == want.tobytes()
+    assert len(np.unique(got["score"])) >= 3                  # (model nil: 0.4 x rule score never reaches review)
