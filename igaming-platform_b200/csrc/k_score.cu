@@ -744,6 +744,9 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
 // (Host-buffer calls arrive here in 131 072-row chunks, below this threshold: sorting them was measured and costs
 // more than it saves end to end — 2.03 -> 2.17 ms per 1M tx through igs_score_batch.)
 constexpr unsigned long long kVisitSortMin = 262144;
+// (A counting sort with an atomic cursor per account — the visit order need not be stable — was measured: the hot
+// account's ~30 000 same-address atomics per kernel make it slower than the radix passes, 1.67 -> 1.86 ms per 1M tx;
+// grouping by buckets of 16 accounts instead of by account: 1.95 ms, worse than no grouping.)
 // key = [account (top bits) | row]: sorted on the account bits by the one-sweep radix sort (onesweep.cuh); the row
 // rides in the low word and is what the score kernel reads back.  The key pass also fills the digit histograms.
 __global__ void __launch_bounds__(kOsThreads)
