@@ -47,8 +47,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// bounded: a hand-over that never comes is a bug (a lost arrive between the CTAs of a pair, say), and a trap beats a hung GPU
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
+    uint32_t ok, spins = 0;
     do {
         asm volatile(
             "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
@@ -56,6 +57,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "=r"(ok)
             : "r"(bar), "r"(parity)
             : "memory");
+        if (!ok && ++spins > (1u << 26)) __trap();
     } while (!ok);
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar) {
@@ -63,6 +65,31 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
+}
+// The load of one CTA of a pair (`cta_group::2`): data into this CTA's shared memory, the bytes credited to a barrier
+// that may live in the pair's other CTA (`bar` is a shared::cluster address, see mapa_rank0).
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA 0 of the cluster
+__device__ __forceinline__ uint32_t mapa_rank0(uint32_t addr) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(r) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t src, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -77,6 +104,22 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// pair form: arrives on the barrier at this offset in both CTAs once the pair's MMAs issued so far have retired
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)0x3)
+                 : "memory");
+}
+// one MMA across the pair: D rows 0-127 in CTA 0's TMEM, 128-255 in CTA 1's; A from each CTA's own shared memory,
+// B's N rows split between them (descriptors are offsets, the same in both CTAs); issued by CTA 0 only
+__device__ __forceinline__ void tc_mma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+        " tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 __device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                            uint32_t accumulate) {
@@ -110,18 +153,22 @@ constexpr uint32_t kSwizzleBytes = BK * 2;          // one k-block row = one swi
 constexpr int kNonEpiWarps = 4;   // TMA producer, MMA issuer, TMEM allocator, spare
 constexpr uint32_t kABytes = BM * BK * 2;     // 16 KB
 constexpr uint32_t kBBytes = BN * BK * 2;     // 32 KB
-constexpr uint32_t kStageBytes = kABytes + kBBytes;
 constexpr uint32_t kTmemCols = 512;           // 2 accumulators x 256 fp32 columns
 // output staging for the TMA store: the bf16 tile as 64-column x 32-row boxes (4 KB, 128B-swizzled), one set per
 // epilogue warp — 128 x 256 x 2 B = 64 KB.  (Three smem stages feed the MMAs as well as four did: the fourth
 // stage's 48 KB went here.)
 constexpr uint32_t kOutBoxCols = 64, kOutBoxRows = 32, kOutBoxBytes = kOutBoxCols * kOutBoxRows * 2;
 constexpr uint32_t kOutStageBytes = BM * BN * 2;
-constexpr uint32_t kGemmSmem = STAGES * kStageBytes + kOutStageBytes + 1024 /* alignment slack */ + 256 /* barriers */ +
-                               4096 /* w4 as fp32 */ + 4096 /* bias */;
+// a CTA of a pair (kCl = 2) keeps half of the W k-block, so a fourth stage fits
+__host__ __device__ constexpr int gemm_stages(int cl) { return cl == 2 ? 4 : STAGES; }
+__host__ __device__ constexpr uint32_t gemm_stage_bytes(int cl) { return kABytes + kBBytes / (uint32_t)cl; }
+__host__ __device__ constexpr uint32_t gemm_smem(int cl) {
+    return (uint32_t)gemm_stages(cl) * gemm_stage_bytes(cl) + kOutStageBytes + 1024 /* alignment slack */ + 256 /* barriers */ +
+           4096 /* w4 as fp32 */ + 4096 /* bias */;
+}
 // instruction descriptor, kind::f16: D=F32 (bit 4), A=BF16 (bit 7), B=BF16 (bit 10), both K-major,
 // N>>3 at bit 17, M>>4 at bit 24
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc(int m) { return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(m >> 4) << 24); }
 // smem matrix descriptor (K-major, SWIZZLE_128B): LBO = 1 (unused for swizzled K-major), SBO = 1024 B
 // between 8-row groups, descriptor version 1 (sm_100), layout type 2
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
@@ -134,6 +181,7 @@ struct GemmParams {
     CUtensorMap tm_a;     // A  [M, K] bf16, K contiguous; box 64 x 128
     CUtensorMap tm_b;     // W  [N, K] bf16, K contiguous; box 64 x 256
     CUtensorMap tm_out;   // out [M, N] bf16; box 64 x 32 (store)
+    CUtensorMap tm_bh;    // W again, box 64 x 128: the half of a W k-block one CTA of a pair loads (kCl == 2)
     const float* bias;    // [N]
     uint16_t* out;        // [M, N] bf16 (null when the head is fused and nobody wants the activations)
     uint32_t M, N, K;
@@ -152,7 +200,12 @@ struct GemmParams {
 // kEpiWarps = 4: one epilogue warp per TMEM lane quarter, all 256 columns each.
 // kEpiWarps = 8: two per quarter, 128 columns each — for the K=256 layer, whose MMAs per tile are too short
 //               to hide a 4-warp epilogue.
-template <bool kHead, int kEpiWarps>
+// kCl = 2: CTA pairs (a cluster of two = the two SMs of a TPC) on 256 x 256 tiles with `cta_group::2` MMAs.  CTA r of
+// the pair owns rows r*128.. of the tile: it loads those rows of A and rows r*128.. of the W k-block (HALF of it), the
+// accumulator rows sit in its own TMEM, and its epilogue warps drain them.  CTA 0 issues the MMAs for both; the TMA
+// loads of both CTAs credit CTA 0's `bar_full`; the commits that free a stage / publish an accumulator arrive in both
+// CTAs; both CTAs' epilogue warps arrive on CTA 0's `bar_tempty`.  Per MMA each SM takes 32 KB from L2 instead of 48.
+template <bool kHead, int kEpiWarps, int kCl>
 __global__ void __launch_bounds__((kNonEpiWarps + kEpiWarps) * 32, 1)
 k_mlp_gemm(const __grid_constant__ GemmParams p) {
     constexpr int kGemmThreads = (kNonEpiWarps + kEpiWarps) * 32;
@@ -162,16 +215,20 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (base - raw);
+    constexpr bool kPair = kCl == 2;
+    constexpr int kStages = gemm_stages(kCl);
+    constexpr uint32_t kBStage = kBBytes / kCl, kStage = gemm_stage_bytes(kCl);
+    constexpr uint32_t kIdesc = make_idesc(BM * kCl);
     const uint32_t a_base = base;
-    const uint32_t b_base = base + STAGES * kABytes;
-    const uint32_t out_base = base + STAGES * kStageBytes;          // 1024-aligned: stages are multiples of 1 KB
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes + kOutStageBytes);
-    const uint32_t bar_full = smem_u32(bars);             // [STAGES]
-    const uint32_t bar_empty = bar_full + 8 * STAGES;     // [STAGES]
-    const uint32_t bar_tfull = bar_empty + 8 * STAGES;    // [2]
+    const uint32_t b_base = base + kStages * kABytes;
+    const uint32_t out_base = base + kStages * kStage;              // 1024-aligned: stages are multiples of 1 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStage + kOutStageBytes);
+    const uint32_t bar_full = smem_u32(bars);             // [kStages]
+    const uint32_t bar_empty = bar_full + 8 * kStages;    // [kStages]
+    const uint32_t bar_tfull = bar_empty + 8 * kStages;   // [2]
     const uint32_t bar_tempty = bar_tfull + 16;           // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-    float* w4s = reinterpret_cast<float*>(smem + STAGES * kStageBytes + kOutStageBytes + 256);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+    float* w4s = reinterpret_cast<float*>(smem + kStages * kStage + kOutStageBytes + 256);
     float* bias_s = w4s + IGS_MLP_HIDDEN;
     if (kHead)
         for (int i = threadIdx.x; i < IGS_MLP_HIDDEN; i += kGemmThreads) w4s[i] = bf16_bits_to_f32(__ldg(p.w4 + i));
@@ -179,67 +236,98 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, kEpiWarps); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, kEpiWarps * kCl); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (warp == 2) {                              // with pairs: one warp of EACH CTA, collectively
+        if (kPair) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                         "r"(kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();                   // the peer's barriers and TMEM exist before anything touches them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // With pairs, the unit of scheduling is the pair: `unit` / `n_units` replace blockIdx.x / gridDim.x, a row tile
+    // of the plain kernel becomes a pair of row tiles (this CTA takes the one of its rank), and row tiles past the
+    // end (odd count) are computed on zero-filled loads and never stored.
+    const uint32_t rank = kCl > 1 ? cluster_ctarank() : 0u;
+    const uint32_t unit = blockIdx.x / kCl, n_units = gridDim.x / kCl;
     const uint32_t m_blks = (p.M + BM - 1) / BM, n_blks = p.N / BN, k_blks = p.K / BK;
-    const uint32_t n_tiles = m_blks * n_blks;
-    // i-th work tile of this CTA -> global tile index (m-major: tile / n_blks = row tile)
-    const uint32_t my_tiles = kHead ? (m_blks > blockIdx.x ? (m_blks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0) * n_blks
-                                    : (n_tiles > blockIdx.x ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0);
-    auto tile_of = [&](uint32_t i) -> uint32_t {
-        return kHead ? (blockIdx.x + (i / n_blks) * gridDim.x) * n_blks + i % n_blks : blockIdx.x + i * gridDim.x;
+    const uint32_t m_grps = (m_blks + kCl - 1) / kCl;
+    const uint32_t n_tiles = m_grps * n_blks;
+    // i-th work tile of this CTA -> tile index in units of (row-tile group, column tile), m-major
+    const uint32_t my_tiles = kHead ? (m_grps > unit ? (m_grps - unit + n_units - 1) / n_units : 0) * n_blks
+                                    : (n_tiles > unit ? (n_tiles - unit + n_units - 1) / n_units : 0);
+    auto tile_of = [&](uint32_t i) -> uint32_t {     // returns (row tile of THIS CTA) * n_blks + column tile
+        const uint32_t g = kHead ? (unit + (i / n_blks) * n_units) * n_blks + i % n_blks : unit + i * n_units;
+        return ((g / n_blks) * kCl + rank) * n_blks + g % n_blks;
     };
 
     if (warp == 0) {
         if (lane == 0) {
+            // pairs: every load of either CTA credits CTA 0's bar_full, which expects both CTAs' stages
+            const uint32_t full0 = kPair ? mapa_rank0(bar_full) : bar_full;
             uint32_t s = 0, ph = 0;
             for (uint32_t i = 0; i < my_tiles; ++i) {
                 const uint32_t t = tile_of(i);
                 const int m0 = (int)(t / n_blks) * BM, n0 = (int)(t % n_blks) * BN;
                 for (uint32_t kb = 0; kb < k_blks; ++kb) {
                     mbar_wait(bar_empty + 8 * s, ph ^ 1);
-                    mbar_expect_tx(bar_full + 8 * s, kStageBytes);
-                    tma_load_2d(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, bar_full + 8 * s);
-                    tma_load_2d(b_base + s * kBBytes, &p.tm_b, (int)(kb * BK), n0, bar_full + 8 * s);
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                    if (!kPair) {
+                        mbar_expect_tx(bar_full + 8 * s, kStage);
+                        tma_load_2d(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, bar_full + 8 * s);
+                        tma_load_2d(b_base + s * kBStage, &p.tm_b, (int)(kb * BK), n0, bar_full + 8 * s);
+                    } else {
+                        if (rank == 0) mbar_expect_tx(bar_full + 8 * s, 2 * kStage);
+                        tma_load_2d_pair(a_base + s * kABytes, &p.tm_a, (int)(kb * BK), m0, full0 + 8 * s);
+                        tma_load_2d_pair(b_base + s * kBStage, &p.tm_bh, (int)(kb * BK), n0 + (int)rank * (BN / 2),
+                                         full0 + 8 * s);
+                    }
+                    if (++s == kStages) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (lane == 0 && rank == 0) {
             uint32_t s = 0, ph = 0, it = 0;
             for (; it < my_tiles; ++it) {
                 const uint32_t acc = it & 1;
-                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue drained this accumulator
+                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue (of both CTAs) drained this accumulator
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
                 for (uint32_t kb = 0; kb < k_blks; ++kb) {
                     mbar_wait(bar_full + 8 * s, ph);
                     tc_fence_after();
                     const uint64_t adesc = make_desc(a_base + s * kABytes);
-                    const uint64_t bdesc = make_desc(b_base + s * kBBytes);
+                    const uint64_t bdesc = make_desc(b_base + s * kBStage);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k)
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
                         // +32 bytes (2 x 16 B units) per K step inside the 128B swizzle atom
-                        tc_mma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
-                                   (kb | (uint32_t)k) != 0 ? 1u : 0u);
-                    tc_commit(bar_empty + 8 * s);                          // frees the smem stage when the MMAs retire
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                        if (kPair)
+                            tc_mma_f16_pair(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
+                                            (kb | (uint32_t)k) != 0 ? 1u : 0u);
+                        else
+                            tc_mma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), kIdesc,
+                                       (kb | (uint32_t)k) != 0 ? 1u : 0u);
+                    }
+                    if (kPair) tc_commit_pair(bar_empty + 8 * s);          // frees the smem stage (in both CTAs) when the MMAs retire
+                    else tc_commit(bar_empty + 8 * s);
+                    if (++s == kStages) { s = 0; ph ^= 1; }
                 }
-                tc_commit(bar_tfull + 8 * acc);                            // accumulator complete
+                if (kPair) tc_commit_pair(bar_tfull + 8 * acc);            // accumulator complete
+                else tc_commit(bar_tfull + 8 * acc);
             }
         }
     } else if (warp >= 4) {
@@ -297,7 +385,10 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+            if (lane == 0) {
+                if (kPair && rank != 0) mbar_arrive_cluster(mapa_rank0(bar_tempty + 8 * acc));
+                else mbar_arrive(bar_tempty + 8 * acc);
+            }
             if (store) {                                                   // whole lines to global, off the LSU path
                 fence_async_smem();
                 __syncwarp();
@@ -325,9 +416,13 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
     if (warp >= kNonEpiWarps && lane == 0) bulk_wait0();                   // outstanding output stores
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();                   // the peer may still be signalling this CTA's barriers / using its TMEM
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+        if (kPair)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
     }
 }
 
@@ -405,12 +500,40 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
     if (head) { p.w4 = head->w4; p.b4 = head->b4; p.rows = head->rows; p.res = head->res; p.raw = head->raw; }
     // the short-K layer gets 8 epilogue warps; long-K layers hide a 4-warp epilogue behind their MMAs
     const bool wide_epi = !head && K <= 256;
-    auto kern = head ? k_mlp_gemm<true, 4> : wide_epi ? k_mlp_gemm<false, 8> : k_mlp_gemm<false, 4>;
+    static const int pairs_knob = getenv("IGS_MLP_PAIRS") ? atoi(getenv("IGS_MLP_PAIRS")) : 1;   // tuning knob: 0 = no CTA pairs
+    const uint32_t m_blks = (M + BM - 1) / BM;
+    const bool pairs = pairs_knob != 0 && m_blks >= 2 * (uint32_t)e->sm_count;     // large M only: small ones gain nothing
     const int threads = (kNonEpiWarps + (wide_epi ? 8 : 4)) * 32;
-    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
-    const uint32_t items = head ? (M + BM - 1) / BM : ((M + BM - 1) / BM) * (N / BN);
-    const uint32_t grid = items < (uint32_t)e->sm_count ? items : (uint32_t)e->sm_count;
-    kern<<<grid, threads, kGemmSmem, st>>>(p);
+    if (!pairs) {
+        auto kern = head ? k_mlp_gemm<true, 4, 1> : wide_epi ? k_mlp_gemm<false, 8, 1> : k_mlp_gemm<false, 4, 1>;
+        IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem(1)));
+        const uint32_t items = head ? m_blks : m_blks * (N / BN);
+        const uint32_t grid = items < (uint32_t)e->sm_count ? items : (uint32_t)e->sm_count;
+        kern<<<grid, threads, gemm_smem(1), st>>>(p);
+        IGS_LAUNCHED(e);
+        return IGS_OK;
+    }
+    rc = make_tmap(e, &p.tm_bh, w, N, K, BN / 2);
+    if (rc != IGS_OK) return rc;
+    auto kern = head ? k_mlp_gemm<true, 4, 2> : wide_epi ? k_mlp_gemm<false, 8, 2> : k_mlp_gemm<false, 4, 2>;
+    IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem(2)));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(e->sm_count & ~1), 1, 1);          // whole pairs; every pair has work (m_blks is large)
+    cfg.blockDim = dim3((unsigned)threads, 1, 1);
+    cfg.dynamicSmemBytes = gemm_smem(2);
+    cfg.stream = st;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    // the schedule is static: a pair that does not fit in the first wave would double the run time, so launch exactly
+    // the pairs that are co-resident (a GPC with an odd number of free SMs leaves one out)
+    int max_pairs = 0;
+    IGS_CUDA(e, cudaOccupancyMaxActiveClusters(&max_pairs, kern, &cfg));
+    IGS_REQUIRE(e, max_pairs > 0, "no CTA pair of the MLP kernel fits on this device");
+    if ((unsigned)max_pairs * 2u < cfg.gridDim.x) cfg.gridDim.x = (unsigned)max_pairs * 2u;
+    IGS_CUDA(e, cudaLaunchKernelEx(&cfg, kern, p));
     IGS_LAUNCHED(e);
     return IGS_OK;
 }
