@@ -742,7 +742,7 @@ def main():
                                 "not stage them: the kernel's producer warps read the 32-byte records over PCIe and the "
                                 "results are written back the same way, all inside the timed call"},
             "gpu_launches": gpu_launches,
-            "roofline": {"bound": "hbm", "kernel": "k_score<tx, Shape<8,10,5,2>> (+ the account-order visit sort)",
+            "roofline": {"bound": "hbm", "kernel": "k_score_ws<WsShape<16,4,10,5>> (+ the account-order visit sort)",
                          "achieved": achieved, "peak": ctx.peaks["hbm"], "unit": "GB/s", "frac": achieved / ctx.peaks["hbm"],
                          "traffic": (ncu or {}).get("dram_bytes"), "traffic_source": (ncu or {}).get("source"),
                          "traffic_stale": (ncu or {}).get("stale"), "peak_source": ctx.peaks["src"], "launch_ms": k_ms,

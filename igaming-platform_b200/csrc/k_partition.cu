@@ -25,6 +25,22 @@ __device__ __forceinline__ uint32_t shard_of(uint32_t account, uint32_t n_shards
     return (uint32_t)(x % n_shards);
 }
 
+// one 32-byte record per instruction (LDG.256 / STG.256): a warp reads 1 KB in one request and every store fills its sector
+struct Rec32 { uint32_t w[8]; };
+static_assert(sizeof(igs_tx) == 32 && offsetof(igs_tx, account) == 8, "Rec32.w[2] is igs_tx.account");
+__device__ __forceinline__ Rec32 ld_rec32(const void* p) {
+    Rec32 r;
+    asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_rec32(void* p, const Rec32& r) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"l"(p), "r"(r.w[0]), "r"(r.w[1]), "r"(r.w[2]), "r"(r.w[3]), "r"(r.w[4]), "r"(r.w[5]), "r"(r.w[6]), "r"(r.w[7])
+                 : "memory");
+}
+
 __global__ void __launch_bounds__(kThreads)
 k_part_hist(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards, uint32_t* __restrict__ counts,
             uint32_t nblocks) {
@@ -35,7 +51,10 @@ k_part_hist(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards, uint32
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
         const uint32_t i = base + r * kThreads + threadIdx.x;
-        if (i < n) atomicAdd(&hist[shard_of(__ldg(&tx[i].account), n_shards)], 1u);
+        // one atomic per distinct shard of the warp, not one per lane: with 8 shards 256 lanes hit 8 words
+        const uint32_t sh = i < n ? shard_of(__ldg(&tx[i].account), n_shards) : kMaxShards;
+        const uint32_t peers = __match_any_sync(0xffffffffu, sh);
+        if (i < n && (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) atomicAdd(&hist[sh], (uint32_t)__popc(peers));
     }
     __syncthreads();
     for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) counts[(size_t)s * nblocks + blockIdx.x] = hist[s];
@@ -84,6 +103,8 @@ k_part_scan(uint32_t* __restrict__ counts, uint32_t m, uint32_t n_shards, uint32
     if (threadIdx.x == 0) offsets[n_shards] = n;
 }
 
+// kWide: both record arrays are 32-byte aligned (anything the allocator returns is)
+template <bool kWide>
 __global__ void __launch_bounds__(kThreads)
 k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
                const uint32_t* __restrict__ bases, uint32_t nblocks, igs_tx* __restrict__ tx_out,
@@ -95,12 +116,20 @@ k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
     uint32_t* my_cnt = cnt + warp * n_shards;
     const uint32_t wbase = blockIdx.x * kTile + warp * (kItems * 32);
     uint32_t shard[kItems], rank[kItems];
+    Rec32 rec[kWide ? kItems : 1];
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
         const uint32_t i = wbase + r * 32 + lane;
         const bool valid = i < n;
-        shard[r] = valid ? shard_of(__ldg(&tx[i].account), n_shards) : (kMaxShards + lane);
+        uint32_t account = 0;
+        if (kWide) {
+            if (valid) rec[r] = ld_rec32(tx + i);
+            account = rec[r].w[2];                                         // igs_tx.account: bytes 8..11
+        } else if (valid) {
+            account = __ldg(&tx[i].account);
+        }
+        shard[r] = valid ? shard_of(account, n_shards) : (kMaxShards + lane);
         const uint32_t peers = __match_any_sync(0xffffffffu, shard[r]);
         const uint32_t before = valid ? my_cnt[shard[r]] : 0;
         __syncwarp();
@@ -124,10 +153,14 @@ k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
         const uint32_t i = wbase + r * 32 + lane;
         if (i < n) {
             const uint32_t pos = my_cnt[shard[r]] + rank[r];
-            const uint4* src = reinterpret_cast<const uint4*>(tx + i);
-            uint4* dst = reinterpret_cast<uint4*>(tx_out + pos);
-            dst[0] = __ldg(src + 0);
-            dst[1] = __ldg(src + 1);
+            if (kWide) {
+                st_rec32(tx_out + pos, rec[r]);
+            } else {
+                const uint4* src = reinterpret_cast<const uint4*>(tx + i);
+                uint4* dst = reinterpret_cast<uint4*>(tx_out + pos);
+                dst[0] = __ldg(src + 0);
+                dst[1] = __ldg(src + 1);
+            }
             if (perm) perm[pos] = i;
         }
     }
@@ -148,7 +181,10 @@ int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t 
     IGS_LAUNCHED(e);
     k_part_scan<<<1, kThreads, 0, stream>>>(counts, n_shards * nblocks, n_shards, nblocks, n, d_offsets);
     IGS_LAUNCHED(e);
-    k_part_scatter<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
+    if ((((uintptr_t)d_tx | (uintptr_t)d_tx_out) & 31u) == 0)
+        k_part_scatter<true><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
+    else
+        k_part_scatter<false><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
     IGS_LAUNCHED(e);
     return IGS_OK;
 }
