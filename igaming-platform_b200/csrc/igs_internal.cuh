@@ -104,6 +104,7 @@ struct igs_engine {
     // cudaFreeAsync pair costs microseconds instead of a round trip to the driver, and calls on different streams
     // still get disjoint memory.
     cudaMemPool_t scratch_pool = nullptr;
+    int mlp_max_pairs[3] = {0, 0, 0};   // co-resident CTA pairs of the three k_mlp_gemm pair variants (0 = not asked yet)
 
     // tree ensemble
     uint8_t* d_model = nullptr;   // n_trees * IGS_DEV_TREE_BYTES

@@ -80,8 +80,15 @@ __device__ __forceinline__ uint32_t mapa_rank0(uint32_t addr) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(r) : "r"(addr));
     return r;
 }
+// No memory is published with this arrive (it says "my tcgen05.ld of the accumulator have completed", which
+// tcgen05.wait::ld has already established), so it carries no cluster-scope release: that would cost a fence per arrive.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {        // one lane of a converged warp
+    uint32_t pred;
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
@@ -258,6 +265,10 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
     if (kPair) cluster_sync();                   // the peer's barriers and TMEM exist before anything touches them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // programmatic dependent launch: everything above (barriers, TMEM, the weights' bias / w4 rows) is independent of
+    // the previous launch; its activations are not.  The next launch may begin its own prologue from here on.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     // With pairs, the unit of scheduling is the pair: `unit` / `n_units` replace blockIdx.x / gridDim.x, a row tile
     // of the plain kernel becomes a pair of row tiles (this CTA takes the one of its rank), and row tiles past the
@@ -297,6 +308,40 @@ k_mlp_gemm(const __grid_constant__ GemmParams p) {
                     }
                     if (++s == kStages) { s = 0; ph ^= 1; }
                 }
+            }
+        }
+    } else if (warp == 1 && kPair) {
+        // The issuing thread is the critical path once the data keeps up: 4 MMAs of 128 cycles each per k-block leave
+        // ~500 cycles for everything else it does per k-block.  So: the whole warp runs the loop (no divergent region
+        // around instructions that want uniform operands), the stage index is a compile-time constant (K / 64 is a
+        // multiple of the 4 stages), and a descriptor is one add on a base computed once.
+        if (rank == 0) {
+            const uint64_t adesc0 = make_desc(a_base), bdesc0 = make_desc(b_base);
+            uint32_t ph = 0;
+            for (uint32_t it = 0; it < my_tiles; ++it) {
+                const uint32_t acc = it & 1;
+                mbar_wait(bar_tempty + 8 * acc, ((it >> 1) & 1) ^ 1);     // epilogue (of both CTAs) drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (uint32_t kb = 0; kb < k_blks; kb += kStages) {
+#pragma unroll
+                    for (int s = 0; s < kStages; ++s) {
+                        mbar_wait(bar_full + 8 * s, ph);
+                        tc_fence_after();
+                        if (elect_one()) {
+#pragma unroll
+                            for (int k = 0; k < BK / UMMA_K; ++k)
+                                tc_mma_f16_pair(tmem_d, adesc0 + (uint64_t)(s * (kABytes >> 4) + k * 2),
+                                                bdesc0 + (uint64_t)(s * (kBStage >> 4) + k * 2), kIdesc,
+                                                (kb | (uint32_t)(s | k)) != 0 ? 1u : 0u);
+                            tc_commit_pair(bar_empty + 8 * s);             // frees the smem stage (in both CTAs) when the MMAs retire
+                        }
+                        __syncwarp();
+                    }
+                    ph ^= 1;
+                }
+                if (elect_one()) tc_commit_pair(bar_tfull + 8 * acc);      // accumulator complete
+                __syncwarp();
             }
         }
     } else if (warp == 1) {
@@ -509,7 +554,17 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
         IGS_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem(1)));
         const uint32_t items = head ? m_blks : m_blks * (N / BN);
         const uint32_t grid = items < (uint32_t)e->sm_count ? items : (uint32_t)e->sm_count;
-        kern<<<grid, threads, gemm_smem(1), st>>>(p);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid, 1, 1);
+        cfg.blockDim = dim3((unsigned)threads, 1, 1);
+        cfg.dynamicSmemBytes = gemm_smem(1);
+        cfg.stream = st;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr.val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+        IGS_CUDA(e, cudaLaunchKernelEx(&cfg, kern, p));
         IGS_LAUNCHED(e);
         return IGS_OK;
     }
@@ -522,15 +577,21 @@ int launch_gemm(igs_engine* e, const uint16_t* a, const uint16_t* w, const float
     cfg.blockDim = dim3((unsigned)threads, 1, 1);
     cfg.dynamicSmemBytes = gemm_smem(2);
     cfg.stream = st;
-    cudaLaunchAttribute attr;
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-    cfg.attrs = &attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
     // the schedule is static: a pair that does not fit in the first wave would double the run time, so launch exactly
     // the pairs that are co-resident (a GPC with an odd number of free SMs leaves one out)
-    int max_pairs = 0;
-    IGS_CUDA(e, cudaOccupancyMaxActiveClusters(&max_pairs, kern, &cfg));
+    int& max_pairs = e->mlp_max_pairs[head ? 2 : wide_epi ? 1 : 0];
+    if (max_pairs == 0) {
+        cfg.numAttrs = 1;
+        IGS_CUDA(e, cudaOccupancyMaxActiveClusters(&max_pairs, kern, &cfg));
+        cfg.numAttrs = 2;
+    }
     IGS_REQUIRE(e, max_pairs > 0, "no CTA pair of the MLP kernel fits on this device");
     if ((unsigned)max_pairs * 2u < cfg.gridDim.x) cfg.gridDim.x = (unsigned)max_pairs * 2u;
     IGS_CUDA(e, cudaLaunchKernelEx(&cfg, kern, p));
