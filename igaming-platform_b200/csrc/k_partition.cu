@@ -11,8 +11,8 @@
 
 namespace {
 
-constexpr int kThreads = 256;
-constexpr int kItems = 8;
+constexpr int kThreads = 512;
+constexpr int kItems = 4;
 constexpr int kTile = kThreads * kItems;   // 2048 records per block
 constexpr int kWarps = kThreads / 32;
 constexpr unsigned kMaxShards = 256;
@@ -27,10 +27,11 @@ __device__ __forceinline__ uint32_t shard_of(uint32_t account, uint32_t n_shards
 
 // one 32-byte record per instruction (LDG.256 / STG.256): a warp reads 1 KB in one request and every store fills its sector
 struct Rec32 { uint32_t w[8]; };
+static_assert(kMaxShards <= kThreads, "one thread per shard fetches the block's bases");
 static_assert(sizeof(igs_tx) == 32 && offsetof(igs_tx, account) == 8, "Rec32.w[2] is igs_tx.account");
 __device__ __forceinline__ Rec32 ld_rec32(const void* p) {
     Rec32 r;
-    asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+    asm("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                  : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
                  : "l"(p));
     return r;
@@ -60,52 +61,68 @@ k_part_hist(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards, uint32
     for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) counts[(size_t)s * nblocks + blockIdx.x] = hist[s];
 }
 
-// single block: exclusive scan of counts[0..m) in place (m = n_shards * nblocks), shard offsets out
-__global__ void __launch_bounds__(kThreads)
+// single block: exclusive scan of counts[0..m) in place (m = n_shards * nblocks), shard offsets out.
+// 1024 threads, 16 384 counters per round (~50 000 counters — 8 shards of a 12.5M-tx slice — are three rounds).  A warp
+// owns 512 consecutive counters and reads them as 16 coalesced rows of 32, carrying its running total from row to row.
+constexpr int kScanThreads = 1024, kScanRows = 16, kScanWarps = kScanThreads / 32;
+__global__ void __launch_bounds__(kScanThreads)
 k_part_scan(uint32_t* __restrict__ counts, uint32_t m, uint32_t n_shards, uint32_t nblocks, uint32_t n,
             uint32_t* __restrict__ offsets) {
-    __shared__ uint32_t warp_tot[kWarps];
-    __shared__ uint32_t carry_s;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
+    __shared__ uint32_t warp_tot[kScanWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint32_t base = 0; base < m; base += kThreads * 4) {
-        const uint32_t i0 = base + threadIdx.x * 4;
-        uint32_t v[4], tot = 0;
+    uint32_t carry = 0;                             // total of all earlier rounds (every thread keeps its own copy)
+    for (uint32_t base = 0; base < m; base += kScanThreads * kScanRows) {
+        const uint32_t w0 = base + warp * (32 * kScanRows);
+        uint32_t v[kScanRows];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t t = i0 + k < m ? counts[i0 + k] : 0;
-            v[k] = tot;
-            tot += t;
+        for (int k = 0; k < kScanRows; ++k) {
+            const uint32_t i = w0 + k * 32 + lane;
+            v[k] = i < m ? counts[i] : 0;
         }
-        uint32_t inc = tot;
+        uint32_t run = 0;                           // exclusive prefix inside the warp's 512 counters
+#pragma unroll
+        for (int k = 0; k < kScanRows; ++k) {
+            uint32_t inc = v[k];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += y;
+            }
+            const uint32_t row_total = __shfl_sync(0xffffffffu, inc, 31);
+            v[k] = run + inc - v[k];
+            run += row_total;
+        }
+        if (lane == 0) warp_tot[warp] = run;
+        __syncthreads();
+        const uint32_t wt = warp_tot[lane];         // kScanWarps == 32: every warp scans the warp totals itself
+        uint32_t winc = wt;
+#pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += y;
+            const uint32_t y = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += y;
         }
-        if (lane == 31) warp_tot[warp] = inc;
-        __syncthreads();
-        uint32_t woff = 0, total = 0;
+        const uint32_t total = __shfl_sync(0xffffffffu, winc, 31);
+        const uint32_t woff = __shfl_sync(0xffffffffu, winc - wt, warp);
 #pragma unroll
-        for (int w = 0; w < kWarps; ++w) {
-            if (w < warp) woff += warp_tot[w];
-            total += warp_tot[w];
+        for (int k = 0; k < kScanRows; ++k) {
+            const uint32_t i = w0 + k * 32 + lane;
+            if (i < m) counts[i] = v[k] + carry + woff;
         }
-        const uint32_t excl = carry_s + woff + inc - tot;
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (i0 + k < m) counts[i0 + k] = v[k] + excl;
-        __syncthreads();
-        if (threadIdx.x == 0) carry_s += total;
-        __syncthreads();
+        carry += total;
+        __syncthreads();                            // warp_tot is rewritten next round
     }
-    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) offsets[s] = counts[(size_t)s * nblocks];
+    __syncthreads();
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kScanThreads) offsets[s] = counts[(size_t)s * nblocks];
     if (threadIdx.x == 0) offsets[n_shards] = n;
 }
+static_assert(kScanWarps == 32, "the warp totals are scanned by one warp-wide shuffle scan");
 
-// kWide: both record arrays are 32-byte aligned (anything the allocator returns is)
-template <bool kWide>
-__global__ void __launch_bounds__(kThreads)
+// kMode 0: 16-byte moves (record arrays not 32-byte aligned).  1: 256-bit moves, records held in registers between
+// the ranking and the store.  (Reading the records a second time for the store instead — a third of the registers,
+// twice the resident warps — measured 3 % slower: the kernel is not short of warps, it runs at ~76 % of the copy
+// bandwidth on one read stream and 2 x n_shards write streams.)
+template <int kMode>
+__global__ void __launch_bounds__(kThreads, 2)
 k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
                const uint32_t* __restrict__ bases, uint32_t nblocks, igs_tx* __restrict__ tx_out,
                uint32_t* __restrict__ perm) {
@@ -115,20 +132,25 @@ k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
     __syncthreads();
     uint32_t* my_cnt = cnt + warp * n_shards;
     const uint32_t wbase = blockIdx.x * kTile + warp * (kItems * 32);
+    constexpr bool kWide = kMode == 1;
     uint32_t shard[kItems], rank[kItems];
     Rec32 rec[kWide ? kItems : 1];
+    // this block's start in each shard's range: asked for now, needed after the ranking
+    uint32_t my_base = 0;
+    if (threadIdx.x < n_shards) my_base = __ldg(bases + (size_t)threadIdx.x * nblocks + blockIdx.x);
     const uint32_t lt_mask = (1u << lane) - 1u;
+    if (kWide) {                                   // all eight loads in flight before the first ranking round needs one
+#pragma unroll
+        for (int r = 0; r < kItems; ++r) {
+            const uint32_t i = wbase + r * 32 + lane;
+            rec[r] = ld_rec32(tx + (i < n ? i : n - 1));
+        }
+    }
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
         const uint32_t i = wbase + r * 32 + lane;
         const bool valid = i < n;
-        uint32_t account = 0;
-        if (kWide) {
-            if (valid) rec[r] = ld_rec32(tx + i);
-            account = rec[r].w[2];                                         // igs_tx.account: bytes 8..11
-        } else if (valid) {
-            account = __ldg(&tx[i].account);
-        }
+        const uint32_t account = kWide ? rec[r].w[2] /* igs_tx.account: bytes 8..11 */ : valid ? __ldg(&tx[i].account) : 0u;
         shard[r] = valid ? shard_of(account, n_shards) : (kMaxShards + lane);
         const uint32_t peers = __match_any_sync(0xffffffffu, shard[r]);
         const uint32_t before = valid ? my_cnt[shard[r]] : 0;
@@ -138,8 +160,8 @@ k_part_scatter(const igs_tx* __restrict__ tx, uint32_t n, uint32_t n_shards,
         rank[r] = before + __popc(peers & lt_mask);
     }
     __syncthreads();
-    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) {
-        uint32_t run = __ldg(bases + (size_t)s * nblocks + blockIdx.x);
+    for (uint32_t s = threadIdx.x; s < n_shards; s += kThreads) {      // (n_shards <= kMaxShards <= kThreads: one round)
+        uint32_t run = my_base;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) {
             const uint32_t c = cnt[w * n_shards + s];
@@ -179,12 +201,12 @@ int igs_partition_run(igs_engine* e, const igs_tx* d_tx, uint64_t n64, uint32_t 
     }
     k_part_hist<<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks);
     IGS_LAUNCHED(e);
-    k_part_scan<<<1, kThreads, 0, stream>>>(counts, n_shards * nblocks, n_shards, nblocks, n, d_offsets);
+    k_part_scan<<<1, kScanThreads, 0, stream>>>(counts, n_shards * nblocks, n_shards, nblocks, n, d_offsets);
     IGS_LAUNCHED(e);
-    if ((((uintptr_t)d_tx | (uintptr_t)d_tx_out) & 31u) == 0)
-        k_part_scatter<true><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
+    if ((((uintptr_t)d_tx | (uintptr_t)d_tx_out) & 31u) != 0)
+        k_part_scatter<0><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
     else
-        k_part_scatter<false><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
+        k_part_scatter<1><<<nblocks, kThreads, 0, stream>>>(d_tx, n, n_shards, counts, nblocks, d_tx_out, d_perm);
     IGS_LAUNCHED(e);
     return IGS_OK;
 }

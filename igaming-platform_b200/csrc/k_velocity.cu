@@ -40,10 +40,27 @@ namespace {
 __global__ void k_minmax(const uint32_t* __restrict__ account, const uint32_t* __restrict__ ts,
                          uint32_t n, uint32_t* __restrict__ out /* ts_min, ts_max, acct_max, unsorted */) {
     uint32_t tmin = 0xFFFFFFFFu, tmax = 0, amax = 0, unsorted = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    // four events per step from the first 16-byte boundary on (both columns start at the same event offset of their
+    // allocation, so they share it); the up to 3 + 3 events before and after go to block 0's first threads
+    const uint32_t head = min(n, (uint32_t)((16u - ((uintptr_t)ts & 15u)) & 15u) >> 2);
+    const uint4* ts4 = reinterpret_cast<const uint4*>(ts + head);
+    const uint4* ac4 = reinterpret_cast<const uint4*>(account + head);
+    const uint32_t n4 = (n - head) >> 2;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n4; j += gridDim.x * blockDim.x) {
+        const uint4 t = __ldg(ts4 + j), a = __ldg(ac4 + j);
+        const uint32_t i = head + 4 * j;
+        const uint32_t prev = i ? __ldg(ts + i - 1) : 0u;
+        tmin = min(min(tmin, min(t.x, t.y)), min(t.z, t.w));
+        tmax = max(max(tmax, max(t.x, t.y)), max(t.z, t.w));
+        amax = max(max(amax, max(a.x, a.y)), max(a.z, a.w));
+        if (prev > t.x || t.x > t.y || t.y > t.z || t.z > t.w) unsorted = 1;    // arrival order is not time order
+    }
+    const uint32_t tail0 = head + (n4 << 2), n_edge = head + (n - tail0);
+    if (blockIdx.x == 0 && threadIdx.x < n_edge) {
+        const uint32_t i = threadIdx.x < head ? threadIdx.x : tail0 + (threadIdx.x - head);
         const uint32_t t = __ldg(ts + i), a = __ldg(account + i);
         tmin = min(tmin, t); tmax = max(tmax, t); amax = max(amax, a);
-        if (i > 0 && __ldg(ts + i - 1) > t) unsorted = 1;    // arrival order is not time order
+        if (i > 0 && __ldg(ts + i - 1) > t) unsorted = 1;
     }
     if (__any_sync(0xffffffffu, unsorted) && (threadIdx.x & 31) == 0) atomicOr(out + 3, 1u);
     for (int o = 16; o; o >>= 1) {

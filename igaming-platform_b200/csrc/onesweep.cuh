@@ -22,7 +22,7 @@
 namespace {
 
 constexpr int kOsThreads = 256;
-constexpr int kOsItems = 16;
+constexpr int kOsItems = 8;
 constexpr int kOsTile = kOsThreads * kOsItems;      // 2048 keys per tile
 constexpr int kOsWarps = kOsThreads / 32;
 constexpr int kOsBins = 256;
@@ -130,7 +130,7 @@ struct OsSmem {
 };
 
 // One digit pass: stable scatter of keys_in into keys_out.
-__global__ void __launch_bounds__(kOsThreads, 3)
+__global__ void __launch_bounds__(kOsThreads, 6)
 k_os_pass(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out, uint32_t n, int pass, int shift,
           uint32_t bins, OsScratch sc) {
     extern __shared__ __align__(16) unsigned char os_smem_raw[];

@@ -54,6 +54,29 @@ def test_partition_matches_stable_grouping(engine, pkg, n, n_shards):
     assert out.tobytes() == want_out.tobytes()
 
 
+def test_partition_of_records_that_are_only_16_byte_aligned(engine, pkg):
+    """Record arrays at a 16-byte offset of their allocation take the kernel variant without 256-bit moves."""
+    import torch
+    abi = pkg.abi
+    n, n_shards = 70_001, 8
+    tx = synth.make_tx(n, 100_000, seed=77)
+    dev = torch.device("cuda", 0)
+    raw = torch.zeros(n * 32 + 16, dtype=torch.uint8, device=dev)
+    raw[16:] = torch.from_numpy(tx.view(np.uint8).reshape(-1).copy()).to(dev)
+    out_raw = torch.zeros(n * 32 + 16, dtype=torch.uint8, device=dev)
+    d_perm = torch.full((n,), -1, dtype=torch.int32, device=dev)
+    d_off = torch.full((n_shards + 1,), -1, dtype=torch.int32, device=dev)
+    assert (raw.data_ptr() + 16) % 32 == 16
+    engine.partition_tx_device(raw.data_ptr() + 16, n, n_shards, out_raw.data_ptr() + 16, d_perm.data_ptr(),
+                               d_off.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    out = np.frombuffer(out_raw[16:].cpu().numpy().tobytes(), dtype=abi.tx_dtype)
+    want_out, want_perm, want_off = expected_partition(tx, n_shards)
+    assert np.array_equal(d_off.cpu().numpy().view(np.uint32), want_off)
+    assert np.array_equal(d_perm.cpu().numpy().view(np.uint32), want_perm)
+    assert out.tobytes() == want_out.tobytes()
+
+
 def test_partition_agrees_with_host_helper(engine, pkg):
     lib = pkg.abi.load_library()
     acc = np.arange(5000, dtype=np.uint32) * 7919
