@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-for m in 1 2; do IGS_PART_MODE=$m timeout 300 python tools/bench_partition.py 2>&1 | tail -1 | cut -c1-40,230-; done
-(timeout 300 python -m pytest tests -m gpu -q -x -k "partition or no_alloc or shard" 2>&1 | tail -2)
+timeout 200 python tools/profile_target.py c3 2 2>&1 | tail -1 || exit 1
+timeout 400 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 80 --csv --log-file gpurun_out/r2z_c3_launches.csv python tools/profile_target.py c3 2 > gpurun_out/r2z_c3_ncu.log 2>&1
+tail -n 1 gpurun_out/r2z_c3_ncu.log

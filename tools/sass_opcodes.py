@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Lists, per kernel of libigs.so, the SASS opcodes that show which Blackwell units it uses: tcgen05 MMAs
 (UTC*MMA), tensor-memory loads / stores (LDTM / STTM), TMA tensor and bulk copies (UTMALDG / UTMASTG / UBLKCP),
-mbarrier waits (SYNCS), system-scope atomics (peer-memory windows), warp match (MATCH).
+mbarrier waits (SYNCS), system-scope atomics (peer-memory windows), warp match (MATCH), 256-bit global moves,
+and the `.2CTA` forms of the CTA-pair MLP kernels.
 
     python tools/sass_opcodes.py [> profiles/r2_sass_opcodes.txt]
 
@@ -14,7 +15,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "igaming-platform_b200", "libigs.so")
-PAT = re.compile(r"\b(UTC[A-Z]*MMA|UTCBAR[.A-Z0-9_]*|LDTM[.A-Za-z0-9_]*|STTM[.A-Za-z0-9_]*|UTMALDG[.A-Z0-9_]*|UTMASTG[.A-Z0-9_]*|"
+PAT = re.compile(r"\b(UTC[A-Z]*MMA[.A-Z0-9_]*|LDG\.E[.A-Z0-9_]*\.256[.A-Z0-9_]*|STG\.E[.A-Z0-9_]*\.256[.A-Z0-9_]*|UTCBAR[.A-Z0-9_]*|LDTM[.A-Za-z0-9_]*|STTM[.A-Za-z0-9_]*|UTMALDG[.A-Z0-9_]*|UTMASTG[.A-Z0-9_]*|"
                  r"UBLKCP[.A-Z0-9_]*|SYNCS[.A-Z0-9_]*|MATCH[.A-Z0-9_]*|ATOM[A-Z]*\.[.A-Z0-9_]*SYS[.A-Z0-9_]*|"
                  r"RED[.A-Z0-9_]*SYS[.A-Z0-9_]*|HMMA[.A-Z0-9_]*|REDUX[.A-Z0-9_]*)")
 
