@@ -138,6 +138,7 @@ int igs_engine_create(int device, igs_engine** out) {
         for (int k = 0; ok && k < IGS_PIPE_STREAMS; ++k)
             ok = cudaStreamCreateWithFlags(&sl.pipe[k], cudaStreamNonBlocking) == cudaSuccess &&
                  cudaEventCreateWithFlags(&sl.ev_join[k], cudaEventDisableTiming) == cudaSuccess;
+        ok = ok && cudaMalloc(&sl.d_ready, 256) == cudaSuccess;
         if (!ok) {
             igs_set_error(nullptr, "stream/event creation failed: %s",
                           cudaGetErrorString(cudaGetLastError()));
@@ -145,6 +146,12 @@ int igs_engine_create(int device, igs_engine** out) {
             return IGS_ERR_CUDA;
         }
     }
+    if (cudaHostAlloc(&e->h_arrival_vals, IGS_ARRIVAL_CHUNKS * sizeof(uint32_t), cudaHostAllocDefault) != cudaSuccess) {
+        igs_set_error(nullptr, "pinned allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        igs_engine_destroy(e);
+        return IGS_ERR_CUDA;
+    }
+    for (int c = 0; c < IGS_ARRIVAL_CHUNKS; ++c) e->h_arrival_vals[c] = (uint32_t)c + 1u;
     *out = e;
     return IGS_OK;
 }
@@ -162,7 +169,9 @@ void igs_engine_destroy(igs_engine* e) {
             if (sl.pipe[k]) cudaStreamDestroy(sl.pipe[k]);
         }
         if (sl.stream) cudaStreamDestroy(sl.stream);
+        if (sl.d_ready) cudaFree(sl.d_ready);
     }
+    if (e->h_arrival_vals) cudaFreeHost(e->h_arrival_vals);
     free_buf(&e->part_scratch);
     if (e->ingest_stream) cudaStreamDestroy(e->ingest_stream);
     if (e->scratch_pool) cudaMemPoolDestroy(e->scratch_pool);
@@ -552,18 +561,63 @@ static bool host_mapped(const void* p) {
     return a.type == cudaMemoryTypeHost && a.devicePointer == p;
 }
 
+// Large batches in pinned host buffers: ONE kernel launch over the whole batch, started at once; the records follow
+// it into device memory in IGS_ARRIVAL_CHUNKS copies on a worker stream, each followed by a 4-byte copy that bumps the
+// slot's arrival counter, and the kernel's producer warps wait for the chunk they are about to read (igs_tx_arrival).
+// The copy engine runs ahead of the kernel after the first chunks (32 MB at ~55 GB/s against 1.7 ms of scoring), so
+// the producers read HBM, not PCIe; the 8-byte results are written straight to the caller's pinned buffer.
+static int score_batch_streamed(igs_engine* e, igs_slot& sl, const igs_config* cfg, const igs_tx* tx,
+                                const igs_tx_ids* ids, uint64_t n, igs_result* out) {
+    IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_tx)));
+    igs_tx* d_tx = (igs_tx*)sl.in0.p;
+    // chunks of whole 512-row tiles
+    const uint64_t rows = ((n + IGS_ARRIVAL_CHUNKS - 1) / IGS_ARRIVAL_CHUNKS + 511) / 512 * 512;
+    IGS_REQUIRE(e, rows <= 0xFFFFFFFFull, "batch too large");
+    cudaStream_t cp = sl.pipe[0];
+    IGS_CUDA(e, cudaMemsetAsync(sl.d_ready, 0, sizeof(uint32_t), sl.stream));
+    IGS_CUDA(e, cudaEventRecord(sl.ev_fork, sl.stream));
+    IGS_CUDA(e, cudaStreamWaitEvent(cp, sl.ev_fork, 0));
+    const igs_tx_arrival arrival = {sl.d_ready, (uint32_t)rows};
+    int rc = igs_launch_score_batch(e, cfg, d_tx, ids, n, out, nullptr, nullptr, sl.stream, &arrival);
+    if (rc != IGS_OK) return rc;                       // nothing was launched
+    // From here on the kernel is waiting for the copies: every chunk must be queued, whatever happens.
+    cudaError_t st = cudaSuccess;
+    int c = 0;
+    for (uint64_t off = 0; off < n && st == cudaSuccess; off += rows, ++c) {
+        const uint64_t cnt = std::min(rows, n - off);
+        st = cudaMemcpyAsync(d_tx + off, tx + off, cnt * sizeof(igs_tx), cudaMemcpyHostToDevice, cp);
+        if (st == cudaSuccess)
+            st = cudaMemcpyAsync(sl.d_ready, e->h_arrival_vals + c, sizeof(uint32_t), cudaMemcpyHostToDevice, cp);
+    }
+    if (st != cudaSuccess) {
+        // release the kernel (it scores whatever is in the staging buffer; the call fails anyway)
+        cudaMemcpyAsync(sl.d_ready, e->h_arrival_vals + IGS_ARRIVAL_CHUNKS - 1, sizeof(uint32_t), cudaMemcpyHostToDevice, cp);
+        igs_set_error(e, "queueing the batch copies failed: %s", cudaGetErrorString(st));
+        rc = IGS_ERR_CUDA;
+    }
+    const cudaError_t a = cudaEventRecord(sl.ev_join[0], cp);
+    const cudaError_t b = a == cudaSuccess ? cudaStreamWaitEvent(sl.stream, sl.ev_join[0], 0) : a;
+    if (b != cudaSuccess) cudaStreamSynchronize(cp);
+    return rc;
+}
+
 static int score_batch_host(igs_engine* e, int s, const igs_config* cfg, const igs_tx* tx, const igs_tx_ids* ids,
                             uint64_t n, igs_result* out, float* features_out, igs_velocity* velocity_out) {
     IGS_REQUIRE(e, cfg != nullptr, "cfg is null");
     IGS_REQUIRE(e, n == 0 || (tx && out), "tx / out is null");
     if (n == 0) return IGS_OK;
     igs_slot& sl = e->slot[s];
-    // Large batches in pinned (mapped) host buffers are not staged: the warp-specialised kernel's producer warps read
-    // the 32-byte records over PCIe as they go and the walkers write the 8-byte results back the same way — 40 B/tx
-    // at ~0.6e9 tx/s is a third of the link, and no copy has to finish before the first tile starts.
+    // Large batches in pinned (mapped) host buffers are not cut into chunk launches: one kernel over the whole batch
+    // with the records streaming in behind its start (score_batch_streamed); results go straight to the host buffer.
     if (!features_out && !velocity_out && igs_fused_direct_eligible(e, n) && host_mapped(tx) && host_mapped(out) &&
-        (!ids || host_mapped(ids)))
-        return igs_launch_score_batch(e, cfg, tx, ids, n, out, nullptr, nullptr, sl.stream, true);
+        (!ids || host_mapped(ids))) {
+        static const int direct = getenv("IGS_SCORE_DIRECT") ? atoi(getenv("IGS_SCORE_DIRECT")) : 1;   // tuning knob
+        // (a kernel that waits for copies queued after its launch cannot run under CUDA_LAUNCH_BLOCKING=1)
+        static const bool blocking = getenv("CUDA_LAUNCH_BLOCKING") && atoi(getenv("CUDA_LAUNCH_BLOCKING")) != 0;
+        if (direct == 2 || blocking)   // the producers read the records themselves, over PCIe
+            return igs_launch_score_batch(e, cfg, tx, ids, n, out, nullptr, nullptr, sl.stream, nullptr, true);
+        return score_batch_streamed(e, sl, cfg, tx, ids, n, out);
+    }
     IGS_TRY(igs_reserve(e, &sl.in0, n * sizeof(igs_tx)));
     if (ids) IGS_TRY(igs_reserve(e, &sl.in1, n * sizeof(igs_tx_ids)));
     igs_tx_ids* d_ids = ids ? (igs_tx_ids*)sl.in1.p : nullptr;

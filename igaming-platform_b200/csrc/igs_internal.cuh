@@ -64,7 +64,16 @@ struct igs_slot {
     cudaEvent_t  ev_fork = nullptr;                   // slot stream -> workers
     cudaEvent_t  ev_join[IGS_PIPE_STREAMS] = {nullptr};  // workers -> slot stream
     igs_buf      in0, in1, out0, aux0, aux1;
+    uint32_t*    d_ready = nullptr;                   // arrival counter of a batch that is copied in while its kernel runs
 };
+
+// A transaction batch that is still arriving in device memory while the kernel that scores it runs: rows
+// [c * chunk_rows, (c + 1) * chunk_rows) are complete once *ready > c (written by the copy stream after each chunk).
+struct igs_tx_arrival {
+    const uint32_t* ready;
+    uint32_t chunk_rows;
+};
+constexpr int IGS_ARRIVAL_CHUNKS = 32;
 
 // one blacklist set: open-addressing table of 64-bit ids, at most half full
 struct igs_idset {
@@ -104,6 +113,7 @@ struct igs_engine {
     // cudaFreeAsync pair costs microseconds instead of a round trip to the driver, and calls on different streams
     // still get disjoint memory.
     cudaMemPool_t scratch_pool = nullptr;
+    uint32_t* h_arrival_vals = nullptr;  // pinned: 1, 2, ... IGS_ARRIVAL_CHUNKS (sources of the arrival-counter copies)
     int mlp_max_pairs[3] = {0, 0, 0};   // co-resident CTA pairs of the three k_mlp_gemm pair variants (0 = not asked yet)
 
     // tree ensemble
@@ -202,7 +212,7 @@ int igs_launch_score_features(igs_engine* e, const igs_config* cfg, const float*
 // tx_over_pcie: d_tx / d_ids / d_out are mapped host memory — read each record once (no visit-order sort)
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
-                           cudaStream_t stream, bool tx_over_pcie = false);
+                           cudaStream_t stream, const igs_tx_arrival* arrival = nullptr, bool tx_over_pcie = false);
 bool igs_fused_direct_eligible(const igs_engine* e, uint64_t n);
 int igs_launch_velocity(igs_engine* e, const igs_query* d_q, uint64_t n, igs_velocity* d_out,
                         cudaStream_t stream);

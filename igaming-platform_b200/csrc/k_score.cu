@@ -74,6 +74,8 @@ struct ScoreParams {
     float* features_out;
     igs_velocity* velocity_out;
     const uint64_t* perm;          // optional: low 32 bits = slot -> row, the batch visited in account order (see launch)
+    const uint32_t* tx_ready;      // optional (k_score_ws only): tx[] is still being copied in, see igs_tx_arrival
+    uint32_t tx_chunk_rows;
     const igs_tx_ids* tx_ids;      // optional: rule 8 evaluated against the blacklist sets
     igs_idset_view bl[3];
     int uniques_from_index;        // the history carries identifiers: ignore the tx's unique counts
@@ -540,6 +542,24 @@ __device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity)
     } while (!ok);
 }
 
+// The batch is being copied in while this kernel runs (igs_tx_arrival): wait until the chunk that holds the warp's 32
+// records is complete.  The copy stream bumps *tx_ready after each chunk; the records were never read before by this
+// SM, so the plain loads that follow see what the copy engine wrote.  Bounded: a copy that never comes traps.
+__device__ __forceinline__ void tx_wait_arrival(const ScoreParams& p, unsigned long long first_row, int lane) {
+    const unsigned long long last = min(first_row + 31ull, p.n - 1ull);
+    const uint32_t need = (uint32_t)(last / p.tx_chunk_rows) + 1u;
+    if (lane == 0) {
+        uint32_t have, spins = 0;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(have) : "l"(p.tx_ready) : "memory");
+            if (have >= need) break;
+            __nanosleep(256);
+            if (++spins > (1u << 25)) __trap();      // ~10 s
+        }
+    }
+    __syncwarp();
+}
+
 template <typename S>
 __global__ void __launch_bounds__(S::kThreads, 1)
 k_score_ws(const __grid_constant__ ScoreParams p) {
@@ -580,6 +600,7 @@ k_score_ws(const __grid_constant__ ScoreParams p) {
                 const bool in_range = slot < p.n;
                 const unsigned long long row = (p.perm != nullptr && in_range) ? (uint32_t)__ldg(p.perm + slot) : slot;
                 mbar_wait_bounded(bar_empty + 8 * (w * 2 + b), (uint32_t)(((k >> 1) & 1) ^ 1));   // the walker is done with it
+                if (p.tx_ready != nullptr) tx_wait_arrival(p, tile * kTileTx + (unsigned)w * 32, lane);
                 float* tile_lane = reinterpret_cast<float*>(tiles + (size_t)(w * 2 + b) * kTileBytes) + lane;
                 RuleIn ri;
                 assemble_tx<true>(p, row, in_range, tile_lane, &ri);
@@ -810,7 +831,10 @@ static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
     const bool eligible = ws != 0 && p.features_out == nullptr && p.velocity_out == nullptr &&
                           p.n >= 4ull * (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx &&
                           (p.cfg.model_kind != IGS_MODEL_GBDT || e->d_model_ws != nullptr);
-    if (!eligible) return launch(e, kSrcTx, p, false, stream);
+    if (!eligible) {
+        IGS_REQUIRE(e, p.tx_ready == nullptr, "a batch that is still arriving needs the warp-specialised kernel");
+        return launch(e, kSrcTx, p, false, stream);
+    }
     p.model = p.model_ws ? p.model_ws : p.model;
     // 16 walkers + 4 producers (640 threads, ~100 registers each).  Measured alternatives, 1M tx against 500k players
     // and a 5M-event index, ms per batch with / without the visit-order sort (k_score: 1.757 / 1.959):
@@ -825,12 +849,13 @@ static int launch_fused(igs_engine* e, ScoreParams& p, cudaStream_t stream) {
 bool igs_fused_direct_eligible(const igs_engine* e, uint64_t n) {
     static const int ws = getenv("IGS_SCORE_WS") ? atoi(getenv("IGS_SCORE_WS")) : 1;
     static const int direct = getenv("IGS_SCORE_DIRECT") ? atoi(getenv("IGS_SCORE_DIRECT")) : 1;   // tuning knob: 0 = always stage
-    return ws != 0 && direct != 0 && n >= 4ull * (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx;
+    return ws != 0 && direct != 0 && n >= 4ull * (unsigned long long)e->sm_count * Shape<16, 14, 7>::kTileTx &&
+           (!e->has_gbdt || e->d_model_ws != nullptr);
 }
 
 int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d_tx, const igs_tx_ids* d_ids,
                            uint64_t n, igs_result* d_out, float* d_features_out, igs_velocity* d_velocity_out,
-                           cudaStream_t stream, bool tx_over_pcie) {
+                           cudaStream_t stream, const igs_tx_arrival* arrival, bool tx_over_pcie) {
     if (n == 0) return IGS_OK;
     int rc = check_model(e, cfg);
     if (rc != IGS_OK) return rc;
@@ -850,7 +875,13 @@ int igs_launch_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* d
     p.n = n;
     static const int visit_passes = getenv("IGS_VISIT_SORT_PASSES") ? atoi(getenv("IGS_VISIT_SORT_PASSES")) : 3;   // tuning knob (0 = off)
     void* scratch = nullptr;
-    if (visit_passes > 0 && !tx_over_pcie && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
+    if (arrival) {
+        IGS_REQUIRE(e, igs_fused_direct_eligible(e, n) && !d_features_out && !d_velocity_out && arrival->chunk_rows > 0,
+                    "a batch that is still arriving needs the warp-specialised kernel");
+        p.tx_ready = arrival->ready;
+        p.tx_chunk_rows = arrival->chunk_rows;
+    }
+    if (visit_passes > 0 && !tx_over_pcie && !arrival && e->has_events && n >= kVisitSortMin && n < 0xFFFFFFFFull) {
         rc = visit_order(e, d_tx, (uint32_t)n, rd.view.base.n_accounts, std::min(visit_passes, 4), stream, &scratch, &p.perm);
         if (rc != IGS_OK) { if (scratch) cudaFreeAsync(scratch, stream); return rc; }
     }

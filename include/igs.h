@@ -467,8 +467,10 @@ int igs_get_velocity_device(igs_engine* e, const igs_query* d_q, uint64_t n, igs
  * assembled model input, velocity_out (optional) the n velocity blocks.                         */
 /* Host buffers.  Pageable memory is staged through the slot's device buffers in chunks (copy, kernel and copy
  * back overlap).  Large batches (>= 4 x 512 tx per SM) whose tx / out (/ ids) buffers come from igs_alloc_pinned
- * and that ask for the results only are not staged at all: the kernel reads the records from, and writes the
- * results to, the pinned host memory directly over PCIe.                                              */
+ * and that ask for the results only run as ONE kernel launch that starts at once: the records follow it into
+ * device memory in 32 copies on a worker stream of the slot, the kernel waits for the chunk it is about to read,
+ * and the results are written straight into the pinned result buffer.  (tx and out must stay untouched until the
+ * call — or igs_wait for the asynchronous form — returns, as for every host-buffer call.)             */
 int igs_score_batch(igs_engine* e, const igs_config* cfg, const igs_tx* tx, uint64_t n,
                     igs_result* out, float* features_out, igs_velocity* velocity_out);
 int igs_score_batch_async(igs_engine* e, int slot, const igs_config* cfg, const igs_tx* tx,

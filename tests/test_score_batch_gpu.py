@@ -165,3 +165,65 @@ def test_large_batches_take_the_warp_specialised_kernel(engine, orc, pkg, kind):
     want = orc.score_batch(cfg, model, players, ev, np.ascontiguousarray(tx[pick]))
     assert got[pick].tobytes() == want.tobytes()
     assert len(np.unique(got["score"])) >= 3                  # (model nil: 0.4 x rule score never reaches review)
+
+
+def test_large_pinned_batches_stream_in_behind_the_kernel(engine, orc, pkg):
+    """igs_score_batch on pinned host buffers of >= 4 x 148 x 512 tx: one k_score_ws launch over the whole batch, the
+    records copied in behind its start in 32 chunks with an arrival counter the producer warps wait on, results written
+    straight into the pinned result buffer.  Ragged size; all rows bit-identical to the staged path (pageable buffers)
+    and a sample to the oracle; then two such calls at once on two slots of the engine."""
+    import ctypes as C
+    import threading
+    abi = pkg.abi
+    lib = abi.load_library()
+    n_players, n_events, n = 5000, 80000, 4 * 148 * 512 + 77_777
+    now = synth.T0 + 6 * 3600
+    players = synth.make_players(n_players, seed=205, now=now)
+    ev = synth.make_events(n_events, n_players, seed=206, span=6 * 3600, collision_rate=0.03)
+    engine.load_players(players)
+    engine.load_events(ev, n_players)
+    model = synth.make_gbdt(n_trees=40, seed=208)
+    engine.load_gbdt(model)
+    cfg = pkg.default_config(model_kind=abi.MODEL_GBDT)
+    txs = [synth.make_tx(n, n_players, seed=207 + k, t_lo=synth.T0 + 3600, t_hi=now, invalid_rate=0.02) for k in range(2)]
+    staged = [engine.score_batch(cfg, t) for t in txs]
+    pinned = []
+
+    def pin(a):
+        p = lib.igs_alloc_pinned(a.nbytes)
+        buf = np.frombuffer((C.c_uint8 * a.nbytes).from_address(p), dtype=a.dtype).reshape(a.shape)
+        buf[...] = a
+        pinned.append(p)
+        return buf
+    try:
+        h_tx = [pin(t) for t in txs]
+        h_out = [pin(np.full(n, 0xEE, dtype=np.uint8).repeat(8).view(abi.result_dtype)) for _ in txs]
+        for rep in range(3):                 # the staging buffer is reused: stale records of the previous call must not be read
+            k = rep % 2
+            h_out[k].view(np.uint8)[...] = 0xEE
+            st = lib.igs_score_batch(engine.handle, C.byref(cfg), h_tx[k].ctypes.data, n, h_out[k].ctypes.data, None, None)
+            assert st == 0, lib.igs_last_error(engine.handle).decode()
+            assert h_out[k].tobytes() == staged[k].tobytes()
+        pick = np.concatenate([np.arange(0, 2000), np.arange(n - 2000, n)])
+        want = orc.score_batch(cfg, model, players, ev, np.ascontiguousarray(txs[0][pick]))
+        assert staged[0][pick].tobytes() == want.tobytes()
+        errors = []
+
+        def worker(k):
+            for _ in range(4):
+                h_out[k].view(np.uint8)[...] = 0xEE
+                st = lib.igs_score_batch_async(engine.handle, 1 + k, C.byref(cfg), h_tx[k].ctypes.data, n, h_out[k].ctypes.data)
+                if st == 0:
+                    st = lib.igs_wait(engine.handle, 1 + k)
+                if st != 0 or h_out[k].tobytes() != staged[k].tobytes():
+                    errors.append((k, st, lib.igs_last_error(engine.handle).decode()))
+                    return
+        threads = [threading.Thread(target=worker, args=(k,)) for k in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=300)
+        assert not errors, errors
+    finally:
+        for p in pinned:
+            lib.igs_free_pinned(p)
