@@ -1,11 +1,6 @@
 mkdir -p gpurun_out
-(timeout 600 python -m pytest tests/test_score_batch_gpu.py tests/test_two_engines_gpu.py -m gpu -q -x 2>&1 | tail -15) > gpurun_out/r3a_test.log
-tail -5 gpurun_out/r3a_test.log
-for d in 2 1; do
-IGS_SCORE_DIRECT=$d timeout 600 python bench.py --steps 10 --warmup 3 --skip path_a,ltv,c3,live_loop --skip-cpu --skip-latency > gpurun_out/r3a_bench_d$d.json 2> gpurun_out/r3a_bench_d$d.err
-python - <<PY
-import json
-d=json.load(open('gpurun_out/r3a_bench_d$d.json'))
-print('direct=$d', d['ms_per_step'], 'e2e', d['e2e']['ms_per_step'], d['e2e']['value'])
-PY
-done
+(timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -4) > gpurun_out/r3b_gputest.log
+tail -2 gpurun_out/r3b_gputest.log
+timeout 200 python tools/profile_target.py fused 2 2>&1 | tail -1 || exit 1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_score_ws|k_visit_keys|k_os_pass" -c 12 -o gpurun_out/r3b_fused -f python tools/profile_target.py fused 2 > gpurun_out/r3b_fused_ncu.log 2>&1
+tail -n 1 gpurun_out/r3b_fused_ncu.log
