@@ -1,1 +1,1 @@
-timeout 300 python tools/_os_prof.py 2>&1 | tail -12
+timeout 300 python tools/_tmp_occ.py 2>&1 | tail -2
