@@ -8,6 +8,7 @@
 // Everything here is marshalling; every number in a response comes from the CUDA library.
 #pragma once
 
+#include <algorithm>
 #include <array>
 #include <chrono>
 #include <cstdint>
@@ -277,7 +278,7 @@ private:
 class ShardedEngine {
 public:
     explicit ShardedEngine(int n_shards, int n_devices = 1) : shards_(n_shards) {
-        if (n_shards < 1 || n_devices < 1) throw Error(IGS_ERR_INVALID, "n_shards and n_devices must be >= 1");
+        if (n_shards < 1 || n_shards > 256 || n_devices < 1) throw Error(IGS_ERR_INVALID, "1 <= n_shards <= 256 and n_devices >= 1");
         for (int s = 0; s < n_shards; ++s)
             if (int rc = igs_engine_create(s % n_devices, &shards_[s].e); rc != IGS_OK) {
                 const std::string msg = igs_last_error(nullptr);
@@ -324,31 +325,63 @@ public:
         }
     }
 
-    // rpc ScoreBatch over all shards: tx[i].account is a GLOBAL index; out[i] belongs to tx[i]
+    // rpc ScoreBatch over all shards: tx[i].account is a GLOBAL index; out[i] belongs to tx[i].
+    // Host side = a parallel stable partition: `route_threads` threads count their slice of the batch per shard, the
+    // counts become offsets, the same threads copy their records (local account index filled in) straight into the
+    // shards' pinned staging; then one host thread per shard (Go: LockOSThread per device) calls igs_score_batch, and
+    // the routing threads scatter the results back.  Records keep their arrival order inside a shard.
     void ScoreBatch(const igs_config& cfg, const igs_tx* tx, uint64_t n, igs_result* out) {
-        for (Shard& sh : shards_) sh.rows.clear();
-        for (uint64_t i = 0; i < n; ++i) shards_[ShardOf(tx[i].account)].rows.push_back(i);
-        std::vector<std::thread> workers;
-        for (Shard& sh : shards_)
-            workers.emplace_back([&, this, shp = &sh] {       // one host thread per shard (Go: LockOSThread per device)
-                Shard& s = *shp;
-                const size_t m = s.rows.size();
-                s.rc = IGS_OK;
-                if (m == 0) return;
-                igs_tx* in = s.tx.reserve(m);
-                igs_result* res = s.out.reserve(m);
-                for (size_t k = 0; k < m; ++k) {
-                    in[k] = tx[s.rows[k]];
-                    const uint32_t g = in[k].account;
-                    in[k].account = g < local_.size() ? local_[g] : 0xFFFFFFFEu;   // unknown account: zero features
-                }
-                s.rc = igs_score_batch(s.e, &cfg, in, m, res, nullptr, nullptr);
-                if (s.rc == IGS_OK)
-                    for (size_t k = 0; k < m; ++k) out[s.rows[k]] = res[k];
-            });
-        for (std::thread& w : workers) w.join();
+        const size_t S = shards_.size();
+        const size_t P = std::max<size_t>(1, std::min<size_t>(route_threads_, n / 65536 + 1));
+        shard_id_.resize(n);
+        std::vector<std::vector<uint64_t>> off(P, std::vector<uint64_t>(S, 0));
+        auto slice = [&](size_t p) { return std::pair<uint64_t, uint64_t>(n * p / P, n * (p + 1) / P); };
+        parallel(P, [&](size_t p) {
+            auto [lo, hi] = slice(p);
+            std::vector<uint64_t>& c = off[p];
+            for (uint64_t i = lo; i < hi; ++i) {
+                const uint8_t sh = (uint8_t)ShardOf(tx[i].account);
+                shard_id_[i] = sh;
+                ++c[sh];
+            }
+        });
+        std::vector<uint64_t> m(S, 0);
+        for (size_t sh = 0; sh < S; ++sh)
+            for (size_t p = 0; p < P; ++p) { const uint64_t c = off[p][sh]; off[p][sh] = m[sh]; m[sh] += c; }
+        std::vector<igs_tx*> in(S);
+        std::vector<igs_result*> res(S);
+        for (size_t sh = 0; sh < S; ++sh) {
+            shards_[sh].rows.resize(m[sh]);
+            in[sh] = shards_[sh].tx.reserve(std::max<uint64_t>(m[sh], 1));
+            res[sh] = shards_[sh].out.reserve(std::max<uint64_t>(m[sh], 1));
+        }
+        parallel(P, [&](size_t p) {
+            auto [lo, hi] = slice(p);
+            std::vector<uint64_t> k = off[p];
+            for (uint64_t i = lo; i < hi; ++i) {
+                const size_t sh = shard_id_[i];
+                const uint64_t at = k[sh]++;
+                igs_tx x = tx[i];
+                x.account = x.account < local_.size() ? local_[x.account] : 0xFFFFFFFEu;   // unknown account: zero features
+                in[sh][at] = x;
+                shards_[sh].rows[at] = i;
+            }
+        });
+        parallel(S, [&](size_t sh) {
+            Shard& s = shards_[sh];
+            s.rc = m[sh] ? igs_score_batch(s.e, &cfg, in[sh], m[sh], res[sh], nullptr, nullptr) : IGS_OK;
+        });
         for (Shard& sh : shards_) check(sh, sh.rc);
+        parallel(P, [&](size_t p) {
+            for (size_t sh = 0; sh < S; ++sh) {
+                const uint64_t lo = m[sh] * p / P, hi = m[sh] * (p + 1) / P;
+                const uint64_t* rows = shards_[sh].rows.data();
+                for (uint64_t k = lo; k < hi; ++k) out[rows[k]] = res[sh][k];
+            }
+        });
     }
+    // host threads that route a batch (default: the hardware threads, at most 16)
+    void set_route_threads(unsigned t) { route_threads_ = t ? t : 1; }
 
 private:
     struct Shard {
@@ -362,8 +395,18 @@ private:
     static void check(const Shard& sh, int rc) {
         if (rc != IGS_OK) throw Error(rc, igs_last_error(sh.e));
     }
+    template <typename F>
+    static void parallel(size_t n_threads, F&& body) {               // body(0 .. n_threads - 1), one std::thread each
+        if (n_threads <= 1) { body(0); return; }
+        std::vector<std::thread> w;
+        w.reserve(n_threads);
+        for (size_t t = 0; t < n_threads; ++t) w.emplace_back([&body, t] { body(t); });
+        for (std::thread& x : w) x.join();
+    }
     std::vector<Shard> shards_;
     std::vector<uint32_t> local_;      // global account -> local index on its shard
+    std::vector<uint8_t> shard_id_;    // per record of the batch in flight
+    unsigned route_threads_ = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
 };
 
 }  // namespace igs
