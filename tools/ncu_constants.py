@@ -23,6 +23,7 @@ SOURCES = {
     "k_score_fused": [CSRC + "k_score.cu", CSRC + "velocity.cuh", CSRC + "igs_math.cuh"],
     "k_score_features": [CSRC + "k_score.cu", CSRC + "igs_math.cuh"],
     "k_mlp_gemm": [CSRC + "k_ltv.cu"],
+    "k_partition": [CSRC + "k_partition.cu"],
     "c3_build": [CSRC + "k_velocity.cu", CSRC + "sortscan.cuh", CSRC + "onesweep.cuh", CSRC + "velocity.cuh"],
 }
 KEEP = {
